@@ -1,0 +1,362 @@
+"""Generate the golden fixtures under tests/golden/ by EXECUTING THE REFERENCE.
+
+Run in the build container only (it needs /root/reference, which does not exist
+on the GPU box):
+
+    python tests/golden/make_golden.py
+
+What is executed verbatim from the reference tree:
+  * generic/eegatconv.py  EEGATConv.forward   (on the DGL primitive shims, oracle/shims/dgl)
+  * generic/gatv3_conv.py GATv3Conv.forward   (on the PyG primitive shims, oracle/shims/torch_geometric)
+  * generic/agent.py      Agent.get_action_and_value / get_action_probs_and_value / predict
+  * generic/mlp.py        MLP.forward
+  * psp/models/edge_embedder.py PspEdgeEmbedder.forward
+  * jssp/utils/utils.py   compute_conflicts_cliques
+  * jssp/models/agent_observation.py AgentObservation.from_gym_observation (DGL shim)
+
+Outputs: small .npz files (float64 for the layers so that the comparison with
+the oracle is tight; float32 where the reference module is float32-only).
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(ROOT, "oracle", "shims"))
+sys.path.insert(0, "/root/reference")
+
+
+def np_(t):
+    return t.detach().cpu().numpy()
+
+
+def rand_graph(gen, n, e, self_loops=True):
+    src = torch.randint(0, n, (e,), generator=gen)
+    dst = torch.randint(0, n, (e,), generator=gen)
+    if self_loops:
+        loop = torch.arange(n)
+        src = torch.cat([src, loop])
+        dst = torch.cat([dst, loop])
+    return src, dst
+
+
+def grads_of(loss, tensors):
+    gs = torch.autograd.grad(loss, tensors, allow_unused=True)
+    return [torch.zeros_like(t) if g is None else g for g, t in zip(gs, tensors)]
+
+
+# ---------------------------------------------------------------- a1: EEGAT
+def golden_eegat(edge_scoring: bool, fname: str, seed: int):
+    import dgl
+    from generic.eegatconv import EEGATConv
+
+    gen = torch.Generator().manual_seed(seed)
+    N, E0, Fin, Fe, Do, De, H = 13, 40, 6, 7, 5, 5, 3
+    src, dst = rand_graph(gen, N, E0)
+    E = src.numel()
+    torch.manual_seed(seed)
+    layer = EEGATConv(Fin, Fe, Do, De, H, bias=True, edge_scoring=edge_scoring).double()
+    with torch.no_grad():
+        layer.bias.copy_(torch.randn(layer.bias.shape, generator=gen, dtype=torch.float64) * 0.1)
+    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64, requires_grad=True)
+    ef = torch.randn(E, Fe, generator=gen, dtype=torch.float64, requires_grad=True)
+    efe = torch.randn(E, Fe, generator=gen, dtype=torch.float64, requires_grad=True)
+    g = dgl.graph((src, dst), num_nodes=N)
+    if edge_scoring:
+        h, f, e_out, a = layer(g, x, ef, efe, get_attention=True)
+    else:
+        h, f, a = layer(g, x, ef, get_attention=True)
+    R = torch.randn(h.shape, generator=gen, dtype=torch.float64)
+    loss = (h * R).sum()
+    names = [k for k, _ in layer.named_parameters()]
+    params = [p for _, p in layer.named_parameters()]
+    gr = grads_of(loss, params + [x, ef])
+    out = dict(src=np_(src), dst=np_(dst), x=np_(x), ef=np_(ef), efe=np_(efe), R=np_(R),
+               h=np_(h), f=np_(f), a=np_(a), gx=np_(gr[-2]), gef=np_(gr[-1]),
+               heads=np.int64(H))
+    if edge_scoring:
+        out["e_out"] = np_(e_out)
+    for k, p, gp in zip(names, params, gr):
+        out["p." + k] = np_(p)
+        out["g." + k] = np_(gp)
+    np.savez_compressed(os.path.join(HERE, fname), **out)
+    # the reference raises on zero-in-degree graphs
+    g_bad = dgl.graph((torch.tensor([0, 1]), torch.tensor([1, 1])), num_nodes=3)
+    try:
+        layer(g_bad, x[:3], ef[:2])
+        raise SystemExit("expected DGLError")
+    except dgl.base.DGLError:
+        pass
+
+
+# ---------------------------------------------------------------- a3: GATv3
+def golden_gatv3(fname: str, seed: int):
+    from generic.gatv3_conv import GATv3Conv
+
+    gen = torch.Generator().manual_seed(seed)
+    N, E0, Fin, C, H = 11, 30, 6, 8, 2
+    src, dst = rand_graph(gen, N, E0, self_loops=False)
+    src[3], dst[3] = 4, 4                      # one pre-existing self loop (gets removed/re-added)
+    ei = torch.stack([src, dst])
+    torch.manual_seed(seed)
+    layer = GATv3Conv(Fin, C, H, dropout=0, edge_dim=Fin, bias=True).double()
+    with torch.no_grad():
+        layer.lin_l.bias.copy_(torch.randn(H * C, generator=gen, dtype=torch.float64) * 0.1)
+        layer.lin_r.bias.copy_(torch.randn(H * C, generator=gen, dtype=torch.float64) * 0.1)
+    assert layer.bias is None                  # reference quirk, generic/gatv3_conv.py:108-113
+    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64, requires_grad=True)
+    ea = torch.randn(E0, Fin, generator=gen, dtype=torch.float64)
+    out, (ei2, alpha) = layer(x, ei, ea, return_attention_weights=True)
+    R = torch.randn(out.shape, generator=gen, dtype=torch.float64)
+    names = [k for k, _ in layer.named_parameters()]
+    params = [p for _, p in layer.named_parameters()]
+    gr = grads_of((out * R).sum(), params + [x])
+    d = dict(edge_index=np_(ei), x=np_(x), ea=np_(ea), R=np_(R), out=np_(out),
+             edge_index_out=np_(ei2), alpha=np_(alpha), gx=np_(gr[-1]), heads=np.int64(H))
+    for k, p, gp in zip(names, params, gr):
+        d["p." + k] = np_(p)
+        d["g." + k] = np_(gp)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+# ---------------------------------------------------------------- a6/a7: head
+def golden_head(fname: str, seed: int):
+    from generic.agent import Agent
+
+    gen = torch.Generator().manual_seed(seed)
+    B, NN, F = 6, 17, 12
+    spec = types.SimpleNamespace(reward_weights=[1.0], two_hot=None, hl_gauss=None, symlog=False)
+    agent = Agent(env_specification=object(), agent_specification=spec)
+    node_features = torch.randn(B, NN, F, generator=gen)
+    graph_embedding = torch.randn(B, 1, F, generator=gen)
+    agent.gnn = lambda x: (node_features, graph_embedding)
+    torch.manual_seed(seed)
+    agent.value_net = torch.nn.Linear(F, 1)
+    agent.action_net = torch.nn.Linear(F, 1)
+    masks = torch.rand(B, NN + 5, generator=gen) < 0.4       # wider than logits: cropped (:202-203)
+    masks[:, 0] = True
+    masks[2, :] = False
+    masks[2, 7] = True                                          # single legal action
+    action_in = torch.tensor([int(torch.nonzero(masks[b, :NN])[0]) for b in range(B)])
+    d = dict(node_features=np_(node_features), graph_embedding=np_(graph_embedding),
+             masks=np_(masks), action_in=np_(action_in),
+             w_action=np_(agent.action_net.weight), b_action=np_(agent.action_net.bias),
+             w_value=np_(agent.value_net.weight), b_value=np_(agent.value_net.bias))
+    # deterministic, masked
+    a, lp, ent, val, um = agent.get_action_and_value(None, None, masks, deterministic=True)
+    d.update(det_action=np_(a), det_logprob=np_(lp), det_entropy=np_(ent), value=np_(val),
+             unmasked_logits=np_(um.logits))
+    # evaluate given actions (the PPO update call, alg/ppo.py:575-581) + grads wrt logits
+    nf = node_features.clone().requires_grad_(True)
+    agent.gnn = lambda x: (nf, graph_embedding)
+    a2, lp2, ent2, _, _ = agent.get_action_and_value(None, action_in, masks)
+    wl = torch.randn(B, generator=gen)
+    we = torch.randn(B, generator=gen)
+    (g_nf,) = torch.autograd.grad((lp2 * wl).sum() + (ent2 * we).sum(), [nf])
+    d.update(eval_logprob=np_(lp2), eval_entropy=np_(ent2), wl=np_(wl), we=np_(we), g_nf=np_(g_nf))
+    agent.gnn = lambda x: (node_features, graph_embedding)
+    # no mask
+    a3, lp3, ent3, _, _ = agent.get_action_and_value(None, action_in, None)
+    d.update(nomask_logprob=np_(lp3), nomask_entropy=np_(ent3))
+    # sampling: seeded
+    torch.manual_seed(1234)
+    a4, lp4, _, _, _ = agent.get_action_and_value(None, None, masks, deterministic=False)
+    d.update(sample_action=np_(a4), sample_logprob=np_(lp4))
+    # pretrain probs (:233-254) and predict (:256-277)
+    probs, _ = agent.get_action_probs_and_value(None, masks)
+    probs_nm, _ = agent.get_action_probs_and_value(None, None)
+    d.update(probs=np_(probs), probs_nomask=np_(probs_nm))
+    d["predict_det"] = np_(agent.predict(None, True, masks))
+    torch.manual_seed(4321)
+    d["predict_sample"] = np_(agent.predict(None, False, masks))
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+# ---------------------------------------------------------------- a8: MLP
+def golden_mlp(fname: str, seed: int):
+    from generic.mlp import MLP
+
+    gen = torch.Generator().manual_seed(seed)
+    d = {}
+    for i, (act, norm) in enumerate([("gelu", False), ("tanh", True), ("relu", False),
+                                     ("elu", False), ("selu", False), ("silu", False)]):
+        torch.manual_seed(seed + i)
+        m = MLP(3, 10, 12, 5, norm, act)
+        x = torch.randn(9, 10, generator=gen, requires_grad=True)
+        y = m(x)
+        R = torch.randn(y.shape, generator=gen)
+        params = list(m.parameters())
+        gr = grads_of((y * R).sum(), params + [x])
+        d[f"{i}.act"] = np.array(act)
+        d[f"{i}.norm"] = np.array(norm)
+        d[f"{i}.x"], d[f"{i}.y"], d[f"{i}.R"], d[f"{i}.gx"] = np_(x), np_(y), np_(R), np_(gr[-1])
+        for (k, p), gp in zip(m.named_parameters(), gr):
+            d[f"{i}.p.{k}"] = np_(p)
+            d[f"{i}.g.{k}"] = np_(gp)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+# ---------------------------------------------------------------- a9: edge embedder
+def golden_edge_embedder(fname: str, seed: int):
+    from psp.models.edge_embedder import PspEdgeEmbedder
+
+    gen = torch.Generator().manual_seed(seed)
+    E, Hd = 23, 8
+    torch.manual_seed(seed)
+    emb = PspEdgeEmbedder("sum", 4, Hd, "all", False, 3, "gelu")
+    etype = torch.randint(0, 16, (E,), generator=gen)
+    att_rc = torch.randn(E, 2, generator=gen)
+    att_rp = torch.randn(E, 3, generator=gen)
+
+    class G:
+        def edata(self, _t, name):
+            return {"type": etype, "att_rc": att_rc, "att_rp": att_rp}[name]
+
+    out = emb(G())
+    d = dict(type=np_(etype), att_rc=np_(att_rc), att_rp=np_(att_rp), out=np_(out))
+    for k, p in emb.named_parameters():
+        d["p." + k] = np_(p)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+# ---------------------------------------------------------------- a4: JSSP (DGL flavour) batching
+def _install_dgl_batching_shim():
+    """dgl.add_self_loop / dgl.batch / DGLGraph.add_edges for
+    jssp/models/agent_observation.py (published DGL semantics: add_self_loop
+    appends one (i,i) edge per node after the existing edges with the named edge
+    features filled with ``fill_data``; batch concatenates graphs in order,
+    offsetting node ids by the cumulative node count)."""
+    import dgl
+
+    def add_edges(self, u, v, data=None):
+        u = torch.as_tensor(u).long()
+        v = torch.as_tensor(v).long()
+        n_old = self._src.numel()
+        self._src = torch.cat([self._src, u])
+        self._dst = torch.cat([self._dst, v])
+        for k in list(self.edata.keys()):
+            new = data[k] if (data is not None and k in data) else torch.zeros(
+                (u.numel(),) + tuple(self.edata[k].shape[1:]), dtype=self.edata[k].dtype)
+            self.edata[k] = torch.cat([self.edata[k], torch.as_tensor(new).to(self.edata[k].dtype)])
+        assert all(v_.shape[0] == n_old + u.numel() for v_ in self.edata.values())
+
+    def to(self, device):
+        return self
+
+    def add_self_loop(g, edge_feat_names=None, fill_data=1.0):
+        new = dgl.graph((g._src.clone(), g._dst.clone()), num_nodes=g._n)
+        new.ndata = dict(g.ndata)
+        new.edata = dict(g.edata)
+        loop = torch.arange(g._n)
+        data = {k: torch.full((g._n,), fill_data, dtype=new.edata[k].dtype)
+                for k in (edge_feat_names or [])}
+        new.add_edges(loop, loop, data=data)
+        return new
+
+    def batch(graphs):
+        off = 0
+        srcs, dsts = [], []
+        for g in graphs:
+            srcs.append(g._src + off)
+            dsts.append(g._dst + off)
+            off += g._n
+        out = dgl.graph((torch.cat(srcs), torch.cat(dsts)), num_nodes=off)
+        for k in graphs[0].ndata:
+            out.ndata[k] = torch.cat([g.ndata[k] for g in graphs])
+        for k in graphs[0].edata:
+            out.edata[k] = torch.cat([g.edata[k] for g in graphs])
+        out.batch_size = len(graphs)
+        out.set_batch_num_nodes = lambda t: setattr(out, "_bnn", t)
+        out.set_batch_num_edges = lambda t: setattr(out, "_bne", t)
+        out.batch_num_nodes = lambda: out._bnn
+        out.batch_num_edges = lambda: out._bne
+        return out
+
+    dgl.DGLGraph.add_edges = add_edges
+    dgl.DGLGraph.to = to
+    dgl.add_self_loop = add_self_loop
+    dgl.batch = batch
+    # agent_observation.py imports generic.tokengt.utils (laplacian PE helper, unused here)
+    stub = types.ModuleType("generic.tokengt.utils")
+    stub.get_laplacian_pe_simple = None
+    sys.modules.setdefault("generic.tokengt", types.ModuleType("generic.tokengt"))
+    sys.modules["generic.tokengt.utils"] = stub
+
+
+def synthetic_jssp_obs(n_j, n_m, batch, seed, scheduled_frac=0.0, feat_dim=10, pad_nodes=0, pad_edges=0):
+    """A padded gym observation dict in the layout of jssp/env/observation.py:83-128:
+    precedence edges ordered as jssp/env/state.py:220-227, plus machine-chain edges for
+    a seeded random dispatch order (state.py:655-674 appends them one by one)."""
+    rng = np.random.default_rng(seed)
+    n = n_j * n_m
+    feats, eis, nes = [], [], []
+    for b in range(batch):
+        machines = np.stack([rng.permutation(n_m) for _ in range(n_j)])   # [n_j, n_m]
+        f = rng.random((n, feat_dim)).astype(np.float32)
+        f[:, 6] = machines.reshape(-1)
+        f[:, 1] = np.where(rng.random(n) < 0.3, -1.0, f[:, 1])
+        edges = [(j * n_m + i, j * n_m + i + 1) for i in range(n_m - 1) for j in range(n_j)]
+        # machine chains: dispatch a random prefix of operations job by job
+        n_sched = int(scheduled_frac * n)
+        next_op = np.zeros(n_j, dtype=np.int64)
+        last_on_machine = {}
+        for _ in range(n_sched):
+            cand = np.nonzero(next_op < n_m)[0]
+            j = int(rng.choice(cand))
+            node = j * n_m + int(next_op[j])
+            m = int(machines[j, next_op[j]])
+            if m in last_on_machine:
+                edges.append((last_on_machine[m], node))
+            last_on_machine[m] = node
+            next_op[j] += 1
+        ei = np.array(edges, dtype=np.int64).T
+        feats.append(f)
+        eis.append(ei)
+        nes.append(ei.shape[1])
+    max_e = max(nes) + pad_edges
+    F = np.zeros((batch, n + pad_nodes, feat_dim), dtype=np.float32)
+    EI = np.zeros((batch, 2, max_e), dtype=np.int64)
+    for b in range(batch):
+        F[b, :n] = feats[b]
+        EI[b, :, : nes[b]] = eis[b]
+    return {"features": torch.tensor(F), "edge_index": torch.tensor(EI),
+            "n_nodes": torch.tensor([n] * batch), "n_edges": torch.tensor(nes)}
+
+
+def golden_jssp_batch(fname: str, seed: int):
+    _install_dgl_batching_shim()
+    from jssp.models.agent_observation import AgentObservation
+    from jssp.utils.utils import compute_conflicts_cliques
+
+    d = {}
+    mid = torch.tensor([0, 1, -1, 1, 0, 2, 2, 0, -1, 1])
+    ce, cemid = compute_conflicts_cliques(mid)
+    d.update(clq_mid=np_(mid), clq_edges=np_(ce), clq_edges_mid=np_(cemid))
+    for tag, conflicts, mie in [("att", "att", False), ("clique", "clique", False),
+                                ("cliquemid", "clique", True)]:
+        obs = synthetic_jssp_obs(4, 3, 3, seed, scheduled_frac=0.5, pad_nodes=2, pad_edges=3)
+        ao = AgentObservation.from_gym_observation(obs, conflicts=conflicts, max_n_machines=3,
+                                                   mid_in_edges=mie)
+        g = ao.to_graph()
+        for k, v in obs.items():
+            d[f"{tag}.obs.{k}"] = np_(v)
+        d[f"{tag}.src"], d[f"{tag}.dst"] = np_(g._src), np_(g._dst)
+        d[f"{tag}.type"] = np_(g.edata["type"])
+        d[f"{tag}.feat"] = np_(g.ndata["feat"])
+        d[f"{tag}.bnn"], d[f"{tag}.bne"] = np_(g.batch_num_nodes()), np_(g.batch_num_edges())
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+if __name__ == "__main__":
+    golden_eegat(False, "eegat.npz", 11)
+    golden_eegat(True, "eegat_edge_scoring.npz", 12)
+    golden_gatv3("gatv3.npz", 13)
+    golden_head("head.npz", 14)
+    golden_mlp("mlp.npz", 15)
+    golden_edge_embedder("edge_embedder.npz", 16)
+    golden_jssp_batch("jssp_batch.npz", 17)
+    print("golden fixtures written to", HERE)
