@@ -1,0 +1,156 @@
+/* b200gat - C ABI of the B200-native graph-attention hot path for Wheatley.
+ *
+ * Wheatley (jolibrain/wheatley @ 7143392) is pure Python: the "FFI" of this path in
+ * the reference is the set of third-party ops its layers dispatch to (SURVEY.md 2.2,
+ * K1-K9).  Each entry point below replaces one of those dispatch sites; the reference
+ * file:line is cited per function.  INTEGRATION.md shows the ctypes binding a Wheatley
+ * maintainer adds (wheatley_b200/_lib.py is that binding).
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless stated otherwise; tensors are dense,
+ *    row-major, fp32 / int32 (int64 only where the reference hands over int64 COO);
+ *  - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no call
+ *    synchronises the device;
+ *  - return value: 0 on success, a B200GAT_ERR_* code otherwise; b200gat_last_error()
+ *    returns a host string describing the last failure of the calling thread;
+ *  - an edge e goes src[e] -> dst[e]; messages are reduced at dst.
+ */
+#ifndef B200GAT_H
+#define B200GAT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200GAT_OK 0
+#define B200GAT_ERR_INVALID 1     /* bad argument (null pointer, negative size, ...)      */
+#define B200GAT_ERR_CUDA 2        /* a CUDA runtime call / launch failed                   */
+#define B200GAT_ERR_UNSUPPORTED 3 /* shape not supported by any kernel variant             */
+
+#define B200GAT_FLAVOUR_ADDITIVE 0 /* EGAT / GATv2: s = attn . leaky_relu(Pi[u]+Pj[v]+Pe) */
+#define B200GAT_FLAVOUR_DOT 1      /* GATv3: s = (w_c . (Pj[v]*Pi[u]) + b_c) / sqrt(D)    */
+
+#define B200GAT_EDGE_NONE 0
+#define B200GAT_EDGE_TABLE 1 /* Pe[e] = table[etype[e]]   (edge features are an Embedding(type)) */
+#define B200GAT_EDGE_DENSE 2 /* Pe[e] = dense[e]          (caller projected [E,Fe] itself)       */
+
+const char* b200gat_last_error(void);
+int b200gat_version(void);
+
+/* ------------------------------------------------------------------ graph plan
+ * Topology of one batched graph in both orders, built once per batch and reused by
+ * every layer and by forward and backward (the topology is layer-invariant,
+ * psp/models/gnn_flat.py:204-208, jssp/models/gnn_dgl.py:366-377).
+ * Replaces: DGL's CSR/CSC materialisation behind apply_edges / edge_softmax /
+ * update_all (generic/eegatconv.py:269,280,292) and PyG's scatter index handling
+ * (generic/gatv3_conv.py:155-160,193).                                              */
+typedef struct {
+  int32_t n_nodes;
+  int32_t n_edges;
+  const int32_t* in_ptr;  /* [N+1] CSR by destination                                    */
+  const int32_t* in_src;  /* [E]   source node of each dst-sorted edge                   */
+  const int32_t* in_eid;  /* [E]   original edge id of each dst-sorted edge (stable:     */
+                          /*       ascending inside a destination segment)               */
+  const int32_t* out_ptr; /* [N+1] CSR by source                                         */
+  const int32_t* out_dst; /* [E]   destination node of each src-sorted edge              */
+  const int32_t* out_pos; /* [E]   position of that edge in the dst-sorted order         */
+} b200gat_graph;
+
+/* Number of int32 scratch elements b200gat_plan_build needs. */
+int64_t b200gat_plan_scratch_elems(int64_t n_nodes, int64_t n_edges);
+
+/* Build the plan from int64 COO (what dgl.batch / Batch.from_data_list hand over,
+ * jssp/models/agent_observation.py:223, psp/graph/pyg_graph.py:321-323).
+ * edge_src/edge_dst: [E] int64.  Outputs as in b200gat_graph (caller-allocated).
+ * stats (int32[4], device): [0] #nodes with zero in-degree, [1] max in-degree,
+ * [2] #edges with an endpoint outside [0,N), [3] max out-degree.                     */
+int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_dst, int64_t n_edges,
+                       int64_t n_nodes, int32_t* in_ptr, int32_t* in_src, int32_t* in_eid,
+                       int32_t* out_ptr, int32_t* out_dst, int32_t* out_pos, int32_t* scratch,
+                       int32_t* stats, void* stream);
+
+/* out[i] = table[idx[i]] for int32 (permute per-edge attributes into dst-sorted order). */
+int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
+                       void* stream);
+/* out[i] = (int32) in[i]  (int64 -> int32 narrowing with 16-byte loads). */
+int b200gat_narrow_i64(const int64_t* in, int64_t n, int32_t* out, void* stream);
+
+/* ------------------------------------------------------------------ attention layer */
+typedef struct {
+  int32_t flavour; /* B200GAT_FLAVOUR_*                                                  */
+  int32_t heads;   /* H                                                                  */
+  int32_t dim;     /* D  (per-head feature size; De == Do is required)                   */
+  float slope;     /* leaky_relu slope: 0.01 EGAT (generic/eegatconv.py:276), 0.2 GATv2  */
+  float softmax_eps;      /* 0 for DGL edge_softmax, 1e-16 for PyG softmax               */
+  const float* attn;      /* additive: [H*D];  dot: w_c [D] (shared by heads)            */
+  const float* attn_bias; /* dot: b_c [1]; else NULL                                     */
+  const float* out_bias;  /* [H*D] added after aggregation (GATv2 `bias`), or NULL       */
+} b200gat_attn;
+
+typedef struct {
+  int32_t mode;         /* B200GAT_EDGE_*                                                */
+  int32_t n_types;      /* rows of `table`                                               */
+  const float* table;   /* [T, H*D]; fold the EGAT pre-activation bias into it           */
+  const int32_t* etype; /* [E] edge type in DST-SORTED order (see b200gat_gather_i32)    */
+  const float* dense;   /* [E, H*D] in ORIGINAL edge order                               */
+} b200gat_edge_feats;
+
+/* Fused per-edge logit + segmented edge-softmax + weighted aggregation.
+ * Replaces generic/eegatconv.py:266-292 (apply_edges u_add_v, leaky_relu, attn dot,
+ * edge_softmax, update_all u_mul_e/sum) and PyG GATv2Conv/GATv3Conv propagate
+ * (psp/graph/graph_conv.py:51-53, generic/gatv3_conv.py:155-198).
+ *   Pi, Pj, V : [N, H*D] projected node tensors (V may alias Pi: GATv2/GATv3 x_l)
+ *   out       : [N, H*D]
+ *   s_save    : [E, H] raw logits in dst-sorted order   (saved for backward)
+ *   m_save,l_save : [N, H] per-destination max and sum of exp(s-m)                      */
+int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
+                     const float* Pi, const float* Pj, const float* V, float* out,
+                     float* s_save, float* m_save, float* l_save, void* stream);
+
+/* Matching fused backward (replaces autograd through the ops above).
+ *   g_out            : [N, H*D]
+ *   gPi, gPj, gV     : [N, H*D] written (not accumulated).  If gV == gPi the sum of both
+ *                      contributions is written there (GATv2: x_l is logit term and value).
+ *   g_attn           : [H*D] (additive) / [D] (dot), ACCUMULATED with atomics: zero it first
+ *   g_attn_bias      : [1] (dot), accumulated; else NULL
+ *   g_table          : [T, H*D] accumulated (EDGE_TABLE) ; g_dense: [E, H*D] written (EDGE_DENSE)
+ *   gs_scratch       : [E, H] scratch (dst-sorted order)                                  */
+int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
+                     const float* Pi, const float* Pj, const float* V, const float* s_save,
+                     const float* m_save, const float* l_save, const float* g_out, float* gPi,
+                     float* gPj, float* gV, float* g_attn, float* g_attn_bias, float* g_table,
+                     float* g_dense, float* gs_scratch, void* stream);
+
+/* alpha[e,h] in ORIGINAL edge order from the saved logits (get_attention=True,
+ * generic/eegatconv.py:304-308; return_attention_weights, generic/gatv3_conv.py:174-179). */
+int b200gat_attention(const b200gat_graph* g, int32_t heads, float softmax_eps,
+                      const float* s_save, const float* m_save, const float* l_save,
+                      float* alpha, void* stream);
+
+/* f_out[e] = leaky_relu(Pi[src]+Pj[dst]+Pe[e]) in ORIGINAL edge order: the edge output of
+ * EGATConv (generic/eegatconv.py:276-277,313), produced on request only.                  */
+int b200gat_edge_out(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
+                     const float* Pi, const float* Pj, float* f_out, void* stream);
+
+/* ------------------------------------------------------------------ masked action head
+ * Replaces the torch.where / logsumexp / Categorical chain of
+ * generic/agent.py:197-231 (fill -1e20), :238-254 (fill -1e10) and :256-277.
+ *   logits [B, n] (row stride ld_logits), mask [B, >=n] bytes (row stride ld_mask) or NULL
+ *   logp   [B, n] normalised log-probabilities of the masked distribution
+ *   entropy[B]    -sum_mask p log p   (all entries when mask == NULL)
+ *   argmax [B]    first index of the maximum masked logit (int64, like torch.argmax)     */
+int b200gat_mask_head_fwd(const float* logits, int64_t ld_logits, const uint8_t* mask,
+                          int64_t ld_mask, int32_t batch, int32_t n, float fill, float* logp,
+                          float* entropy, int64_t* argmax, void* stream);
+/* g_logits[b,j] = mask ? (1[j==action_b] - p_bj) * g_logprob_b - p_bj (logp_bj + H_b) * g_entropy_b : 0 */
+int b200gat_mask_head_bwd(const float* logp, const uint8_t* mask, int64_t ld_mask,
+                          const int64_t* action, const float* entropy, const float* g_logprob,
+                          const float* g_entropy, int32_t batch, int32_t n, float* g_logits,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GAT_H */

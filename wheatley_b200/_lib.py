@@ -1,0 +1,87 @@
+"""ctypes binding of libb200gat.so - the C-ABI declared in include/b200gat.h.
+
+This is the binding a Wheatley maintainer would add.  There is no
+fallback: if the library is missing the import fails loudly."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200gat.so")
+
+EDGE_NONE, EDGE_TABLE, EDGE_DENSE = 0, 1, 2
+FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
+
+# every symbol include/b200gat.h declares (tests check that the library exports all of them)
+SYMBOLS = (
+    "b200gat_last_error", "b200gat_version", "b200gat_plan_scratch_elems", "b200gat_plan_build",
+    "b200gat_gather_i32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
+    "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
+)
+
+
+class Graph(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
+                ("in_ptr", C.c_void_p), ("in_src", C.c_void_p), ("in_eid", C.c_void_p),
+                ("out_ptr", C.c_void_p), ("out_dst", C.c_void_p), ("out_pos", C.c_void_p)]
+
+
+class Attn(C.Structure):
+    _fields_ = [("flavour", C.c_int32), ("heads", C.c_int32), ("dim", C.c_int32),
+                ("slope", C.c_float), ("softmax_eps", C.c_float),
+                ("attn", C.c_void_p), ("attn_bias", C.c_void_p), ("out_bias", C.c_void_p)]
+
+
+class EdgeFeats(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("n_types", C.c_int32),
+                ("table", C.c_void_p), ("etype", C.c_void_p), ("dense", C.c_void_p)]
+
+
+class B200GatError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m wheatley_b200.build` "
+            "(or __graft_entry__.build()).  wheatley_b200 has no CPU / PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp, i64, i32, f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_float
+    lib.b200gat_last_error.restype = C.c_char_p
+    lib.b200gat_last_error.argtypes = []
+    lib.b200gat_version.restype = C.c_int
+    lib.b200gat_plan_scratch_elems.restype = i64
+    lib.b200gat_plan_scratch_elems.argtypes = [i64, i64]
+    lib.b200gat_plan_build.argtypes = [vp, vp, i64, i64] + [vp] * 9
+    lib.b200gat_gather_i32.argtypes = [vp, vp, i64, vp, vp]
+    lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]
+    gp, ap, ep = C.POINTER(Graph), C.POINTER(Attn), C.POINTER(EdgeFeats)
+    lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 8
+    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 16
+    lib.b200gat_attention.argtypes = [gp, i32, f32, vp, vp, vp, vp, vp]
+    lib.b200gat_edge_out.argtypes = [gp, ap, ep, vp, vp, vp, vp]
+    lib.b200gat_mask_head_fwd.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, vp, vp, vp]
+    lib.b200gat_mask_head_bwd.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32, i32, vp, vp]
+    for name in SYMBOLS:
+        fn = getattr(lib, name)
+        if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems"):
+            fn.restype = C.c_int
+    return lib
+
+
+lib = _load()
+
+
+def check(rc, what):
+    if rc != 0:
+        raise B200GatError(f"{what} failed (code {rc}): {lib.b200gat_last_error().decode()}")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,45 @@
+// Shared helpers for the b200gat kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/b200gat.h"
+
+namespace b200gat {
+
+void set_error(const char* fmt, ...);
+
+#define B200_CHECK_ARG(cond, msg)                       \
+  do {                                                  \
+    if (!(cond)) {                                      \
+      b200gat::set_error("invalid argument: %s", msg);  \
+      return B200GAT_ERR_INVALID;                       \
+    }                                                   \
+  } while (0)
+
+#define B200_CHECK_LAUNCH(name)                                                     \
+  do {                                                                              \
+    cudaError_t e__ = cudaGetLastError();                                           \
+    if (e__ != cudaSuccess) {                                                       \
+      b200gat::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__));   \
+      return B200GAT_ERR_CUDA;                                                      \
+    }                                                                               \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200
+
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float leaky(float z, float slope) { return z > 0.f ? z : z * slope; }
+
+}  // namespace b200gat

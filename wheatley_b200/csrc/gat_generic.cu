@@ -1,0 +1,380 @@
+// Generic (any H, any D <= 128) fused graph-attention kernels: one warp per
+// (destination, head) for the forward and the destination half of the backward, one warp
+// per (source, head) for the source half of the backward.  All segmented reductions run
+// in CSR order -> bit-reproducible; only the parameter gradients (attn, edge table) use
+// float atomics.  These kernels are the always-available path and the cross-check for
+// the specialised kernels in gat_fast.cu.
+#include <math.h>
+#include "common.cuh"
+#include "gat_kernels.cuh"
+
+namespace b200gat {
+
+constexpr int kMaxK = 4;  // D <= 128
+
+struct GenericArgs {
+  // graph
+  int N, E;
+  const int32_t *in_ptr, *in_src, *in_eid, *out_ptr, *out_dst, *out_pos;
+  // attention
+  int H, D;
+  float slope, eps, inv_sqrt_d;
+  const float *attn, *attn_bias, *out_bias;
+  // edge features
+  int emode;
+  const float* table;
+  const int32_t* etype;
+  const float* dense;
+};
+
+__device__ __forceinline__ float edge_feat(const GenericArgs& A, int pos, int f) {
+  if (A.emode == B200GAT_EDGE_TABLE) return __ldg(A.table + (int64_t)A.etype[pos] * (A.H * A.D) + f);
+  if (A.emode == B200GAT_EDGE_DENSE) return __ldg(A.dense + (int64_t)A.in_eid[pos] * (A.H * A.D) + f);
+  return 0.f;
+}
+
+template <int FLAV>
+__global__ void __launch_bounds__(128) k_fwd_generic(GenericArgs A, const float* __restrict__ Pi,
+                                                     const float* __restrict__ Pj,
+                                                     const float* __restrict__ V,
+                                                     float* __restrict__ out, float* __restrict__ s_save,
+                                                     float* __restrict__ m_save, float* __restrict__ l_save) {
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (int64_t)A.N * A.H) return;
+  const int v = (int)(wid / A.H), h = (int)(wid % A.H);
+  const int HD = A.H * A.D, hoff = h * A.D;
+  const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
+  float pj[kMaxK], at[kMaxK];
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    bool ok = d < A.D;
+    pj[k] = ok ? Pj[(int64_t)v * HD + hoff + d] : 0.f;
+    if (FLAV == B200GAT_FLAVOUR_ADDITIVE) at[k] = ok ? A.attn[hoff + d] : 0.f;
+    else at[k] = ok ? A.attn[d] : 0.f;
+  }
+  const float sbias = (FLAV == B200GAT_FLAVOUR_DOT) ? A.attn_bias[0] : 0.f;
+  float mx = -INFINITY;
+  for (int e = b; e < en; ++e) {
+    const int u = A.in_src[e];
+    float part = 0.f;
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D) {
+        float pi = __ldg(Pi + (int64_t)u * HD + hoff + d);
+        if (FLAV == B200GAT_FLAVOUR_ADDITIVE) {
+          float z = pi + pj[k] + edge_feat(A, e, hoff + d);
+          part += at[k] * leaky(z, A.slope);
+        } else {
+          part += at[k] * (pj[k] * pi);
+        }
+      }
+    }
+    float sc = warp_sum(part);
+    if (FLAV == B200GAT_FLAVOUR_DOT) sc = (sc + sbias) * A.inv_sqrt_d;
+    if (lane == 0) s_save[(int64_t)e * A.H + h] = sc;
+    mx = fmaxf(mx, sc);
+  }
+  __syncwarp();
+  float l = 0.f, acc[kMaxK] = {0.f, 0.f, 0.f, 0.f};
+  for (int e = b; e < en; ++e) {
+    const int u = A.in_src[e];
+    const float p = expf(s_save[(int64_t)e * A.H + h] - mx);
+    l += p;
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D) acc[k] = fmaf(p, __ldg(V + (int64_t)u * HD + hoff + d), acc[k]);
+    }
+  }
+  const float inv = en > b ? 1.f / (l + A.eps) : 0.f;
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    if (d < A.D) {
+      float o = acc[k] * inv;
+      if (A.out_bias) o += A.out_bias[hoff + d];
+      out[(int64_t)v * HD + hoff + d] = o;
+    }
+  }
+  if (lane == 0) {
+    m_save[(int64_t)v * A.H + h] = en > b ? mx : 0.f;
+    l_save[(int64_t)v * A.H + h] = l;
+  }
+}
+
+template <int FLAV>
+__global__ void __launch_bounds__(128) k_bwd_dst_generic(
+    GenericArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj,
+    const float* __restrict__ V, const float* __restrict__ s_save, const float* __restrict__ m_save,
+    const float* __restrict__ l_save, const float* __restrict__ G, float* __restrict__ gPj,
+    float* __restrict__ g_attn, float* __restrict__ g_attn_bias, float* __restrict__ g_table,
+    float* __restrict__ g_dense, float* __restrict__ gs) {
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (int64_t)A.N * A.H) return;
+  const int v = (int)(wid / A.H), h = (int)(wid % A.H);
+  const int HD = A.H * A.D, hoff = h * A.D;
+  const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
+  float pj[kMaxK], at[kMaxK], g[kMaxK];
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    bool ok = d < A.D;
+    pj[k] = ok ? Pj[(int64_t)v * HD + hoff + d] : 0.f;
+    g[k] = ok ? G[(int64_t)v * HD + hoff + d] : 0.f;
+    if (FLAV == B200GAT_FLAVOUR_ADDITIVE) at[k] = ok ? A.attn[hoff + d] : 0.f;
+    else at[k] = ok ? A.attn[d] : 0.f;
+  }
+  const float mx = m_save[(int64_t)v * A.H + h];
+  const float linv = en > b ? 1.f / (l_save[(int64_t)v * A.H + h] + A.eps) : 0.f;
+  // pass A: ga_e = <G[v], V[u]>,  dot = sum_e a_e ga_e
+  float dot = 0.f;
+  for (int e = b; e < en; ++e) {
+    const int u = A.in_src[e];
+    float part = 0.f;
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D) part = fmaf(g[k], __ldg(V + (int64_t)u * HD + hoff + d), part);
+    }
+    const float ga = warp_sum(part);
+    const float a = expf(s_save[(int64_t)e * A.H + h] - mx) * linv;
+    dot = fmaf(a, ga, dot);
+    if (lane == 0) gs[(int64_t)e * A.H + h] = ga;
+  }
+  __syncwarp();
+  // pass B
+  float gat[kMaxK] = {0.f, 0.f, 0.f, 0.f}, gpj[kMaxK] = {0.f, 0.f, 0.f, 0.f};
+  float gb = 0.f;
+  for (int e = b; e < en; ++e) {
+    const int u = A.in_src[e];
+    const float ga = gs[(int64_t)e * A.H + h];
+    const float a = expf(s_save[(int64_t)e * A.H + h] - mx) * linv;
+    const float gsv = a * (ga - dot);
+    __syncwarp();
+    if (lane == 0) gs[(int64_t)e * A.H + h] = gsv;
+    if (FLAV == B200GAT_FLAVOUR_DOT) gb += gsv * A.inv_sqrt_d;
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D) {
+        float pi = __ldg(Pi + (int64_t)u * HD + hoff + d);
+        if (FLAV == B200GAT_FLAVOUR_ADDITIVE) {
+          float z = pi + pj[k] + edge_feat(A, e, hoff + d);
+          gat[k] = fmaf(gsv, leaky(z, A.slope), gat[k]);
+          float gz = gsv * at[k] * (z > 0.f ? 1.f : A.slope);
+          gpj[k] += gz;
+          if (A.emode == B200GAT_EDGE_DENSE) g_dense[(int64_t)A.in_eid[e] * HD + hoff + d] = gz;
+          else if (A.emode == B200GAT_EDGE_TABLE)
+            atomicAdd(g_table + (int64_t)A.etype[e] * HD + hoff + d, gz);
+        } else {
+          float c = gsv * A.inv_sqrt_d;
+          gat[k] = fmaf(c, pj[k] * pi, gat[k]);
+          gpj[k] = fmaf(c * at[k], pi, gpj[k]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    if (d < A.D) {
+      gPj[(int64_t)v * HD + hoff + d] = gpj[k];
+      if (en > b) atomicAdd(g_attn + (FLAV == B200GAT_FLAVOUR_ADDITIVE ? hoff + d : d), gat[k]);
+    }
+  }
+  if (FLAV == B200GAT_FLAVOUR_DOT && lane == 0 && en > b) atomicAdd(g_attn_bias, gb);
+}
+
+template <int FLAV>
+__global__ void __launch_bounds__(128) k_bwd_src_generic(
+    GenericArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj,
+    const float* __restrict__ s_save, const float* __restrict__ m_save,
+    const float* __restrict__ l_save, const float* __restrict__ G, const float* __restrict__ gs,
+    float* __restrict__ gPi, float* __restrict__ gV) {
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (int64_t)A.N * A.H) return;
+  const int u = (int)(wid / A.H), h = (int)(wid % A.H);
+  const int HD = A.H * A.D, hoff = h * A.D;
+  const int b = A.out_ptr[u], en = A.out_ptr[u + 1];
+  float pi[kMaxK], at[kMaxK];
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    bool ok = d < A.D;
+    pi[k] = ok ? Pi[(int64_t)u * HD + hoff + d] : 0.f;
+    if (FLAV == B200GAT_FLAVOUR_ADDITIVE) at[k] = ok ? A.attn[hoff + d] : 0.f;
+    else at[k] = ok ? A.attn[d] : 0.f;
+  }
+  float gpi[kMaxK] = {0.f, 0.f, 0.f, 0.f}, gv[kMaxK] = {0.f, 0.f, 0.f, 0.f};
+  for (int q = b; q < en; ++q) {
+    const int pos = A.out_pos[q], v = A.out_dst[q];
+    const float gsv = gs[(int64_t)pos * A.H + h];
+    const float a = expf(s_save[(int64_t)pos * A.H + h] - m_save[(int64_t)v * A.H + h]) /
+                    (l_save[(int64_t)v * A.H + h] + A.eps);
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D) {
+        float pjv = __ldg(Pj + (int64_t)v * HD + hoff + d);
+        if (FLAV == B200GAT_FLAVOUR_ADDITIVE) {
+          float z = pi[k] + pjv + edge_feat(A, pos, hoff + d);
+          gpi[k] += gsv * at[k] * (z > 0.f ? 1.f : A.slope);
+        } else {
+          gpi[k] = fmaf(gsv * A.inv_sqrt_d * at[k], pjv, gpi[k]);
+        }
+        gv[k] = fmaf(a, __ldg(G + (int64_t)v * HD + hoff + d), gv[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < kMaxK; ++k) {
+    int d = lane + 32 * k;
+    if (d < A.D) {
+      int64_t o = (int64_t)u * HD + hoff + d;
+      if (gV == gPi) gPi[o] = gpi[k] + gv[k];
+      else { gPi[o] = gpi[k]; gV[o] = gv[k]; }
+    }
+  }
+}
+
+__global__ void k_attention(int N, int H, float eps, const int32_t* __restrict__ in_ptr,
+                            const int32_t* __restrict__ in_eid, const float* __restrict__ s_save,
+                            const float* __restrict__ m_save, const float* __restrict__ l_save,
+                            float* __restrict__ alpha) {
+  const int64_t v = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (v >= N) return;
+  const int b = in_ptr[v], en = in_ptr[v + 1];
+  const int64_t n = (int64_t)(en - b) * H;
+  for (int64_t i = lane; i < n; i += 32) {
+    int e = b + (int)(i / H), h = (int)(i % H);
+    alpha[(int64_t)in_eid[e] * H + h] =
+        expf(s_save[(int64_t)e * H + h] - m_save[v * H + h]) / (l_save[v * H + h] + eps);
+  }
+}
+
+__global__ void k_edge_out(GenericArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj,
+                           float* __restrict__ f_out) {
+  const int64_t v = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (v >= A.N) return;
+  const int HD = A.H * A.D;
+  for (int e = A.in_ptr[v]; e < A.in_ptr[v + 1]; ++e) {
+    const int u = A.in_src[e];
+    const int64_t eid = A.in_eid[e];
+    for (int f = lane; f < HD; f += 32)
+      f_out[eid * HD + f] = leaky(Pi[(int64_t)u * HD + f] + Pj[v * HD + f] + edge_feat(A, e, f), A.slope);
+  }
+}
+
+static int fill_args(GenericArgs& A, const b200gat_graph* g, const b200gat_attn* a,
+                     const b200gat_edge_feats* ef) {
+  B200_CHECK_ARG(g && a, "null graph/attn descriptor");
+  B200_CHECK_ARG(g->n_nodes >= 0 && g->n_edges >= 0, "negative graph size");
+  B200_CHECK_ARG(a->heads > 0 && a->dim > 0, "heads/dim must be positive");
+  B200_CHECK_ARG(a->flavour == B200GAT_FLAVOUR_ADDITIVE || a->flavour == B200GAT_FLAVOUR_DOT,
+                 "unknown flavour");
+  B200_CHECK_ARG(g->n_nodes == 0 || (g->in_ptr && g->out_ptr), "null CSR pointers");
+  B200_CHECK_ARG(g->n_edges == 0 || (g->in_src && g->in_eid && g->out_dst && g->out_pos),
+                 "null CSR edge arrays");
+  B200_CHECK_ARG(a->attn, "null attn");
+  B200_CHECK_ARG(a->flavour != B200GAT_FLAVOUR_DOT || a->attn_bias, "dot flavour needs attn_bias");
+  A.N = g->n_nodes; A.E = g->n_edges;
+  A.in_ptr = g->in_ptr; A.in_src = g->in_src; A.in_eid = g->in_eid;
+  A.out_ptr = g->out_ptr; A.out_dst = g->out_dst; A.out_pos = g->out_pos;
+  A.H = a->heads; A.D = a->dim; A.slope = a->slope; A.eps = a->softmax_eps;
+  A.inv_sqrt_d = 1.0f / sqrtf((float)a->dim);
+  A.attn = a->attn; A.attn_bias = a->attn_bias; A.out_bias = a->out_bias;
+  A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
+  A.table = ef ? ef->table : nullptr; A.etype = ef ? ef->etype : nullptr;
+  A.dense = ef ? ef->dense : nullptr;
+  if (a->flavour == B200GAT_FLAVOUR_DOT) A.emode = B200GAT_EDGE_NONE;  // GATv3 ignores edge_attr
+  if (A.emode == B200GAT_EDGE_TABLE) B200_CHECK_ARG(A.table && (A.E == 0 || A.etype), "null edge table/etype");
+  if (A.emode == B200GAT_EDGE_DENSE) B200_CHECK_ARG(A.E == 0 || A.dense, "null dense edge features");
+  return B200GAT_OK;
+}
+
+int generic_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
+                const float* Pi, const float* Pj, const float* V, float* out, float* s_save,
+                float* m_save, float* l_save, cudaStream_t st) {
+  GenericArgs A;
+  int rc = fill_args(A, g, a, ef);
+  if (rc) return rc;
+  if (A.D > 32 * kMaxK) {
+    set_error("generic kernels support dim <= %d (got %d)", 32 * kMaxK, A.D);
+    return B200GAT_ERR_UNSUPPORTED;
+  }
+  if (A.N == 0) return B200GAT_OK;
+  unsigned blocks = (unsigned)ceil_div((int64_t)A.N * A.H * 32, 128);
+  if (a->flavour == B200GAT_FLAVOUR_ADDITIVE)
+    k_fwd_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save);
+  else
+    k_fwd_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save);
+  B200_CHECK_LAUNCH("k_fwd_generic");
+  return B200GAT_OK;
+}
+
+int generic_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
+                const float* Pi, const float* Pj, const float* V, const float* s_save,
+                const float* m_save, const float* l_save, const float* g_out, float* gPi, float* gPj,
+                float* gV, float* g_attn, float* g_attn_bias, float* g_table, float* g_dense,
+                float* gs, cudaStream_t st) {
+  GenericArgs A;
+  int rc = fill_args(A, g, a, ef);
+  if (rc) return rc;
+  if (A.D > 32 * kMaxK) {
+    set_error("generic kernels support dim <= %d (got %d)", 32 * kMaxK, A.D);
+    return B200GAT_ERR_UNSUPPORTED;
+  }
+  if (A.emode == B200GAT_EDGE_TABLE) B200_CHECK_ARG(g_table, "null g_table");
+  if (A.emode == B200GAT_EDGE_DENSE) B200_CHECK_ARG(A.E == 0 || g_dense, "null g_dense");
+  if (A.N == 0) return B200GAT_OK;
+  unsigned blocks = (unsigned)ceil_div((int64_t)A.N * A.H * 32, 128);
+  if (a->flavour == B200GAT_FLAVOUR_ADDITIVE) {
+    k_bwd_dst_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(
+        A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, gs);
+    k_bwd_src_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
+                                                                      g_out, gs, gPi, gV);
+  } else {
+    k_bwd_dst_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(
+        A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, gs);
+    k_bwd_src_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
+                                                                 g_out, gs, gPi, gV);
+  }
+  B200_CHECK_LAUNCH("k_bwd_generic");
+  return B200GAT_OK;
+}
+
+}  // namespace b200gat
+
+using namespace b200gat;
+
+extern "C" int b200gat_attention(const b200gat_graph* g, int32_t heads, float eps, const float* s_save,
+                                 const float* m_save, const float* l_save, float* alpha, void* stream) {
+  B200_CHECK_ARG(g && heads > 0, "bad arguments");
+  if (g->n_nodes == 0 || g->n_edges == 0) return B200GAT_OK;
+  B200_CHECK_ARG(s_save && m_save && l_save && alpha, "null pointer");
+  k_attention<<<(unsigned)ceil_div((int64_t)g->n_nodes * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+      g->n_nodes, heads, eps, g->in_ptr, g->in_eid, s_save, m_save, l_save, alpha);
+  B200_CHECK_LAUNCH("k_attention");
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_edge_out(const b200gat_graph* g, const b200gat_attn* a,
+                                const b200gat_edge_feats* ef, const float* Pi, const float* Pj,
+                                float* f_out, void* stream) {
+  GenericArgs A;
+  int rc = fill_args(A, g, a, ef);
+  if (rc) return rc;
+  B200_CHECK_ARG(a->flavour == B200GAT_FLAVOUR_ADDITIVE, "edge_out is defined for the additive flavour");
+  if (A.N == 0 || A.E == 0) return B200GAT_OK;
+  B200_CHECK_ARG(Pi && Pj && f_out, "null pointer");
+  k_edge_out<<<(unsigned)ceil_div((int64_t)A.N * 32, 256), 256, 0, (cudaStream_t)stream>>>(A, Pi, Pj, f_out);
+  B200_CHECK_LAUNCH("k_edge_out");
+  return B200GAT_OK;
+}

@@ -1,0 +1,343 @@
+// Graph plan: int64 COO -> int32 CSR by destination + CSR by source, both STABLE
+// (edges keep their original relative order inside a segment), so every segmented
+// reduction downstream runs in a fixed order and is bit-reproducible.
+//
+// Pipeline (all on `stream`, no host sync):
+//   count   : 16-byte loads of the int64 endpoints, atomic histogram into ptr[i+1]
+//   scan    : 3-phase inclusive scan over N+1 counters (2048 per block)
+//   fill    : atomic slot claim inside each segment (order arbitrary)
+//   sort    : per-segment rank-by-counting on the original edge id (warp per node for
+//             degree <= 256, block per node above) -> stable order
+//   finish  : in_src / inverse permutation / out_dst / out_pos, degree statistics
+#include "common.cuh"
+
+namespace b200gat {
+
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;  // 2048
+constexpr int kWarpSortMax = 256;
+
+__global__ void k_count(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E,
+                        int32_t N, int32_t* __restrict__ in_ptr, int32_t* __restrict__ out_ptr,
+                        int32_t* __restrict__ stats, int vec) {
+  // two edges per thread: one 16-byte load per endpoint array when both are 16-byte aligned
+  int64_t i = (int64_t)(blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
+  int bad = 0;
+  if (i + 1 < E) {
+    longlong2 s, d;
+    if (vec) {
+      s = *reinterpret_cast<const longlong2*>(src + i);
+      d = *reinterpret_cast<const longlong2*>(dst + i);
+    } else {
+      s = make_longlong2(src[i], src[i + 1]);
+      d = make_longlong2(dst[i], dst[i + 1]);
+    }
+    if (s.x < 0 || s.x >= N || d.x < 0 || d.x >= N) bad++;
+    else { atomicAdd(&in_ptr[d.x + 1], 1); atomicAdd(&out_ptr[s.x + 1], 1); }
+    if (s.y < 0 || s.y >= N || d.y < 0 || d.y >= N) bad++;
+    else { atomicAdd(&in_ptr[d.y + 1], 1); atomicAdd(&out_ptr[s.y + 1], 1); }
+  } else if (i < E) {
+    int64_t s = src[i], d = dst[i];
+    if (s < 0 || s >= N || d < 0 || d >= N) bad++;
+    else { atomicAdd(&in_ptr[d + 1], 1); atomicAdd(&out_ptr[s + 1], 1); }
+  }
+  if (bad) atomicAdd(&stats[2], bad);
+}
+
+// ---- scan -----------------------------------------------------------------------------
+__device__ __forceinline__ int block_inclusive_scan(int v, int* smem_warp) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  if (lane == 31) smem_warp[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    int x = lane < (kScanThreads / 32) ? smem_warp[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += t;
+    }
+    smem_warp[lane] = x;
+  }
+  __syncthreads();
+  if (w > 0) v += smem_warp[w - 1];
+  __syncthreads();
+  return v;
+}
+
+// mode 0: block sums only; mode 1: in-place inclusive scan with block offsets.
+__global__ void k_scan_tiles(int32_t* __restrict__ a, int64_t n, int32_t* __restrict__ bsum,
+                             int mode) {
+  __shared__ int sw[32];
+  int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  int v[kScanItems];
+  int tsum = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    v[k] = (base + k < n) ? a[base + k] : 0;
+    tsum += v[k];
+  }
+  int incl = block_inclusive_scan(tsum, sw);
+  if (mode == 0) {
+    if (threadIdx.x == kScanThreads - 1) bsum[blockIdx.x] = incl;
+    return;
+  }
+  int run = incl - tsum + (blockIdx.x > 0 ? bsum[blockIdx.x - 1] : 0);
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    run += v[k];
+    if (base + k < n) a[base + k] = run;
+  }
+}
+
+// single block: inclusive scan of bsum[0..nb) in place
+__global__ void k_scan_bsums(int32_t* __restrict__ bsum, int nb) {
+  __shared__ int sw[32];
+  __shared__ int carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += kScanThreads) {
+    int i = base + threadIdx.x;
+    int v = i < nb ? bsum[i] : 0;
+    int incl = block_inclusive_scan(v, sw);
+    int carry = carry_s;
+    if (i < nb) bsum[i] = incl + carry;
+    __syncthreads();
+    if (threadIdx.x == kScanThreads - 1) carry_s = carry + incl;
+    __syncthreads();
+  }
+}
+
+// ---- fill -----------------------------------------------------------------------------
+__global__ void k_fill(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E,
+                       int32_t N, const int32_t* __restrict__ in_ptr,
+                       const int32_t* __restrict__ out_ptr, int32_t* __restrict__ fill_in,
+                       int32_t* __restrict__ fill_out, int32_t* __restrict__ tmp_in,
+                       int32_t* __restrict__ tmp_out) {
+  int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  int64_t s = src[e], d = dst[e];
+  if (s < 0 || s >= N || d < 0 || d >= N) return;
+  tmp_in[in_ptr[d] + atomicAdd(&fill_in[d], 1)] = (int32_t)e;
+  tmp_out[out_ptr[s] + atomicAdd(&fill_out[s], 1)] = (int32_t)e;
+}
+
+// ---- stable order inside segments: rank by counting -------------------------------------
+// One warp per node.  Segments longer than kWarpSortMax are pushed to `large` instead.
+__global__ void k_sort_small(const int32_t* __restrict__ ptr, int32_t N,
+                             const int32_t* __restrict__ tmp, int32_t* __restrict__ sorted,
+                             int32_t* __restrict__ large, int32_t* __restrict__ n_large) {
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (warp >= N) return;
+  int b = ptr[warp], deg = ptr[warp + 1] - b;
+  if (deg <= 0) return;
+  if (deg > kWarpSortMax) {
+    if (lane == 0) large[atomicAdd(n_large, 1)] = warp;
+    return;
+  }
+  if (deg <= 32) {
+    int v = lane < deg ? tmp[b + lane] : 0x7fffffff;
+    int rank = 0;
+    for (int j = 0; j < deg; ++j) rank += (__shfl_sync(0xffffffffu, v, j) < v);
+    if (lane < deg) sorted[b + rank] = v;
+    return;
+  }
+  for (int i = lane; i < deg; i += 32) {
+    int v = tmp[b + i];
+    int rank = 0;
+    for (int j = 0; j < deg; ++j) rank += (__ldg(tmp + b + j) < v);
+    sorted[b + rank] = v;
+  }
+}
+
+// Persistent blocks over the list of long segments; shared-memory tiles of the segment.
+__global__ void k_sort_large(const int32_t* __restrict__ ptr, const int32_t* __restrict__ tmp,
+                             int32_t* __restrict__ sorted, const int32_t* __restrict__ large,
+                             const int32_t* __restrict__ n_large) {
+  constexpr int kTile = 2048;
+  __shared__ int tile[kTile];
+  int nl = *n_large;
+  for (int li = blockIdx.x; li < nl; li += gridDim.x) {
+    int node = large[li];
+    int b = ptr[node], deg = ptr[node + 1] - b;
+    for (int i0 = 0; i0 < deg; i0 += blockDim.x) {
+      int i = i0 + threadIdx.x;
+      int v = i < deg ? tmp[b + i] : 0;
+      int rank = 0;
+      for (int t0 = 0; t0 < deg; t0 += kTile) {
+        int tn = min(kTile, deg - t0);
+        __syncthreads();
+        for (int k = threadIdx.x; k < tn; k += blockDim.x) tile[k] = tmp[b + t0 + k];
+        __syncthreads();
+        if (i < deg)
+          for (int k = 0; k < tn; ++k) rank += (tile[k] < v);
+      }
+      if (i < deg) sorted[b + rank] = v;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- finish -----------------------------------------------------------------------------
+__global__ void k_finish_in(const int64_t* __restrict__ src, int64_t E,
+                            const int32_t* __restrict__ in_eid, int32_t* __restrict__ in_src,
+                            int32_t* __restrict__ inv) {
+  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= E) return;
+  int e = in_eid[p];
+  in_src[p] = (int32_t)src[e];
+  inv[e] = (int32_t)p;
+}
+__global__ void k_finish_out(const int64_t* __restrict__ dst, int64_t E,
+                             const int32_t* __restrict__ out_eid, const int32_t* __restrict__ inv,
+                             int32_t* __restrict__ out_dst, int32_t* __restrict__ out_pos) {
+  int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (q >= E) return;
+  int e = out_eid[q];
+  out_dst[q] = (int32_t)dst[e];
+  out_pos[q] = inv[e];
+}
+__global__ void k_degree_stats(const int32_t* __restrict__ in_ptr,
+                               const int32_t* __restrict__ out_ptr, int32_t N,
+                               int32_t* __restrict__ stats) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int din = 0, dout = 0, zero = 0;
+  if (i < N) {
+    din = in_ptr[i + 1] - in_ptr[i];
+    dout = out_ptr[i + 1] - out_ptr[i];
+    zero = din == 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    din = max(din, __shfl_xor_sync(0xffffffffu, din, o));
+    dout = max(dout, __shfl_xor_sync(0xffffffffu, dout, o));
+    zero += __shfl_xor_sync(0xffffffffu, zero, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (zero) atomicAdd(&stats[0], zero);
+    atomicMax(&stats[1], din);
+    atomicMax(&stats[3], dout);
+  }
+}
+
+__global__ void k_gather_i32(const int32_t* __restrict__ table, const int32_t* __restrict__ idx,
+                             int64_t n, int32_t* __restrict__ out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = table[idx[i]];
+}
+__global__ void k_narrow_i64(const int64_t* __restrict__ in, int64_t n, int32_t* __restrict__ out) {
+  int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
+  if (i + 1 < n) {
+    longlong2 v = *reinterpret_cast<const longlong2*>(in + i);
+    *reinterpret_cast<int2*>(out + i) = make_int2((int)v.x, (int)v.y);
+  } else if (i < n) {
+    out[i] = (int)in[i];
+  }
+}
+
+static int scan_inplace(int32_t* a, int64_t n, int32_t* bsum, cudaStream_t st) {
+  int nb = (int)ceil_div(n, kScanTile);
+  if (nb > 1) {
+    k_scan_tiles<<<nb, kScanThreads, 0, st>>>(a, n, bsum, 0);
+    k_scan_bsums<<<1, kScanThreads, 0, st>>>(bsum, nb);
+  }
+  k_scan_tiles<<<nb, kScanThreads, 0, st>>>(a, n, bsum, 1);
+  return 0;
+}
+
+}  // namespace b200gat
+
+using namespace b200gat;
+
+extern "C" int64_t b200gat_plan_scratch_elems(int64_t N, int64_t E) {
+  int64_t nb = ceil_div(N + 1, kScanTile) + 1;
+  return 4 * E + 4 * N + 2 * nb + 64;
+}
+
+extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_dst, int64_t E,
+                                  int64_t N, int32_t* in_ptr, int32_t* in_src, int32_t* in_eid,
+                                  int32_t* out_ptr, int32_t* out_dst, int32_t* out_pos,
+                                  int32_t* scratch, int32_t* stats, void* stream) {
+  B200_CHECK_ARG(E >= 0 && N >= 0, "negative size");
+  B200_CHECK_ARG(E < (1ll << 31) - 2048 && N < (1ll << 31) - 2048, "graph too large for int32 ids");
+  B200_CHECK_ARG(in_ptr && out_ptr && stats && scratch, "null output pointer");
+  B200_CHECK_ARG(E == 0 || (edge_src && edge_dst && in_src && in_eid && out_dst && out_pos),
+                 "null edge pointer");
+  const int vec = (reinterpret_cast<uintptr_t>(edge_src) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(edge_dst) & 15) == 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t nb = ceil_div(N + 1, kScanTile) + 1;
+  int32_t* tmp_in = scratch;
+  int32_t* tmp_out = tmp_in + E;
+  int32_t* out_eid = tmp_out + E;
+  int32_t* inv = out_eid + E;
+  int32_t* fill_in = inv + E;
+  int32_t* fill_out = fill_in + N;
+  int32_t* large_in = fill_out + N;
+  int32_t* large_out = large_in + N;
+  int32_t* bsum_in = large_out + N;
+  int32_t* bsum_out = bsum_in + nb;
+  int32_t* counters = bsum_out + nb;  // [0] n_large_in, [1] n_large_out
+
+  cudaMemsetAsync(in_ptr, 0, sizeof(int32_t) * (N + 1), st);
+  cudaMemsetAsync(out_ptr, 0, sizeof(int32_t) * (N + 1), st);
+  cudaMemsetAsync(stats, 0, sizeof(int32_t) * 4, st);
+  cudaMemsetAsync(fill_in, 0, sizeof(int32_t) * 2 * N, st);
+  cudaMemsetAsync(counters, 0, sizeof(int32_t) * 8, st);
+  if (E > 0) {
+    int64_t pairs = ceil_div(E, 2);
+    k_count<<<(unsigned)ceil_div(pairs, 256), 256, 0, st>>>(edge_src, edge_dst, E, (int32_t)N,
+                                                            in_ptr, out_ptr, stats, vec);
+    B200_CHECK_LAUNCH("k_count");
+  }
+  scan_inplace(in_ptr, N + 1, bsum_in, st);
+  scan_inplace(out_ptr, N + 1, bsum_out, st);
+  B200_CHECK_LAUNCH("k_scan");
+  if (E > 0) {
+    unsigned eb = (unsigned)ceil_div(E, 256);
+    k_fill<<<eb, 256, 0, st>>>(edge_src, edge_dst, E, (int32_t)N, in_ptr, out_ptr, fill_in,
+                               fill_out, tmp_in, tmp_out);
+    B200_CHECK_LAUNCH("k_fill");
+    unsigned wb = (unsigned)ceil_div(N * 32, 256);
+    k_sort_small<<<wb, 256, 0, st>>>(in_ptr, (int32_t)N, tmp_in, in_eid, large_in, counters + 0);
+    k_sort_small<<<wb, 256, 0, st>>>(out_ptr, (int32_t)N, tmp_out, out_eid, large_out, counters + 1);
+    k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(in_ptr, tmp_in, in_eid, large_in, counters + 0);
+    k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(out_ptr, tmp_out, out_eid, large_out, counters + 1);
+    B200_CHECK_LAUNCH("k_sort");
+    k_finish_in<<<eb, 256, 0, st>>>(edge_src, E, in_eid, in_src, inv);
+    k_finish_out<<<eb, 256, 0, st>>>(edge_dst, E, out_eid, inv, out_dst, out_pos);
+    B200_CHECK_LAUNCH("k_finish");
+  }
+  if (N > 0) {
+    k_degree_stats<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(in_ptr, out_ptr, (int32_t)N, stats);
+    B200_CHECK_LAUNCH("k_degree_stats");
+  }
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
+                                  void* stream) {
+  B200_CHECK_ARG(n >= 0, "negative size");
+  if (n == 0) return B200GAT_OK;
+  B200_CHECK_ARG(table && idx && out, "null pointer");
+  k_gather_i32<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, out);
+  B200_CHECK_LAUNCH("k_gather_i32");
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_narrow_i64(const int64_t* in, int64_t n, int32_t* out, void* stream) {
+  B200_CHECK_ARG(n >= 0, "negative size");
+  if (n == 0) return B200GAT_OK;
+  B200_CHECK_ARG(in && out, "null pointer");
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+                 "misaligned pointer");
+  k_narrow_i64<<<(unsigned)ceil_div(ceil_div(n, 2), 256), 256, 0, (cudaStream_t)stream>>>(in, n, out);
+  B200_CHECK_LAUNCH("k_narrow_i64");
+  return B200GAT_OK;
+}

@@ -1,0 +1,236 @@
+"""autograd.Function wrappers around the C-ABI kernels (the only place the extension is
+called from).  No PyTorch fallback exists: CPU tensors raise."""
+import torch
+
+from . import _lib
+from .plan import GraphPlan
+
+
+class EdgeFeatures:
+    """Factored edge features handed to the fused layer.
+
+    ``mode='table'``: ``Pe[e] = table[etype[e]]`` with ``table [T, H*D]`` already projected
+    (the reference computes ``fc_fij(Embedding(type))`` per edge, jssp/models/gnn_dgl.py:364 +
+    generic/eegatconv.py:262; projecting the T-row table instead is the same map).
+    ``mode='dense'``: ``Pe [E, H*D]`` in the original edge order.
+    """
+
+    def __init__(self, mode, table=None, etype_sorted=None, dense=None):
+        self.mode, self.table, self.etype_sorted, self.dense = mode, table, etype_sorted, dense
+
+    @classmethod
+    def none(cls):
+        return cls(_lib.EDGE_NONE)
+
+
+def _f32c(t):
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        raise _lib.B200GatError(f"fp32 tensors required, got {t.dtype}")
+    return t.contiguous()
+
+
+class _FusedGATConv(torch.autograd.Function):
+    """out[v] = sum_{e->v} softmax_v(s_e) * V[src_e],  s_e by flavour (include/b200gat.h)."""
+
+    @staticmethod
+    def forward(ctx, plan: GraphPlan, cfg: dict, Pi, Pj, V, attn, attn_bias, out_bias,
+                e_table, e_dense, etype_sorted):
+        if not Pi.is_cuda:
+            raise _lib.B200GatError("wheatley_b200 kernels need CUDA tensors (no CPU fallback)")
+        H, D = cfg["heads"], cfg["dim"]
+        N, E, HD = plan.n_nodes, plan.n_edges, H * D
+        Pi, Pj = _f32c(Pi), _f32c(Pj)
+        v_alias = V is None
+        Vt = Pi if v_alias else _f32c(V)
+        attn_c = _f32c(attn.reshape(-1))
+        attn_bias_c = _f32c(attn_bias)
+        out_bias_c = _f32c(out_bias)
+        e_table_c, e_dense_c = _f32c(e_table), _f32c(e_dense)
+        mode = _lib.EDGE_TABLE if e_table is not None else (_lib.EDGE_DENSE if e_dense is not None
+                                                           else _lib.EDGE_NONE)
+        assert Pi.shape == (N, HD) and Pj.shape == (N, HD) and Vt.shape == (N, HD)
+        out = torch.empty((N, HD), dtype=torch.float32, device=Pi.device)
+        s = torch.empty((E, H), dtype=torch.float32, device=Pi.device)
+        m = torch.empty((N, H), dtype=torch.float32, device=Pi.device)
+        l = torch.empty((N, H), dtype=torch.float32, device=Pi.device)
+        a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
+                      _lib.ptr(attn_bias_c), _lib.ptr(out_bias_c))
+        ef = _lib.EdgeFeats(mode, 0 if e_table_c is None else e_table_c.shape[0],
+                            _lib.ptr(e_table_c), _lib.ptr(etype_sorted), _lib.ptr(e_dense_c))
+        with torch.cuda.device(Pi.device):
+            _lib.check(_lib.lib.b200gat_conv_fwd(plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
+                                                 _lib.ptr(out), _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
+                                                 _lib.stream_ptr()), "b200gat_conv_fwd")
+        ctx.plan, ctx.cfg, ctx.mode, ctx.v_alias = plan, cfg, mode, v_alias
+        ctx.etype_sorted = etype_sorted
+        ctx.has_out_bias = out_bias is not None
+        ctx.attn_shape = attn.shape
+        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, s, m, l)
+        ctx.mark_non_differentiable(s, m, l)
+        return out, s, m, l
+
+    @staticmethod
+    def backward(ctx, g_out, _gs, _gm, _gl):
+        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, s, m, l = ctx.saved_tensors
+        plan, cfg = ctx.plan, ctx.cfg
+        H, D = cfg["heads"], cfg["dim"]
+        g_out = _f32c(g_out)
+        gPi = torch.empty_like(Pi)
+        gPj = torch.empty_like(Pj)
+        gV = gPi if ctx.v_alias else torch.empty_like(Vt)
+        g_attn = torch.zeros_like(attn_c)
+        g_attn_bias = torch.zeros_like(attn_bias_c) if attn_bias_c is not None else None
+        g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None
+        g_dense = torch.empty_like(e_dense_c) if e_dense_c is not None else None
+        gs = torch.empty_like(s)
+        a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
+                      _lib.ptr(attn_bias_c), None)
+        ef = _lib.EdgeFeats(ctx.mode, 0 if e_table_c is None else e_table_c.shape[0],
+                            _lib.ptr(e_table_c), _lib.ptr(ctx.etype_sorted), _lib.ptr(e_dense_c))
+        with torch.cuda.device(Pi.device):
+            _lib.check(_lib.lib.b200gat_conv_bwd(
+                plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
+                _lib.ptr(l), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj), _lib.ptr(gV),
+                _lib.ptr(g_attn), _lib.ptr(g_attn_bias), _lib.ptr(g_table), _lib.ptr(g_dense),
+                _lib.ptr(gs), _lib.stream_ptr()), "b200gat_conv_bwd")
+        g_bias = g_out.sum(0) if ctx.has_out_bias else None
+        return (None, None, gPi, gPj, None if ctx.v_alias else gV, g_attn.view(ctx.attn_shape),
+                g_attn_bias, g_bias, g_table, g_dense, None)
+
+
+def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_ADDITIVE, slope=0.2,
+                   eps=0.0, attn_bias=None, out_bias=None, edge_feats: EdgeFeatures = None):
+    """Returns ``(out [N, H*D], (s, m, l))``; ``V=None`` means V aliases Pi."""
+    cfg = dict(heads=int(heads), dim=int(dim), flavour=int(flavour), slope=float(slope), eps=float(eps))
+    ef = edge_feats or EdgeFeatures.none()
+    e_table = ef.table if ef.mode == _lib.EDGE_TABLE else None
+    e_dense = ef.dense if ef.mode == _lib.EDGE_DENSE else None
+    out, s, m, l = _FusedGATConv.apply(plan, cfg, Pi, Pj, V, attn, attn_bias, out_bias, e_table,
+                                       e_dense, ef.etype_sorted if e_table is not None else None)
+    return out, (s, m, l)
+
+
+def attention_weights(plan: GraphPlan, saved, heads: int, eps: float) -> torch.Tensor:
+    """alpha [E, H] in the original edge order from the logits saved by the forward."""
+    s, m, l = saved
+    alpha = torch.empty((plan.n_edges, heads), dtype=torch.float32, device=s.device)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.lib.b200gat_attention(plan.c, heads, eps, _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
+                                              _lib.ptr(alpha), _lib.stream_ptr()), "b200gat_attention")
+    return alpha
+
+
+def edge_output(plan: GraphPlan, Pi, Pj, edge_feats: EdgeFeatures, *, heads, dim, slope, attn):
+    """f_out [E, H, D] = leaky_relu(Pi[src]+Pj[dst]+Pe) (no autograd: materialised on request)."""
+    Pi, Pj = _f32c(Pi.detach()), _f32c(Pj.detach())
+    ef = edge_feats or EdgeFeatures.none()
+    tbl = _f32c(ef.table.detach()) if ef.mode == _lib.EDGE_TABLE else None
+    dns = _f32c(ef.dense.detach()) if ef.mode == _lib.EDGE_DENSE else None
+    attn_c = _f32c(attn.detach().reshape(-1))
+    a = _lib.Attn(_lib.FLAVOUR_ADDITIVE, heads, dim, slope, 0.0, _lib.ptr(attn_c), None, None)
+    efc = _lib.EdgeFeats(ef.mode, 0 if tbl is None else tbl.shape[0], _lib.ptr(tbl),
+                         _lib.ptr(ef.etype_sorted), _lib.ptr(dns))
+    f = torch.empty((plan.n_edges, heads, dim), dtype=torch.float32, device=Pi.device)
+    with torch.cuda.device(Pi.device):
+        _lib.check(_lib.lib.b200gat_edge_out(plan.c, a, efc, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(f),
+                                             _lib.stream_ptr()), "b200gat_edge_out")
+    return f
+
+
+class _MaskedHead(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, mask_u8, fill):
+        if not logits.is_cuda:
+            raise _lib.B200GatError("wheatley_b200 kernels need CUDA tensors (no CPU fallback)")
+        logits = _f32c(logits)
+        B, n = logits.shape
+        logp = torch.empty_like(logits)
+        ent = torch.empty(B, dtype=torch.float32, device=logits.device)
+        amax = torch.empty(B, dtype=torch.int64, device=logits.device)
+        with torch.cuda.device(logits.device):
+            _lib.check(_lib.lib.b200gat_mask_head_fwd(
+                _lib.ptr(logits), logits.stride(0), _lib.ptr(mask_u8),
+                0 if mask_u8 is None else mask_u8.stride(0), B, n, fill, _lib.ptr(logp), _lib.ptr(ent),
+                _lib.ptr(amax), _lib.stream_ptr()), "b200gat_mask_head_fwd")
+        ctx.save_for_backward(logp, ent, mask_u8)
+        ctx.mark_non_differentiable(amax)
+        return logp, ent, amax
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent, _g_amax):
+        logp, ent, mask_u8 = ctx.saved_tensors
+        B, n = logp.shape
+        # general path: logp is used through arbitrary downstream ops -> dense softmax backward
+        # d logits = g_logp - p * sum(g_logp)  (masked entries get 0), entropy term via the kernel.
+        g_logits = torch.empty_like(logp)
+        with torch.cuda.device(logp.device):
+            _lib.check(_lib.lib.b200gat_mask_head_bwd(
+                _lib.ptr(logp), _lib.ptr(mask_u8), 0 if mask_u8 is None else mask_u8.stride(0), None,
+                _lib.ptr(ent), None, _lib.ptr(_f32c(g_ent)) if g_ent is not None else None, B, n,
+                _lib.ptr(g_logits), _lib.stream_ptr()), "b200gat_mask_head_bwd")
+        if g_logp is not None:
+            p = logp.exp()
+            dense = g_logp - p * g_logp.sum(-1, keepdim=True)
+            if mask_u8 is not None:
+                dense = dense * mask_u8[:, :n].to(dense.dtype)
+            g_logits = g_logits + dense
+        return g_logits, None, None
+
+
+class _MaskedHeadEval(torch.autograd.Function):
+    """logprob[action] and entropy with the fused backward (the PPO update call,
+    alg/ppo.py:575-581)."""
+
+    @staticmethod
+    def forward(ctx, logits, mask_u8, action, fill):
+        logits = _f32c(logits)
+        B, n = logits.shape
+        logp = torch.empty_like(logits)
+        ent = torch.empty(B, dtype=torch.float32, device=logits.device)
+        with torch.cuda.device(logits.device):
+            _lib.check(_lib.lib.b200gat_mask_head_fwd(
+                _lib.ptr(logits), logits.stride(0), _lib.ptr(mask_u8),
+                0 if mask_u8 is None else mask_u8.stride(0), B, n, fill, _lib.ptr(logp), _lib.ptr(ent),
+                None, _lib.stream_ptr()), "b200gat_mask_head_fwd")
+        action = action.long().contiguous()
+        lp = logp.gather(1, action.view(-1, 1)).squeeze(1)
+        ctx.save_for_backward(logp, ent, mask_u8, action)
+        return lp, ent
+
+    @staticmethod
+    def backward(ctx, g_lp, g_ent):
+        logp, ent, mask_u8, action = ctx.saved_tensors
+        B, n = logp.shape
+        g_logits = torch.empty_like(logp)
+        with torch.cuda.device(logp.device):
+            _lib.check(_lib.lib.b200gat_mask_head_bwd(
+                _lib.ptr(logp), _lib.ptr(mask_u8), 0 if mask_u8 is None else mask_u8.stride(0),
+                _lib.ptr(action), _lib.ptr(ent), _lib.ptr(_f32c(g_lp)) if g_lp is not None else None,
+                _lib.ptr(_f32c(g_ent)) if g_ent is not None else None, B, n, _lib.ptr(g_logits),
+                _lib.stream_ptr()), "b200gat_mask_head_bwd")
+        return g_logits, None, None, None
+
+
+def _mask_u8(action_masks, n, device):
+    """Crop to the logits width (generic/agent.py:202-203) and view the bools as bytes."""
+    if action_masks is None:
+        return None
+    mk = torch.as_tensor(action_masks, device=device)
+    if mk.dtype != torch.bool:
+        mk = mk.to(torch.bool)
+    mk = mk[:, :n]
+    if mk.stride(-1) != 1:
+        mk = mk.contiguous()
+    return mk.view(torch.uint8)
+
+
+def masked_log_softmax(logits, action_masks=None, fill=-1e20):
+    """(logp [B,n], entropy [B], argmax [B]) of the masked categorical."""
+    return _MaskedHead.apply(logits, _mask_u8(action_masks, logits.shape[1], logits.device), float(fill))
+
+
+def masked_logprob_entropy(logits, action, action_masks=None, fill=-1e20):
+    return _MaskedHeadEval.apply(logits, _mask_u8(action_masks, logits.shape[1], logits.device), action,
+                                 float(fill))
