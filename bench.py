@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py - GNN fwd+bwd graph-edges/sec of the B200-native Wheatley hot path.
+
+    python bench.py --gpus N --steps K --warmup W            # this implementation
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port)
+
+A *step* is one PPO-minibatch pass of the hot path over one batch of synthetic schedule graphs:
+batched-graph plan -> L x (projections, fused edge-attention conv, MLP) -> masked action head ->
+loss -> fused backward -> gradient all-reduce (N > 1) -> Adam step.  Metric: graph edges of the
+batch (all ranks) / step time.  Default workload = BASELINE.json north_star's target config:
+Taillard 100x20 schedule graphs, DGL-flavour clique conflicts + learned pooling node
+(2,001 nodes / 205,801 edges per graph), 8 graphs per GPU, 6 layers x 4 heads x 64.
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {  # name: (n_jobs, n_machines, default graphs per GPU)
+    "taillard100x20": (100, 20, 8),
+    "taillard15x15": (15, 15, 128),
+    "taillard30x20": (30, 20, 64),
+    "jssp10x10": (10, 10, 128),
+}
+METRIC = "gnn_fwd_bwd_graph_edges_per_sec"
+UNIT = "edges/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="taillard100x20", choices=sorted(WORKLOADS))
+    ap.add_argument("--graphs-per-gpu", type=int, default=0)
+    ap.add_argument("--layers", type=int, default=6)
+    ap.add_argument("--hidden", type=int, default=64)
+    ap.add_argument("--heads", type=int, default=4)
+    ap.add_argument("--progress", type=float, default=0.0, help="episode progress of the graph snapshot")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--gemm", default=None, help="override WHEATLEY_B200_GEMM (cublas|tcgen05)")
+    return ap.parse_args()
+
+
+def model_config(args):
+    n_j, n_m, b = WORKLOADS[args.workload]
+    return dict(n_j=n_j, n_m=n_m, graphs=args.graphs_per_gpu or b, input_dim=6 + n_m + 4,
+                max_n_nodes=n_j * n_m, layers=args.layers, hidden=args.hidden, heads=args.heads)
+
+
+def synth_targets(batch, n_nodes, seed):
+    g = torch.Generator().manual_seed(seed)
+    masks = torch.rand(batch, n_nodes, generator=g) < 0.3
+    masks[:, 0] = True
+    action = torch.multinomial(masks.float(), 1, generator=g).squeeze(1)
+    adv = torch.randn(batch, generator=g)
+    ret = torch.randn(batch, generator=g)
+    return masks, action, adv, ret
+
+
+# ------------------------------------------------------------------------- reference / CPU arm
+def build_oracle(cfg, seed=0):
+    from oracle import trunk_oracle
+    torch.manual_seed(seed)
+    gnn = trunk_oracle.OracleGnnDGL(cfg["input_dim"], "learn", cfg["max_n_nodes"], cfg["n_m"], 3,
+                                    cfg["layers"], cfg["hidden"], "gelu", cfg["heads"])
+    return trunk_oracle.OracleAgent(gnn, cfg["input_dim"] + cfg["hidden"] * (cfg["layers"] + 1))
+
+
+def cpu_step_fn(cfg, n_graphs, progress, seed0=0):
+    """The oracle's fwd+bwd over ``n_graphs`` graphs of the workload on the host cores."""
+    from wheatley_b200_workload import jssp_batch
+    agent = build_oracle(cfg)
+    b = jssp_batch(cfg["n_j"], cfg["n_m"], n_graphs, seed0, progress)
+    masks, action, adv, ret = synth_targets(n_graphs, cfg["max_n_nodes"], 1)
+    args_ = (b["src"], b["dst"], b["etype"], b["feat"], n_graphs, cfg["max_n_nodes"], b["n_task_nodes"])
+
+    def step():
+        agent.zero_grad(set_to_none=True)
+        loss = agent.loss(args_, action, masks, adv, ret)
+        loss.backward()
+        return loss.item()
+    return step, b["n_edges"]
+
+
+def time_cpu(cfg, args, steps, warmup, budget_s=None):
+    """Bounded CPU sample: graphs per step chosen so a step is ~1-3 s of host work."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    n_graphs = 1 if cfg["n_j"] * cfg["n_m"] >= 1000 else min(cfg["graphs"], 16)
+    step, edges = cpu_step_fn(cfg, n_graphs, args.progress)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        step()
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = (time.perf_counter() - t0) / done
+    return dict(value=edges / dt, unit=UNIT, cores=torch.get_num_threads(), kind="port",
+                sample=f"{done} steps x {n_graphs} graph(s) of {args.workload} ({edges} edges/step), "
+                       f"oracle trunk fwd+bwd fp32 on CPU, {dt * 1e3:.1f} ms/step"), dt, n_graphs
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = model_config(args)
+    cb, dt, n_graphs = time_cpu(cfg, args, args.steps, args.warmup, budget_s=150.0)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, cfg, n_graphs, note="CPU oracle port of the reference path "
+                                      "(DGL/PyG not installable here); bounded sample"),
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, cfg, graphs, note=None):
+    c = {"workload": f"{args.workload} DGL-flavour clique conflicts + learned pool node, progress {args.progress}",
+         "graphs_per_gpu": graphs, "nodes_per_graph": cfg["max_n_nodes"] + 1, "layers": cfg["layers"],
+         "hidden": cfg["hidden"], "heads": cfg["heads"], "mlp_layers": 3, "activation": "gelu"}
+    if note:
+        c["note"] = note
+    return c
+
+
+# ------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.f.read().splitlines():
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1])); mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------- B200 arm
+def algorithmic_bytes(kind, N, E, HD, H, P=3, T=4):
+    """DESIGN.md 'Algorithmic bytes' (SURVEY 8d): fp32 node rows, int32 indices, type-table edge
+    features, [E,H,D] edge output not materialised."""
+    row = N * HD * 4
+    if kind == "conv_fwd":            # read Pi,Pj,V ; write out ; per edge: src+dst ids, type, saved logits
+        return row * (P + 1) + E * (8 + T + 4 * H)
+    if kind == "conv_bwd":            # read dOut + P saved ; write P grads ; per edge ids, type, alpha
+        return row * (1 + 2 * P) + E * (8 + T + 4 * H)
+    raise KeyError(kind)
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    if args.gemm:
+        os.environ["WHEATLEY_B200_GEMM"] = args.gemm
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: wheatley_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import wheatley_b200 as wb
+    from wheatley_b200 import _lib
+    from wheatley_b200.agent import JsspAgent
+    from wheatley_b200.gnn_dgl import JsspBatch
+    from wheatley_b200.ppo import FlatGradAllReduce, ppo_like_loss
+    from wheatley_b200.workload import jssp_batch
+
+    torch.backends.cuda.matmul.allow_tf32 = True       # the reference's matmul precision (psp/train_psp.py:47)
+    cfg = model_config(args)
+    B = cfg["graphs"]
+    torch.manual_seed(0)                               # identical replicas on every rank
+    agent = JsspAgent(cfg["input_dim"], cfg["max_n_nodes"], cfg["n_m"], cfg["hidden"], cfg["layers"],
+                      cfg["heads"]).to(dev)
+    bucket = FlatGradAllReduce(list(agent.parameters()))
+    opt = torch.optim.Adam(agent.parameters(), lr=2e-4, fused=True)
+
+    hb = jssp_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress)
+    masks, action, adv, ret = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
+    host = dict(src=hb["src"], dst=hb["dst"], etype=hb["etype"], feat=hb["feat"], masks=masks,
+                action=action, adv=adv, ret=ret)
+    host = {k: v.contiguous().pin_memory() for k, v in host.items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+    N, E, NT = hb["n_nodes"], hb["n_edges"], hb["n_task_nodes"]
+
+    def to_dev():
+        return {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+
+    def make_batch(d):
+        plan = wb.GraphPlan(d["src"], d["dst"], N)
+        pool = torch.arange(NT, NT + B, device=dev)
+        return JsspBatch(plan, d["etype"], d["feat"], B, cfg["max_n_nodes"], NT, poolnodes=pool)
+
+    def train_step(jb, d):
+        bucket.zero()
+        _, logprob, entropy, value, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
+        loss = ppo_like_loss(logprob, entropy, value, d["adv"], d["ret"])
+        loss.backward()
+        bucket.reduce()
+        opt.step()
+        return loss
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(fn, steps, warmup, sampler=False):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        smp = ClockSampler(local) if sampler and rank == 0 else None
+        l0 = _lib.launch_count()
+        total = 0.0
+        evs = []
+        for _ in range(steps):
+            flush.zero_()                                  # L2 flush, outside the event pair
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        clocks = smp.stop() if smp else None
+        total = sum(a.elapsed_time(b) for a, b in evs)
+        launches = _lib.launch_count() - l0
+        t = torch.tensor([total], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t) / steps, launches // steps, clocks
+
+    # ---- value: inputs resident in HBM, plan prebuilt (topology is layer- and epoch-invariant)
+    d_res = to_dev()
+    jb_res = make_batch(d_res)
+    torch.cuda.synchronize()
+    _lib.timing_enable(True)
+    ms_dev, launches, clocks = timed(lambda: train_step(jb_res, d_res), args.steps, args.warmup, sampler=True)
+    tm = _lib.timing_read()
+    _lib.timing_enable(False)
+
+    # ---- e2e: host buffers in, loss out, through the public module API, every step
+    def e2e_step():
+        d = to_dev()
+        jb = make_batch(d)
+        return float(train_step(jb, d))                    # .item(): device->host read of the loss
+    ms_e2e, _, _ = timed(e2e_step, max(3, args.steps // 2), 3)
+
+    edges_all = torch.tensor([E], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(edges_all)
+    edges_total = float(edges_all)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    import json as _json
+    peaks = {}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = _json.load(open(pk))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    HD, H = cfg["hidden"] * cfg["heads"], cfg["heads"]
+    fwd_ms, fwd_n = tm["conv_fwd"]
+    bd_ms, bd_n = tm["conv_bwd_dst"]
+    bs_ms, bs_n = tm["conv_bwd_src"]
+    per = {}
+    if fwd_n:
+        per["conv_fwd"] = (fwd_ms / fwd_n, algorithmic_bytes("conv_fwd", N, E, HD, H))
+    if bd_n:
+        per["conv_bwd"] = ((bd_ms + bs_ms) / bd_n, algorithmic_bytes("conv_bwd", N, E, HD, H))
+    dom = max(per, key=lambda k: per[k][0] * (fwd_n if k == "conv_fwd" else bd_n)) if per else None
+    roofline = None
+    if dom:
+        ms, byt = per[dom]
+        ach = byt / (ms * 1e-3) / 1e9
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": ach / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": byt, "avg_launch_ms": ms,
+                    "kernels": {k: {"avg_ms": v[0], "algorithmic_bytes": v[1],
+                                    "gbps": v[1] / (v[0] * 1e-3) / 1e9} for k, v in per.items()},
+                    "share_of_step": {k: (t_ms / args.steps) / ms_dev for k, (t_ms, _) in tm.items() if t_ms}}
+    line = {"metric": METRIC, "value": edges_total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (conv kernels fp32; dense projections TF32 like the reference)",
+            "data": "synthetic",
+            "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
+                           l2="flushed between timed steps (256 MiB write)",
+                           parallelism=f"dp{world}", gemm=os.environ.get("WHEATLEY_B200_GEMM", "cublas"),
+                           step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam"),
+            "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+    if world == 1 and not args.no_cpu_baseline:
+        cb, _, _ = time_cpu(cfg, args, 1000, 1, budget_s=args.cpu_seconds)
+        line["cpu_baseline"] = cb
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    # the workload generator is plain numpy: load it by path so the reference arm does not need
+    # the CUDA library (wheatley_b200/__init__ refuses to import without it)
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("wheatley_b200_workload",
+                                                  os.path.join(ROOT, "wheatley_b200", "workload.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    sys.modules["wheatley_b200_workload"] = mod
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

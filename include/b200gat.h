@@ -35,9 +35,32 @@ extern "C" {
 #define B200GAT_EDGE_NONE 0
 #define B200GAT_EDGE_TABLE 1 /* Pe[e] = table[etype[e]]   (edge features are an Embedding(type)) */
 #define B200GAT_EDGE_DENSE 2 /* Pe[e] = dense[e]          (caller projected [E,Fe] itself)       */
+#define B200GAT_EDGE_AFFINE 3 /* Pe[e] = table[etype[e]] + sum_k attr[e,k] * affine[k]          */
+                              /* (psp/models/edge_embedder.py:130-143 folded through lin_edge)   */
+#define B200GAT_MAX_ATTR 8
 
 const char* b200gat_last_error(void);
 int b200gat_version(void);
+
+/* Number of CUDA kernels this library has launched in the calling process (monotonic):
+ * bench.py reports the difference over its timed region as "gpu_launches". */
+int64_t b200gat_launch_count(void);
+
+/* Optional device timing per kernel class: when enabled, every launch of that class is
+ * bracketed by CUDA events recorded on the launch stream.  b200gat_timing_enable(on) clears
+ * the accumulators; b200gat_timing_read synchronises the recorded events and returns the
+ * summed kernel time and the number of launches since the last enable.  Used by bench.py for
+ * the live roofline figure; off by default (no events, no overhead). */
+#define B200GAT_TIMING_CONV_FWD 0
+#define B200GAT_TIMING_CONV_BWD_DST 1
+#define B200GAT_TIMING_CONV_BWD_SRC 2
+#define B200GAT_TIMING_PLAN 3
+#define B200GAT_TIMING_HEAD 4
+#define B200GAT_TIMING_GEMM 5
+#define B200GAT_TIMING_BATCH 6
+#define B200GAT_TIMING_CLASSES 8
+void b200gat_timing_enable(int on);
+int b200gat_timing_read(int cls, double* total_ms, int64_t* count);
 
 /* ------------------------------------------------------------------ graph plan
  * Topology of one batched graph in both orders, built once per batch and reused by
@@ -74,6 +97,9 @@ int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_dst, int64_t
 /* out[i] = table[idx[i]] for int32 (permute per-edge attributes into dst-sorted order). */
 int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
                        void* stream);
+/* out[i, :] = table[idx[i], :] for fp32 rows of `width` elements (per-edge attributes). */
+int b200gat_gather_rows_f32(const float* table, const int32_t* idx, int64_t n, int32_t width,
+                            float* out, void* stream);
 /* out[i] = (int32) in[i]  (int64 -> int32 narrowing with 16-byte loads). */
 int b200gat_narrow_i64(const int64_t* in, int64_t n, int32_t* out, void* stream);
 
@@ -95,6 +121,9 @@ typedef struct {
   const float* table;   /* [T, H*D]; fold the EGAT pre-activation bias into it           */
   const int32_t* etype; /* [E] edge type in DST-SORTED order (see b200gat_gather_i32)    */
   const float* dense;   /* [E, H*D] in ORIGINAL edge order                               */
+  int32_t n_attr;       /* K <= B200GAT_MAX_ATTR (EDGE_AFFINE)                           */
+  const float* attr;    /* [E, K] per-edge scalars in DST-SORTED order (b200gat_gather_rows_f32) */
+  const float* affine;  /* [K, H*D]                                                      */
 } b200gat_edge_feats;
 
 /* Fused per-edge logit + segmented edge-softmax + weighted aggregation.
@@ -115,13 +144,14 @@ int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200ga
  *                      contributions is written there (GATv2: x_l is logit term and value).
  *   g_attn           : [H*D] (additive) / [D] (dot), ACCUMULATED with atomics: zero it first
  *   g_attn_bias      : [1] (dot), accumulated; else NULL
- *   g_table          : [T, H*D] accumulated (EDGE_TABLE) ; g_dense: [E, H*D] written (EDGE_DENSE)
+ *   g_table          : [T, H*D] accumulated (EDGE_TABLE / EDGE_AFFINE) ; g_dense: [E, H*D]
+ *                      written (EDGE_DENSE) ; g_affine: [K, H*D] accumulated (EDGE_AFFINE)
  *   gs_scratch       : [E, H] scratch (dst-sorted order)                                  */
 int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                      const float* Pi, const float* Pj, const float* V, const float* s_save,
                      const float* m_save, const float* l_save, const float* g_out, float* gPi,
                      float* gPj, float* gV, float* g_attn, float* g_attn_bias, float* g_table,
-                     float* g_dense, float* gs_scratch, void* stream);
+                     float* g_dense, float* g_affine, float* gs_scratch, void* stream);
 
 /* alpha[e,h] in ORIGINAL edge order from the saved logits (get_attention=True,
  * generic/eegatconv.py:304-308; return_attention_weights, generic/gatv3_conv.py:174-179). */

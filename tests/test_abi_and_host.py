@@ -1,0 +1,179 @@
+"""CPU-only: the C-ABI library loads and exports every symbol include/b200gat.h declares;
+host-side logic (edge-feature factorisation, sharding, flat gradient bucket over gloo)."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    import __graft_entry__ as ge
+    ge.build()
+    import wheatley_b200
+    return wheatley_b200
+
+
+def test_library_exports_every_declared_symbol(built):
+    import ctypes
+    from wheatley_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "b200gat.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(b200gat_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/b200gat.h but not exported"
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    assert _lib.lib.b200gat_version() >= 100
+    assert _lib.launch_count() == 0          # nothing may launch without a GPU
+
+
+def test_argument_validation_without_gpu(built):
+    from wheatley_b200 import _lib
+    rc = _lib.lib.b200gat_plan_build(None, None, -1, 3, None, None, None, None, None, None, None, None, None)
+    assert rc == 1 and b"negative" in _lib.lib.b200gat_last_error()
+    rc = _lib.lib.b200gat_mask_head_fwd(None, 0, None, 0, 2, 3, -1e20, None, None, None, None)
+    assert rc == 1
+
+
+def test_no_cpu_fallback(built):
+    wb = built
+    with pytest.raises(wb.B200GatError):
+        wb.GraphPlan(torch.tensor([0]), torch.tensor([0]), 1)
+    with pytest.raises(wb.B200GatError):
+        wb.masked_log_softmax(torch.randn(2, 3))
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "wheatley_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
+                assert "/root/reference" not in txt, f
+
+
+def test_psp_edge_embedder_factorisation_matches_reference_golden(built, golden_dir):
+    from wheatley_b200.edge_feats import PspEdgeEmbedder
+    g = np.load(os.path.join(golden_dir, "edge_embedder.npz"))
+    H = g["out"].shape[1]
+    emb = PspEdgeEmbedder("sum", 4, H, "all", False)
+    emb.load_state_dict({k[2:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("p.")})
+    ef = emb.factor(torch.from_numpy(g["type"]), torch.from_numpy(g["att_rc"]), torch.from_numpy(g["att_rp"]))
+    np.testing.assert_allclose(ef.dense().detach().numpy(), g["out"], rtol=1e-6, atol=1e-6)
+    assert ef.attrs.shape[1] == 5 and ef.attr_weight.shape == (H, 5)
+
+
+def test_mlp_matches_reference_golden(built, golden_dir):
+    g = np.load(os.path.join(golden_dir, "mlp.npz"))
+    n = len({k.split(".")[0] for k in g.files})
+    for i in range(n):
+        act, norm = str(g[f"{i}.act"]), bool(g[f"{i}.norm"])
+        sd = {k[len(f"{i}.p."):]: torch.from_numpy(g[k]) for k in g.files if k.startswith(f"{i}.p.")}
+        m = built.MLP(3, 10, 12, 5, norm, act)
+        m.load_state_dict(sd)
+        x = torch.from_numpy(g[f"{i}.x"]).requires_grad_(True)
+        y = m(x)
+        np.testing.assert_allclose(y.detach().numpy(), g[f"{i}.y"], rtol=1e-5, atol=1e-6)
+        (y * torch.from_numpy(g[f"{i}.R"])).sum().backward()
+        np.testing.assert_allclose(x.grad.numpy(), g[f"{i}.gx"], rtol=1e-4, atol=1e-6)
+
+
+def test_state_dict_names_match_reference(built):
+    wb = built
+    assert sorted(wb.EEGATConv(4, 4, 3, 3, 2, edge_scoring=True).state_dict()) == sorted(
+        ["fc_node_src.weight", "fc_ni.weight", "fc_nj.weight", "fc_edge_src.weight", "fc_fij.weight",
+         "attn", "fc_fij_e.weight", "attn_e", "bias"])          # generic/eegatconv.py:134-162
+    assert sorted(wb.GATv3Conv(4, 3, 2, edge_dim=4).state_dict()) == sorted(
+        ["context_attention_layer.weight", "context_attention_layer.bias", "lin_l.weight", "lin_l.bias",
+         "lin_r.weight", "lin_r.bias", "lin_edge.weight"])
+    from wheatley_b200.gnn_dgl import GnnDGL
+    keys = set(GnnDGL(10, "gatv2", "learn", False, 20, 4, 3, 2, 8, "gelu", 2, conflicts="clique").state_dict())
+    for k in ("node_embedder.weight", "edge_embedder.0.weight", "embedder.layers.0.weight",
+              "features_extractors.1.fc_fij.weight", "features_extractors.0.attn", "mlps.1.layers.2.bias"):
+        assert k in keys, k
+
+
+def test_workload_sizes_match_survey(built):
+    from wheatley_b200.workload import jssp_batch
+    for (nj, nm), (n, e) in {(10, 10): (101, 1281), (15, 15): (226, 4021), (30, 20): (601, 19741)}.items():
+        b = jssp_batch(nj, nm, 1)
+        assert (b["n_nodes"], b["n_edges"]) == (n, e)
+
+
+def test_workload_batch_matches_oracle_batching(built):
+    from oracle import batch_oracle
+    from wheatley_b200.workload import jssp_batch, jssp_observation
+    obs = [jssp_observation(6, 4, s, progress=0.5) for s in range(3)]
+    maxe = max(o["n_edges"] for o in obs)
+    feat = np.stack([o["features"] for o in obs])
+    ei = np.zeros((3, 2, maxe), np.int64)
+    for i, o in enumerate(obs):
+        ei[i, :, : o["n_edges"]] = o["edge_index"]
+    ob = batch_oracle.jssp_batch(feat, ei, [o["n_nodes"] for o in obs], [o["n_edges"] for o in obs],
+                                 conflicts="clique")
+    ob = batch_oracle.jssp_add_pool_and_machine_nodes(ob, "learn", "clique")
+    wbat = jssp_batch(6, 4, 3, progress=0.5)
+    assert np.array_equal(ob["src"], wbat["src"].numpy())
+    assert np.array_equal(ob["dst"], wbat["dst"].numpy())
+    assert np.array_equal(ob["type"], wbat["etype"].numpy())
+
+
+def test_sharding(built):
+    from wheatley_b200.ppo import shard_by_edges, shard_range
+    for n, w in [(10, 4), (3, 8), (128, 8), (7, 1)]:
+        r = [shard_range(n, k, w) for k in range(w)]
+        assert r[0][0] == 0 and r[-1][1] == n and all(a[1] == b[0] for a, b in zip(r, r[1:]))
+    rng = np.random.default_rng(0)
+    for w in (1, 2, 4, 8):
+        e = rng.integers(100, 5000, 64).tolist()
+        sh = shard_by_edges(e, w)
+        assert sh[0][0] == 0 and sh[-1][1] == 64 and all(a[1] == b[0] for a, b in zip(sh, sh[1:]))
+        assert all(hi > lo for lo, hi in sh)
+        loads = [sum(e[lo:hi]) for lo, hi in sh]
+        assert max(loads) <= sum(e) / w + max(e)
+
+
+_GLOO = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, %r)
+rank, world = int(sys.argv[1]), int(sys.argv[2])
+os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=sys.argv[3], RANK=str(rank), WORLD_SIZE=str(world))
+dist.init_process_group("gloo", rank=rank, world_size=world)
+import wheatley_b200
+from wheatley_b200.ppo import FlatGradAllReduce, shard_range
+torch.manual_seed(0)
+model = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+bucket = FlatGradAllReduce(model.parameters())
+x = torch.randn(10, 6)
+lo, hi = shard_range(10, rank, world)
+bucket.zero()
+(model(x[lo:hi]).sum() / 10 * world).backward()        # each rank: its shard of the global mean
+bucket.reduce()
+ref = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+ref.load_state_dict(model.state_dict())
+(ref(x).sum() / 10).backward()
+for p, q in zip(model.parameters(), ref.parameters()):
+    assert p.grad.data_ptr() >= bucket.flat.data_ptr()
+    assert torch.allclose(p.grad, q.grad, atol=1e-6), (p.grad - q.grad).abs().max()
+dist.destroy_process_group()
+print("ok", rank)
+'''
+
+
+def test_flat_gradient_allreduce_world_size_2_gloo(built, tmp_path):
+    script = tmp_path / "gloo_worker.py"
+    script.write_text(_GLOO % ROOT)
+    port = str(29500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), "2", port], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o

@@ -8,13 +8,15 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200gat.so")
 
-EDGE_NONE, EDGE_TABLE, EDGE_DENSE = 0, 1, 2
+EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
+MAX_ATTR = 8
 FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
 
 # every symbol include/b200gat.h declares (tests check that the library exports all of them)
 SYMBOLS = (
-    "b200gat_last_error", "b200gat_version", "b200gat_plan_scratch_elems", "b200gat_plan_build",
-    "b200gat_gather_i32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
+    "b200gat_last_error", "b200gat_version", "b200gat_launch_count", "b200gat_timing_enable",
+    "b200gat_timing_read", "b200gat_plan_scratch_elems", "b200gat_plan_build",
+    "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
 )
 
@@ -33,7 +35,8 @@ class Attn(C.Structure):
 
 class EdgeFeats(C.Structure):
     _fields_ = [("mode", C.c_int32), ("n_types", C.c_int32),
-                ("table", C.c_void_p), ("etype", C.c_void_p), ("dense", C.c_void_p)]
+                ("table", C.c_void_p), ("etype", C.c_void_p), ("dense", C.c_void_p),
+                ("n_attr", C.c_int32), ("attr", C.c_void_p), ("affine", C.c_void_p)]
 
 
 class B200GatError(RuntimeError):
@@ -50,21 +53,28 @@ def _load():
     lib.b200gat_last_error.restype = C.c_char_p
     lib.b200gat_last_error.argtypes = []
     lib.b200gat_version.restype = C.c_int
+    lib.b200gat_launch_count.restype = i64
+    lib.b200gat_launch_count.argtypes = []
+    lib.b200gat_timing_enable.restype = None
+    lib.b200gat_timing_enable.argtypes = [C.c_int]
+    lib.b200gat_timing_read.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(i64)]
     lib.b200gat_plan_scratch_elems.restype = i64
     lib.b200gat_plan_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_plan_build.argtypes = [vp, vp, i64, i64] + [vp] * 9
     lib.b200gat_gather_i32.argtypes = [vp, vp, i64, vp, vp]
+    lib.b200gat_gather_rows_f32.argtypes = [vp, vp, i64, i32, vp, vp]
     lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]
     gp, ap, ep = C.POINTER(Graph), C.POINTER(Attn), C.POINTER(EdgeFeats)
     lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 8
-    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 16
+    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 17
     lib.b200gat_attention.argtypes = [gp, i32, f32, vp, vp, vp, vp, vp]
     lib.b200gat_edge_out.argtypes = [gp, ap, ep, vp, vp, vp, vp]
     lib.b200gat_mask_head_fwd.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, vp, vp, vp]
     lib.b200gat_mask_head_bwd.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32, i32, vp, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
-        if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems"):
+        if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
+                        "b200gat_timing_enable"):
             fn.restype = C.c_int
     return lib
 
@@ -75,6 +85,28 @@ lib = _load()
 def check(rc, what):
     if rc != 0:
         raise B200GatError(f"{what} failed (code {rc}): {lib.b200gat_last_error().decode()}")
+
+
+TIMING_CLASSES = {"conv_fwd": 0, "conv_bwd_dst": 1, "conv_bwd_src": 2, "plan": 3, "head": 4, "gemm": 5,
+                  "batch": 6}
+
+
+def launch_count() -> int:
+    return int(lib.b200gat_launch_count())
+
+
+def timing_enable(on: bool):
+    lib.b200gat_timing_enable(1 if on else 0)
+
+
+def timing_read():
+    """{class: (total_ms, launches)} since the last ``timing_enable``."""
+    out = {}
+    for name, cls in TIMING_CLASSES.items():
+        ms, n = C.c_double(0), C.c_int64(0)
+        check(lib.b200gat_timing_read(cls, C.byref(ms), C.byref(n)), "b200gat_timing_read")
+        out[name] = (ms.value, n.value)
+    return out
 
 
 def ptr(t):

@@ -1,6 +1,8 @@
 """Build wheatley_b200/libb200gat.so (the C-ABI library) with nvcc for sm_100a.
 
-In-tree on purpose: the .so travels with the repo snapshot to the GPU box."""
+In-tree on purpose: the .so travels with the repo snapshot to the GPU box.
+Stand-alone (no package-relative imports): run it as ``python wheatley_b200/build.py`` or load
+it by path (``__graft_entry__.build``) - importing the package needs the library to exist."""
 import os
 import subprocess
 import sys
@@ -10,8 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200gat.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--use_fast_math=false"]
-FLAGS = [f for f in FLAGS if not f.startswith("--use_fast_math")]
+         "-Xcompiler", "-fPIC"]
 
 
 def sources():
@@ -43,7 +44,7 @@ def build(force=False, verbose=False):
         if p.returncode:
             raise RuntimeError(f"nvcc failed on {src}")
     if force or procs or _stale(OUT, objs):
-        cmd = [NVCC, "-shared", "-o", OUT] + objs
+        cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs
         subprocess.check_call(cmd)
     return OUT
 

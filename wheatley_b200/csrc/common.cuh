@@ -8,6 +8,18 @@
 namespace b200gat {
 
 void set_error(const char* fmt, ...);
+void note_launch(int n);  // counts kernel launches (b200gat_launch_count)
+
+// Optional per-kernel-class device timing (CUDA events on the launch stream), switched on by
+// bench.py through b200gat_timing_enable(); a no-op otherwise.
+struct ScopedTimer {
+  ScopedTimer(int cls, cudaStream_t st);
+  ~ScopedTimer();
+  int cls_;
+  cudaStream_t st_;
+  cudaEvent_t e0_, e1_;
+  bool on_;
+};
 
 #define B200_CHECK_ARG(cond, msg)                       \
   do {                                                  \
@@ -17,8 +29,10 @@ void set_error(const char* fmt, ...);
     }                                                   \
   } while (0)
 
-#define B200_CHECK_LAUNCH(name)                                                     \
+#define B200_CHECK_LAUNCH(name) B200_CHECK_LAUNCHES(name, 1)
+#define B200_CHECK_LAUNCHES(name, n)                                                \
   do {                                                                              \
+    b200gat::note_launch(n);                                                        \
     cudaError_t e__ = cudaGetLastError();                                           \
     if (e__ != cudaSuccess) {                                                       \
       b200gat::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__));   \

@@ -27,7 +27,7 @@ extern "C" int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a,
                                 const float* V, const float* s_save, const float* m_save,
                                 const float* l_save, const float* g_out, float* gPi, float* gPj,
                                 float* gV, float* g_attn, float* g_attn_bias, float* g_table,
-                                float* g_dense, float* gs_scratch, void* stream) {
+                                float* g_dense, float* g_affine, float* gs_scratch, void* stream) {
   B200_CHECK_ARG(g && a, "null descriptor");
   if (g->n_nodes > 0)
     B200_CHECK_ARG(Pi && Pj && V && m_save && l_save && g_out && gPi && gPj && gV && g_attn,
@@ -36,7 +36,7 @@ extern "C" int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a,
   if (a->flavour == B200GAT_FLAVOUR_DOT) B200_CHECK_ARG(g_attn_bias, "null g_attn_bias");
   if (!force_generic() && fast_supported(a, ef))
     return fast_bwd(g, a, ef, Pi, Pj, V, s_save, m_save, l_save, g_out, gPi, gPj, gV, g_attn,
-                    g_attn_bias, g_table, g_dense, gs_scratch, (cudaStream_t)stream);
+                    g_attn_bias, g_table, g_dense, g_affine, gs_scratch, (cudaStream_t)stream);
   return generic_bwd(g, a, ef, Pi, Pj, V, s_save, m_save, l_save, g_out, gPi, gPj, gV, g_attn,
-                     g_attn_bias, g_table, g_dense, gs_scratch, (cudaStream_t)stream);
+                     g_attn_bias, g_table, g_dense, g_affine, gs_scratch, (cudaStream_t)stream);
 }

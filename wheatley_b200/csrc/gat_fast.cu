@@ -10,7 +10,7 @@ int fast_fwd(const b200gat_graph*, const b200gat_attn*, const b200gat_edge_feats
 }
 int fast_bwd(const b200gat_graph*, const b200gat_attn*, const b200gat_edge_feats*, const float*,
              const float*, const float*, const float*, const float*, const float*, const float*,
-             float*, float*, float*, float*, float*, float*, float*, float*, cudaStream_t) {
+             float*, float*, float*, float*, float*, float*, float*, float*, float*, cudaStream_t) {
   set_error("no specialised kernel for this shape");
   return B200GAT_ERR_UNSUPPORTED;
 }

@@ -25,10 +25,19 @@ struct GenericArgs {
   const float* table;
   const int32_t* etype;
   const float* dense;
+  int K;
+  const float* attr;
+  const float* affine;
 };
 
 __device__ __forceinline__ float edge_feat(const GenericArgs& A, int pos, int f) {
   if (A.emode == B200GAT_EDGE_TABLE) return __ldg(A.table + (int64_t)A.etype[pos] * (A.H * A.D) + f);
+  if (A.emode == B200GAT_EDGE_AFFINE) {
+    float r = __ldg(A.table + (int64_t)A.etype[pos] * (A.H * A.D) + f);
+    for (int k = 0; k < A.K; ++k)
+      r = fmaf(__ldg(A.attr + (int64_t)pos * A.K + k), __ldg(A.affine + (int64_t)k * (A.H * A.D) + f), r);
+    return r;
+  }
   if (A.emode == B200GAT_EDGE_DENSE) return __ldg(A.dense + (int64_t)A.in_eid[pos] * (A.H * A.D) + f);
   return 0.f;
 }
@@ -111,7 +120,7 @@ __global__ void __launch_bounds__(128) k_bwd_dst_generic(
     const float* __restrict__ V, const float* __restrict__ s_save, const float* __restrict__ m_save,
     const float* __restrict__ l_save, const float* __restrict__ G, float* __restrict__ gPj,
     float* __restrict__ g_attn, float* __restrict__ g_attn_bias, float* __restrict__ g_table,
-    float* __restrict__ g_dense, float* __restrict__ gs) {
+    float* __restrict__ g_dense, float* __restrict__ g_affine, float* __restrict__ gs) {
   const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (wid >= (int64_t)A.N * A.H) return;
@@ -170,6 +179,13 @@ __global__ void __launch_bounds__(128) k_bwd_dst_generic(
           if (A.emode == B200GAT_EDGE_DENSE) g_dense[(int64_t)A.in_eid[e] * HD + hoff + d] = gz;
           else if (A.emode == B200GAT_EDGE_TABLE)
             atomicAdd(g_table + (int64_t)A.etype[e] * HD + hoff + d, gz);
+          else if (A.emode == B200GAT_EDGE_AFFINE) {
+            atomicAdd(g_table + (int64_t)A.etype[e] * HD + hoff + d, gz);
+            for (int q = 0; q < A.K; ++q) {
+              float av = __ldg(A.attr + (int64_t)e * A.K + q);
+              if (av != 0.f) atomicAdd(g_affine + (int64_t)q * HD + hoff + d, gz * av);
+            }
+          }
         } else {
           float c = gsv * A.inv_sqrt_d;
           gat[k] = fmaf(c, pj[k] * pi, gat[k]);
@@ -293,8 +309,13 @@ static int fill_args(GenericArgs& A, const b200gat_graph* g, const b200gat_attn*
   A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
   A.table = ef ? ef->table : nullptr; A.etype = ef ? ef->etype : nullptr;
   A.dense = ef ? ef->dense : nullptr;
+  A.K = ef ? ef->n_attr : 0; A.attr = ef ? ef->attr : nullptr; A.affine = ef ? ef->affine : nullptr;
   if (a->flavour == B200GAT_FLAVOUR_DOT) A.emode = B200GAT_EDGE_NONE;  // GATv3 ignores edge_attr
-  if (A.emode == B200GAT_EDGE_TABLE) B200_CHECK_ARG(A.table && (A.E == 0 || A.etype), "null edge table/etype");
+  if (A.emode == B200GAT_EDGE_TABLE || A.emode == B200GAT_EDGE_AFFINE)
+    B200_CHECK_ARG(A.table && (A.E == 0 || A.etype), "null edge table/etype");
+  if (A.emode == B200GAT_EDGE_AFFINE)
+    B200_CHECK_ARG(A.K >= 0 && A.K <= B200GAT_MAX_ATTR && (A.K == 0 || (A.affine && (A.E == 0 || A.attr))),
+                   "bad affine edge attributes");
   if (A.emode == B200GAT_EDGE_DENSE) B200_CHECK_ARG(A.E == 0 || A.dense, "null dense edge features");
   return B200GAT_OK;
 }
@@ -311,6 +332,7 @@ int generic_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
   }
   if (A.N == 0) return B200GAT_OK;
   unsigned blocks = (unsigned)ceil_div((int64_t)A.N * A.H * 32, 128);
+  ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
   if (a->flavour == B200GAT_FLAVOUR_ADDITIVE)
     k_fwd_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save);
   else
@@ -323,7 +345,7 @@ int generic_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
                 const float* Pi, const float* Pj, const float* V, const float* s_save,
                 const float* m_save, const float* l_save, const float* g_out, float* gPi, float* gPj,
                 float* gV, float* g_attn, float* g_attn_bias, float* g_table, float* g_dense,
-                float* gs, cudaStream_t st) {
+                float* g_affine, float* gs, cudaStream_t st) {
   GenericArgs A;
   int rc = fill_args(A, g, a, ef);
   if (rc) return rc;
@@ -331,22 +353,30 @@ int generic_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
     set_error("generic kernels support dim <= %d (got %d)", 32 * kMaxK, A.D);
     return B200GAT_ERR_UNSUPPORTED;
   }
-  if (A.emode == B200GAT_EDGE_TABLE) B200_CHECK_ARG(g_table, "null g_table");
+  if (A.emode == B200GAT_EDGE_TABLE || A.emode == B200GAT_EDGE_AFFINE) B200_CHECK_ARG(g_table, "null g_table");
+  if (A.emode == B200GAT_EDGE_AFFINE && A.K > 0) B200_CHECK_ARG(g_affine, "null g_affine");
   if (A.emode == B200GAT_EDGE_DENSE) B200_CHECK_ARG(A.E == 0 || g_dense, "null g_dense");
   if (A.N == 0) return B200GAT_OK;
   unsigned blocks = (unsigned)ceil_div((int64_t)A.N * A.H * 32, 128);
-  if (a->flavour == B200GAT_FLAVOUR_ADDITIVE) {
-    k_bwd_dst_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(
-        A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, gs);
-    k_bwd_src_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
-                                                                      g_out, gs, gPi, gV);
-  } else {
-    k_bwd_dst_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(
-        A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, gs);
-    k_bwd_src_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
-                                                                 g_out, gs, gPi, gV);
+  {
+    ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
+    if (a->flavour == B200GAT_FLAVOUR_ADDITIVE)
+      k_bwd_dst_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(
+          A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, g_affine, gs);
+    else
+      k_bwd_dst_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(
+          A, Pi, Pj, V, s_save, m_save, l_save, g_out, gPj, g_attn, g_attn_bias, g_table, g_dense, g_affine, gs);
   }
-  B200_CHECK_LAUNCH("k_bwd_generic");
+  {
+    ScopedTimer tm(B200GAT_TIMING_CONV_BWD_SRC, st);
+    if (a->flavour == B200GAT_FLAVOUR_ADDITIVE)
+      k_bwd_src_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
+                                                                        g_out, gs, gPi, gV);
+    else
+      k_bwd_src_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, s_save, m_save, l_save,
+                                                                   g_out, gs, gPi, gV);
+  }
+  B200_CHECK_LAUNCHES("k_bwd_generic", 2);
   return B200GAT_OK;
 }
 

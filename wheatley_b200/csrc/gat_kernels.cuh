@@ -11,7 +11,7 @@ int generic_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
                 const float* Pi, const float* Pj, const float* V, const float* s_save,
                 const float* m_save, const float* l_save, const float* g_out, float* gPi, float* gPj,
                 float* gV, float* g_attn, float* g_attn_bias, float* g_table, float* g_dense,
-                float* gs, cudaStream_t st);
+                float* g_affine, float* gs, cudaStream_t st);
 
 // Specialised kernels (gat_fast.cu); return B200GAT_ERR_UNSUPPORTED without touching
 // anything when the shape is not covered, so the caller falls through to the generic path.
@@ -23,6 +23,6 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
              const float* Pi, const float* Pj, const float* V, const float* s_save,
              const float* m_save, const float* l_save, const float* g_out, float* gPi, float* gPj,
              float* gV, float* g_attn, float* g_attn_bias, float* g_table, float* g_dense,
-             float* gs, cudaStream_t st);
+             float* g_affine, float* gs, cudaStream_t st);
 
 }  // namespace b200gat

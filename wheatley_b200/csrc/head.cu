@@ -87,6 +87,7 @@ extern "C" int b200gat_mask_head_fwd(const float* logits, int64_t ld_logits, con
   if (batch == 0) return B200GAT_OK;
   B200_CHECK_ARG(logits && logp && entropy, "null pointer");
   B200_CHECK_ARG(ld_logits >= n && (!mask || ld_mask >= n), "row stride smaller than n");
+  ScopedTimer tm(B200GAT_TIMING_HEAD, (cudaStream_t)stream);
   k_mask_head_fwd<<<(unsigned)ceil_div((int64_t)batch * 32, 128), 128, 0, (cudaStream_t)stream>>>(
       logits, ld_logits, mask, ld_mask, batch, n, fill, logp, entropy, argmax);
   B200_CHECK_LAUNCH("k_mask_head_fwd");
@@ -100,6 +101,7 @@ extern "C" int b200gat_mask_head_bwd(const float* logp, const uint8_t* mask, int
   B200_CHECK_ARG(batch >= 0 && n >= 0, "negative size");
   if (batch == 0 || n == 0) return B200GAT_OK;
   B200_CHECK_ARG(logp && entropy && g_logits, "null pointer");
+  ScopedTimer tm(B200GAT_TIMING_HEAD, (cudaStream_t)stream);
   k_mask_head_bwd<<<(unsigned)ceil_div((int64_t)batch * 32, 128), 128, 0, (cudaStream_t)stream>>>(
       logp, mask, ld_mask, action, entropy, g_logprob, g_entropy, batch, n, g_logits);
   B200_CHECK_LAUNCH("k_mask_head_bwd");

@@ -231,6 +231,14 @@ __global__ void k_gather_i32(const int32_t* __restrict__ table, const int32_t* _
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) out[i] = table[idx[i]];
 }
+__global__ void k_gather_rows_f32(const float* __restrict__ table, const int32_t* __restrict__ idx,
+                                  int64_t n, int width, float* __restrict__ out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n * width) return;
+  int64_t r = i / width;
+  int c = (int)(i - r * width);
+  out[i] = table[(int64_t)idx[r] * width + c];
+}
 __global__ void k_narrow_i64(const int64_t* __restrict__ in, int64_t n, int32_t* __restrict__ out) {
   int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
   if (i + 1 < n) {
@@ -248,6 +256,7 @@ static int scan_inplace(int32_t* a, int64_t n, int32_t* bsum, cudaStream_t st) {
     k_scan_bsums<<<1, kScanThreads, 0, st>>>(bsum, nb);
   }
   k_scan_tiles<<<nb, kScanThreads, 0, st>>>(a, n, bsum, 1);
+  note_launch(nb > 1 ? 3 : 1);
   return 0;
 }
 
@@ -285,6 +294,7 @@ extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_d
   int32_t* bsum_out = bsum_in + nb;
   int32_t* counters = bsum_out + nb;  // [0] n_large_in, [1] n_large_out
 
+  ScopedTimer tm(B200GAT_TIMING_PLAN, st);
   cudaMemsetAsync(in_ptr, 0, sizeof(int32_t) * (N + 1), st);
   cudaMemsetAsync(out_ptr, 0, sizeof(int32_t) * (N + 1), st);
   cudaMemsetAsync(stats, 0, sizeof(int32_t) * 4, st);
@@ -298,7 +308,7 @@ extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_d
   }
   scan_inplace(in_ptr, N + 1, bsum_in, st);
   scan_inplace(out_ptr, N + 1, bsum_out, st);
-  B200_CHECK_LAUNCH("k_scan");
+  if (cudaGetLastError() != cudaSuccess) { set_error("k_scan: launch failed"); return B200GAT_ERR_CUDA; }
   if (E > 0) {
     unsigned eb = (unsigned)ceil_div(E, 256);
     k_fill<<<eb, 256, 0, st>>>(edge_src, edge_dst, E, (int32_t)N, in_ptr, out_ptr, fill_in,
@@ -309,10 +319,10 @@ extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_d
     k_sort_small<<<wb, 256, 0, st>>>(out_ptr, (int32_t)N, tmp_out, out_eid, large_out, counters + 1);
     k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(in_ptr, tmp_in, in_eid, large_in, counters + 0);
     k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(out_ptr, tmp_out, out_eid, large_out, counters + 1);
-    B200_CHECK_LAUNCH("k_sort");
+    B200_CHECK_LAUNCHES("k_sort", 4);
     k_finish_in<<<eb, 256, 0, st>>>(edge_src, E, in_eid, in_src, inv);
     k_finish_out<<<eb, 256, 0, st>>>(edge_dst, E, out_eid, inv, out_dst, out_pos);
-    B200_CHECK_LAUNCH("k_finish");
+    B200_CHECK_LAUNCHES("k_finish", 2);
   }
   if (N > 0) {
     k_degree_stats<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(in_ptr, out_ptr, (int32_t)N, stats);
@@ -328,6 +338,17 @@ extern "C" int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int6
   B200_CHECK_ARG(table && idx && out, "null pointer");
   k_gather_i32<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, out);
   B200_CHECK_LAUNCH("k_gather_i32");
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_gather_rows_f32(const float* table, const int32_t* idx, int64_t n, int32_t width,
+                                       float* out, void* stream) {
+  B200_CHECK_ARG(n >= 0 && width >= 0, "negative size");
+  if (n == 0 || width == 0) return B200GAT_OK;
+  B200_CHECK_ARG(table && idx && out, "null pointer");
+  k_gather_rows_f32<<<(unsigned)ceil_div(n * width, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n,
+                                                                                         width, out);
+  B200_CHECK_LAUNCH("k_gather_rows_f32");
   return B200GAT_OK;
 }
 

@@ -7,6 +7,7 @@ Passing the factors instead of the materialised ``[E, F]`` tensor lets the layer
 the T-row table once and gather inside the kernel (no ``[E,F]x[F,H*D]`` GEMM, no
 ``[E,H*D]`` intermediate)."""
 import torch
+from torch import nn
 
 
 class TypedEdgeFeats:
@@ -14,6 +15,8 @@ class TypedEdgeFeats:
 
     def __init__(self, etype: torch.Tensor, weight: torch.Tensor):
         self.etype, self.weight = etype, weight
+        self.attrs = None
+        self.attr_weight = None
 
     @property
     def shape(self):
@@ -21,3 +24,65 @@ class TypedEdgeFeats:
 
     def dense(self) -> torch.Tensor:
         return torch.nn.functional.embedding(self.etype.long(), self.weight)
+
+
+class AffineEdgeFeats(TypedEdgeFeats):
+    """``efeats[e] = weight[etype[e]] + attrs[e] @ attr_weight.T``  with ``attrs [E, K]``,
+    ``attr_weight [F, K]`` (K small: 5 for the PSP embedder, psp/models/edge_embedder.py:130-143,
+    whose two ``Linear`` biases are folded into ``weight``)."""
+
+    def __init__(self, etype, weight, attrs, attr_weight):
+        super().__init__(etype, weight)
+        self.attrs, self.attr_weight = attrs, attr_weight
+
+    def dense(self) -> torch.Tensor:
+        return super().dense() + self.attrs.to(self.attr_weight.dtype) @ self.attr_weight.t()
+
+
+class PspEdgeEmbedder(nn.Module):
+    """``edge_embedding_flavor == "sum"`` branch of psp/models/edge_embedder.py:25-143 with the
+    reference parameter names (``edge_type_embedder``, ``rc_att_embedder``, ``rp_att_embedder``).
+
+    ``forward(g)`` returns the factored :class:`AffineEdgeFeats`; ``.dense()`` of it is exactly
+    the reference's ``[E, hidden]`` tensor (golden: tests/golden/edge_embedder.npz)."""
+
+    def __init__(self, edge_embedding_flavor, max_n_resources, hidden_dim, add_rp_edges,
+                 factored_rp, n_mlp_layers_features_extractor=None,
+                 activation_features_extractor=None):
+        super().__init__()
+        if edge_embedding_flavor != "sum":
+            raise NotImplementedError("only the default 'sum' edge embedding is on the live path "
+                                      "(args.py default; SURVEY F13)")
+        self.edge_embedding_flavor = edge_embedding_flavor
+        self.max_n_resources = max_n_resources
+        self.hidden_dim = hidden_dim
+        self.add_rp_edges = add_rp_edges
+        self.factored_rp = factored_rp
+        self.n_edge_type = 16
+        self.edge_type_embedder = nn.Embedding(self.n_edge_type, hidden_dim)
+        self.rc_att_embedder = nn.Linear(2, hidden_dim)
+        if add_rp_edges != "none":
+            self.rp_att_embedder = nn.Linear(3 * max_n_resources if factored_rp else 3, hidden_dim)
+
+    def factor(self, etype, att_rc=None, att_rp=None) -> AffineEdgeFeats:
+        table = self.edge_type_embedder.weight
+        attrs, ws = [], []
+        if att_rc is not None:                      # psp/models/edge_embedder.py:134-137
+            table = table + self.rc_att_embedder.bias
+            attrs.append(att_rc.float())
+            ws.append(self.rc_att_embedder.weight)
+        if self.add_rp_edges != "none" and att_rp is not None:   # :138-142
+            table = table + self.rp_att_embedder.bias
+            attrs.append(att_rp.float())
+            ws.append(self.rp_att_embedder.weight)
+        if not attrs:
+            return TypedEdgeFeats(etype, table)
+        return AffineEdgeFeats(etype, table, torch.cat(attrs, dim=1), torch.cat(ws, dim=1))
+
+    def forward(self, g):
+        def get(key):
+            try:
+                return g.edata(None, key)
+            except KeyError:
+                return None
+        return self.factor(g.edata(None, "type"), get("att_rc"), get("att_rp"))

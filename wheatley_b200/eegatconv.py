@@ -11,7 +11,8 @@ from torch.nn import init
 
 from . import _lib
 from .edge_feats import TypedEdgeFeats
-from .functional import EdgeFeatures, attention_weights, edge_output, fused_gat_conv
+from .functional import (EdgeFeatures, attention_weights, edge_output, fused_gat_conv,
+                         project_edge_feats)
 from .plan import GraphPlan
 
 
@@ -114,17 +115,11 @@ class EEGATConv(nn.Module):
 
     def _edge_features(self, plan, efeats, efeats_e):
         """Projected edge term (+ pre-activation bias, eegatconv.py:262,271-275)."""
-        if isinstance(efeats, TypedEdgeFeats) and not self._edge_scoring:
-            table = self.fc_fij(efeats.weight)                       # [T, H*De]
-            if self.bias is not None:
-                table = table + self.bias
-            return EdgeFeatures(_lib.EDGE_TABLE, table=table,
-                                etype_sorted=plan.sort_edge_ints(efeats.etype))
+        if not self._edge_scoring:
+            return project_edge_feats(plan, efeats, self.fc_fij.weight, self.bias)
         if isinstance(efeats, TypedEdgeFeats):
             efeats = efeats.dense()
-        dense = self.fc_fij(efeats)
-        if self._edge_scoring:
-            dense = dense + self.fc_fij_e(efeats_e)
+        dense = self.fc_fij(efeats) + self.fc_fij_e(efeats_e)
         if self.bias is not None:
             dense = dense + self.bias
         return EdgeFeatures(_lib.EDGE_DENSE, dense=dense)

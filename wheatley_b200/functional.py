@@ -15,12 +15,33 @@ class EdgeFeatures:
     ``mode='dense'``: ``Pe [E, H*D]`` in the original edge order.
     """
 
-    def __init__(self, mode, table=None, etype_sorted=None, dense=None):
+    def __init__(self, mode, table=None, etype_sorted=None, dense=None, attr_sorted=None, affine=None):
         self.mode, self.table, self.etype_sorted, self.dense = mode, table, etype_sorted, dense
+        self.attr_sorted, self.affine = attr_sorted, affine     # 'affine' mode: [E,K] sorted, [K,H*D]
 
     @classmethod
     def none(cls):
         return cls(_lib.EDGE_NONE)
+
+
+def project_edge_feats(plan: GraphPlan, efeats, weight, pre_bias=None) -> EdgeFeatures:
+    """Edge term of the logit, ``Pe = efeats @ weight.T (+ pre_bias)``, in the cheapest exact form:
+    typed/affine factors are projected as a T-row table (+ a K-row affine map) and gathered
+    inside the kernel; a dense ``[E, F]`` tensor is projected with one GEMM."""
+    from .edge_feats import TypedEdgeFeats
+    if efeats is None:
+        return EdgeFeatures.none()
+    if isinstance(efeats, TypedEdgeFeats):
+        table = torch.nn.functional.linear(efeats.weight, weight, pre_bias)     # [T, H*D]
+        etype_sorted = plan.sort_edge_ints(efeats.etype)
+        if efeats.attrs is not None and efeats.attrs.shape[1] <= _lib.MAX_ATTR:
+            affine = (weight @ efeats.attr_weight).t()                            # [K, H*D]
+            return EdgeFeatures(_lib.EDGE_AFFINE, table=table, etype_sorted=etype_sorted,
+                                attr_sorted=plan.sort_edge_rows(efeats.attrs), affine=affine)
+        if efeats.attrs is None:
+            return EdgeFeatures(_lib.EDGE_TABLE, table=table, etype_sorted=etype_sorted)
+        efeats = efeats.dense()
+    return EdgeFeatures(_lib.EDGE_DENSE, dense=torch.nn.functional.linear(efeats, weight, pre_bias))
 
 
 def _f32c(t):
@@ -36,7 +57,7 @@ class _FusedGATConv(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, plan: GraphPlan, cfg: dict, Pi, Pj, V, attn, attn_bias, out_bias,
-                e_table, e_dense, etype_sorted):
+                e_table, e_dense, etype_sorted, e_affine, attr_sorted):
         if not Pi.is_cuda:
             raise _lib.B200GatError("wheatley_b200 kernels need CUDA tensors (no CPU fallback)")
         H, D = cfg["heads"], cfg["dim"]
@@ -47,9 +68,12 @@ class _FusedGATConv(torch.autograd.Function):
         attn_c = _f32c(attn.reshape(-1))
         attn_bias_c = _f32c(attn_bias)
         out_bias_c = _f32c(out_bias)
-        e_table_c, e_dense_c = _f32c(e_table), _f32c(e_dense)
+        e_table_c, e_dense_c, e_affine_c = _f32c(e_table), _f32c(e_dense), _f32c(e_affine)
         mode = _lib.EDGE_TABLE if e_table is not None else (_lib.EDGE_DENSE if e_dense is not None
                                                            else _lib.EDGE_NONE)
+        if e_affine is not None:
+            mode = _lib.EDGE_AFFINE
+        n_attr = 0 if e_affine_c is None else e_affine_c.shape[0]
         assert Pi.shape == (N, HD) and Pj.shape == (N, HD) and Vt.shape == (N, HD)
         out = torch.empty((N, HD), dtype=torch.float32, device=Pi.device)
         s = torch.empty((E, H), dtype=torch.float32, device=Pi.device)
@@ -58,22 +82,23 @@ class _FusedGATConv(torch.autograd.Function):
         a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
                       _lib.ptr(attn_bias_c), _lib.ptr(out_bias_c))
         ef = _lib.EdgeFeats(mode, 0 if e_table_c is None else e_table_c.shape[0],
-                            _lib.ptr(e_table_c), _lib.ptr(etype_sorted), _lib.ptr(e_dense_c))
+                            _lib.ptr(e_table_c), _lib.ptr(etype_sorted), _lib.ptr(e_dense_c),
+                            n_attr, _lib.ptr(attr_sorted), _lib.ptr(e_affine_c))
         with torch.cuda.device(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_fwd(plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
                                                  _lib.ptr(out), _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
                                                  _lib.stream_ptr()), "b200gat_conv_fwd")
         ctx.plan, ctx.cfg, ctx.mode, ctx.v_alias = plan, cfg, mode, v_alias
-        ctx.etype_sorted = etype_sorted
+        ctx.etype_sorted, ctx.attr_sorted = etype_sorted, attr_sorted
         ctx.has_out_bias = out_bias is not None
         ctx.attn_shape = attn.shape
-        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, s, m, l)
+        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l)
         ctx.mark_non_differentiable(s, m, l)
         return out, s, m, l
 
     @staticmethod
     def backward(ctx, g_out, _gs, _gm, _gl):
-        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, s, m, l = ctx.saved_tensors
+        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l = ctx.saved_tensors
         plan, cfg = ctx.plan, ctx.cfg
         H, D = cfg["heads"], cfg["dim"]
         g_out = _f32c(g_out)
@@ -84,20 +109,23 @@ class _FusedGATConv(torch.autograd.Function):
         g_attn_bias = torch.zeros_like(attn_bias_c) if attn_bias_c is not None else None
         g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None
         g_dense = torch.empty_like(e_dense_c) if e_dense_c is not None else None
+        g_affine = torch.zeros_like(e_affine_c) if e_affine_c is not None else None
         gs = torch.empty_like(s)
         a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
                       _lib.ptr(attn_bias_c), None)
         ef = _lib.EdgeFeats(ctx.mode, 0 if e_table_c is None else e_table_c.shape[0],
-                            _lib.ptr(e_table_c), _lib.ptr(ctx.etype_sorted), _lib.ptr(e_dense_c))
+                            _lib.ptr(e_table_c), _lib.ptr(ctx.etype_sorted), _lib.ptr(e_dense_c),
+                            0 if e_affine_c is None else e_affine_c.shape[0], _lib.ptr(ctx.attr_sorted),
+                            _lib.ptr(e_affine_c))
         with torch.cuda.device(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_bwd(
                 plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
                 _lib.ptr(l), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj), _lib.ptr(gV),
                 _lib.ptr(g_attn), _lib.ptr(g_attn_bias), _lib.ptr(g_table), _lib.ptr(g_dense),
-                _lib.ptr(gs), _lib.stream_ptr()), "b200gat_conv_bwd")
+                _lib.ptr(g_affine), _lib.ptr(gs), _lib.stream_ptr()), "b200gat_conv_bwd")
         g_bias = g_out.sum(0) if ctx.has_out_bias else None
         return (None, None, gPi, gPj, None if ctx.v_alias else gV, g_attn.view(ctx.attn_shape),
-                g_attn_bias, g_bias, g_table, g_dense, None)
+                g_attn_bias, g_bias, g_table, g_dense, None, g_affine, None)
 
 
 def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_ADDITIVE, slope=0.2,
@@ -105,10 +133,12 @@ def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_AD
     """Returns ``(out [N, H*D], (s, m, l))``; ``V=None`` means V aliases Pi."""
     cfg = dict(heads=int(heads), dim=int(dim), flavour=int(flavour), slope=float(slope), eps=float(eps))
     ef = edge_feats or EdgeFeatures.none()
-    e_table = ef.table if ef.mode == _lib.EDGE_TABLE else None
+    e_table = ef.table if ef.mode in (_lib.EDGE_TABLE, _lib.EDGE_AFFINE) else None
     e_dense = ef.dense if ef.mode == _lib.EDGE_DENSE else None
+    e_affine = ef.affine if ef.mode == _lib.EDGE_AFFINE else None
     out, s, m, l = _FusedGATConv.apply(plan, cfg, Pi, Pj, V, attn, attn_bias, out_bias, e_table,
-                                       e_dense, ef.etype_sorted if e_table is not None else None)
+                                       e_dense, ef.etype_sorted if e_table is not None else None,
+                                       e_affine, ef.attr_sorted if e_affine is not None else None)
     return out, (s, m, l)
 
 
@@ -126,12 +156,14 @@ def edge_output(plan: GraphPlan, Pi, Pj, edge_feats: EdgeFeatures, *, heads, dim
     """f_out [E, H, D] = leaky_relu(Pi[src]+Pj[dst]+Pe) (no autograd: materialised on request)."""
     Pi, Pj = _f32c(Pi.detach()), _f32c(Pj.detach())
     ef = edge_feats or EdgeFeatures.none()
-    tbl = _f32c(ef.table.detach()) if ef.mode == _lib.EDGE_TABLE else None
+    tbl = _f32c(ef.table.detach()) if ef.mode in (_lib.EDGE_TABLE, _lib.EDGE_AFFINE) else None
     dns = _f32c(ef.dense.detach()) if ef.mode == _lib.EDGE_DENSE else None
+    aff = _f32c(ef.affine.detach()) if ef.mode == _lib.EDGE_AFFINE else None
     attn_c = _f32c(attn.detach().reshape(-1))
     a = _lib.Attn(_lib.FLAVOUR_ADDITIVE, heads, dim, slope, 0.0, _lib.ptr(attn_c), None, None)
     efc = _lib.EdgeFeats(ef.mode, 0 if tbl is None else tbl.shape[0], _lib.ptr(tbl),
-                         _lib.ptr(ef.etype_sorted), _lib.ptr(dns))
+                         _lib.ptr(ef.etype_sorted), _lib.ptr(dns), 0 if aff is None else aff.shape[0],
+                         _lib.ptr(ef.attr_sorted), _lib.ptr(aff))
     f = torch.empty((plan.n_edges, heads, dim), dtype=torch.float32, device=Pi.device)
     with torch.cuda.device(Pi.device):
         _lib.check(_lib.lib.b200gat_edge_out(plan.c, a, efc, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(f),

@@ -1,0 +1,121 @@
+"""GnnDGL - the JSSP trunk of jssp/models/gnn_dgl.py:36-431 (``gconv_type in {"gat","gatv2"}``
+branch, the default) on the fused CUDA attention layer.
+
+Same constructor arguments, sub-module / parameter names (``node_embedder``,
+``edge_embedder.0``, ``embedder.layers.*``, ``features_extractors.<l>.fc_*``, ``mlps.<l>.layers.*``)
+and return layout, so ``Agent.save`` / ``load_state_dict`` round-trip with reference
+checkpoints.  Differences, all inside the boundary:
+
+* the batched graph arrives as a :class:`JsspBatch` (built once per batch on the device by
+  ``wheatley_b200.batch``) instead of being rebuilt with per-graph Python loops on the CPU
+  (``agent_observation.py:191-225``, ``gnn_dgl.py:272-286``);
+* edge features stay factored: ``EGATConv`` gets ``TypedEdgeFeats(type, edge_embedder[0].weight)``
+  so ``fc_fij`` projects the T-row table, not ``[E, hidden]`` (:364, generic/eegatconv.py:262);
+* the ``[E, H, D]`` edge output of the layer is never materialised (its only caller drops it, :374-379).
+"""
+import torch
+from torch import nn
+
+from .edge_feats import TypedEdgeFeats
+from .eegatconv import EGATConv
+from .mlp import MLP
+
+
+class JsspBatch:
+    """What ``GnnDGL.forward`` needs from one batched observation."""
+
+    def __init__(self, plan, etype, feat, batch_size, n_nodes, num_task_nodes, poolnodes=None,
+                 machinenodes=None):
+        self.plan, self.etype, self.feat = plan, etype, feat
+        self.batch_size, self.n_nodes, self.num_task_nodes = batch_size, n_nodes, num_task_nodes
+        self.poolnodes, self.machinenodes = poolnodes, machinenodes
+
+
+class GnnDGL(nn.Module):
+    def __init__(self, input_dim_features_extractor, gconv_type, graph_pooling, graph_has_relu,
+                 max_n_nodes, max_n_machines, n_mlp_layers_features_extractor,
+                 n_layers_features_extractor, hidden_dim_features_extractor,
+                 activation_features_extractor, n_attention_heads, residual=True, normalize=False,
+                 conflicts="att", no_tct=False, mid_in_edges=False, split_output=False):
+        super().__init__()
+        # split_output=True returns the (node_features, graph_embedding) pair the generic Agent
+        # unpacks (generic/agent.py:193); False keeps the reference's concatenated tensor (:427-431)
+        self.split_output = split_output
+        if gconv_type not in ("gat", "gatv2"):
+            raise NotImplementedError("only the gat/gatv2 trunk is on the hot path (SURVEY 8a)")
+        if normalize:
+            raise NotImplementedError("normalize=True is not on the live path (args.py:446-448)")
+        self.conflicts, self.residual, self.normalize = conflicts, residual, normalize
+        self.max_n_nodes, self.max_n_machines = max_n_nodes, max_n_machines
+        self.features_dim = 2 * (input_dim_features_extractor
+                                 + hidden_dim_features_extractor * (n_layers_features_extractor + 1))
+        self.hidden_dim = hidden_dim_features_extractor
+        self.gconv_type, self.graph_has_relu, self.graph_pooling = gconv_type, graph_has_relu, graph_pooling
+        self.n_layers_features_extractor = n_layers_features_extractor
+        self.no_tct, self.mid_in_edges = no_tct, mid_in_edges
+        self.features_extractors = nn.ModuleList()
+        self.edge_embedder = nn.ModuleList()
+        self.node_embedder = nn.Embedding(1 + max_n_machines, input_dim_features_extractor)
+        if conflicts in ("clique", "node"):                      # gnn_dgl.py:89-113
+            nmachineid = max_n_machines if conflicts == "clique" else 2 * max_n_machines
+            n_types = 5 + nmachineid + 1 if mid_in_edges else 5 + 1
+        else:
+            n_types = 5
+        self.edge_embedder.append(nn.Embedding(n_types, hidden_dim_features_extractor))
+        self.embedder = MLP(n_mlp_layers_features_extractor, input_dim_features_extractor,
+                            hidden_dim_features_extractor, hidden_dim_features_extractor,
+                            norm=normalize, activation=activation_features_extractor)
+        self.mlps = nn.ModuleList()
+        for _ in range(n_layers_features_extractor):
+            self.features_extractors.append(EGATConv(self.hidden_dim, self.hidden_dim, self.hidden_dim,
+                                                     self.hidden_dim, num_heads=n_attention_heads))
+            self.mlps.append(MLP(n_mlp_layers_features_extractor,
+                                 hidden_dim_features_extractor * n_attention_heads,
+                                 hidden_dim_features_extractor * n_attention_heads,
+                                 hidden_dim_features_extractor, norm=normalize,
+                                 activation=activation_features_extractor))
+
+    def node_embeddings(self, b: JsspBatch):
+        """Concatenation of all layers' node embeddings ``[N_total, F]`` (gnn_dgl.py:339-401)."""
+        features = b.feat
+        if self.graph_pooling == "learn" and b.poolnodes is not None:           # :341-344
+            features = features.clone()
+            features[b.poolnodes] = self.node_embedder.weight[0].to(features.dtype)
+        if self.conflicts == "node" and b.machinenodes is not None:             # :346-351
+            ids = (torch.arange(self.max_n_machines, device=features.device) + 1).repeat(b.batch_size)
+            features = features.clone()
+            features[b.machinenodes] = self.node_embedder(ids)
+        features_list = [features]
+        features = self.embedder(features)                                      # :355
+        features_list.append(features)
+        efeats = TypedEdgeFeats(b.etype, self.edge_embedder[0].weight)          # :364
+        for layer in range(self.n_layers_features_extractor):
+            h, _ = self.features_extractors[layer](b.plan, features, efeats)    # :374-376
+            features = self.mlps[layer](h.flatten(start_dim=-2, end_dim=-1))    # :377
+            if self.residual:
+                features = features + features_list[-1]                         # :395-396
+            features_list.append(features)
+        return torch.cat(features_list, dim=1)                                  # :401
+
+    def forward_split(self, b: JsspBatch):
+        """``(node_features [B, max_n_nodes, F], graph_embedding [B, 1, F])`` - the pair the generic
+        ``Agent`` unpacks (generic/agent.py:193)."""
+        features = self.node_embeddings(b)
+        node_features = features[: b.num_task_nodes].reshape(b.batch_size, b.n_nodes, -1)   # :402-405
+        if self.graph_pooling == "max":
+            graph_embedding = node_features.max(dim=1)[0]
+        elif self.graph_pooling == "avg":
+            graph_embedding = node_features.mean(dim=1)
+        elif self.graph_pooling in ("learn", "learninv"):
+            graph_embedding = features[b.num_task_nodes: b.num_task_nodes + b.batch_size]
+        else:
+            raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
+        node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - node_features.shape[1]))
+        return node_features, graph_embedding.reshape(b.batch_size, 1, -1)
+
+    def forward(self, b: JsspBatch):
+        """Reference return layout (:427-431): ``cat(node_features, repeated graph embedding)``."""
+        node_features, graph_embedding = self.forward_split(b)
+        if self.split_output:
+            return node_features, graph_embedding
+        return torch.cat((node_features, graph_embedding.expand(node_features.shape)), dim=2)

@@ -87,6 +87,24 @@ class GraphPlan:
         return out
 
 
+    def sort_edge_rows(self, per_edge: torch.Tensor, key=None) -> torch.Tensor:
+        """Permute fp32 per-edge attribute rows ``[E, K]`` into destination-sorted order."""
+        key = key if key is not None else ("rows", per_edge.data_ptr(), per_edge._version)
+        hit = self._sorted_cache.get(key)
+        if hit is not None:
+            return hit
+        t = per_edge.detach()
+        if t.dtype != torch.float32:
+            t = t.float()
+        t = t.contiguous().view(self.n_edges, -1)
+        out = torch.empty_like(t)
+        _lib.check(_lib.lib.b200gat_gather_rows_f32(_lib.ptr(t), _lib.ptr(self.in_eid), self.n_edges,
+                                                    t.shape[1], _lib.ptr(out), _lib.stream_ptr()),
+                   "b200gat_gather_rows_f32")
+        self._sorted_cache[key] = out
+        return out
+
+
 def plan_for_edge_index(edge_index: torch.Tensor, n_nodes: int, holder=None) -> GraphPlan:
     """Plan cache: the plan is stored on ``holder`` (the graph object the reference passes
     around, or the edge_index tensor itself) and reused while the tensor is unchanged."""

@@ -1,0 +1,134 @@
+"""Synthetic schedule graphs with the topology Wheatley's JSSP path produces.
+
+Used by ``bench.py``, ``__graft_entry__.smoke()`` and the parity tests to make inputs of the
+sizes BASELINE.json names without the reference tree (which does not exist on the GPU box).
+
+Topology sources (reference): job chains ``jssp/env/state.py:220-227``; bidirectional
+precedence edges typed 1/2 ``jssp/models/agent_observation.py:57-71``; machine cliques typed 5
+``jssp/utils/utils.py:460-478`` + ``agent_observation.py:81-88``; self loops typed 0 ``:211``;
+``dgl.batch`` ``:223``; pool nodes/edges ``jssp/models/gnn_dgl.py:263-286``.
+Instances: machine order per job is a seeded random permutation and durations are U[1,99]
+like ``instances/generate_taillard.py:19-36``."""
+import numpy as np
+import torch
+
+
+def taillard_instance(n_j: int, n_m: int, seed: int):
+    """(durations [n_j, n_m] int64 in [1, 99], machines [n_j, n_m] int64 permutation per job)."""
+    rng = np.random.default_rng(seed)
+    durations = rng.integers(1, 100, size=(n_j, n_m))
+    machines = np.stack([rng.permutation(n_m) for _ in range(n_j)])
+    return durations.astype(np.int64), machines.astype(np.int64)
+
+
+def jssp_observation(n_j: int, n_m: int, seed: int, n_features: int = None, progress: float = 0.0):
+    """One env observation in the layout of ``jssp/env/observation.py:83-128`` (unpadded):
+    ``features [N, F]`` (col 6 = machine id, ``agent_observation.py:162``), ``edge_index [2, n_e]``
+    = job-chain precedence edges, plus machine-chain edges between consecutively dispatched
+    operations of a machine for a seeded random dispatch of ``progress`` of the operations
+    (``jssp/env/state.py:655-674``)."""
+    durations, machines = taillard_instance(n_j, n_m, seed)
+    N = n_j * n_m
+    F = n_features if n_features is not None else 6 + n_m + 4
+    rng = np.random.default_rng(seed + 7919)
+    feat = rng.random((N, F), dtype=np.float32)
+    feat[:, 6] = machines.reshape(-1).astype(np.float32)
+    feat[:, 4] = durations.reshape(-1).astype(np.float32) / 99.0
+    ids = np.arange(N).reshape(n_j, n_m)
+    src = [ids[:, :-1].reshape(-1)]
+    dst = [ids[:, 1:].reshape(-1)]
+    n_sched = int(round(progress * N))
+    if n_sched > 0:
+        nxt = np.zeros(n_j, dtype=np.int64)          # next operation of each job
+        last = -np.ones(n_m, dtype=np.int64)         # last dispatched node per machine
+        cs, cd = [], []
+        for _ in range(n_sched):
+            cand = np.nonzero(nxt < n_m)[0]
+            j = int(cand[rng.integers(0, len(cand))])
+            node = int(ids[j, nxt[j]])
+            m = int(machines[j, nxt[j]])
+            if last[m] >= 0 and ids.reshape(-1)[last[m]] // n_m != j:
+                cs.append(last[m]); cd.append(node)
+            last[m] = node
+            nxt[j] += 1
+        src.append(np.array(cs, dtype=np.int64)); dst.append(np.array(cd, dtype=np.int64))
+    ei = np.stack([np.concatenate(src), np.concatenate(dst)]).astype(np.int64)
+    return dict(features=feat, edge_index=ei, n_nodes=N, n_edges=ei.shape[1], n_jobs=n_j, n_machines=n_m)
+
+
+def clique_edges(machineid: np.ndarray):
+    """All ordered pairs (r, c), r != c, sharing a machine id (id -1 conflicts with nobody), in
+    row-major order of r then c - the order ``jssp/utils/utils.py:460-478`` yields.  O(E) memory."""
+    m = np.asarray(machineid).astype(np.int64)
+    n = m.shape[0]
+    valid = m >= 0
+    nmach = int(m.max(initial=-1)) + 1
+    if nmach <= 0:
+        z = np.zeros(0, dtype=np.int64)
+        return z, z, z
+    order = np.argsort(np.where(valid, m, nmach), kind="stable")   # members per machine, ascending node id
+    cnt = np.bincount(m[valid], minlength=nmach)
+    start = np.concatenate([[0], np.cumsum(cnt)])
+    nvalid = int(cnt.sum())
+    rank = np.zeros(n, dtype=np.int64)                             # position of a node in its machine's list
+    rank[order[:nvalid]] = np.arange(nvalid) - np.repeat(start[:-1], cnt)
+    deg = np.where(valid, cnt[np.where(valid, m, 0)] - 1, 0)
+    off = np.concatenate([[0], np.cumsum(deg)])
+    r = np.repeat(np.arange(n), deg)
+    k = np.arange(int(off[-1])) - off[r]                           # rank among r's neighbours
+    kk = k + (k >= rank[r])                                        # skip r itself
+    c = order[start[m[r]] + kk]
+    return r.astype(np.int64), c.astype(np.int64), m[r]
+
+
+def jssp_graph_edges(obs, conflicts="clique", mid_in_edges=False, bidir=True, add_self_loops=True):
+    """Per-graph edge list in the reference order: [prec fwd (1) | prec rev (2)] | clique (5 or
+    5+mid) | self loops (0).  ``agent_observation.py:53-88,186-211``."""
+    e0, e1 = obs["edge_index"][0], obs["edge_index"][1]
+    ne, nn = e0.shape[0], obs["n_nodes"]
+    if bidir:
+        s, d = np.concatenate([e0, e1]), np.concatenate([e1, e0])
+        t = np.concatenate([np.full(ne, 1), np.full(ne, 2)])
+    else:
+        s, d, t = e0, e1, np.full(ne, 1)
+    if conflicts == "clique":
+        r, c, mid = clique_edges(obs["features"][:nn, 6].astype(np.int64))
+        s, d = np.concatenate([s, r]), np.concatenate([d, c])
+        t = np.concatenate([t, mid + 5 if mid_in_edges else np.full(r.shape[0], 5)])
+    if add_self_loops:
+        loop = np.arange(nn)
+        s, d, t = np.concatenate([s, loop]), np.concatenate([d, loop]), np.concatenate([t, np.zeros(nn, np.int64)])
+    return s.astype(np.int64), d.astype(np.int64), t.astype(np.int64)
+
+
+def jssp_batch(n_j, n_m, batch, seed0=0, progress=0.0, conflicts="clique", pool=True, n_features=None):
+    """A ``dgl.batch`` of ``batch`` schedule graphs + one learned-pool node per graph.
+    Returns dict(src, dst, etype [E] int64 torch, feat [N, F] fp32, n_nodes, n_task_nodes,
+    batch_num_nodes, edges_per_graph)."""
+    S, D, T, feats, bnn = [], [], [], [], []
+    off = 0
+    for b in range(batch):
+        obs = jssp_observation(n_j, n_m, seed0 + b, n_features, progress)
+        s, d, t = jssp_graph_edges(obs, conflicts)
+        S.append(s + off); D.append(d + off); T.append(t)
+        feats.append(obs["features"]); bnn.append(obs["n_nodes"])
+        off += obs["n_nodes"]
+    n_task = off
+    feat = np.concatenate(feats)
+    if pool:                                               # jssp/models/gnn_dgl.py:263-286
+        bnn_a = np.array(bnn)
+        poolnodes = np.arange(n_task, n_task + batch)
+        S.append(poolnodes); D.append(poolnodes); T.append(np.zeros(batch, np.int64))
+        S.append(np.arange(n_task)); D.append(np.repeat(poolnodes, bnn_a)); T.append(np.full(n_task, 4))
+        feat = np.concatenate([feat, np.zeros((batch, feat.shape[1]), np.float32)])
+        off += batch
+    src, dst, et = np.concatenate(S), np.concatenate(D), np.concatenate(T)
+    return dict(src=torch.from_numpy(src), dst=torch.from_numpy(dst), etype=torch.from_numpy(et),
+                feat=torch.from_numpy(feat), n_nodes=off, n_task_nodes=n_task,
+                batch_num_nodes=bnn, n_edges=int(src.shape[0]))
+
+
+def jssp_clique_graph(n_j, n_m, seed=0):
+    """One full-size graph (tasks + pool node): ``(src, dst, etype, n_nodes)``."""
+    b = jssp_batch(n_j, n_m, 1, seed)
+    return b["src"], b["dst"], b["etype"], b["n_nodes"]
