@@ -260,6 +260,8 @@ def run_b200(args):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        if sampler:
+            _lib.timing_enable(True)                       # per-kernel events over the timed steps only
         smp = ClockSampler(local) if sampler and rank == 0 else None
         l0 = _lib.launch_count()
         total = 0.0
@@ -286,7 +288,6 @@ def run_b200(args):
     d_res = to_dev()
     jb_res = make_batch(d_res)
     torch.cuda.synchronize()
-    _lib.timing_enable(True)
     ms_dev, launches, clocks = timed(lambda: train_step(jb_res, d_res), args.steps, args.warmup, sampler=True)
     tm = _lib.timing_read()
     _lib.timing_enable(False)
@@ -295,7 +296,7 @@ def run_b200(args):
     def e2e_step():
         d = to_dev()
         jb = make_batch(d)
-        return float(train_step(jb, d))                    # .item(): device->host read of the loss
+        return train_step(jb, d).item()                    # .item(): device->host read of the loss
     ms_e2e, _, _ = timed(e2e_step, max(3, args.steps // 2), 3)
 
     edges_all = torch.tensor([E], device=dev, dtype=torch.float64)

@@ -79,6 +79,10 @@ typedef struct {
   const int32_t* out_ptr; /* [N+1] CSR by source                                         */
   const int32_t* out_dst; /* [E]   destination node of each src-sorted edge              */
   const int32_t* out_pos; /* [E]   position of that edge in the dst-sorted order         */
+  const int32_t* dst_order; /* [N] processing order of destinations (b200gat_node_order on   */
+                            /*     in_ptr/in_src), or NULL = identity.  A permutation: it   */
+                            /*     changes which warps run side by side, never a result.    */
+  const int32_t* src_order; /* [N] same for the source-side backward pass, or NULL          */
 } b200gat_graph;
 
 /* Number of int32 scratch elements b200gat_plan_build needs. */
@@ -93,6 +97,14 @@ int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_dst, int64_t
                        int64_t n_nodes, int32_t* in_ptr, int32_t* in_src, int32_t* in_eid,
                        int32_t* out_ptr, int32_t* out_dst, int32_t* out_pos, int32_t* scratch,
                        int32_t* stats, void* stream);
+
+/* Locality order of the nodes of one CSR side: nodes sorted (stably) by the neighbour in the
+ * middle of their adjacency segment, so that nodes with overlapping neighbourhoods (the tasks of
+ * one machine clique, jssp/utils/utils.py:460-478) are processed by neighbouring warps.
+ * ptr [N+1], nbr [E] (in_ptr/in_src or out_ptr/out_dst) -> order [N]. */
+int64_t b200gat_node_order_scratch_elems(int64_t n_nodes);
+int b200gat_node_order(const int32_t* ptr, const int32_t* nbr, int64_t n_nodes, int32_t* order,
+                       int32_t* scratch, void* stream);
 
 /* out[i] = table[idx[i]] for int32 (permute per-edge attributes into dst-sorted order). */
 int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
@@ -133,10 +145,12 @@ typedef struct {
  *   Pi, Pj, V : [N, H*D] projected node tensors (V may alias Pi: GATv2/GATv3 x_l)
  *   out       : [N, H*D]
  *   s_save    : [E, H] raw logits in dst-sorted order   (saved for backward)
- *   m_save,l_save : [N, H] per-destination max and sum of exp(s-m)                      */
+ *   m_save,l_save : [N, H] per-destination max and sum of exp(s-m)
+ *   agg_save  : [N, H*D] the aggregate WITHOUT out_bias, a private copy for the backward
+ *               (callers add residuals into `out` in place, psp/models/gnn_flat.py:230), or NULL */
 int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                      const float* Pi, const float* Pj, const float* V, float* out,
-                     float* s_save, float* m_save, float* l_save, void* stream);
+                     float* s_save, float* m_save, float* l_save, float* agg_save, void* stream);
 
 /* Matching fused backward (replaces autograd through the ops above).
  *   g_out            : [N, H*D]
@@ -146,10 +160,12 @@ int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200ga
  *   g_attn_bias      : [1] (dot), accumulated; else NULL
  *   g_table          : [T, H*D] accumulated (EDGE_TABLE / EDGE_AFFINE) ; g_dense: [E, H*D]
  *                      written (EDGE_DENSE) ; g_affine: [K, H*D] accumulated (EDGE_AFFINE)
- *   gs_scratch       : [E, H] scratch (dst-sorted order)                                  */
+ *   gs_scratch       : [2, E, H] scratch (dst-sorted order): d loss / d logit, attention weight
+ *   agg_save         : [N, H*D] from the forward, or NULL (then recomputed with one more pass)  */
 int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                      const float* Pi, const float* Pj, const float* V, const float* s_save,
-                     const float* m_save, const float* l_save, const float* g_out, float* gPi,
+                     const float* m_save, const float* l_save, const float* agg_save,
+                     const float* g_out, float* gPi,
                      float* gPj, float* gV, float* g_attn, float* g_attn_bias, float* g_table,
                      float* g_dense, float* g_affine, float* gs_scratch, void* stream);
 

@@ -36,6 +36,8 @@ def check_plan(wb, src, dst, n):
     assert max_in == (int(np.bincount(d, minlength=n).max()) if E else 0)
     assert max_out == (int(np.bincount(s, minlength=n).max()) if E else 0)
     assert bad == 0
+    for order in (plan.dst_order, plan.src_order):           # locality orders are permutations
+        assert np.array_equal(np.sort(order.cpu().numpy()), np.arange(n))
     return plan
 
 
@@ -174,7 +176,7 @@ def test_trunk_and_agent_match_oracle(wb):
     loss_r.backward()
 
     def rel(a, b):
-        return float((a.detach().double().cpu() - b.detach()).abs().max()) / max(float(b.abs().max()), 1e-30)
+        return float((a.detach().double().cpu() - b.detach()).abs().max()) / max(float(b.abs().max()), 1e-3)
     assert rel(lp, lp_r) < 1e-4 and rel(ent, ent_r) < 1e-4 and rel(val, val_r) < 1e-4
     assert rel(loss, loss_r) < 1e-4
     refp = dict(ref.named_parameters())

@@ -16,6 +16,7 @@ FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
 SYMBOLS = (
     "b200gat_last_error", "b200gat_version", "b200gat_launch_count", "b200gat_timing_enable",
     "b200gat_timing_read", "b200gat_plan_scratch_elems", "b200gat_plan_build",
+    "b200gat_node_order_scratch_elems", "b200gat_node_order",
     "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
 )
@@ -24,7 +25,8 @@ SYMBOLS = (
 class Graph(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
                 ("in_ptr", C.c_void_p), ("in_src", C.c_void_p), ("in_eid", C.c_void_p),
-                ("out_ptr", C.c_void_p), ("out_dst", C.c_void_p), ("out_pos", C.c_void_p)]
+                ("out_ptr", C.c_void_p), ("out_dst", C.c_void_p), ("out_pos", C.c_void_p),
+                ("dst_order", C.c_void_p), ("src_order", C.c_void_p)]
 
 
 class Attn(C.Structure):
@@ -61,12 +63,15 @@ def _load():
     lib.b200gat_plan_scratch_elems.restype = i64
     lib.b200gat_plan_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_plan_build.argtypes = [vp, vp, i64, i64] + [vp] * 9
+    lib.b200gat_node_order_scratch_elems.restype = i64
+    lib.b200gat_node_order_scratch_elems.argtypes = [i64]
+    lib.b200gat_node_order.argtypes = [vp, vp, i64, vp, vp, vp]
     lib.b200gat_gather_i32.argtypes = [vp, vp, i64, vp, vp]
     lib.b200gat_gather_rows_f32.argtypes = [vp, vp, i64, i32, vp, vp]
     lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]
     gp, ap, ep = C.POINTER(Graph), C.POINTER(Attn), C.POINTER(EdgeFeats)
-    lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 8
-    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 17
+    lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 9
+    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 18
     lib.b200gat_attention.argtypes = [gp, i32, f32, vp, vp, vp, vp, vp]
     lib.b200gat_edge_out.argtypes = [gp, ap, ep, vp, vp, vp, vp]
     lib.b200gat_mask_head_fwd.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, vp, vp, vp]
@@ -74,7 +79,7 @@ def _load():
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
-                        "b200gat_timing_enable"):
+                        "b200gat_timing_enable", "b200gat_node_order_scratch_elems"):
             fn.restype = C.c_int
     return lib
 

@@ -1,17 +1,508 @@
-// Specialised attention kernels (placeholder until the tuned variants land).
+// Specialised fused graph-attention kernels for the additive flavour (EGAT / GATv2) with
+// H*D in {32,64,128,256} and factored (none / table / affine) edge features - the shapes
+// Wheatley runs (H=4, D=64 default; D=32 in 272.sh).
+//
+// Work decomposition: ONE WARP PER NODE, ALL HEADS.  Lane l owns the VPL = H*D/32 contiguous
+// features [l*VPL, (l+1)*VPL) of a row, so a row gather is one or two 16-byte loads per lane
+// (a full 128-byte line per 4-8 lanes, fully coalesced) and a head is LPH = D/VPL adjacent
+// lanes (a log2(LPH)-step xor-shuffle reduction instead of a 5-step one per head).
+// Nodes are visited in the plan's locality order (b200gat_node_order) so the warps of a CTA
+// work on destinations of the same machine clique and re-use each other's gathered rows in L1.
+//
+//   forward      : single pass over the in-edges with an online (running max / rescale) softmax,
+//                  UNROLL edges in flight; V aliasing Pi (GATv2) is gathered once.
+//   backward dst : per destination: d logit from <G[v], V[u]> and <G[v], agg[v]> (one pass, the
+//                  softmax Jacobian's dot product comes from the saved aggregate), d attn,
+//                  d Pj[v], d edge table (accumulated per type run in registers -> shared -> global)
+//   backward src : per source: d Pi[u], d V[u] over the out-edges (CSR by source), deterministic.
+#include <math.h>
+#include "common.cuh"
 #include "gat_kernels.cuh"
 
 namespace b200gat {
-bool fast_supported(const b200gat_attn*, const b200gat_edge_feats*) { return false; }
-int fast_fwd(const b200gat_graph*, const b200gat_attn*, const b200gat_edge_feats*, const float*,
-             const float*, const float*, float*, float*, float*, float*, cudaStream_t) {
-  set_error("no specialised kernel for this shape");
-  return B200GAT_ERR_UNSUPPORTED;
+
+struct FastArgs {
+  int N, E;
+  const int32_t *in_ptr, *in_src, *out_ptr, *out_dst, *out_pos, *dst_order, *src_order;
+  int H;
+  float slope, eps;
+  const float *attn, *out_bias;
+  int emode, T, K;
+  const float* table;
+  const int32_t* etype;
+  const float* attr;
+  const float* affine;
+};
+
+template <int VPL>
+__device__ __forceinline__ void ldrow(float (&r)[VPL], const float* __restrict__ p) {
+  if constexpr (VPL == 8) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+  } else if constexpr (VPL == 4) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+  } else if constexpr (VPL == 2) {
+    float2 a = __ldg(reinterpret_cast<const float2*>(p));
+    r[0] = a.x; r[1] = a.y;
+  } else {
+    r[0] = __ldg(p);
+  }
 }
-int fast_bwd(const b200gat_graph*, const b200gat_attn*, const b200gat_edge_feats*, const float*,
-             const float*, const float*, const float*, const float*, const float*, const float*,
-             float*, float*, float*, float*, float*, float*, float*, float*, float*, cudaStream_t) {
-  set_error("no specialised kernel for this shape");
-  return B200GAT_ERR_UNSUPPORTED;
+template <int VPL>
+__device__ __forceinline__ void strow(float* __restrict__ p, const float (&r)[VPL]) {
+  if constexpr (VPL == 8) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(r[0], r[1], r[2], r[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(r[4], r[5], r[6], r[7]);
+  } else if constexpr (VPL == 4) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(r[0], r[1], r[2], r[3]);
+  } else if constexpr (VPL == 2) {
+    reinterpret_cast<float2*>(p)[0] = make_float2(r[0], r[1]);
+  } else {
+    p[0] = r[0];
+  }
 }
+template <int LPH>
+__device__ __forceinline__ float head_sum(float v) {
+#pragma unroll
+  for (int o = LPH >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Edge term for the current type: qt = base + table[t]  (base = Pj[v] or Pi[u]).
+template <int VPL>
+__device__ __forceinline__ void type_row(const FastArgs& A, int t, int c0, const float (&base)[VPL],
+                                         float (&qt)[VPL]) {
+  float pe[VPL];
+  ldrow<VPL>(pe, A.table + (int64_t)t * (32 * VPL) + c0);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) qt[i] = base[i] + pe[i];
+}
+// Affine part of the edge term: z += sum_k attr[pos,k] * affine[k]   (warp-uniform branches)
+template <int VPL>
+__device__ __forceinline__ void affine_add(const FastArgs& A, int64_t pos, int c0, float (&z)[VPL]) {
+  for (int k = 0; k < A.K; ++k) {
+    const float av = __ldg(A.attr + pos * A.K + k);
+    if (av != 0.f) {
+      float w[VPL];
+      ldrow<VPL>(w, A.affine + (int64_t)k * (32 * VPL) + c0);
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) z[i] = fmaf(av, w[i], z[i]);
+    }
+  }
+}
+
+constexpr int kFastThreads = 256;
+constexpr int kUnroll = 4;
+
+// ------------------------------------------------------------------------------ forward
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads) k_fwd_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+    float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
+    float* __restrict__ l_save, float* __restrict__ agg_save) {
+  constexpr int HD = 32 * VPL;
+  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
+  if (w >= A.N) return;
+  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  const bool head_lead = (lane % LPH) == 0;
+  const int v = A.dst_order ? A.dst_order[w] : w;
+  const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
+  float q[VPL], at[VPL], qt[VPL], acc[VPL];
+  ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
+  ldrow<VPL>(at, A.attn + c0);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) { qt[i] = q[i]; acc[i] = 0.f; }
+  float m = -INFINITY, l = 0.f;
+  int t_cur = -1;
+  const bool typed = A.emode != B200GAT_EDGE_NONE;
+  const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
+
+  for (int e0 = b; e0 < en; e0 += 32) {
+    const int n = min(32, en - e0);
+    const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
+    const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+    for (int j0 = 0; j0 < n; j0 += kUnroll) {
+      float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL];
+      int tt[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const int idx = min(j0 + k, n - 1);
+        const int u = __shfl_sync(0xffffffffu, my_u, idx);
+        tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+        ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
+        if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
+      }
+      float sc[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const bool valid = j0 + k < n;
+        if (typed && tt[k] != t_cur) {
+          t_cur = tt[k];
+          type_row<VPL>(A, t_cur, c0, q, qt);
+        }
+        float z[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
+        if (affine && valid) affine_add<VPL>(A, e0 + j0 + k, c0, z);
+        float part = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
+        part = head_sum<LPH>(part);
+        if (valid && head_lead) s_save[(int64_t)(e0 + j0 + k) * A.H + h] = part;
+        sc[k] = valid ? part : -INFINITY;
+      }
+      float mnew = m;
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) mnew = fmaxf(mnew, sc[k]);
+      const float scale = __expf(m - mnew);       // m = -inf on the first chunk -> 0
+      l *= scale;
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) acc[i] *= scale;
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const float p = __expf(sc[k] - mnew);     // invalid slot: exp(-inf) = 0
+        l += p;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) acc[i] = fmaf(p, ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], acc[i]);
+      }
+      m = mnew;
+    }
+  }
+  const float inv = en > b ? 1.f / (l + A.eps) : 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] *= inv;
+  if (agg_save) strow<VPL>(agg_save + (int64_t)v * HD + c0, acc);
+  if (A.out_bias) {
+    float ob[VPL];
+    ldrow<VPL>(ob, A.out_bias + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] += ob[i];
+  }
+  strow<VPL>(out + (int64_t)v * HD + c0, acc);
+  if (head_lead) {
+    m_save[(int64_t)v * A.H + h] = en > b ? m : 0.f;
+    l_save[(int64_t)v * A.H + h] = l;
+  }
+}
+
+// ------------------------------------------------------------------------------ backward, by destination
+// Shared memory: sh_gat[HD] (d attn of the CTA) + sh_tab[T][HD] (d edge table of the CTA, when it fits).
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads) k_bwd_dst_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+    const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
+    const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
+    float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
+    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem) {
+  constexpr int HD = 32 * VPL;
+  extern __shared__ float sh[];
+  float* sh_gat = sh;
+  float* sh_tab = sh + HD;
+  const bool typed = A.emode != B200GAT_EDGE_NONE;
+  const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
+  const int n_sh = HD + (tab_in_smem ? A.T * HD : 0);
+  for (int i = threadIdx.x; i < n_sh; i += kFastThreads) sh[i] = 0.f;
+  __syncthreads();
+
+  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  const bool head_lead = (lane % LPH) == 0;
+  if (w < A.N) {
+    const int v = A.dst_order ? A.dst_order[w] : w;
+    const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
+    float q[VPL], at[VPL], qt[VPL], g[VPL], gat[VPL], gpj[VPL], gtab[VPL];
+    ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
+    ldrow<VPL>(at, A.attn + c0);
+    ldrow<VPL>(g, G + (int64_t)v * HD + c0);
+    float dot = 0.f;
+    {
+      float ag[VPL];
+      ldrow<VPL>(ag, agg_save + (int64_t)v * HD + c0);
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) dot = fmaf(g[i], ag[i], dot);
+      dot = head_sum<LPH>(dot);
+    }
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) { qt[i] = q[i]; gat[i] = 0.f; gpj[i] = 0.f; gtab[i] = 0.f; }
+    const float mh = m_save[(int64_t)v * A.H + h];
+    const float linv = en > b ? 1.f / (l_save[(int64_t)v * A.H + h] + A.eps) : 0.f;
+    int t_cur = -1;
+
+    auto flush_tab = [&]() {
+      if (t_cur < 0) return;
+      float* dst = tab_in_smem ? sh_tab + t_cur * HD + c0 : g_table + (int64_t)t_cur * HD + c0;
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        if (gtab[i] != 0.f) atomicAdd(dst + i, gtab[i]);
+        gtab[i] = 0.f;
+      }
+    };
+
+    for (int e0 = b; e0 < en; e0 += 32) {
+      const int n = min(32, en - e0);
+      const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
+      const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+      for (int j0 = 0; j0 < n; j0 += kUnroll) {
+        float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL], sv[kUnroll];
+        int tt[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k) {
+          const int idx = min(j0 + k, n - 1);
+          const int u = __shfl_sync(0xffffffffu, my_u, idx);
+          tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+          ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
+          if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
+          sv[k] = __ldg(s_save + (int64_t)(e0 + idx) * A.H + h);
+        }
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k) {
+          const bool valid = j0 + k < n;
+          const int64_t pos = e0 + j0 + k;
+          float ga = 0.f;
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) ga = fmaf(g[i], ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], ga);
+          ga = head_sum<LPH>(ga);
+          const float alpha = __expf(sv[k] - mh) * linv;
+          float gsv = alpha * (ga - dot);
+          if (valid && head_lead) {
+            gs_out[pos * A.H + h] = gsv;
+            alpha_out[pos * A.H + h] = alpha;
+          }
+          if (!valid) gsv = 0.f;
+          if (typed && tt[k] != t_cur) {
+            flush_tab();
+            t_cur = tt[k];
+            type_row<VPL>(A, t_cur, c0, q, qt);
+          }
+          float z[VPL];
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
+          if (affine && valid) affine_add<VPL>(A, pos, c0, z);
+          float gz[VPL];
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) {
+            const bool posz = z[i] > 0.f;
+            gat[i] = fmaf(gsv, posz ? z[i] : z[i] * A.slope, gat[i]);
+            gz[i] = gsv * (posz ? at[i] : at[i] * A.slope);
+            gpj[i] += gz[i];
+            gtab[i] += gz[i];
+          }
+          if (affine && valid) {
+            for (int kk = 0; kk < A.K; ++kk) {
+              const float av = __ldg(A.attr + pos * A.K + kk);
+              if (av != 0.f) {
+#pragma unroll
+                for (int i = 0; i < VPL; ++i) atomicAdd(g_affine + (int64_t)kk * HD + c0 + i, gz[i] * av);
+              }
+            }
+          }
+        }
+      }
+    }
+    if (typed) flush_tab();
+    strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
+    if (en > b) {
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) atomicAdd(sh_gat + c0 + i, gat[i]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < HD; i += kFastThreads)
+    if (sh_gat[i] != 0.f) atomicAdd(g_attn + i, sh_gat[i]);
+  if (tab_in_smem)
+    for (int i = threadIdx.x; i < A.T * HD; i += kFastThreads)
+      if (sh_tab[i] != 0.f) atomicAdd(g_table + i, sh_tab[i]);
+}
+
+// ------------------------------------------------------------------------------ backward, by source
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads) k_bwd_src_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
+    const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
+    float* __restrict__ gV) {
+  constexpr int HD = 32 * VPL;
+  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
+  if (w >= A.N) return;
+  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  const int u = A.src_order ? A.src_order[w] : w;
+  const int b = A.out_ptr[u], en = A.out_ptr[u + 1];
+  const bool typed = A.emode != B200GAT_EDGE_NONE;
+  const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
+  float p[VPL], at[VPL], ats[VPL], pt[VPL], gpi[VPL], gv[VPL];
+  ldrow<VPL>(p, Pi + (int64_t)u * HD + c0);
+  ldrow<VPL>(at, A.attn + c0);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) { ats[i] = at[i] * A.slope; pt[i] = p[i]; gpi[i] = 0.f; gv[i] = 0.f; }
+  int t_cur = -1;
+  for (int q0 = b; q0 < en; q0 += 32) {
+    const int n = min(32, en - q0);
+    const int my_pos = lane < n ? A.out_pos[q0 + lane] : 0;
+    const int my_v = lane < n ? A.out_dst[q0 + lane] : 0;
+    const int my_t = (typed && lane < n) ? A.etype[my_pos] : 0;
+    for (int j0 = 0; j0 < n; j0 += kUnroll) {
+      float pj[kUnroll][VPL], gg[kUnroll][VPL], gsv[kUnroll], al[kUnroll];
+      int tt[kUnroll], pp[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const int idx = min(j0 + k, n - 1);
+        const int v = __shfl_sync(0xffffffffu, my_v, idx);
+        pp[k] = __shfl_sync(0xffffffffu, my_pos, idx);
+        tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+        ldrow<VPL>(pj[k], Pj + (int64_t)v * HD + c0);
+        ldrow<VPL>(gg[k], G + (int64_t)v * HD + c0);
+        const bool valid = j0 + k < n;
+        gsv[k] = valid ? __ldg(gs_in + (int64_t)pp[k] * A.H + h) : 0.f;
+        al[k] = valid ? __ldg(alpha_in + (int64_t)pp[k] * A.H + h) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const bool valid = j0 + k < n;
+        if (typed && tt[k] != t_cur) {
+          t_cur = tt[k];
+          type_row<VPL>(A, t_cur, c0, p, pt);
+        }
+        float z[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) z[i] = pj[k][i] + pt[i];
+        if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+          gpi[i] = fmaf(gsv[k], z[i] > 0.f ? at[i] : ats[i], gpi[i]);
+          gv[i] = fmaf(al[k], gg[k][i], gv[i]);
+        }
+      }
+    }
+  }
+  if constexpr (ALIAS) {
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) gpi[i] += gv[i];
+    strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
+  } else {
+    strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
+    strow<VPL>(gV + (int64_t)u * HD + c0, gv);
+  }
+}
+
+// ------------------------------------------------------------------------------ dispatch
+static bool shape_of(const b200gat_attn* a, int& vpl, int& lph) {
+  const int HD = a->heads * a->dim;
+  if (HD != 64 && HD != 128 && HD != 256) return false;
+  vpl = HD / 32;
+  if (a->dim % vpl) return false;
+  lph = a->dim / vpl;
+  return lph == 4 || lph == 8 || lph == 16 || lph == 32;
+}
+
+bool fast_supported(const b200gat_attn* a, const b200gat_edge_feats* ef) {
+  if (a->flavour != B200GAT_FLAVOUR_ADDITIVE) return false;
+  const int mode = ef ? ef->mode : B200GAT_EDGE_NONE;
+  if (mode == B200GAT_EDGE_DENSE) return false;
+  if (mode == B200GAT_EDGE_AFFINE && (ef->n_attr < 0 || ef->n_attr > B200GAT_MAX_ATTR)) return false;
+  int vpl, lph;
+  return shape_of(a, vpl, lph);
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef) {
+  B200_CHECK_ARG(g->n_nodes >= 0 && g->n_edges >= 0, "negative graph size");
+  B200_CHECK_ARG(g->n_nodes == 0 || (g->in_ptr && g->out_ptr), "null CSR pointers");
+  B200_CHECK_ARG(g->n_edges == 0 || (g->in_src && g->out_dst && g->out_pos), "null CSR edge arrays");
+  B200_CHECK_ARG(a->attn, "null attn");
+  A.N = g->n_nodes; A.E = g->n_edges;
+  A.in_ptr = g->in_ptr; A.in_src = g->in_src; A.out_ptr = g->out_ptr; A.out_dst = g->out_dst;
+  A.out_pos = g->out_pos; A.dst_order = g->dst_order; A.src_order = g->src_order;
+  A.H = a->heads; A.slope = a->slope; A.eps = a->softmax_eps; A.attn = a->attn; A.out_bias = a->out_bias;
+  A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
+  A.T = ef ? ef->n_types : 0; A.K = ef ? ef->n_attr : 0;
+  A.table = ef ? ef->table : nullptr; A.etype = ef ? ef->etype : nullptr;
+  A.attr = ef ? ef->attr : nullptr; A.affine = ef ? ef->affine : nullptr;
+  if (A.emode != B200GAT_EDGE_NONE)
+    B200_CHECK_ARG(A.table && A.T > 0 && (A.E == 0 || A.etype), "null edge table/etype");
+  if (A.emode == B200GAT_EDGE_AFFINE && A.K > 0)
+    B200_CHECK_ARG(A.affine && (A.E == 0 || A.attr), "null affine edge attributes");
+  return B200GAT_OK;
+}
+
+#define FAST_DISPATCH_LPH(VPL_, lph, ALIAS_, CALL)        \
+  switch (lph) {                                          \
+    case 4: { constexpr int VPL = VPL_, LPH = 4; constexpr bool ALIAS = ALIAS_; CALL; } break;   \
+    case 8: { constexpr int VPL = VPL_, LPH = 8; constexpr bool ALIAS = ALIAS_; CALL; } break;   \
+    case 16: { constexpr int VPL = VPL_, LPH = 16; constexpr bool ALIAS = ALIAS_; CALL; } break; \
+    default: { constexpr int VPL = VPL_, LPH = 32; constexpr bool ALIAS = ALIAS_; CALL; } break; \
+  }
+#define FAST_DISPATCH_VPL(vpl, lph, ALIAS_, CALL)                   \
+  switch (vpl) {                                                    \
+    case 2: FAST_DISPATCH_LPH(2, lph, ALIAS_, CALL) break;          \
+    case 4: FAST_DISPATCH_LPH(4, lph, ALIAS_, CALL) break;          \
+    default: FAST_DISPATCH_LPH(8, lph, ALIAS_, CALL) break;         \
+  }
+#define FAST_DISPATCH(vpl, lph, alias, CALL)                        \
+  if (alias) { FAST_DISPATCH_VPL(vpl, lph, true, CALL) } else { FAST_DISPATCH_VPL(vpl, lph, false, CALL) }
+
+int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef, const float* Pi,
+             const float* Pj, const float* V, float* out, float* s_save, float* m_save, float* l_save,
+             float* agg_save, cudaStream_t st) {
+  int vpl, lph;
+  if (!shape_of(a, vpl, lph) || !aligned16(Pi) || !aligned16(Pj) || !aligned16(V) || !aligned16(out) ||
+      !aligned16(a->attn) || !aligned16(a->out_bias) || !aligned16(agg_save) ||
+      (ef && (!aligned16(ef->table) || !aligned16(ef->affine))))
+    return B200GAT_ERR_UNSUPPORTED;
+  FastArgs A;
+  int rc = fill_fast(A, g, a, ef);
+  if (rc) return rc;
+  if (A.N == 0) return B200GAT_OK;
+  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
+  const bool alias = (V == Pi);
+  ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
+  FAST_DISPATCH(vpl, lph, alias,
+                (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
+                                                                              l_save, agg_save)));
+  B200_CHECK_LAUNCH("k_fwd_fast");
+  return B200GAT_OK;
+}
+
+int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef, const float* Pi,
+             const float* Pj, const float* V, const float* s_save, const float* m_save, const float* l_save,
+             const float* agg_save, const float* g_out, float* gPi, float* gPj, float* gV, float* g_attn,
+             float* g_attn_bias, float* g_table, float* g_dense, float* g_affine, float* gs,
+             cudaStream_t st) {
+  (void)g_attn_bias; (void)g_dense;
+  int vpl, lph;
+  if (!agg_save || !shape_of(a, vpl, lph) || !aligned16(Pi) || !aligned16(Pj) || !aligned16(V) ||
+      !aligned16(g_out) || !aligned16(gPi) || !aligned16(gPj) || !aligned16(gV) || !aligned16(a->attn) ||
+      !aligned16(agg_save) || (ef && (!aligned16(ef->table) || !aligned16(ef->affine))))
+    return B200GAT_ERR_UNSUPPORTED;
+  FastArgs A;
+  int rc = fill_fast(A, g, a, ef);
+  if (rc) return rc;
+  if (A.emode != B200GAT_EDGE_NONE) B200_CHECK_ARG(g_table, "null g_table");
+  if (A.emode == B200GAT_EDGE_AFFINE && A.K > 0) B200_CHECK_ARG(g_affine, "null g_affine");
+  if (A.N == 0) return B200GAT_OK;
+  const int HD = 32 * vpl;
+  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
+  const bool alias = (V == Pi);
+  B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
+  const int tab_in_smem = (A.emode != B200GAT_EDGE_NONE && (int64_t)A.T * HD * 4 <= 40 * 1024) ? 1 : 0;
+  const size_t smem = sizeof(float) * (HD + (tab_in_smem ? (size_t)A.T * HD : 0));
+  float* alpha = gs + (int64_t)A.E * A.H;
+  {
+    ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
+    FAST_DISPATCH(vpl, lph, alias,
+                  (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
+                      A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
+                      gs, alpha, tab_in_smem)));
+  }
+  {
+    ScopedTimer tm(B200GAT_TIMING_CONV_BWD_SRC, st);
+    FAST_DISPATCH(vpl, lph, alias,
+                  (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
+                                                                                   gPi, gV)));
+  }
+  B200_CHECK_LAUNCHES("k_bwd_fast", 2);
+  return B200GAT_OK;
+}
+
 }  // namespace b200gat

@@ -47,7 +47,8 @@ __global__ void __launch_bounds__(128) k_fwd_generic(GenericArgs A, const float*
                                                      const float* __restrict__ Pj,
                                                      const float* __restrict__ V,
                                                      float* __restrict__ out, float* __restrict__ s_save,
-                                                     float* __restrict__ m_save, float* __restrict__ l_save) {
+                                                     float* __restrict__ m_save, float* __restrict__ l_save,
+                                                     float* __restrict__ agg_save) {
   const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (wid >= (int64_t)A.N * A.H) return;
@@ -104,6 +105,7 @@ __global__ void __launch_bounds__(128) k_fwd_generic(GenericArgs A, const float*
     int d = lane + 32 * k;
     if (d < A.D) {
       float o = acc[k] * inv;
+      if (agg_save) agg_save[(int64_t)v * HD + hoff + d] = o;
       if (A.out_bias) o += A.out_bias[hoff + d];
       out[(int64_t)v * HD + hoff + d] = o;
     }
@@ -322,7 +324,7 @@ static int fill_args(GenericArgs& A, const b200gat_graph* g, const b200gat_attn*
 
 int generic_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                 const float* Pi, const float* Pj, const float* V, float* out, float* s_save,
-                float* m_save, float* l_save, cudaStream_t st) {
+                float* m_save, float* l_save, float* agg_save, cudaStream_t st) {
   GenericArgs A;
   int rc = fill_args(A, g, a, ef);
   if (rc) return rc;
@@ -334,9 +336,9 @@ int generic_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
   unsigned blocks = (unsigned)ceil_div((int64_t)A.N * A.H * 32, 128);
   ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
   if (a->flavour == B200GAT_FLAVOUR_ADDITIVE)
-    k_fwd_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save);
+    k_fwd_generic<B200GAT_FLAVOUR_ADDITIVE><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save);
   else
-    k_fwd_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save);
+    k_fwd_generic<B200GAT_FLAVOUR_DOT><<<blocks, 128, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save);
   B200_CHECK_LAUNCH("k_fwd_generic");
   return B200GAT_OK;
 }

@@ -226,6 +226,28 @@ __global__ void k_degree_stats(const int32_t* __restrict__ in_ptr,
   }
 }
 
+// ---- locality order of the nodes --------------------------------------------------------
+// key[v] = neighbour at the middle of v's adjacency segment (v itself when the segment is
+// empty).  Nodes whose neighbourhoods overlap heavily (members of one machine clique) get
+// nearly equal keys, so sorting the nodes by key puts them next to each other and the warps of
+// one CTA then gather the same rows (L1 hits instead of L2 round trips).
+__global__ void k_order_key(const int32_t* __restrict__ ptr, const int32_t* __restrict__ nbr, int32_t N,
+                            int32_t* __restrict__ key, int32_t* __restrict__ hist) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  int b = ptr[v], e = ptr[v + 1];
+  int k = e > b ? nbr[b + ((e - b) >> 1)] : v;
+  key[v] = k;
+  atomicAdd(&hist[k + 1], 1);
+}
+__global__ void k_order_fill(const int32_t* __restrict__ key, int32_t N, const int32_t* __restrict__ hist,
+                             int32_t* __restrict__ fill, int32_t* __restrict__ tmp) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  int k = key[v];
+  tmp[hist[k] + atomicAdd(&fill[k], 1)] = v;
+}
+
 __global__ void k_gather_i32(const int32_t* __restrict__ table, const int32_t* __restrict__ idx,
                              int64_t n, int32_t* __restrict__ out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -328,6 +350,38 @@ extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_d
     k_degree_stats<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(in_ptr, out_ptr, (int32_t)N, stats);
     B200_CHECK_LAUNCH("k_degree_stats");
   }
+  return B200GAT_OK;
+}
+
+extern "C" int64_t b200gat_node_order_scratch_elems(int64_t N) {
+  int64_t nb = ceil_div(N + 1, kScanTile) + 1;
+  return 5 * N + nb + 72;
+}
+
+extern "C" int b200gat_node_order(const int32_t* ptr, const int32_t* nbr, int64_t N, int32_t* order,
+                                  int32_t* scratch, void* stream) {
+  B200_CHECK_ARG(N >= 0, "negative size");
+  if (N == 0) return B200GAT_OK;
+  B200_CHECK_ARG(ptr && order && scratch, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  ScopedTimer tm(B200GAT_TIMING_PLAN, st);
+  int64_t nb = ceil_div(N + 1, kScanTile) + 1;
+  int32_t* key = scratch;
+  int32_t* hist = key + N;          // [N+1]
+  int32_t* fill = hist + N + 1;     // [N]
+  int32_t* tmp = fill + N;          // [N]
+  int32_t* large = tmp + N;         // [N]
+  int32_t* bsum = large + N;        // [nb]
+  int32_t* counter = bsum + nb;     // [1]
+  cudaMemsetAsync(hist, 0, sizeof(int32_t) * (2 * N + 1), st);   // hist + fill
+  cudaMemsetAsync(counter, 0, sizeof(int32_t) * 8, st);
+  unsigned nbk = (unsigned)ceil_div(N, 256);
+  k_order_key<<<nbk, 256, 0, st>>>(ptr, nbr, (int32_t)N, key, hist);
+  scan_inplace(hist, N + 1, bsum, st);
+  k_order_fill<<<nbk, 256, 0, st>>>(key, (int32_t)N, hist, fill, tmp);
+  k_sort_small<<<(unsigned)ceil_div(N * 32, 256), 256, 0, st>>>(hist, (int32_t)N, tmp, order, large, counter);
+  k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(hist, tmp, order, large, counter);
+  B200_CHECK_LAUNCHES("b200gat_node_order", 4);
   return B200GAT_OK;
 }
 

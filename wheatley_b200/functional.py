@@ -79,6 +79,8 @@ class _FusedGATConv(torch.autograd.Function):
         s = torch.empty((E, H), dtype=torch.float32, device=Pi.device)
         m = torch.empty((N, H), dtype=torch.float32, device=Pi.device)
         l = torch.empty((N, H), dtype=torch.float32, device=Pi.device)
+        need_grad = any(ctx.needs_input_grad)
+        agg = torch.empty((N, HD), dtype=torch.float32, device=Pi.device) if need_grad else None
         a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
                       _lib.ptr(attn_bias_c), _lib.ptr(out_bias_c))
         ef = _lib.EdgeFeats(mode, 0 if e_table_c is None else e_table_c.shape[0],
@@ -87,18 +89,18 @@ class _FusedGATConv(torch.autograd.Function):
         with torch.cuda.device(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_fwd(plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
                                                  _lib.ptr(out), _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
-                                                 _lib.stream_ptr()), "b200gat_conv_fwd")
+                                                 _lib.ptr(agg), _lib.stream_ptr()), "b200gat_conv_fwd")
         ctx.plan, ctx.cfg, ctx.mode, ctx.v_alias = plan, cfg, mode, v_alias
         ctx.etype_sorted, ctx.attr_sorted = etype_sorted, attr_sorted
         ctx.has_out_bias = out_bias is not None
         ctx.attn_shape = attn.shape
-        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l)
+        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg)
         ctx.mark_non_differentiable(s, m, l)
         return out, s, m, l
 
     @staticmethod
     def backward(ctx, g_out, _gs, _gm, _gl):
-        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l = ctx.saved_tensors
+        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg = ctx.saved_tensors
         plan, cfg = ctx.plan, ctx.cfg
         H, D = cfg["heads"], cfg["dim"]
         g_out = _f32c(g_out)
@@ -110,7 +112,7 @@ class _FusedGATConv(torch.autograd.Function):
         g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None
         g_dense = torch.empty_like(e_dense_c) if e_dense_c is not None else None
         g_affine = torch.zeros_like(e_affine_c) if e_affine_c is not None else None
-        gs = torch.empty_like(s)
+        gs = torch.empty((2,) + tuple(s.shape), dtype=s.dtype, device=s.device)
         a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
                       _lib.ptr(attn_bias_c), None)
         ef = _lib.EdgeFeats(ctx.mode, 0 if e_table_c is None else e_table_c.shape[0],
@@ -120,7 +122,7 @@ class _FusedGATConv(torch.autograd.Function):
         with torch.cuda.device(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_bwd(
                 plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
-                _lib.ptr(l), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj), _lib.ptr(gV),
+                _lib.ptr(l), _lib.ptr(agg), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj), _lib.ptr(gV),
                 _lib.ptr(g_attn), _lib.ptr(g_attn_bias), _lib.ptr(g_table), _lib.ptr(g_dense),
                 _lib.ptr(g_affine), _lib.ptr(gs), _lib.stream_ptr()), "b200gat_conv_bwd")
         g_bias = g_out.sum(0) if ctx.has_out_bias else None

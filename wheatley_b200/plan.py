@@ -37,9 +37,19 @@ class GraphPlan:
                 _lib.ptr(self.in_eid), _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst),
                 _lib.ptr(self.out_pos), _lib.ptr(scratch), _lib.ptr(self.stats),
                 _lib.stream_ptr()), "b200gat_plan_build")
+            # locality order of destinations / sources (a permutation: affects scheduling only)
+            self.dst_order = torch.empty(N, **i32)
+            self.src_order = torch.empty(N, **i32)
+            oscr = torch.empty(_lib.lib.b200gat_node_order_scratch_elems(N), **i32)
+            for ptr_, nbr_, out_ in ((self.in_ptr, self.in_src, self.dst_order),
+                                     (self.out_ptr, self.out_dst, self.src_order)):
+                _lib.check(_lib.lib.b200gat_node_order(_lib.ptr(ptr_), _lib.ptr(nbr_), N, _lib.ptr(out_),
+                                                       _lib.ptr(oscr), _lib.stream_ptr()),
+                           "b200gat_node_order")
         self._stats_host = None
         self._c = _lib.Graph(N, E, _lib.ptr(self.in_ptr), _lib.ptr(self.in_src), _lib.ptr(self.in_eid),
-                             _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst), _lib.ptr(self.out_pos))
+                             _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst), _lib.ptr(self.out_pos),
+                             _lib.ptr(self.dst_order), _lib.ptr(self.src_order))
         self._sorted_cache = {}
 
     @classmethod
