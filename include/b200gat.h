@@ -83,6 +83,14 @@ typedef struct {
                             /*     in_ptr/in_src), or NULL = identity.  A permutation: it   */
                             /*     changes which warps run side by side, never a result.    */
   const int32_t* src_order; /* [N] same for the source-side backward pass, or NULL          */
+  /* Hub nodes: adjacency segments longer than hub_degree are split over the warps of a CTA    */
+  /* (the learned pooling node of a 100x20 schedule graph has 2,000 in-edges,                   */
+  /* jssp/models/gnn_dgl.py:263-286).  Lists built by b200gat_hub_lists; NULL = no splitting.  */
+  int32_t hub_degree;
+  const int32_t* hub_dst;   /* [<=N] destinations with in-degree  > hub_degree               */
+  const int32_t* n_hub_dst; /* [1]   device-side count                                       */
+  const int32_t* hub_src;   /* [<=N] sources with out-degree > hub_degree                    */
+  const int32_t* n_hub_src; /* [1]                                                           */
 } b200gat_graph;
 
 /* Number of int32 scratch elements b200gat_plan_build needs. */
@@ -105,6 +113,10 @@ int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_dst, int64_t
 int64_t b200gat_node_order_scratch_elems(int64_t n_nodes);
 int b200gat_node_order(const int32_t* ptr, const int32_t* nbr, int64_t n_nodes, int32_t* order,
                        int32_t* scratch, void* stream);
+
+/* Nodes whose adjacency segment is longer than `hub_degree`: list [<=N] + device count [1]. */
+int b200gat_hub_list(const int32_t* ptr, int64_t n_nodes, int32_t hub_degree, int32_t* list,
+                     int32_t* count, void* stream);
 
 /* out[i] = table[idx[i]] for int32 (permute per-edge attributes into dst-sorted order). */
 int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,

@@ -10,13 +10,14 @@ LIB_PATH = os.path.join(_HERE, "libb200gat.so")
 
 EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
 MAX_ATTR = 8
+HUB_DEGREE = 256
 FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
 
 # every symbol include/b200gat.h declares (tests check that the library exports all of them)
 SYMBOLS = (
     "b200gat_last_error", "b200gat_version", "b200gat_launch_count", "b200gat_timing_enable",
     "b200gat_timing_read", "b200gat_plan_scratch_elems", "b200gat_plan_build",
-    "b200gat_node_order_scratch_elems", "b200gat_node_order",
+    "b200gat_node_order_scratch_elems", "b200gat_node_order", "b200gat_hub_list",
     "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
 )
@@ -26,7 +27,9 @@ class Graph(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
                 ("in_ptr", C.c_void_p), ("in_src", C.c_void_p), ("in_eid", C.c_void_p),
                 ("out_ptr", C.c_void_p), ("out_dst", C.c_void_p), ("out_pos", C.c_void_p),
-                ("dst_order", C.c_void_p), ("src_order", C.c_void_p)]
+                ("dst_order", C.c_void_p), ("src_order", C.c_void_p),
+                ("hub_degree", C.c_int32), ("hub_dst", C.c_void_p), ("n_hub_dst", C.c_void_p),
+                ("hub_src", C.c_void_p), ("n_hub_src", C.c_void_p)]
 
 
 class Attn(C.Structure):
@@ -66,6 +69,7 @@ def _load():
     lib.b200gat_node_order_scratch_elems.restype = i64
     lib.b200gat_node_order_scratch_elems.argtypes = [i64]
     lib.b200gat_node_order.argtypes = [vp, vp, i64, vp, vp, vp]
+    lib.b200gat_hub_list.argtypes = [vp, i64, i32, vp, vp, vp]
     lib.b200gat_gather_i32.argtypes = [vp, vp, i64, vp, vp]
     lib.b200gat_gather_rows_f32.argtypes = [vp, vp, i64, i32, vp, vp]
     lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]

@@ -24,6 +24,8 @@ namespace b200gat {
 struct FastArgs {
   int N, E;
   const int32_t *in_ptr, *in_src, *out_ptr, *out_dst, *out_pos, *dst_order, *src_order;
+  const int32_t *hub_dst, *n_hub_dst, *hub_src, *n_hub_src;
+  int hub_degree, hub_blocks;   // hub_blocks = 0 disables segment splitting
   int H;
   float slope, eps;
   const float *attn, *out_bias;
@@ -94,110 +96,191 @@ __device__ __forceinline__ void affine_add(const FastArgs& A, int64_t pos, int c
 }
 
 constexpr int kFastThreads = 256;
+constexpr int kWarps = kFastThreads / 32;
+constexpr int kHubBlocks = 64;   // CTAs at the front of the grid that walk the hub list
 constexpr int kUnroll = 4;
+
+// Work assignment shared by the three kernels.  Blocks [0, hub_blocks) walk the hub list: the
+// whole CTA takes one hub node at a time and each warp a contiguous slice of its adjacency
+// segment.  The other blocks take one node per warp (in the locality order) and skip hubs.
+struct WorkItem {
+  int node, rb, re, seg_b, seg_e;
+  bool active;
+};
+__device__ __forceinline__ WorkItem hub_item(const int32_t* __restrict__ ptr, int node, int wi) {
+  WorkItem it;
+  it.node = node;
+  it.seg_b = ptr[node];
+  it.seg_e = ptr[node + 1];
+  const int per = (((it.seg_e - it.seg_b) + kWarps - 1) / kWarps + kUnroll - 1) & ~(kUnroll - 1);
+  it.rb = min(it.seg_e, it.seg_b + wi * per);
+  it.re = min(it.seg_e, it.rb + per);
+  it.active = true;
+  return it;
+}
+__device__ __forceinline__ WorkItem node_item(const FastArgs& A, const int32_t* __restrict__ ptr,
+                                              const int32_t* __restrict__ order, int wi) {
+  WorkItem it;
+  const int w = (blockIdx.x - A.hub_blocks) * kWarps + wi;
+  it.active = w < A.N;
+  it.node = 0; it.seg_b = it.seg_e = 0;
+  if (it.active) {
+    it.node = order ? order[w] : w;
+    it.seg_b = ptr[it.node];
+    it.seg_e = ptr[it.node + 1];
+    if (A.hub_blocks > 0 && it.seg_e - it.seg_b > A.hub_degree) it.active = false;   // a hub CTA has it
+  }
+  it.rb = it.seg_b;
+  it.re = it.seg_e;
+  return it;
+}
 
 // ------------------------------------------------------------------------------ forward
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads) k_fwd_fast(
+__global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
     float* __restrict__ l_save, float* __restrict__ agg_save) {
   constexpr int HD = 32 * VPL;
-  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
-  if (w >= A.N) return;
-  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  __shared__ float sm_acc[kWarps][HD];
+  __shared__ float sm_m[kWarps][32], sm_l[kWarps][32];
+  const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
   const bool head_lead = (lane % LPH) == 0;
-  const int v = A.dst_order ? A.dst_order[w] : w;
-  const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
-  float q[VPL], at[VPL], qt[VPL], acc[VPL];
-  ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
-  ldrow<VPL>(at, A.attn + c0);
-#pragma unroll
-  for (int i = 0; i < VPL; ++i) { qt[i] = q[i]; acc[i] = 0.f; }
-  float m = -INFINITY, l = 0.f;
-  int t_cur = -1;
+  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
+  const int n_items = hub_block ? *A.n_hub_dst : 1;
+  float at[VPL];
+  ldrow<VPL>(at, A.attn + c0);
 
-  for (int e0 = b; e0 < en; e0 += 32) {
-    const int n = min(32, en - e0);
-    const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
-    const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
-    for (int j0 = 0; j0 < n; j0 += kUnroll) {
-      float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL];
-      int tt[kUnroll];
+  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item], wi)
+                                  : node_item(A, A.in_ptr, A.dst_order, wi);
+    const int v = it.node;
+    float acc[VPL];
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        const int idx = min(j0 + k, n - 1);
-        const int u = __shfl_sync(0xffffffffu, my_u, idx);
-        tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
-        ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
-        if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
-      }
-      float sc[kUnroll];
+    for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+    float m = -INFINITY, l = 0.f;
+    if (it.active && it.re > it.rb) {
+      float q[VPL], qt[VPL];
+      ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        const bool valid = j0 + k < n;
-        if (typed && tt[k] != t_cur) {
-          t_cur = tt[k];
-          type_row<VPL>(A, t_cur, c0, q, qt);
+      for (int i = 0; i < VPL; ++i) qt[i] = q[i];
+      int t_cur = -1;
+      for (int e0 = it.rb; e0 < it.re; e0 += 32) {
+        const int n = min(32, it.re - e0);
+        const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
+        const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+        for (int j0 = 0; j0 < n; j0 += kUnroll) {
+          float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL];
+          int tt[kUnroll];
+#pragma unroll
+          for (int k = 0; k < kUnroll; ++k) {
+            const int idx = min(j0 + k, n - 1);
+            const int u = __shfl_sync(0xffffffffu, my_u, idx);
+            tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+            ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
+            if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
+          }
+          float sc[kUnroll];
+#pragma unroll
+          for (int k = 0; k < kUnroll; ++k) {
+            const bool valid = j0 + k < n;
+            if (typed && tt[k] != t_cur) {
+              t_cur = tt[k];
+              type_row<VPL>(A, t_cur, c0, q, qt);
+            }
+            float z[VPL];
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
+            if (affine && valid) affine_add<VPL>(A, e0 + j0 + k, c0, z);
+            float part = 0.f;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
+            part = head_sum<LPH>(part);
+            if (valid && head_lead) s_save[(int64_t)(e0 + j0 + k) * A.H + h] = part;
+            sc[k] = valid ? part : -INFINITY;
+          }
+          float mnew = m;
+#pragma unroll
+          for (int k = 0; k < kUnroll; ++k) mnew = fmaxf(mnew, sc[k]);
+          const float scale = __expf(m - mnew);       // m = -inf on the first chunk -> 0
+          l *= scale;
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) acc[i] *= scale;
+#pragma unroll
+          for (int k = 0; k < kUnroll; ++k) {
+            const float p = __expf(sc[k] - mnew);     // invalid slot: exp(-inf) = 0
+            l += p;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) acc[i] = fmaf(p, ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], acc[i]);
+          }
+          m = mnew;
         }
-        float z[VPL];
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-        if (affine && valid) affine_add<VPL>(A, e0 + j0 + k, c0, z);
-        float part = 0.f;
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
-        part = head_sum<LPH>(part);
-        if (valid && head_lead) s_save[(int64_t)(e0 + j0 + k) * A.H + h] = part;
-        sc[k] = valid ? part : -INFINITY;
       }
-      float mnew = m;
-#pragma unroll
-      for (int k = 0; k < kUnroll; ++k) mnew = fmaxf(mnew, sc[k]);
-      const float scale = __expf(m - mnew);       // m = -inf on the first chunk -> 0
-      l *= scale;
-#pragma unroll
-      for (int i = 0; i < VPL; ++i) acc[i] *= scale;
-#pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        const float p = __expf(sc[k] - mnew);     // invalid slot: exp(-inf) = 0
-        l += p;
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) acc[i] = fmaf(p, ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], acc[i]);
-      }
-      m = mnew;
     }
-  }
-  const float inv = en > b ? 1.f / (l + A.eps) : 0.f;
+    bool finalize = it.active;
+    if (hub_block) {                       // merge the warps' partial softmax states in warp order
+      strow<VPL>(&sm_acc[wi][c0], acc);
+      sm_m[wi][lane] = m;
+      sm_l[wi][lane] = l;
+      __syncthreads();
+      finalize = wi == 0;
+      if (finalize) {
+        float M = -INFINITY;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) acc[i] *= inv;
-  if (agg_save) strow<VPL>(agg_save + (int64_t)v * HD + c0, acc);
-  if (A.out_bias) {
-    float ob[VPL];
-    ldrow<VPL>(ob, A.out_bias + c0);
+        for (int w2 = 0; w2 < kWarps; ++w2) M = fmaxf(M, sm_m[w2][lane]);
+        l = 0.f;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) acc[i] += ob[i];
-  }
-  strow<VPL>(out + (int64_t)v * HD + c0, acc);
-  if (head_lead) {
-    m_save[(int64_t)v * A.H + h] = en > b ? m : 0.f;
-    l_save[(int64_t)v * A.H + h] = l;
+        for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+        for (int w2 = 0; w2 < kWarps; ++w2) {
+          const float f = __expf(sm_m[w2][lane] - M);   // empty slice: exp(-inf) = 0
+          l = fmaf(sm_l[w2][lane], f, l);
+          float pa[VPL];
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) pa[i] = sm_acc[w2][c0 + i];
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) acc[i] = fmaf(pa[i], f, acc[i]);
+        }
+        m = M;
+      }
+      __syncthreads();
+    }
+    if (finalize) {
+      const bool any = it.seg_e > it.seg_b;
+      const float inv = any ? 1.f / (l + A.eps) : 0.f;
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) acc[i] *= inv;
+      if (agg_save) strow<VPL>(agg_save + (int64_t)v * HD + c0, acc);
+      if (A.out_bias) {
+        float ob[VPL];
+        ldrow<VPL>(ob, A.out_bias + c0);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) acc[i] += ob[i];
+      }
+      strow<VPL>(out + (int64_t)v * HD + c0, acc);
+      if (head_lead) {
+        m_save[(int64_t)v * A.H + h] = any ? m : 0.f;
+        l_save[(int64_t)v * A.H + h] = l;
+      }
+    }
   }
 }
 
 // ------------------------------------------------------------------------------ backward, by destination
-// Shared memory: sh_gat[HD] (d attn of the CTA) + sh_tab[T][HD] (d edge table of the CTA, when it fits).
+// Dynamic shared memory: sh_gat[HD] (d attn of the CTA) + sh_tab[T][HD] (d edge table of the CTA,
+// when it fits).  Static: per-warp partial d Pj rows for the hub merge.
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads) k_bwd_dst_fast(
+__global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
     const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
     float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
     float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem) {
   constexpr int HD = 32 * VPL;
+  constexpr int U = 2;                      // edges in flight (register budget: 128/thread)
   extern __shared__ float sh[];
+  __shared__ float sm_part[kWarps][HD];
   float* sh_gat = sh;
   float* sh_tab = sh + HD;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
@@ -206,108 +289,131 @@ __global__ void __launch_bounds__(kFastThreads) k_bwd_dst_fast(
   for (int i = threadIdx.x; i < n_sh; i += kFastThreads) sh[i] = 0.f;
   __syncthreads();
 
-  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
   const bool head_lead = (lane % LPH) == 0;
-  if (w < A.N) {
-    const int v = A.dst_order ? A.dst_order[w] : w;
-    const int b = A.in_ptr[v], en = A.in_ptr[v + 1];
-    float q[VPL], at[VPL], qt[VPL], g[VPL], gat[VPL], gpj[VPL], gtab[VPL];
-    ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
-    ldrow<VPL>(at, A.attn + c0);
-    ldrow<VPL>(g, G + (int64_t)v * HD + c0);
-    float dot = 0.f;
-    {
-      float ag[VPL];
-      ldrow<VPL>(ag, agg_save + (int64_t)v * HD + c0);
+  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
+  const int n_items = hub_block ? *A.n_hub_dst : 1;
+  float at[VPL], gat[VPL];
+  ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) dot = fmaf(g[i], ag[i], dot);
-      dot = head_sum<LPH>(dot);
-    }
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) { qt[i] = q[i]; gat[i] = 0.f; gpj[i] = 0.f; gtab[i] = 0.f; }
-    const float mh = m_save[(int64_t)v * A.H + h];
-    const float linv = en > b ? 1.f / (l_save[(int64_t)v * A.H + h] + A.eps) : 0.f;
-    int t_cur = -1;
+  for (int i = 0; i < VPL; ++i) gat[i] = 0.f;
 
-    auto flush_tab = [&]() {
-      if (t_cur < 0) return;
-      float* dst = tab_in_smem ? sh_tab + t_cur * HD + c0 : g_table + (int64_t)t_cur * HD + c0;
+  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item], wi)
+                                  : node_item(A, A.in_ptr, A.dst_order, wi);
+    const int v = it.node;
+    float gpj[VPL];
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
-        if (gtab[i] != 0.f) atomicAdd(dst + i, gtab[i]);
-        gtab[i] = 0.f;
+    for (int i = 0; i < VPL; ++i) gpj[i] = 0.f;
+    if (it.active && it.re > it.rb) {
+      float q[VPL], qt[VPL], g[VPL], gtab[VPL];
+      ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
+      ldrow<VPL>(g, G + (int64_t)v * HD + c0);
+      float dot = 0.f;
+      {
+        float ag[VPL];
+        ldrow<VPL>(ag, agg_save + (int64_t)v * HD + c0);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) dot = fmaf(g[i], ag[i], dot);
+        dot = head_sum<LPH>(dot);
       }
-    };
-
-    for (int e0 = b; e0 < en; e0 += 32) {
-      const int n = min(32, en - e0);
-      const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
-      const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
-      for (int j0 = 0; j0 < n; j0 += kUnroll) {
-        float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL], sv[kUnroll];
-        int tt[kUnroll];
 #pragma unroll
-        for (int k = 0; k < kUnroll; ++k) {
-          const int idx = min(j0 + k, n - 1);
-          const int u = __shfl_sync(0xffffffffu, my_u, idx);
-          tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
-          ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
-          if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
-          sv[k] = __ldg(s_save + (int64_t)(e0 + idx) * A.H + h);
+      for (int i = 0; i < VPL; ++i) { qt[i] = q[i]; gtab[i] = 0.f; }
+      const float mh = m_save[(int64_t)v * A.H + h];
+      const float linv = 1.f / (l_save[(int64_t)v * A.H + h] + A.eps);
+      int t_cur = -1;
+      auto flush_tab = [&]() {
+        if (t_cur < 0) return;
+        float* dst = tab_in_smem ? sh_tab + t_cur * HD + c0 : g_table + (int64_t)t_cur * HD + c0;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+          if (gtab[i] != 0.f) atomicAdd(dst + i, gtab[i]);
+          gtab[i] = 0.f;
         }
+      };
+      for (int e0 = it.rb; e0 < it.re; e0 += 32) {
+        const int n = min(32, it.re - e0);
+        const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
+        const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+        for (int j0 = 0; j0 < n; j0 += U) {
+          float pi[U][VPL], vv[ALIAS ? 1 : U][VPL], sv[U];
+          int tt[U];
 #pragma unroll
-        for (int k = 0; k < kUnroll; ++k) {
-          const bool valid = j0 + k < n;
-          const int64_t pos = e0 + j0 + k;
-          float ga = 0.f;
-#pragma unroll
-          for (int i = 0; i < VPL; ++i) ga = fmaf(g[i], ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], ga);
-          ga = head_sum<LPH>(ga);
-          const float alpha = __expf(sv[k] - mh) * linv;
-          float gsv = alpha * (ga - dot);
-          if (valid && head_lead) {
-            gs_out[pos * A.H + h] = gsv;
-            alpha_out[pos * A.H + h] = alpha;
+          for (int k = 0; k < U; ++k) {
+            const int idx = min(j0 + k, n - 1);
+            const int u = __shfl_sync(0xffffffffu, my_u, idx);
+            tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+            ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
+            if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
+            sv[k] = __ldg(s_save + (int64_t)(e0 + idx) * A.H + h);
           }
-          if (!valid) gsv = 0.f;
-          if (typed && tt[k] != t_cur) {
-            flush_tab();
-            t_cur = tt[k];
-            type_row<VPL>(A, t_cur, c0, q, qt);
-          }
-          float z[VPL];
 #pragma unroll
-          for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-          if (affine && valid) affine_add<VPL>(A, pos, c0, z);
-          float gz[VPL];
+          for (int k = 0; k < U; ++k) {
+            const bool valid = j0 + k < n;
+            const int64_t pos = e0 + j0 + k;
+            float ga = 0.f;
 #pragma unroll
-          for (int i = 0; i < VPL; ++i) {
-            const bool posz = z[i] > 0.f;
-            gat[i] = fmaf(gsv, posz ? z[i] : z[i] * A.slope, gat[i]);
-            gz[i] = gsv * (posz ? at[i] : at[i] * A.slope);
-            gpj[i] += gz[i];
-            gtab[i] += gz[i];
-          }
-          if (affine && valid) {
-            for (int kk = 0; kk < A.K; ++kk) {
-              const float av = __ldg(A.attr + pos * A.K + kk);
-              if (av != 0.f) {
+            for (int i = 0; i < VPL; ++i) ga = fmaf(g[i], ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], ga);
+            ga = head_sum<LPH>(ga);
+            const float alpha = __expf(sv[k] - mh) * linv;
+            float gsv = alpha * (ga - dot);
+            if (valid && head_lead) {
+              gs_out[pos * A.H + h] = gsv;
+              alpha_out[pos * A.H + h] = alpha;
+            }
+            if (!valid) gsv = 0.f;
+            if (typed && tt[k] != t_cur) {
+              flush_tab();
+              t_cur = tt[k];
+              type_row<VPL>(A, t_cur, c0, q, qt);
+            }
+            float z[VPL];
 #pragma unroll
-                for (int i = 0; i < VPL; ++i) atomicAdd(g_affine + (int64_t)kk * HD + c0 + i, gz[i] * av);
+            for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
+            if (affine && valid) affine_add<VPL>(A, pos, c0, z);
+            float gz[VPL];
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+              const bool posz = z[i] > 0.f;
+              gat[i] = fmaf(gsv, posz ? z[i] : z[i] * A.slope, gat[i]);
+              gz[i] = gsv * (posz ? at[i] : at[i] * A.slope);
+              gpj[i] += gz[i];
+              gtab[i] += gz[i];
+            }
+            if (affine && valid) {
+              for (int kk = 0; kk < A.K; ++kk) {
+                const float av = __ldg(A.attr + pos * A.K + kk);
+                if (av != 0.f) {
+#pragma unroll
+                  for (int i = 0; i < VPL; ++i) atomicAdd(g_affine + (int64_t)kk * HD + c0 + i, gz[i] * av);
+                }
               }
             }
           }
         }
       }
+      if (typed) flush_tab();
     }
-    if (typed) flush_tab();
-    strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
-    if (en > b) {
+    if (hub_block) {                       // ordered sum of the warps' partial d Pj rows
+      strow<VPL>(&sm_part[wi][c0], gpj);
+      __syncthreads();
+      if (wi == 0) {
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) atomicAdd(sh_gat + c0 + i, gat[i]);
+        for (int i = 0; i < VPL; ++i) gpj[i] = 0.f;
+        for (int w2 = 0; w2 < kWarps; ++w2) {
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) gpj[i] += sm_part[w2][c0 + i];
+        }
+        strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
+      }
+      __syncthreads();
+    } else if (it.active) {
+      strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
     }
   }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i)
+    if (gat[i] != 0.f) atomicAdd(sh_gat + c0 + i, gat[i]);
   __syncthreads();
   for (int i = threadIdx.x; i < HD; i += kFastThreads)
     if (sh_gat[i] != 0.f) atomicAdd(g_attn + i, sh_gat[i]);
@@ -318,70 +424,101 @@ __global__ void __launch_bounds__(kFastThreads) k_bwd_dst_fast(
 
 // ------------------------------------------------------------------------------ backward, by source
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads) k_bwd_src_fast(
+__global__ void __launch_bounds__(kFastThreads, 2) k_bwd_src_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
     const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
     float* __restrict__ gV) {
   constexpr int HD = 32 * VPL;
-  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5;
-  if (w >= A.N) return;
-  const int lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
-  const int u = A.src_order ? A.src_order[w] : w;
-  const int b = A.out_ptr[u], en = A.out_ptr[u + 1];
+  __shared__ float sm_part[kWarps][2 * HD];
+  const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
+  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
-  float p[VPL], at[VPL], ats[VPL], pt[VPL], gpi[VPL], gv[VPL];
-  ldrow<VPL>(p, Pi + (int64_t)u * HD + c0);
+  const int n_items = hub_block ? *A.n_hub_src : 1;
+  float at[VPL], ats[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) { ats[i] = at[i] * A.slope; pt[i] = p[i]; gpi[i] = 0.f; gv[i] = 0.f; }
-  int t_cur = -1;
-  for (int q0 = b; q0 < en; q0 += 32) {
-    const int n = min(32, en - q0);
-    const int my_pos = lane < n ? A.out_pos[q0 + lane] : 0;
-    const int my_v = lane < n ? A.out_dst[q0 + lane] : 0;
-    const int my_t = (typed && lane < n) ? A.etype[my_pos] : 0;
-    for (int j0 = 0; j0 < n; j0 += kUnroll) {
-      float pj[kUnroll][VPL], gg[kUnroll][VPL], gsv[kUnroll], al[kUnroll];
-      int tt[kUnroll], pp[kUnroll];
+  for (int i = 0; i < VPL; ++i) ats[i] = at[i] * A.slope;
+
+  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+    const WorkItem it = hub_block ? hub_item(A.out_ptr, A.hub_src[item], wi)
+                                  : node_item(A, A.out_ptr, A.src_order, wi);
+    const int u = it.node;
+    float gpi[VPL], gv[VPL];
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        const int idx = min(j0 + k, n - 1);
-        const int v = __shfl_sync(0xffffffffu, my_v, idx);
-        pp[k] = __shfl_sync(0xffffffffu, my_pos, idx);
-        tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
-        ldrow<VPL>(pj[k], Pj + (int64_t)v * HD + c0);
-        ldrow<VPL>(gg[k], G + (int64_t)v * HD + c0);
-        const bool valid = j0 + k < n;
-        gsv[k] = valid ? __ldg(gs_in + (int64_t)pp[k] * A.H + h) : 0.f;
-        al[k] = valid ? __ldg(alpha_in + (int64_t)pp[k] * A.H + h) : 0.f;
-      }
+    for (int i = 0; i < VPL; ++i) { gpi[i] = 0.f; gv[i] = 0.f; }
+    if (it.active && it.re > it.rb) {
+      float p[VPL], pt[VPL];
+      ldrow<VPL>(p, Pi + (int64_t)u * HD + c0);
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        const bool valid = j0 + k < n;
-        if (typed && tt[k] != t_cur) {
-          t_cur = tt[k];
-          type_row<VPL>(A, t_cur, c0, p, pt);
-        }
-        float z[VPL];
+      for (int i = 0; i < VPL; ++i) pt[i] = p[i];
+      int t_cur = -1;
+      for (int q0 = it.rb; q0 < it.re; q0 += 32) {
+        const int n = min(32, it.re - q0);
+        const int my_pos = lane < n ? A.out_pos[q0 + lane] : 0;
+        const int my_v = lane < n ? A.out_dst[q0 + lane] : 0;
+        const int my_t = (typed && lane < n) ? A.etype[my_pos] : 0;
+        for (int j0 = 0; j0 < n; j0 += kUnroll) {
+          float pj[kUnroll][VPL], gg[kUnroll][VPL], gsv[kUnroll], al[kUnroll];
+          int tt[kUnroll], pp[kUnroll];
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) z[i] = pj[k][i] + pt[i];
-        if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+          for (int k = 0; k < kUnroll; ++k) {
+            const int idx = min(j0 + k, n - 1);
+            const int v = __shfl_sync(0xffffffffu, my_v, idx);
+            pp[k] = __shfl_sync(0xffffffffu, my_pos, idx);
+            tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+            ldrow<VPL>(pj[k], Pj + (int64_t)v * HD + c0);
+            ldrow<VPL>(gg[k], G + (int64_t)v * HD + c0);
+            const bool valid = j0 + k < n;
+            gsv[k] = valid ? __ldg(gs_in + (int64_t)pp[k] * A.H + h) : 0.f;
+            al[k] = valid ? __ldg(alpha_in + (int64_t)pp[k] * A.H + h) : 0.f;
+          }
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-          gpi[i] = fmaf(gsv[k], z[i] > 0.f ? at[i] : ats[i], gpi[i]);
-          gv[i] = fmaf(al[k], gg[k][i], gv[i]);
+          for (int k = 0; k < kUnroll; ++k) {
+            const bool valid = j0 + k < n;
+            if (typed && tt[k] != t_cur) {
+              t_cur = tt[k];
+              type_row<VPL>(A, t_cur, c0, p, pt);
+            }
+            float z[VPL];
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) z[i] = pj[k][i] + pt[i];
+            if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+              gpi[i] = fmaf(gsv[k], z[i] > 0.f ? at[i] : ats[i], gpi[i]);
+              gv[i] = fmaf(al[k], gg[k][i], gv[i]);
+            }
+          }
         }
       }
     }
-  }
-  if constexpr (ALIAS) {
+    bool finalize = it.active;
+    if (hub_block) {
+      strow<VPL>(&sm_part[wi][c0], gpi);
+      strow<VPL>(&sm_part[wi][HD + c0], gv);
+      __syncthreads();
+      finalize = wi == 0;
+      if (finalize) {
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) gpi[i] += gv[i];
-    strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
-  } else {
-    strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
-    strow<VPL>(gV + (int64_t)u * HD + c0, gv);
+        for (int i = 0; i < VPL; ++i) { gpi[i] = 0.f; gv[i] = 0.f; }
+        for (int w2 = 0; w2 < kWarps; ++w2) {
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) { gpi[i] += sm_part[w2][c0 + i]; gv[i] += sm_part[w2][HD + c0 + i]; }
+        }
+      }
+      __syncthreads();
+    }
+    if (finalize) {
+      if constexpr (ALIAS) {
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) gpi[i] += gv[i];
+        strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
+      } else {
+        strow<VPL>(gPi + (int64_t)u * HD + c0, gpi);
+        strow<VPL>(gV + (int64_t)u * HD + c0, gv);
+      }
+    }
   }
 }
 
@@ -414,6 +551,8 @@ static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a,
   A.N = g->n_nodes; A.E = g->n_edges;
   A.in_ptr = g->in_ptr; A.in_src = g->in_src; A.out_ptr = g->out_ptr; A.out_dst = g->out_dst;
   A.out_pos = g->out_pos; A.dst_order = g->dst_order; A.src_order = g->src_order;
+  A.hub_dst = g->hub_dst; A.n_hub_dst = g->n_hub_dst; A.hub_src = g->hub_src; A.n_hub_src = g->n_hub_src;
+  A.hub_degree = g->hub_degree; A.hub_blocks = 0;
   A.H = a->heads; A.slope = a->slope; A.eps = a->softmax_eps; A.attn = a->attn; A.out_bias = a->out_bias;
   A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
   A.T = ef ? ef->n_types : 0; A.K = ef ? ef->n_attr : 0;
@@ -454,7 +593,8 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   int rc = fill_fast(A, g, a, ef);
   if (rc) return rc;
   if (A.N == 0) return B200GAT_OK;
-  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
+  A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
+  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads) + A.hub_blocks;
   const bool alias = (V == Pi);
   ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
   FAST_DISPATCH(vpl, lph, alias,
@@ -482,7 +622,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   if (A.emode == B200GAT_EDGE_AFFINE && A.K > 0) B200_CHECK_ARG(g_affine, "null g_affine");
   if (A.N == 0) return B200GAT_OK;
   const int HD = 32 * vpl;
-  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
+  const unsigned nblocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
   const bool alias = (V == Pi);
   B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
   const int tab_in_smem = (A.emode != B200GAT_EDGE_NONE && (int64_t)A.T * HD * 4 <= 40 * 1024) ? 1 : 0;
@@ -490,6 +630,8 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   float* alpha = gs + (int64_t)A.E * A.H;
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
+    A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
+    const unsigned blocks = nblocks + A.hub_blocks;
     FAST_DISPATCH(vpl, lph, alias,
                   (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
                       A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
@@ -497,6 +639,8 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   }
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_SRC, st);
+    A.hub_blocks = (A.hub_src && A.n_hub_src && A.hub_degree > 0) ? kHubBlocks : 0;
+    const unsigned blocks = nblocks + A.hub_blocks;
     FAST_DISPATCH(vpl, lph, alias,
                   (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
                                                                                    gPi, gV)));

@@ -160,8 +160,21 @@ __global__ void __launch_bounds__(128) k_bwd_dst_generic(
   // pass B
   float gat[kMaxK] = {0.f, 0.f, 0.f, 0.f}, gpj[kMaxK] = {0.f, 0.f, 0.f, 0.f};
   float gb = 0.f;
+  float gtab[kMaxK] = {0.f, 0.f, 0.f, 0.f};
+  const bool typed = A.emode == B200GAT_EDGE_TABLE || A.emode == B200GAT_EDGE_AFFINE;
+  int t_cur = -1;
+  auto flush_tab = [&]() {
+    if (t_cur < 0) return;
+#pragma unroll
+    for (int k = 0; k < kMaxK; ++k) {
+      int d = lane + 32 * k;
+      if (d < A.D && gtab[k] != 0.f) atomicAdd(g_table + (int64_t)t_cur * HD + hoff + d, gtab[k]);
+      gtab[k] = 0.f;
+    }
+  };
   for (int e = b; e < en; ++e) {
     const int u = A.in_src[e];
+    if (typed && A.etype[e] != t_cur) { flush_tab(); t_cur = A.etype[e]; }
     const float ga = gs[(int64_t)e * A.H + h];
     const float a = expf(s_save[(int64_t)e * A.H + h] - mx) * linv;
     const float gsv = a * (ga - dot);
@@ -179,14 +192,13 @@ __global__ void __launch_bounds__(128) k_bwd_dst_generic(
           float gz = gsv * at[k] * (z > 0.f ? 1.f : A.slope);
           gpj[k] += gz;
           if (A.emode == B200GAT_EDGE_DENSE) g_dense[(int64_t)A.in_eid[e] * HD + hoff + d] = gz;
-          else if (A.emode == B200GAT_EDGE_TABLE)
-            atomicAdd(g_table + (int64_t)A.etype[e] * HD + hoff + d, gz);
-          else if (A.emode == B200GAT_EDGE_AFFINE) {
-            atomicAdd(g_table + (int64_t)A.etype[e] * HD + hoff + d, gz);
-            for (int q = 0; q < A.K; ++q) {
-              float av = __ldg(A.attr + (int64_t)e * A.K + q);
-              if (av != 0.f) atomicAdd(g_affine + (int64_t)q * HD + hoff + d, gz * av);
-            }
+          else if (A.emode == B200GAT_EDGE_TABLE || A.emode == B200GAT_EDGE_AFFINE) {
+            gtab[k] += gz;                     // flushed once per run of equal edge types
+            if (A.emode == B200GAT_EDGE_AFFINE)
+              for (int q = 0; q < A.K; ++q) {
+                float av = __ldg(A.attr + (int64_t)e * A.K + q);
+                if (av != 0.f) atomicAdd(g_affine + (int64_t)q * HD + hoff + d, gz * av);
+              }
           }
         } else {
           float c = gsv * A.inv_sqrt_d;
@@ -196,6 +208,7 @@ __global__ void __launch_bounds__(128) k_bwd_dst_generic(
       }
     }
   }
+  if (typed) flush_tab();
 #pragma unroll
   for (int k = 0; k < kMaxK; ++k) {
     int d = lane + 32 * k;

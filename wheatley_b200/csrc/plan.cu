@@ -248,6 +248,13 @@ __global__ void k_order_fill(const int32_t* __restrict__ key, int32_t N, const i
   tmp[hist[k] + atomicAdd(&fill[k], 1)] = v;
 }
 
+__global__ void k_hub_list(const int32_t* __restrict__ ptr, int32_t N, int32_t thresh,
+                           int32_t* __restrict__ list, int32_t* __restrict__ count) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  if (ptr[v + 1] - ptr[v] > thresh) list[atomicAdd(count, 1)] = v;
+}
+
 __global__ void k_gather_i32(const int32_t* __restrict__ table, const int32_t* __restrict__ idx,
                              int64_t n, int32_t* __restrict__ out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -382,6 +389,19 @@ extern "C" int b200gat_node_order(const int32_t* ptr, const int32_t* nbr, int64_
   k_sort_small<<<(unsigned)ceil_div(N * 32, 256), 256, 0, st>>>(hist, (int32_t)N, tmp, order, large, counter);
   k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(hist, tmp, order, large, counter);
   B200_CHECK_LAUNCHES("b200gat_node_order", 4);
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_hub_list(const int32_t* ptr, int64_t N, int32_t hub_degree, int32_t* list,
+                                int32_t* count, void* stream) {
+  B200_CHECK_ARG(N >= 0 && hub_degree > 0, "bad arguments");
+  B200_CHECK_ARG(count, "null count");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(count, 0, sizeof(int32_t), st);
+  if (N == 0) return B200GAT_OK;
+  B200_CHECK_ARG(ptr && list, "null pointer");
+  k_hub_list<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(ptr, (int32_t)N, hub_degree, list, count);
+  B200_CHECK_LAUNCH("k_hub_list");
   return B200GAT_OK;
 }
 

@@ -46,10 +46,20 @@ class GraphPlan:
                 _lib.check(_lib.lib.b200gat_node_order(_lib.ptr(ptr_), _lib.ptr(nbr_), N, _lib.ptr(out_),
                                                        _lib.ptr(oscr), _lib.stream_ptr()),
                            "b200gat_node_order")
+            # hub nodes (segments longer than HUB_DEGREE are split over a CTA's warps)
+            self.hub_dst = torch.empty(N, **i32)
+            self.hub_src = torch.empty(N, **i32)
+            self.n_hub = torch.empty(2, **i32)
+            for k, (ptr_, lst_) in enumerate(((self.in_ptr, self.hub_dst), (self.out_ptr, self.hub_src))):
+                _lib.check(_lib.lib.b200gat_hub_list(_lib.ptr(ptr_), N, _lib.HUB_DEGREE, _lib.ptr(lst_),
+                                                     self.n_hub.data_ptr() + 4 * k, _lib.stream_ptr()),
+                           "b200gat_hub_list")
         self._stats_host = None
         self._c = _lib.Graph(N, E, _lib.ptr(self.in_ptr), _lib.ptr(self.in_src), _lib.ptr(self.in_eid),
                              _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst), _lib.ptr(self.out_pos),
-                             _lib.ptr(self.dst_order), _lib.ptr(self.src_order))
+                             _lib.ptr(self.dst_order), _lib.ptr(self.src_order), _lib.HUB_DEGREE,
+                             _lib.ptr(self.hub_dst), self.n_hub.data_ptr(), _lib.ptr(self.hub_src),
+                             self.n_hub.data_ptr() + 4)
         self._sorted_cache = {}
 
     @classmethod
