@@ -58,7 +58,10 @@ int64_t b200gat_launch_count(void);
 #define B200GAT_TIMING_HEAD 4
 #define B200GAT_TIMING_GEMM 5
 #define B200GAT_TIMING_BATCH 6
-#define B200GAT_TIMING_CLASSES 8
+#define B200GAT_TIMING_CLQ_FWD 8
+#define B200GAT_TIMING_CLQ_BWD_MMA 9
+#define B200GAT_TIMING_CLQ_BWD_ELEM 10
+#define B200GAT_TIMING_CLASSES 12
 void b200gat_timing_enable(int on);
 int b200gat_timing_read(int cls, double* total_ms, int64_t* count);
 
@@ -69,7 +72,8 @@ int b200gat_timing_read(int cls, double* total_ms, int64_t* count);
  * Replaces: DGL's CSR/CSC materialisation behind apply_edges / edge_softmax /
  * update_all (generic/eegatconv.py:269,280,292) and PyG's scatter index handling
  * (generic/gatv3_conv.py:155-160,193).                                              */
-typedef struct {
+struct b200gat_cliques_s;
+typedef struct b200gat_graph_s {
   int32_t n_nodes;
   int32_t n_edges;
   const int32_t* in_ptr;  /* [N+1] CSR by destination                                    */
@@ -91,7 +95,57 @@ typedef struct {
   const int32_t* n_hub_dst; /* [1]   device-side count                                       */
   const int32_t* hub_src;   /* [<=N] sources with out-degree > hub_degree                    */
   const int32_t* n_hub_src; /* [1]                                                           */
+  /* Optional scratch for splitting hub destinations over several CTAs: hub_cap * hub_parts records   */
+  /* of (256 + 64) floats; used when the device-side hub count fits hub_cap, ignored (NULL/0) else.   */
+  /* One conv call at a time may use a graph's scratch (single-stream use, like the reference).       */
+  float* hub_scratch;
+  int32_t hub_parts;
+  int32_t hub_cap;
+  /* Residual graphs only (b200gat_clique_build): position of each in-edge in the destination-   */
+  /* sorted order of the FULL graph (index into etype / attr / s_save); NULL = identity.          */
+  const int32_t* in_pos;
+  /* Dense clique blocks of this graph and the CSR of the edges outside them, or NULL/NULL.      */
+  const struct b200gat_cliques_s* cliques;
+  const struct b200gat_graph_s* residual;
 } b200gat_graph;
+
+/* ------------------------------------------------------------------ clique blocks
+ * Machine-conflict cliques (jssp/utils/utils.py:460-478; psp/utils/utils.py:62-92) are complete
+ * digraphs: every member reads the same source rows.  A block is a node set S,
+ * min_size <= |S| <= B200GAT_MAX_CLIQUE, such that every v in S has the sources S \ {v}, in ascending
+ * node id, as ONE contiguous same-typed run of its destination-sorted in-edges.  Blocks are computed
+ * as dense tiles (shared-memory staged rows, register-tiled logits, tensor-core aggregation); all other
+ * edges stay on the residual CSR.  Blocks are numbered by ascending smallest member.                */
+#define B200GAT_MAX_CLIQUE 128
+typedef struct b200gat_cliques_s {
+  int32_t n_blocks;          /* host copies of counts[0], counts[1], counts[3]                      */
+  int32_t max_block;
+  int32_t n_members;
+  int32_t s_elems;           /* per-head elements of the dense logit buffer = blk_soff[n_blocks]    */
+  const int32_t* blk_ptr;    /* [n_blocks+1] offsets into blk_nodes                                  */
+  const int32_t* blk_nodes;  /* [n_members]  members of each block, ascending                        */
+  const int32_t* blk_type;   /* [n_blocks]   edge type of the block's edges (0 when untyped)         */
+  const int32_t* blk_soff;   /* [n_blocks+1] prefix of n_b * roundup4(n_b): block b / head h owns     */
+                             /* s_dense[blk_soff[b]*H + h*n_b*roundup4(n_b) ...][dst rank][src rank]   */
+  const int32_t* node_blk;   /* [N] block of each node or -1                                         */
+  const int32_t* node_run;   /* [N] position (full dst-sorted order) of the first block in-edge      */
+  const int32_t* node_rank;  /* [N] rank of the node inside its block                                */
+} b200gat_cliques;
+
+int64_t b200gat_clique_scratch_elems(int64_t n_nodes, int64_t n_edges);
+
+/* Detect the blocks of `g` (exact, deterministic) and build the residual CSR.
+ * etype_sorted: [E] edge types in destination-sorted order, or NULL (untyped).
+ * Outputs (caller-allocated, device): node_blk/node_run/node_rank [N]; blk_ptr/blk_soff [N+1];
+ * blk_nodes/blk_type [N]; residual CSR r_in_ptr/r_out_ptr [N+1], r_in_src/r_in_pos/r_out_dst/
+ * r_out_pos [E] (upper bounds); counts int32[8] = {n_blocks, max_block, n_residual_edges, n_members,
+ * s_elems, 0, 0, 0};
+ * scratch: b200gat_clique_scratch_elems int32, 8-byte aligned.                                        */
+int b200gat_clique_build(const b200gat_graph* g, const int32_t* etype_sorted, int32_t min_size,
+                         int32_t* node_blk, int32_t* node_run, int32_t* node_rank, int32_t* blk_ptr,
+                         int32_t* blk_nodes, int32_t* blk_type, int32_t* blk_soff, int32_t* r_in_ptr,
+                         int32_t* r_in_src, int32_t* r_in_pos, int32_t* r_out_ptr, int32_t* r_out_dst,
+                         int32_t* r_out_pos, int32_t* counts, int32_t* scratch, void* stream);
 
 /* Number of int32 scratch elements b200gat_plan_build needs. */
 int64_t b200gat_plan_scratch_elems(int64_t n_nodes, int64_t n_edges);
@@ -159,10 +213,14 @@ typedef struct {
  *   s_save    : [E, H] raw logits in dst-sorted order   (saved for backward)
  *   m_save,l_save : [N, H] per-destination max and sum of exp(s-m)
  *   agg_save  : [N, H*D] the aggregate WITHOUT out_bias, a private copy for the backward
- *               (callers add residuals into `out` in place, psp/models/gnn_flat.py:230), or NULL */
+ *               (callers add residuals into `out` in place, psp/models/gnn_flat.py:230), or NULL
+ *   s_dense   : [H * g->cliques->s_elems] raw logits of the clique-block edges (those are NOT written
+ *               to s_save); required when g->cliques has blocks and the dense path applies
+ *               (additive flavour, D == 64, edge mode NONE/TABLE), else may be NULL */
 int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                      const float* Pi, const float* Pj, const float* V, float* out,
-                     float* s_save, float* m_save, float* l_save, float* agg_save, void* stream);
+                     float* s_save, float* m_save, float* l_save, float* agg_save, float* s_dense,
+                     void* stream);
 
 /* Matching fused backward (replaces autograd through the ops above).
  *   g_out            : [N, H*D]
@@ -172,12 +230,14 @@ int b200gat_conv_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200ga
  *   g_attn_bias      : [1] (dot), accumulated; else NULL
  *   g_table          : [T, H*D] accumulated (EDGE_TABLE / EDGE_AFFINE) ; g_dense: [E, H*D]
  *                      written (EDGE_DENSE) ; g_affine: [K, H*D] accumulated (EDGE_AFFINE)
- *   gs_scratch       : [2, E, H] scratch (dst-sorted order): d loss / d logit, attention weight
+ *   gs_scratch       : [2, E, H] scratch (dst-sorted order): d loss / d logit, attention weight;
+ *                      when the dense clique path applies (b200gat_conv_uses_cliques) it must hold
+ *                      2*E*H + roundup4(H * s_elems) + 2*N*H floats, 16-byte aligned
  *   agg_save         : [N, H*D] from the forward, or NULL (then recomputed with one more pass)  */
 int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef,
                      const float* Pi, const float* Pj, const float* V, const float* s_save,
                      const float* m_save, const float* l_save, const float* agg_save,
-                     const float* g_out, float* gPi,
+                     const float* s_dense, const float* g_out, float* gPi,
                      float* gPj, float* gV, float* g_attn, float* g_attn_bias, float* g_table,
                      float* g_dense, float* g_affine, float* gs_scratch, void* stream);
 
@@ -185,7 +245,9 @@ int b200gat_conv_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200ga
  * generic/eegatconv.py:304-308; return_attention_weights, generic/gatv3_conv.py:174-179). */
 int b200gat_attention(const b200gat_graph* g, int32_t heads, float softmax_eps,
                       const float* s_save, const float* m_save, const float* l_save,
-                      float* alpha, void* stream);
+                      const float* s_dense, float* alpha, void* stream);
+/* 1 when b200gat_conv_fwd/bwd would take the dense clique path for this configuration. */
+int b200gat_conv_uses_cliques(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef);
 
 /* f_out[e] = leaky_relu(Pi[src]+Pj[dst]+Pe[e]) in ORIGINAL edge order: the edge output of
  * EGATConv (generic/eegatconv.py:276-277,313), produced on request only.                  */

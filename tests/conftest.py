@@ -17,3 +17,12 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(autouse=True)
+def _deterministic_seed():
+    """Every test starts from the same torch RNG state (layer initialisations use the global generator),
+    so results do not depend on which tests ran before."""
+    import torch
+    torch.manual_seed(1234)
+    yield

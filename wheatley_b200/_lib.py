@@ -11,6 +11,8 @@ LIB_PATH = os.path.join(_HERE, "libb200gat.so")
 EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
 MAX_ATTR = 8
 HUB_DEGREE = 256
+HUB_PARTS = 16        # CTAs a hub destination's in-edges are split over
+HUB_REC = 256 + 64    # floats per partial record (include/b200gat.h)
 FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
 
 # every symbol include/b200gat.h declares (tests check that the library exports all of them)
@@ -20,16 +22,32 @@ SYMBOLS = (
     "b200gat_node_order_scratch_elems", "b200gat_node_order", "b200gat_hub_list",
     "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
+    "b200gat_clique_scratch_elems", "b200gat_clique_build", "b200gat_conv_uses_cliques",
 )
+MAX_CLIQUE = 128
+MIN_CLIQUE = 8        # smaller cliques stay on the sparse kernels
+
+
+class Cliques(C.Structure):
+    _fields_ = [("n_blocks", C.c_int32), ("max_block", C.c_int32), ("n_members", C.c_int32),
+                ("s_elems", C.c_int32),
+                ("blk_ptr", C.c_void_p), ("blk_nodes", C.c_void_p), ("blk_type", C.c_void_p),
+                ("blk_soff", C.c_void_p), ("node_blk", C.c_void_p), ("node_run", C.c_void_p),
+                ("node_rank", C.c_void_p)]
 
 
 class Graph(C.Structure):
-    _fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
+    pass
+
+
+Graph._fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
                 ("in_ptr", C.c_void_p), ("in_src", C.c_void_p), ("in_eid", C.c_void_p),
                 ("out_ptr", C.c_void_p), ("out_dst", C.c_void_p), ("out_pos", C.c_void_p),
                 ("dst_order", C.c_void_p), ("src_order", C.c_void_p),
                 ("hub_degree", C.c_int32), ("hub_dst", C.c_void_p), ("n_hub_dst", C.c_void_p),
-                ("hub_src", C.c_void_p), ("n_hub_src", C.c_void_p)]
+                ("hub_src", C.c_void_p), ("n_hub_src", C.c_void_p),
+                ("hub_scratch", C.c_void_p), ("hub_parts", C.c_int32), ("hub_cap", C.c_int32),
+                ("in_pos", C.c_void_p), ("cliques", C.POINTER(Cliques)), ("residual", C.POINTER(Graph))]
 
 
 class Attn(C.Structure):
@@ -74,16 +92,21 @@ def _load():
     lib.b200gat_gather_rows_f32.argtypes = [vp, vp, i64, i32, vp, vp]
     lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]
     gp, ap, ep = C.POINTER(Graph), C.POINTER(Attn), C.POINTER(EdgeFeats)
-    lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 9
-    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 18
-    lib.b200gat_attention.argtypes = [gp, i32, f32, vp, vp, vp, vp, vp]
+    lib.b200gat_conv_fwd.argtypes = [gp, ap, ep] + [vp] * 10
+    lib.b200gat_conv_bwd.argtypes = [gp, ap, ep] + [vp] * 19
+    lib.b200gat_attention.argtypes = [gp, i32, f32, vp, vp, vp, vp, vp, vp]
+    lib.b200gat_clique_scratch_elems.restype = i64
+    lib.b200gat_clique_scratch_elems.argtypes = [i64, i64]
+    lib.b200gat_clique_build.argtypes = [gp, vp, i32] + [vp] * 16
+    lib.b200gat_conv_uses_cliques.argtypes = [gp, ap, ep]
     lib.b200gat_edge_out.argtypes = [gp, ap, ep, vp, vp, vp, vp]
     lib.b200gat_mask_head_fwd.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, vp, vp, vp]
     lib.b200gat_mask_head_bwd.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32, i32, vp, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
-                        "b200gat_timing_enable", "b200gat_node_order_scratch_elems"):
+                        "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
+                        "b200gat_clique_scratch_elems"):
             fn.restype = C.c_int
     return lib
 
@@ -97,7 +120,7 @@ def check(rc, what):
 
 
 TIMING_CLASSES = {"conv_fwd": 0, "conv_bwd_dst": 1, "conv_bwd_src": 2, "plan": 3, "head": 4, "gemm": 5,
-                  "batch": 6}
+                  "batch": 6, "clq_fwd": 8, "clq_bwd_mma": 9, "clq_bwd_elem": 10}
 
 
 def launch_count() -> int:

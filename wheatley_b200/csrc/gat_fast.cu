@@ -24,8 +24,12 @@ namespace b200gat {
 struct FastArgs {
   int N, E;
   const int32_t *in_ptr, *in_src, *out_ptr, *out_dst, *out_pos, *dst_order, *src_order;
+  const int32_t *in_pos;      // residual graphs: position of each in-edge in the full dst-sorted order
+  const int32_t *node_blk;    // clique members (>= 0): the forward leaves their softmax state un-normalised
   const int32_t *hub_dst, *n_hub_dst, *hub_src, *n_hub_src;
   int hub_degree, hub_blocks;   // hub_blocks = 0 disables segment splitting
+  float* hub_scratch;           // [hub_cap][hub_parts][HD + 64] partial states of split hub segments, or NULL
+  int hub_parts, hub_cap;
   int H;
   float slope, eps;
   const float *attn, *out_bias;
@@ -97,7 +101,8 @@ __device__ __forceinline__ void affine_add(const FastArgs& A, int64_t pos, int c
 
 constexpr int kFastThreads = 256;
 constexpr int kWarps = kFastThreads / 32;
-constexpr int kHubBlocks = 64;   // CTAs at the front of the grid that walk the hub list
+constexpr int kHubBlocks = 148;  // CTAs at the front of the grid that walk the hub list
+constexpr int kHubRec = 64;      // extra floats per partial record: m[32] + l[32] (one per lane)
 constexpr int kUnroll = 4;
 
 // Work assignment shared by the three kernels.  Blocks [0, hub_blocks) walk the hub list: the
@@ -107,16 +112,23 @@ struct WorkItem {
   int node, rb, re, seg_b, seg_e;
   bool active;
 };
-__device__ __forceinline__ WorkItem hub_item(const int32_t* __restrict__ ptr, int node, int wi) {
+// A hub segment is cut into `parts` slices (one CTA each) of kWarps sub-slices (one warp each).
+__device__ __forceinline__ WorkItem hub_item(const int32_t* __restrict__ ptr, int node, int wi, int part = 0,
+                                             int parts = 1) {
   WorkItem it;
   it.node = node;
   it.seg_b = ptr[node];
   it.seg_e = ptr[node + 1];
-  const int per = (((it.seg_e - it.seg_b) + kWarps - 1) / kWarps + kUnroll - 1) & ~(kUnroll - 1);
-  it.rb = min(it.seg_e, it.seg_b + wi * per);
+  const int ns = kWarps * parts;
+  const int per = (((it.seg_e - it.seg_b) + ns - 1) / ns + kUnroll - 1) & ~(kUnroll - 1);
+  it.rb = min(it.seg_e, it.seg_b + (part * kWarps + wi) * per);
   it.re = min(it.seg_e, it.rb + per);
   it.active = true;
   return it;
+}
+// Number of slices per hub: the scratch must exist and hold every hub of the list.
+__device__ __forceinline__ int hub_parts_of(const FastArgs& A, int n_hub) {
+  return (A.hub_scratch && A.hub_parts > 1 && n_hub <= A.hub_cap) ? A.hub_parts : 1;
 }
 __device__ __forceinline__ WorkItem node_item(const FastArgs& A, const int32_t* __restrict__ ptr,
                                               const int32_t* __restrict__ order, int wi) {
@@ -135,6 +147,39 @@ __device__ __forceinline__ WorkItem node_item(const FastArgs& A, const int32_t* 
   return it;
 }
 
+// Last step of the forward for one destination: clique members keep the un-normalised state (the
+// dense kernel continues and finalises it); everybody else is normalised, biased and saved.
+template <int VPL>
+__device__ __forceinline__ void fwd_finalize(const FastArgs& A, int v, bool any, float (&acc)[VPL], float m,
+                                             float l, int c0, int h, bool head_lead, float* __restrict__ out,
+                                             float* __restrict__ m_save, float* __restrict__ l_save,
+                                             float* __restrict__ agg_save) {
+  constexpr int HD = 32 * VPL;
+  if (A.node_blk && A.node_blk[v] >= 0) {
+    strow<VPL>(out + (int64_t)v * HD + c0, acc);
+    if (head_lead) {
+      m_save[(int64_t)v * A.H + h] = m;
+      l_save[(int64_t)v * A.H + h] = l;
+    }
+    return;
+  }
+  const float inv = any ? 1.f / (l + A.eps) : 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] *= inv;
+  if (agg_save) strow<VPL>(agg_save + (int64_t)v * HD + c0, acc);
+  if (A.out_bias) {
+    float ob[VPL];
+    ldrow<VPL>(ob, A.out_bias + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] += ob[i];
+  }
+  strow<VPL>(out + (int64_t)v * HD + c0, acc);
+  if (head_lead) {
+    m_save[(int64_t)v * A.H + h] = any ? m : 0.f;
+    l_save[(int64_t)v * A.H + h] = l;
+  }
+}
+
 // ------------------------------------------------------------------------------ forward
 template <int VPL, int LPH, bool ALIAS>
 __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
@@ -149,12 +194,14 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
   const bool hub_block = (int)blockIdx.x < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
-  const int n_items = hub_block ? *A.n_hub_dst : 1;
+  const int n_hub = hub_block ? *A.n_hub_dst : 0;
+  const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
+  const int n_items = hub_block ? n_hub * P : 1;
   float at[VPL];
   ldrow<VPL>(at, A.attn + c0);
 
   for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
-    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item], wi)
+    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item / P], wi, item % P, P)
                                   : node_item(A, A.in_ptr, A.dst_order, wi);
     const int v = it.node;
     float acc[VPL];
@@ -170,15 +217,17 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
       for (int e0 = it.rb; e0 < it.re; e0 += 32) {
         const int n = min(32, it.re - e0);
         const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
-        const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+        const int my_p = lane < n ? (A.in_pos ? A.in_pos[e0 + lane] : e0 + lane) : 0;
+        const int my_t = (typed && lane < n) ? A.etype[my_p] : 0;
         for (int j0 = 0; j0 < n; j0 += kUnroll) {
           float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL];
-          int tt[kUnroll];
+          int tt[kUnroll], pp[kUnroll];
 #pragma unroll
           for (int k = 0; k < kUnroll; ++k) {
             const int idx = min(j0 + k, n - 1);
             const int u = __shfl_sync(0xffffffffu, my_u, idx);
             tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+            pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
             ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
             if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
           }
@@ -193,12 +242,12 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
             float z[VPL];
 #pragma unroll
             for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-            if (affine && valid) affine_add<VPL>(A, e0 + j0 + k, c0, z);
+            if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
             float part = 0.f;
 #pragma unroll
             for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
             part = head_sum<LPH>(part);
-            if (valid && head_lead) s_save[(int64_t)(e0 + j0 + k) * A.H + h] = part;
+            if (valid && head_lead) s_save[(int64_t)pp[k] * A.H + h] = part;
             sc[k] = valid ? part : -INFINITY;
           }
           float mnew = m;
@@ -234,7 +283,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
 #pragma unroll
         for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
         for (int w2 = 0; w2 < kWarps; ++w2) {
-          const float f = __expf(sm_m[w2][lane] - M);   // empty slice: exp(-inf) = 0
+          const float f = sm_m[w2][lane] == -INFINITY ? 0.f : __expf(sm_m[w2][lane] - M);   // empty slice
           l = fmaf(sm_l[w2][lane], f, l);
           float pa[VPL];
 #pragma unroll
@@ -245,26 +294,48 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
         m = M;
       }
       __syncthreads();
-    }
-    if (finalize) {
-      const bool any = it.seg_e > it.seg_b;
-      const float inv = any ? 1.f / (l + A.eps) : 0.f;
-#pragma unroll
-      for (int i = 0; i < VPL; ++i) acc[i] *= inv;
-      if (agg_save) strow<VPL>(agg_save + (int64_t)v * HD + c0, acc);
-      if (A.out_bias) {
-        float ob[VPL];
-        ldrow<VPL>(ob, A.out_bias + c0);
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) acc[i] += ob[i];
-      }
-      strow<VPL>(out + (int64_t)v * HD + c0, acc);
-      if (head_lead) {
-        m_save[(int64_t)v * A.H + h] = any ? m : 0.f;
-        l_save[(int64_t)v * A.H + h] = l;
+      if (finalize && P > 1) {             // one slice of a split hub: park the partial state
+        float* rec = A.hub_scratch + (int64_t)item * (HD + kHubRec);
+        strow<VPL>(rec + c0, acc);
+        rec[HD + lane] = m;
+        rec[HD + 32 + lane] = l;
+        finalize = false;
       }
     }
+    if (finalize)
+      fwd_finalize<VPL>(A, v, it.seg_e > it.seg_b, acc, m, l, c0, h, head_lead, out, m_save, l_save, agg_save);
   }
+}
+
+// Merge the partial softmax states of the slices of each split hub (in slice order) and finalise.
+template <int VPL, int LPH>
+__global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, float* __restrict__ out,
+                                                                float* __restrict__ m_save,
+                                                                float* __restrict__ l_save,
+                                                                float* __restrict__ agg_save) {
+  constexpr int HD = 32 * VPL;
+  const int n_hub = *A.n_hub_dst, P = hub_parts_of(A, n_hub);
+  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (P == 1 || w >= n_hub) return;
+  const int c0 = lane * VPL, h = lane / LPH;
+  const int v = A.hub_dst[w];
+  const float* rec0 = A.hub_scratch + (int64_t)w * P * (HD + kHubRec);
+  float M = -INFINITY;
+  for (int p = 0; p < P; ++p) M = fmaxf(M, rec0[(int64_t)p * (HD + kHubRec) + HD + lane]);
+  float acc[VPL], l = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+  for (int p = 0; p < P; ++p) {
+    const float* rec = rec0 + (int64_t)p * (HD + kHubRec);
+    const float mp = rec[HD + lane];
+    const float f = mp == -INFINITY ? 0.f : __expf(mp - M);  // empty slice
+    l = fmaf(rec[HD + 32 + lane], f, l);
+    float pa[VPL];
+    ldrow<VPL>(pa, rec + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] = fmaf(pa[i], f, acc[i]);
+  }
+  fwd_finalize<VPL>(A, v, true, acc, M, l, c0, h, (lane % LPH) == 0, out, m_save, l_save, agg_save);
 }
 
 // ------------------------------------------------------------------------------ backward, by destination
@@ -292,14 +363,16 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
   const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
   const bool head_lead = (lane % LPH) == 0;
   const bool hub_block = (int)blockIdx.x < A.hub_blocks;
-  const int n_items = hub_block ? *A.n_hub_dst : 1;
+  const int n_hub = hub_block ? *A.n_hub_dst : 0;
+  const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
+  const int n_items = hub_block ? n_hub * P : 1;
   float at[VPL], gat[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
   for (int i = 0; i < VPL; ++i) gat[i] = 0.f;
 
   for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
-    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item], wi)
+    const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item / P], wi, item % P, P)
                                   : node_item(A, A.in_ptr, A.dst_order, wi);
     const int v = it.node;
     float gpj[VPL];
@@ -334,23 +407,25 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
       for (int e0 = it.rb; e0 < it.re; e0 += 32) {
         const int n = min(32, it.re - e0);
         const int my_u = lane < n ? A.in_src[e0 + lane] : 0;
-        const int my_t = (typed && lane < n) ? A.etype[e0 + lane] : 0;
+        const int my_p = lane < n ? (A.in_pos ? A.in_pos[e0 + lane] : e0 + lane) : 0;
+        const int my_t = (typed && lane < n) ? A.etype[my_p] : 0;
         for (int j0 = 0; j0 < n; j0 += U) {
           float pi[U][VPL], vv[ALIAS ? 1 : U][VPL], sv[U];
-          int tt[U];
+          int tt[U], pp[U];
 #pragma unroll
           for (int k = 0; k < U; ++k) {
             const int idx = min(j0 + k, n - 1);
             const int u = __shfl_sync(0xffffffffu, my_u, idx);
             tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
+            pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
             ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
             if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
-            sv[k] = __ldg(s_save + (int64_t)(e0 + idx) * A.H + h);
+            sv[k] = __ldg(s_save + (int64_t)pp[k] * A.H + h);
           }
 #pragma unroll
           for (int k = 0; k < U; ++k) {
             const bool valid = j0 + k < n;
-            const int64_t pos = e0 + j0 + k;
+            const int64_t pos = pp[k];
             float ga = 0.f;
 #pragma unroll
             for (int i = 0; i < VPL; ++i) ga = fmaf(g[i], ALIAS ? pi[k][i] : vv[ALIAS ? 0 : k][i], ga);
@@ -404,7 +479,8 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
 #pragma unroll
           for (int i = 0; i < VPL; ++i) gpj[i] += sm_part[w2][c0 + i];
         }
-        strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
+        if (P > 1) strow<VPL>(A.hub_scratch + (int64_t)item * (HD + kHubRec) + c0, gpj);   // slice partial
+        else strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
       }
       __syncthreads();
     } else if (it.active) {
@@ -420,6 +496,26 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
   if (tab_in_smem)
     for (int i = threadIdx.x; i < A.T * HD; i += kFastThreads)
       if (sh_tab[i] != 0.f) atomicAdd(g_table + i, sh_tab[i]);
+}
+
+// Sum the partial d Pj rows of the slices of each split hub (in slice order).
+template <int VPL>
+__global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, float* __restrict__ gPj) {
+  constexpr int HD = 32 * VPL;
+  const int n_hub = *A.n_hub_dst, P = hub_parts_of(A, n_hub);
+  const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (P == 1 || w >= n_hub) return;
+  const int c0 = lane * VPL;
+  float acc[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+  for (int p = 0; p < P; ++p) {
+    float pa[VPL];
+    ldrow<VPL>(pa, A.hub_scratch + ((int64_t)w * P + p) * (HD + kHubRec) + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] += pa[i];
+  }
+  strow<VPL>(gPj + (int64_t)A.hub_dst[w] * HD + c0, acc);
 }
 
 // ------------------------------------------------------------------------------ backward, by source
@@ -551,8 +647,10 @@ static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a,
   A.N = g->n_nodes; A.E = g->n_edges;
   A.in_ptr = g->in_ptr; A.in_src = g->in_src; A.out_ptr = g->out_ptr; A.out_dst = g->out_dst;
   A.out_pos = g->out_pos; A.dst_order = g->dst_order; A.src_order = g->src_order;
+  A.in_pos = g->in_pos; A.node_blk = nullptr;
   A.hub_dst = g->hub_dst; A.n_hub_dst = g->n_hub_dst; A.hub_src = g->hub_src; A.n_hub_src = g->n_hub_src;
   A.hub_degree = g->hub_degree; A.hub_blocks = 0;
+  A.hub_scratch = g->hub_scratch; A.hub_parts = g->hub_parts; A.hub_cap = g->hub_cap;
   A.H = a->heads; A.slope = a->slope; A.eps = a->softmax_eps; A.attn = a->attn; A.out_bias = a->out_bias;
   A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
   A.T = ef ? ef->n_types : 0; A.K = ef ? ef->n_attr : 0;
@@ -583,7 +681,7 @@ static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a,
 
 int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef, const float* Pi,
              const float* Pj, const float* V, float* out, float* s_save, float* m_save, float* l_save,
-             float* agg_save, cudaStream_t st) {
+             float* agg_save, const int32_t* node_blk, cudaStream_t st) {
   int vpl, lph;
   if (!shape_of(a, vpl, lph) || !aligned16(Pi) || !aligned16(Pj) || !aligned16(V) || !aligned16(out) ||
       !aligned16(a->attn) || !aligned16(a->out_bias) || !aligned16(agg_save) ||
@@ -593,6 +691,7 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   int rc = fill_fast(A, g, a, ef);
   if (rc) return rc;
   if (A.N == 0) return B200GAT_OK;
+  A.node_blk = node_blk;
   A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
   const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads) + A.hub_blocks;
   const bool alias = (V == Pi);
@@ -601,6 +700,15 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
                 (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
                                                                               l_save, agg_save)));
   B200_CHECK_LAUNCH("k_fwd_fast");
+  if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
+    const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
+    switch (vpl) {
+      case 2: FAST_DISPATCH_LPH(2, lph, false, (k_hub_merge_fwd<VPL, LPH><<<mb, kFastThreads, 0, st>>>(A, out, m_save, l_save, agg_save))) break;
+      case 4: FAST_DISPATCH_LPH(4, lph, false, (k_hub_merge_fwd<VPL, LPH><<<mb, kFastThreads, 0, st>>>(A, out, m_save, l_save, agg_save))) break;
+      default: FAST_DISPATCH_LPH(8, lph, false, (k_hub_merge_fwd<VPL, LPH><<<mb, kFastThreads, 0, st>>>(A, out, m_save, l_save, agg_save))) break;
+    }
+    B200_CHECK_LAUNCH("k_hub_merge_fwd");
+  }
   return B200GAT_OK;
 }
 
@@ -608,7 +716,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
              const float* Pj, const float* V, const float* s_save, const float* m_save, const float* l_save,
              const float* agg_save, const float* g_out, float* gPi, float* gPj, float* gV, float* g_attn,
              float* g_attn_bias, float* g_table, float* g_dense, float* g_affine, float* gs,
-             cudaStream_t st) {
+             int64_t n_pos, cudaStream_t st) {
   (void)g_attn_bias; (void)g_dense;
   int vpl, lph;
   if (!agg_save || !shape_of(a, vpl, lph) || !aligned16(Pi) || !aligned16(Pj) || !aligned16(V) ||
@@ -627,7 +735,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
   const int tab_in_smem = (A.emode != B200GAT_EDGE_NONE && (int64_t)A.T * HD * 4 <= 40 * 1024) ? 1 : 0;
   const size_t smem = sizeof(float) * (HD + (tab_in_smem ? (size_t)A.T * HD : 0));
-  float* alpha = gs + (int64_t)A.E * A.H;
+  float* alpha = gs + (n_pos > 0 ? n_pos : (int64_t)A.E) * A.H;   // edge positions may be those of the full graph
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
     A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
@@ -636,6 +744,13 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
                   (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
                       A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
                       gs, alpha, tab_in_smem)));
+    if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
+      const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
+      if (vpl == 2) k_hub_merge_bwd<2><<<mb, kFastThreads, 0, st>>>(A, gPj);
+      else if (vpl == 4) k_hub_merge_bwd<4><<<mb, kFastThreads, 0, st>>>(A, gPj);
+      else k_hub_merge_bwd<8><<<mb, kFastThreads, 0, st>>>(A, gPj);
+      note_launch(1);
+    }
   }
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_SRC, st);

@@ -273,19 +273,40 @@ __global__ void __launch_bounds__(128) k_bwd_src_generic(
   }
 }
 
+// Clique members (cl != NULL, node_blk[v] >= 0) keep the logits of their block in-edges
+// [run, run + n_b - 1) in s_dense[blk_soff[b]*H + h*n_b*npad + rank(v)*npad + rank(u)].
 __global__ void k_attention(int N, int H, float eps, const int32_t* __restrict__ in_ptr,
                             const int32_t* __restrict__ in_eid, const float* __restrict__ s_save,
                             const float* __restrict__ m_save, const float* __restrict__ l_save,
+                            const float* __restrict__ s_dense, const int32_t* __restrict__ node_blk,
+                            const int32_t* __restrict__ node_run, const int32_t* __restrict__ node_rank,
+                            const int32_t* __restrict__ blk_ptr, const int32_t* __restrict__ blk_soff,
                             float* __restrict__ alpha) {
   const int64_t v = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (v >= N) return;
   const int b = in_ptr[v], en = in_ptr[v + 1];
+  int run = 0, nb = 0, rank = 0, npad = 0;
+  int64_t soff = 0;
+  if (s_dense && node_blk && node_blk[v] >= 0) {
+    const int blk = node_blk[v];
+    nb = blk_ptr[blk + 1] - blk_ptr[blk];
+    npad = (nb + 3) & ~3;
+    run = node_run[v];
+    rank = node_rank[v];
+    soff = (int64_t)blk_soff[blk] * H + (int64_t)rank * npad;
+  }
   const int64_t n = (int64_t)(en - b) * H;
   for (int64_t i = lane; i < n; i += 32) {
     int e = b + (int)(i / H), h = (int)(i % H);
-    alpha[(int64_t)in_eid[e] * H + h] =
-        expf(s_save[(int64_t)e * H + h] - m_save[v * H + h]) / (l_save[v * H + h] + eps);
+    float s;
+    if (nb > 0 && e >= run && e < run + nb - 1) {
+      const int k = e - run, ur = k + (k >= rank ? 1 : 0);
+      s = s_dense[soff + (int64_t)h * nb * npad + ur];
+    } else {
+      s = s_save[(int64_t)e * H + h];
+    }
+    alpha[(int64_t)in_eid[e] * H + h] = expf(s - m_save[v * H + h]) / (l_save[v * H + h] + eps);
   }
 }
 
@@ -400,12 +421,16 @@ int generic_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edg
 using namespace b200gat;
 
 extern "C" int b200gat_attention(const b200gat_graph* g, int32_t heads, float eps, const float* s_save,
-                                 const float* m_save, const float* l_save, float* alpha, void* stream) {
+                                 const float* m_save, const float* l_save, const float* s_dense,
+                                 float* alpha, void* stream) {
   B200_CHECK_ARG(g && heads > 0, "bad arguments");
   if (g->n_nodes == 0 || g->n_edges == 0) return B200GAT_OK;
-  B200_CHECK_ARG(s_save && m_save && l_save && alpha, "null pointer");
+  B200_CHECK_ARG(s_save && m_save && l_save && alpha && g->in_eid, "null pointer");
+  const b200gat_cliques* c = (s_dense && g->cliques && g->cliques->n_blocks > 0) ? g->cliques : nullptr;
   k_attention<<<(unsigned)ceil_div((int64_t)g->n_nodes * 32, 256), 256, 0, (cudaStream_t)stream>>>(
-      g->n_nodes, heads, eps, g->in_ptr, g->in_eid, s_save, m_save, l_save, alpha);
+      g->n_nodes, heads, eps, g->in_ptr, g->in_eid, s_save, m_save, l_save, c ? s_dense : nullptr,
+      c ? c->node_blk : nullptr, c ? c->node_run : nullptr, c ? c->node_rank : nullptr,
+      c ? c->blk_ptr : nullptr, c ? c->blk_soff : nullptr, alpha);
   B200_CHECK_LAUNCH("k_attention");
   return B200GAT_OK;
 }

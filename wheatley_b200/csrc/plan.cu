@@ -278,7 +278,9 @@ __global__ void k_narrow_i64(const int64_t* __restrict__ in, int64_t n, int32_t*
   }
 }
 
-static int scan_inplace(int32_t* a, int64_t n, int32_t* bsum, cudaStream_t st) {
+int64_t scan_bsum_elems(int64_t n) { return ceil_div(n, kScanTile) + 1; }
+
+int scan_inplace(int32_t* a, int64_t n, int32_t* bsum, cudaStream_t st) {
   int nb = (int)ceil_div(n, kScanTile);
   if (nb > 1) {
     k_scan_tiles<<<nb, kScanThreads, 0, st>>>(a, n, bsum, 0);

@@ -19,6 +19,15 @@ class EdgeFeatures:
         self.mode, self.table, self.etype_sorted, self.dense = mode, table, etype_sorted, dense
         self.attr_sorted, self.affine = attr_sorted, affine     # 'affine' mode: [E,K] sorted, [K,H*D]
 
+    def graph_view(self, plan):
+        """The graph descriptor the kernels get: with clique blocks for the table / untyped modes
+        (a block needs one edge type), the plain plan otherwise."""
+        if self.mode == _lib.EDGE_TABLE:
+            return plan.clique_view(self.etype_sorted)
+        if self.mode == _lib.EDGE_NONE:
+            return plan.clique_view(None)
+        return plan
+
     @classmethod
     def none(cls):
         return cls(_lib.EDGE_NONE)
@@ -56,7 +65,7 @@ class _FusedGATConv(torch.autograd.Function):
     """out[v] = sum_{e->v} softmax_v(s_e) * V[src_e],  s_e by flavour (include/b200gat.h)."""
 
     @staticmethod
-    def forward(ctx, plan: GraphPlan, cfg: dict, Pi, Pj, V, attn, attn_bias, out_bias,
+    def forward(ctx, plan: GraphPlan, view, cfg: dict, Pi, Pj, V, attn, attn_bias, out_bias,
                 e_table, e_dense, etype_sorted, e_affine, attr_sorted):
         if not Pi.is_cuda:
             raise _lib.B200GatError("wheatley_b200 kernels need CUDA tensors (no CPU fallback)")
@@ -86,22 +95,32 @@ class _FusedGATConv(torch.autograd.Function):
         ef = _lib.EdgeFeats(mode, 0 if e_table_c is None else e_table_c.shape[0],
                             _lib.ptr(e_table_c), _lib.ptr(etype_sorted), _lib.ptr(e_dense_c),
                             n_attr, _lib.ptr(attr_sorted), _lib.ptr(e_affine_c))
+        dense = bool(_lib.lib.b200gat_conv_uses_cliques(view.c, a, ef))
+        s_dense = torch.empty(H * view.s_elems, dtype=torch.float32, device=Pi.device) if dense else None
+        if dense and agg is None:           # the dense backward needs it; the forward writes it anyway
+            agg = torch.empty((N, HD), dtype=torch.float32, device=Pi.device)
         with torch.cuda.device(Pi.device):
-            _lib.check(_lib.lib.b200gat_conv_fwd(plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
+            _lib.check(_lib.lib.b200gat_conv_fwd(view.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
                                                  _lib.ptr(out), _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
-                                                 _lib.ptr(agg), _lib.stream_ptr()), "b200gat_conv_fwd")
-        ctx.plan, ctx.cfg, ctx.mode, ctx.v_alias = plan, cfg, mode, v_alias
+                                                 _lib.ptr(agg), _lib.ptr(s_dense), _lib.stream_ptr()),
+                       "b200gat_conv_fwd")
+        ctx.plan, ctx.view, ctx.cfg, ctx.mode, ctx.v_alias = plan, view, cfg, mode, v_alias
+        ctx.dense = dense
         ctx.etype_sorted, ctx.attr_sorted = etype_sorted, attr_sorted
         ctx.has_out_bias = out_bias is not None
         ctx.attn_shape = attn.shape
-        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg)
-        ctx.mark_non_differentiable(s, m, l)
-        return out, s, m, l
+        ctx.save_for_backward(Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg,
+                              s_dense)
+        if s_dense is None:
+            s_dense = torch.empty(0, dtype=torch.float32, device=Pi.device)
+        ctx.mark_non_differentiable(s, m, l, s_dense)
+        return out, s, m, l, s_dense
 
     @staticmethod
-    def backward(ctx, g_out, _gs, _gm, _gl):
-        Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg = ctx.saved_tensors
-        plan, cfg = ctx.plan, ctx.cfg
+    def backward(ctx, g_out, _gs, _gm, _gl, _gsd):
+        (Pi, Pj, Vt, attn_c, attn_bias_c, e_table_c, e_dense_c, e_affine_c, s, m, l, agg,
+         s_dense) = ctx.saved_tensors
+        plan, view, cfg = ctx.plan, ctx.view, ctx.cfg
         H, D = cfg["heads"], cfg["dim"]
         g_out = _f32c(g_out)
         gPi = torch.empty_like(Pi)
@@ -112,7 +131,10 @@ class _FusedGATConv(torch.autograd.Function):
         g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None
         g_dense = torch.empty_like(e_dense_c) if e_dense_c is not None else None
         g_affine = torch.zeros_like(e_affine_c) if e_affine_c is not None else None
-        gs = torch.empty((2,) + tuple(s.shape), dtype=s.dtype, device=s.device)
+        n_gs = 2 * s.numel()
+        if ctx.dense:       # + gs_dense [H*s_elems] + gsum_u / gsum_v [N*H]   (include/b200gat.h)
+            n_gs += ((H * view.s_elems + 3) // 4) * 4 + 2 * plan.n_nodes * H
+        gs = torch.empty(n_gs, dtype=s.dtype, device=s.device)
         a = _lib.Attn(cfg["flavour"], H, D, cfg["slope"], cfg["eps"], _lib.ptr(attn_c),
                       _lib.ptr(attn_bias_c), None)
         ef = _lib.EdgeFeats(ctx.mode, 0 if e_table_c is None else e_table_c.shape[0],
@@ -121,12 +143,13 @@ class _FusedGATConv(torch.autograd.Function):
                             _lib.ptr(e_affine_c))
         with torch.cuda.device(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_bwd(
-                plan.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
-                _lib.ptr(l), _lib.ptr(agg), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj), _lib.ptr(gV),
+                view.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
+                _lib.ptr(l), _lib.ptr(agg), _lib.ptr(s_dense), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj),
+                _lib.ptr(gV),
                 _lib.ptr(g_attn), _lib.ptr(g_attn_bias), _lib.ptr(g_table), _lib.ptr(g_dense),
                 _lib.ptr(g_affine), _lib.ptr(gs), _lib.stream_ptr()), "b200gat_conv_bwd")
         g_bias = g_out.sum(0) if ctx.has_out_bias else None
-        return (None, None, gPi, gPj, None if ctx.v_alias else gV, g_attn.view(ctx.attn_shape),
+        return (None, None, None, gPi, gPj, None if ctx.v_alias else gV, g_attn.view(ctx.attn_shape),
                 g_attn_bias, g_bias, g_table, g_dense, None, g_affine, None)
 
 
@@ -138,19 +161,21 @@ def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_AD
     e_table = ef.table if ef.mode in (_lib.EDGE_TABLE, _lib.EDGE_AFFINE) else None
     e_dense = ef.dense if ef.mode == _lib.EDGE_DENSE else None
     e_affine = ef.affine if ef.mode == _lib.EDGE_AFFINE else None
-    out, s, m, l = _FusedGATConv.apply(plan, cfg, Pi, Pj, V, attn, attn_bias, out_bias, e_table,
-                                       e_dense, ef.etype_sorted if e_table is not None else None,
-                                       e_affine, ef.attr_sorted if e_affine is not None else None)
-    return out, (s, m, l)
+    view = ef.graph_view(plan) if flavour == _lib.FLAVOUR_ADDITIVE else plan
+    out, s, m, l, s_dense = _FusedGATConv.apply(plan, view, cfg, Pi, Pj, V, attn, attn_bias, out_bias, e_table,
+                                                e_dense, ef.etype_sorted if e_table is not None else None,
+                                                e_affine, ef.attr_sorted if e_affine is not None else None)
+    return out, (s, m, l, s_dense if s_dense.numel() else None, view)
 
 
 def attention_weights(plan: GraphPlan, saved, heads: int, eps: float) -> torch.Tensor:
     """alpha [E, H] in the original edge order from the logits saved by the forward."""
-    s, m, l = saved
+    s, m, l, s_dense, view = saved
     alpha = torch.empty((plan.n_edges, heads), dtype=torch.float32, device=s.device)
     with torch.cuda.device(s.device):
-        _lib.check(_lib.lib.b200gat_attention(plan.c, heads, eps, _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
-                                              _lib.ptr(alpha), _lib.stream_ptr()), "b200gat_attention")
+        _lib.check(_lib.lib.b200gat_attention(view.c, heads, eps, _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
+                                              _lib.ptr(s_dense), _lib.ptr(alpha), _lib.stream_ptr()),
+                   "b200gat_attention")
     return alpha
 
 

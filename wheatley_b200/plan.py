@@ -5,9 +5,105 @@ by forward and backward.
 Replaces what DGL builds behind ``apply_edges / edge_softmax / update_all``
 (generic/eegatconv.py:269,280,292) and PyG behind ``propagate``
 (generic/gatv3_conv.py:155-160)."""
+import ctypes as C
+import os
+
 import torch
 
 from . import _lib
+
+
+def _orders_and_hubs(in_ptr, in_src, out_ptr, out_dst, N, dev):
+    """Locality orders and hub lists of one CSR pair (full graph or residual)."""
+    i32 = dict(dtype=torch.int32, device=dev)
+    dst_order = torch.empty(N, **i32)
+    src_order = torch.empty(N, **i32)
+    oscr = torch.empty(_lib.lib.b200gat_node_order_scratch_elems(N), **i32)
+    for ptr_, nbr_, out_ in ((in_ptr, in_src, dst_order), (out_ptr, out_dst, src_order)):
+        _lib.check(_lib.lib.b200gat_node_order(_lib.ptr(ptr_), _lib.ptr(nbr_), N, _lib.ptr(out_),
+                                               _lib.ptr(oscr), _lib.stream_ptr()), "b200gat_node_order")
+    hub_dst = torch.empty(N, **i32)
+    hub_src = torch.empty(N, **i32)
+    n_hub = torch.empty(2, **i32)
+    for k, (ptr_, lst_) in enumerate(((in_ptr, hub_dst), (out_ptr, hub_src))):
+        _lib.check(_lib.lib.b200gat_hub_list(_lib.ptr(ptr_), N, _lib.HUB_DEGREE, _lib.ptr(lst_),
+                                             n_hub.data_ptr() + 4 * k, _lib.stream_ptr()), "b200gat_hub_list")
+    return dst_order, src_order, hub_dst, hub_src, n_hub
+
+
+def _graph_struct(N, E, in_ptr, in_src, in_eid, out_ptr, out_dst, out_pos, dst_order, src_order, hub_dst,
+                  hub_src, n_hub, in_pos=None):
+    g = _lib.Graph()
+    g.n_nodes, g.n_edges = N, E
+    g.in_ptr, g.in_src, g.in_eid = _lib.ptr(in_ptr), _lib.ptr(in_src), _lib.ptr(in_eid)
+    g.out_ptr, g.out_dst, g.out_pos = _lib.ptr(out_ptr), _lib.ptr(out_dst), _lib.ptr(out_pos)
+    g.dst_order, g.src_order = _lib.ptr(dst_order), _lib.ptr(src_order)
+    g.hub_degree = _lib.HUB_DEGREE
+    g.hub_dst, g.n_hub_dst = _lib.ptr(hub_dst), n_hub.data_ptr()
+    g.hub_src, g.n_hub_src = _lib.ptr(hub_src), n_hub.data_ptr() + 4
+    g.in_pos = _lib.ptr(in_pos)
+    return g
+
+
+def _attach_hub_scratch(g, n_hub_dst, dev):
+    """Scratch for splitting each hub destination over HUB_PARTS CTAs (include/b200gat.h)."""
+    if n_hub_dst <= 0:
+        return None
+    scratch = torch.empty(n_hub_dst * _lib.HUB_PARTS * _lib.HUB_REC, dtype=torch.float32, device=dev)
+    g.hub_scratch, g.hub_parts, g.hub_cap = scratch.data_ptr(), _lib.HUB_PARTS, n_hub_dst
+    return scratch
+
+
+class CliqueView:
+    """The plan's graph descriptor with the dense clique blocks of ONE edge typing attached
+    (``b200gat_clique_build``): block tables + the residual CSR of the edges outside the blocks.
+    ``c`` is what ``b200gat_conv_fwd/bwd`` take; it equals the plain plan when no block was found."""
+
+    def __init__(self, plan, etype_sorted):
+        N, E, dev = plan.n_nodes, plan.n_edges, plan.device
+        i32 = dict(dtype=torch.int32, device=dev)
+        self.plan, self.etype_sorted = plan, etype_sorted
+        self.n_blocks = self.max_block = self.n_members = self.s_elems = self.n_res_edges = 0
+        self.c = plan.c
+        if N == 0 or E == 0:
+            return
+        with torch.cuda.device(dev):
+            self.node_blk, self.node_run, self.node_rank = (torch.empty(N, **i32) for _ in range(3))
+            self.blk_ptr, self.blk_soff = torch.empty(N + 1, **i32), torch.empty(N + 1, **i32)
+            self.blk_nodes, self.blk_type = torch.empty(N, **i32), torch.empty(N, **i32)
+            r_in_ptr, r_out_ptr = torch.empty(N + 1, **i32), torch.empty(N + 1, **i32)
+            r_in_src, r_in_pos, r_out_dst, r_out_pos = (torch.empty(E, **i32) for _ in range(4))
+            counts = torch.empty(8, **i32)
+            scratch = torch.empty(_lib.lib.b200gat_clique_scratch_elems(N, E) + 2, **i32)
+            off = (-scratch.data_ptr() // 4) % 2          # 8-byte alignment
+            _lib.check(_lib.lib.b200gat_clique_build(
+                plan.c, _lib.ptr(etype_sorted), _lib.MIN_CLIQUE, _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
+                _lib.ptr(self.node_rank), _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes),
+                _lib.ptr(self.blk_type), _lib.ptr(self.blk_soff), _lib.ptr(r_in_ptr), _lib.ptr(r_in_src),
+                _lib.ptr(r_in_pos), _lib.ptr(r_out_ptr), _lib.ptr(r_out_dst), _lib.ptr(r_out_pos),
+                _lib.ptr(counts), scratch.data_ptr() + 4 * off, _lib.stream_ptr()), "b200gat_clique_build")
+            self.r_aux = _orders_and_hubs(r_in_ptr, r_in_src, r_out_ptr, r_out_dst, N, dev)
+            host = torch.cat([counts, self.r_aux[4]]).tolist()          # the one device->host copy
+            self.n_blocks, self.max_block, self.n_res_edges, self.n_members, self.s_elems = host[:5]
+            n_hub_dst = host[8]
+            if self.n_blocks == 0:
+                return
+            Er = self.n_res_edges
+            self.r = (r_in_ptr, r_in_src[:Er], r_in_pos[:Er], r_out_ptr, r_out_dst[:Er], r_out_pos[:Er])
+        dst_order, src_order, hub_dst, hub_src, n_hub = self.r_aux
+        self._res_c = _graph_struct(N, Er, r_in_ptr, r_in_src, None, r_out_ptr, r_out_dst, r_out_pos, dst_order,
+                                    src_order, hub_dst, hub_src, n_hub, in_pos=r_in_pos)
+        self._hub_scratch = _attach_hub_scratch(self._res_c, n_hub_dst, dev)
+        self._cl = _lib.Cliques(self.n_blocks, self.max_block, self.n_members, self.s_elems,
+                                _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes), _lib.ptr(self.blk_type),
+                                _lib.ptr(self.blk_soff), _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
+                                _lib.ptr(self.node_rank))
+        base = plan.c
+        self.c = _lib.Graph()
+        for f, _ in _lib.Graph._fields_:
+            setattr(self.c, f, getattr(base, f))
+        self.c.cliques = C.pointer(self._cl)
+        self.c.residual = C.pointer(self._res_c)
 
 
 class GraphPlan:
@@ -37,30 +133,17 @@ class GraphPlan:
                 _lib.ptr(self.in_eid), _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst),
                 _lib.ptr(self.out_pos), _lib.ptr(scratch), _lib.ptr(self.stats),
                 _lib.stream_ptr()), "b200gat_plan_build")
-            # locality order of destinations / sources (a permutation: affects scheduling only)
-            self.dst_order = torch.empty(N, **i32)
-            self.src_order = torch.empty(N, **i32)
-            oscr = torch.empty(_lib.lib.b200gat_node_order_scratch_elems(N), **i32)
-            for ptr_, nbr_, out_ in ((self.in_ptr, self.in_src, self.dst_order),
-                                     (self.out_ptr, self.out_dst, self.src_order)):
-                _lib.check(_lib.lib.b200gat_node_order(_lib.ptr(ptr_), _lib.ptr(nbr_), N, _lib.ptr(out_),
-                                                       _lib.ptr(oscr), _lib.stream_ptr()),
-                           "b200gat_node_order")
+            # locality order of destinations / sources (a permutation: affects scheduling only) and
             # hub nodes (segments longer than HUB_DEGREE are split over a CTA's warps)
-            self.hub_dst = torch.empty(N, **i32)
-            self.hub_src = torch.empty(N, **i32)
-            self.n_hub = torch.empty(2, **i32)
-            for k, (ptr_, lst_) in enumerate(((self.in_ptr, self.hub_dst), (self.out_ptr, self.hub_src))):
-                _lib.check(_lib.lib.b200gat_hub_list(_lib.ptr(ptr_), N, _lib.HUB_DEGREE, _lib.ptr(lst_),
-                                                     self.n_hub.data_ptr() + 4 * k, _lib.stream_ptr()),
-                           "b200gat_hub_list")
+            (self.dst_order, self.src_order, self.hub_dst, self.hub_src,
+             self.n_hub) = _orders_and_hubs(self.in_ptr, self.in_src, self.out_ptr, self.out_dst, N, dev)
         self._stats_host = None
-        self._c = _lib.Graph(N, E, _lib.ptr(self.in_ptr), _lib.ptr(self.in_src), _lib.ptr(self.in_eid),
-                             _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst), _lib.ptr(self.out_pos),
-                             _lib.ptr(self.dst_order), _lib.ptr(self.src_order), _lib.HUB_DEGREE,
-                             _lib.ptr(self.hub_dst), self.n_hub.data_ptr(), _lib.ptr(self.hub_src),
-                             self.n_hub.data_ptr() + 4)
+        self._hub_scratch = None
+        self._c = _graph_struct(N, E, self.in_ptr, self.in_src, self.in_eid, self.out_ptr, self.out_dst,
+                                self.out_pos, self.dst_order, self.src_order, self.hub_dst, self.hub_src,
+                                self.n_hub)
         self._sorted_cache = {}
+        self._clique_views = {}
 
     @classmethod
     def from_edge_index(cls, edge_index: torch.Tensor, n_nodes: int):
@@ -69,13 +152,30 @@ class GraphPlan:
 
     @property
     def c(self):
+        self.stats_host()                  # first use: one device->host copy, sizes the hub scratch
         return self._c
+
+    def clique_view(self, etype_sorted=None) -> CliqueView:
+        """Dense clique blocks for one edge typing (``None`` = untyped), built once and cached.
+        One small device->host copy (block counts) per (plan, typing)."""
+        key = None if etype_sorted is None else (etype_sorted.data_ptr(), etype_sorted._version)
+        view = self._clique_views.get(key)
+        if view is None:
+            if os.environ.get("WHEATLEY_B200_CLIQUES", "1") == "0":
+                view = CliqueView.__new__(CliqueView)
+                view.plan, view.c, view.n_blocks, view.s_elems = self, self.c, 0, 0
+            else:
+                view = CliqueView(self, etype_sorted)
+            self._clique_views[key] = view
+        return view
 
     def stats_host(self):
         """(n_zero_in_degree, max_in_degree, n_bad_edges, max_out_degree); one device sync,
         cached."""
         if self._stats_host is None:
-            self._stats_host = tuple(int(x) for x in self.stats.tolist())
+            host = torch.cat([self.stats, self.n_hub]).tolist()
+            self._stats_host = tuple(int(x) for x in host[:4])
+            self._hub_scratch = _attach_hub_scratch(self._c, int(host[4]), self.device)
         return self._stats_host
 
     def validate(self):
