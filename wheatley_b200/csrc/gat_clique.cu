@@ -84,36 +84,47 @@ __device__ __forceinline__ void stage_item(const CliqueArgs& A, const ItemSmem& 
                                            const float* __restrict__ Pi, const float* __restrict__ Pj,
                                            const float* __restrict__ V) {
   const int hoff = h * kD;
-  for (int idx = tid; idx < A.rv * 16; idx += nthr) {
-    const int row = idx >> 4, c4 = (idx & 15) * 4;
-    const bool valid = row < n;
-    const int64_t node = valid ? nodes[row] : 0;
-    float4 a4 = __ldg(reinterpret_cast<const float4*>(A.attn + hoff + c4));
-    float4 pi = make_float4(0.f, 0.f, 0.f, 0.f), pj = pi, vv = pi;
-    if (valid) {
-      pi = __ldg(reinterpret_cast<const float4*>(Pi + node * A.HD + hoff + c4));
-      pj = __ldg(reinterpret_cast<const float4*>(Pj + node * A.HD + hoff + c4));
-      if (A.table) {
-        const float4 tb = __ldg(reinterpret_cast<const float4*>(A.table + (int64_t)type * A.HD + hoff + c4));
-        pj.x += tb.x; pj.y += tb.y; pj.z += tb.z; pj.w += tb.w;
-      }
-      if (WITH_V && !ALIAS) vv = __ldg(reinterpret_cast<const float4*>(V + node * A.HD + hoff + c4));
-    }
-    if (row < A.ru) {
-      *reinterpret_cast<float4*>(S.pi + row * kSP + c4) = pi;
-      if (WITH_V && !ALIAS) *reinterpret_cast<float4*>(S.v + row * kSP + c4) = vv;
-    }
-    *reinterpret_cast<float4*>(S.npj + row * kSQ + c4) = make_float4(-pj.x, -pj.y, -pj.z, -pj.w);
-    float di = a4.x * pi.x + a4.y * pi.y + a4.z * pi.z + a4.w * pi.w;
-    float dj = a4.x * pj.x + a4.y * pj.y + a4.z * pj.z + a4.w * pj.w;
+  const int c4 = (tid & 15) * 4;
+  const float4 a4 = __ldg(reinterpret_cast<const float4*>(A.attn + hoff + c4));
+  float4 tb = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (A.table) tb = __ldg(reinterpret_cast<const float4*>(A.table + (int64_t)type * A.HD + hoff + c4));
+  // rv * 16 == 8 * nthr float4 slots: two batches of four, all global loads of a batch in flight together
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    float4 pi[4], pj[4], vv[4];
 #pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {
-      di += __shfl_xor_sync(0xffffffffu, di, o);
-      dj += __shfl_xor_sync(0xffffffffu, dj, o);
+    for (int k = 0; k < 4; ++k) {
+      const int row = (tid + (half * 4 + k) * nthr) >> 4;
+      pi[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      pj[k] = pi[k];
+      vv[k] = pi[k];
+      if (row < n) {
+        const int64_t node = nodes[row];
+        pi[k] = __ldg(reinterpret_cast<const float4*>(Pi + node * A.HD + hoff + c4));
+        pj[k] = __ldg(reinterpret_cast<const float4*>(Pj + node * A.HD + hoff + c4));
+        if (WITH_V && !ALIAS) vv[k] = __ldg(reinterpret_cast<const float4*>(V + node * A.HD + hoff + c4));
+      }
     }
-    if ((idx & 15) == 0) {
-      if (row < A.ru) S.ai[row] = A.slope * di;
-      S.aj[row] = dj;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int row = (tid + (half * 4 + k) * nthr) >> 4;
+      if (row < n) { pj[k].x += tb.x; pj[k].y += tb.y; pj[k].z += tb.z; pj[k].w += tb.w; }
+      if (row < A.ru) {
+        *reinterpret_cast<float4*>(S.pi + row * kSP + c4) = pi[k];
+        if (WITH_V && !ALIAS) *reinterpret_cast<float4*>(S.v + row * kSP + c4) = vv[k];
+      }
+      *reinterpret_cast<float4*>(S.npj + row * kSQ + c4) = make_float4(-pj[k].x, -pj[k].y, -pj[k].z, -pj[k].w);
+      float di = a4.x * pi[k].x + a4.y * pi[k].y + a4.z * pi[k].z + a4.w * pi[k].w;
+      float dj = a4.x * pj[k].x + a4.y * pj[k].y + a4.z * pj[k].z + a4.w * pj[k].w;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        di += __shfl_xor_sync(0xffffffffu, di, o);
+        dj += __shfl_xor_sync(0xffffffffu, dj, o);
+      }
+      if ((tid & 15) == 0) {
+        if (row < A.ru) S.ai[row] = A.slope * di;
+        S.aj[row] = dj;
+      }
     }
   }
   if (tid < 16) *reinterpret_cast<float4*>(S.at + tid * 4) = __ldg(reinterpret_cast<const float4*>(A.attn + hoff + tid * 4));
@@ -426,26 +437,44 @@ __global__ void __launch_bounds__(256, 2) k_clq_bwd_mma(CliqueArgs A, const floa
     n = A.blk_ptr[b + 1] - A.blk_ptr[b];
     nodes = A.blk_nodes + A.blk_ptr[b];
     const int hoff = h * kD;
-    for (int idx = tid; idx < A.rv * 16; idx += nthr) {
-      const int row = idx >> 4, c4 = (idx & 15) * 4;
-      const bool valid = row < n;
-      const int64_t node = valid ? nodes[row] : 0;
-      float4 vv = make_float4(0.f, 0.f, 0.f, 0.f), gg = vv, ag = vv;
-      if (valid) {
-        vv = __ldg(reinterpret_cast<const float4*>(V + node * A.HD + hoff + c4));
-        gg = __ldg(reinterpret_cast<const float4*>(G + node * A.HD + hoff + c4));
-        ag = __ldg(reinterpret_cast<const float4*>(agg + node * A.HD + hoff + c4));
-      }
-      *reinterpret_cast<float4*>(S.v + row * kSB + c4) = vv;
-      *reinterpret_cast<float4*>(S.g + row * kSB + c4) = gg;
-      float d = gg.x * ag.x + gg.y * ag.y + gg.z * ag.z + gg.w * ag.w;
+    const int c4 = (tid & 15) * 4;
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {      // rv * 16 == 8 * nthr float4 slots, loads of a batch in flight together
+      float4 vv[4], gg[4], ag[4];
+      float mm[4], ll[4];
 #pragma unroll
-      for (int o = 8; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-      if ((idx & 15) == 0) {
-        S.dot[row] = d;
-        S.m[row] = valid ? m_save[node * A.H + h] : 0.f;
-        S.linv[row] = valid ? 1.f / (l_save[node * A.H + h] + A.eps) : 0.f;
-        S.gsv[row] = 0.f;
+      for (int k = 0; k < 4; ++k) {
+        const int row = (tid + (half * 4 + k) * nthr) >> 4;
+        vv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        gg[k] = vv[k];
+        ag[k] = vv[k];
+        mm[k] = 0.f;
+        ll[k] = 0.f;
+        if (row < n) {
+          const int64_t node = nodes[row];
+          vv[k] = __ldg(reinterpret_cast<const float4*>(V + node * A.HD + hoff + c4));
+          gg[k] = __ldg(reinterpret_cast<const float4*>(G + node * A.HD + hoff + c4));
+          ag[k] = __ldg(reinterpret_cast<const float4*>(agg + node * A.HD + hoff + c4));
+          if ((tid & 15) == 0) {
+            mm[k] = m_save[node * A.H + h];
+            ll[k] = 1.f / (l_save[node * A.H + h] + A.eps);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int row = (tid + (half * 4 + k) * nthr) >> 4;
+        *reinterpret_cast<float4*>(S.v + row * kSB + c4) = vv[k];
+        *reinterpret_cast<float4*>(S.g + row * kSB + c4) = gg[k];
+        float d = gg[k].x * ag[k].x + gg[k].y * ag[k].y + gg[k].z * ag[k].z + gg[k].w * ag[k].w;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        if ((tid & 15) == 0) {
+          S.dot[row] = d;
+          S.m[row] = mm[k];
+          S.linv[row] = ll[k];
+          S.gsv[row] = 0.f;
+        }
       }
     }
   }
@@ -502,17 +531,21 @@ __global__ void __launch_bounds__(256, 2) k_clq_bwd_mma(CliqueArgs A, const floa
 
 
 // ------------------------------------------------------------------------------------------ backward, part 2
-// Element-wise part, one work item = (block, head), warp = 16 sources, lane = features {2*lane, 2*lane+1}:
+// Element-wise part, one work item = (block, head) on one 8-warp CTA.  Warp w owns the features
+// d in [8w, 8w+8); lane = (dl = lane/4, ug = lane%4) owns feature d = 8w + dl and the GU sources
+// u in [ug*GU, (ug+1)*GU) (4*GU >= n), so a thread holds Pi[u,d] and Qu[u,d] of its sources in registers:
 //   step[u,v,d] = Pi[u,d] > -Pj'[v,d]                       (== z > 0)
 //   Qu[u,d] = sum_v gs[u,v] step ,  Qv[v,d] = sum_u gs[u,v] step        (one compare + two predicated adds)
 //   gPi'[u,d] = slope*gsum_u[u] + (1-slope)*Qu[u,d]   ->  gPi[u,d] += a_d gPi'
 //   gPj'[v,d] = slope*gsum_v[v] + (1-slope)*Qv[v,d]   ->  gPj[v,d] += a_d gPj' ; g_table[type,d] += a_d gPj'
 //   g_attn[d] += sum_u Pi[u,d] gPi'[u,d] + sum_v Pj'[v,d] gPj'[v,d]
 // (leaky'(z) = slope + (1-slope) step ; leaky(z) = leaky'(z) z ; z = Pi[u] + Pj'[v].)
-__host__ __device__ inline int clique_bwd2_floats(int rows, int tiles) {
-  return 2 * rows * kD + 2 * kD + tiles * rows * 16;      // -Pj' | Qv | g_attn, g_table partials | per-warp gs slabs
+// Qv[v,d] is complete inside the CTA's four ug lanes (two shuffles): no atomics on node rows, no second phase.
+__host__ __device__ inline int clique_bwd2_floats(int n_max, int gu) {
+  return n_max * kD + n_max * (4 * gu > kD ? 4 * gu : kD) + 3 * n_max;
 }
 
+template <int GU>
 __global__ void __launch_bounds__(256, 2) k_clq_bwd_elem(CliqueArgs A, const float* __restrict__ Pi,
                                                           const float* __restrict__ Pj,
                                                           const float* __restrict__ gs_dense,
@@ -521,130 +554,135 @@ __global__ void __launch_bounds__(256, 2) k_clq_bwd_elem(CliqueArgs A, const flo
                                                           float* __restrict__ gPj, float* __restrict__ g_attn,
                                                           float* __restrict__ g_table) {
   extern __shared__ __align__(16) float smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot = warp / A.tiles, ut = warp - slot * A.tiles;
-  const int item = blockIdx.x * A.ipc + slot;
-  const bool item_ok = item < A.n_items;
-  float* base = smem + (size_t)slot * A.item_floats;
-  float* sNPj = base;                 // [rows][64]  -(Pj + table)
-  float* sQv = base + A.rv * kD;      // [rows][64]
-  float* sGat = sQv + A.rv * kD;      // [64]
-  float* sTab = sGat + kD;            // [64]
-  float* sGs = sTab + kD + (size_t)ut * A.rv * 16;   // [rows][16] gs[v][ub .. ub+15] of this warp's sources
-  int b = 0, h = 0, n = 0, type = 0;
-  const int32_t* nodes = nullptr;
-  const int tid = threadIdx.x - slot * A.tiles * 32, nthr = A.tiles * 32;
-  if (item_ok) {
-    b = item / A.H;
-    h = item - b * A.H;
-    n = A.blk_ptr[b + 1] - A.blk_ptr[b];
-    nodes = A.blk_nodes + A.blk_ptr[b];
-    type = A.blk_type[b];
-    const int hoff = h * kD;
-    for (int idx = tid; idx < n * 16; idx += nthr) {
-      const int row = idx >> 4, c4 = (idx & 15) * 4;
-      const int64_t node = nodes[row];
-      float4 pj = __ldg(reinterpret_cast<const float4*>(Pj + node * A.HD + hoff + c4));
-      if (A.table) {
-        const float4 tb = __ldg(reinterpret_cast<const float4*>(A.table + (int64_t)type * A.HD + hoff + c4));
-        pj.x += tb.x; pj.y += tb.y; pj.z += tb.z; pj.w += tb.w;
-      }
-      *reinterpret_cast<float4*>(sNPj + row * kD + c4) = make_float4(-pj.x, -pj.y, -pj.z, -pj.w);
-      *reinterpret_cast<float4*>(sQv + row * kD + c4) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    for (int i = tid; i < 2 * kD; i += nthr) sGat[i] = 0.f;      // sGat + sTab are contiguous
-  }
-  __syncthreads();
-  const int hcol = h * kD + 2 * lane;
-  const float c1 = 1.f - A.slope;
-  float2 at = make_float2(0.f, 0.f);
-  float gat0 = 0.f, gat1 = 0.f;
-  if (item_ok) at = __ldg(reinterpret_cast<const float2*>(A.attn + hcol));
-  if (item_ok && ut * 16 < n) {
-    const int ub = ut * 16, nu = min(16, n - ub);
-    const int npad = (n + 3) & ~3;
-    const float* gsd = gs_dense + (int64_t)A.blk_soff[b] * A.H + (int64_t)h * n * npad + ub;
-    float2 pi[16], qu[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      pi[i] = make_float2(0.f, 0.f);
-      qu[i] = make_float2(0.f, 0.f);
-      if (i < nu) pi[i] = __ldg(reinterpret_cast<const float2*>(Pi + (int64_t)nodes[ub + i] * A.HD + hcol));
-    }
-    // gs[v][ub .. ub+15] of all destinations -> this warp's slab (coalesced 16-byte loads, sources beyond
-    // the block masked to 0), then four broadcast 16-byte shared loads per destination
-    {
-      const int rr = lane >> 2, k4 = (lane & 3) * 4;
+  constexpr int SG = 4 * GU;                 // row stride of the gs tile
+  const int item = blockIdx.x;
+  const int b = item / A.H, h = item - b * A.H;
+  const int n = A.blk_ptr[b + 1] - A.blk_ptr[b];
+  const int32_t* __restrict__ nodes = A.blk_nodes + A.blk_ptr[b];
+  const int type = A.blk_type[b];
+  const int hoff = h * kD, npad = (n + 3) & ~3;
+  float* sNPj = smem;                        // [n][64]   -(Pj + table)
+  float* sGs = sNPj + A.ru * kD;             // [n][SG]   gs[v][u], zero beyond the block
+  float* sGv = sGs + A.ru * (SG > kD ? SG : kD);   // [n]  slope * gsum_v
+  float* sGu = sGv + A.ru;                   // [n]       slope * gsum_u
+  int* sNode = reinterpret_cast<int*>(sGu + A.ru);   // [n]
+  const float* gsd = gs_dense + (int64_t)A.blk_soff[b] * A.H + (int64_t)h * n * npad;
+
 #pragma unroll 4
-      for (int r0 = 0; r0 < n; r0 += 8) {
-        const int r = r0 + rr;
-        float4 gq = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < n && k4 < nu) gq = __ldg(reinterpret_cast<const float4*>(gsd + (int64_t)r * npad + k4));
-        if (k4 + 1 >= nu) gq.y = 0.f;
-        if (k4 + 2 >= nu) gq.z = 0.f;
-        if (k4 + 3 >= nu) gq.w = 0.f;
-        if (r < n) *reinterpret_cast<float4*>(sGs + r * 16 + k4) = gq;
-      }
-      __syncwarp();
+  for (int idx = threadIdx.x; idx < n * 16; idx += 256) {
+    const int row = idx >> 4, c4 = (idx & 15) * 4;
+    const int64_t node = nodes[row];
+    float4 pj = __ldg(reinterpret_cast<const float4*>(Pj + node * A.HD + hoff + c4));
+    if (A.table) {
+      const float4 tb = __ldg(reinterpret_cast<const float4*>(A.table + (int64_t)type * A.HD + hoff + c4));
+      pj.x += tb.x; pj.y += tb.y; pj.z += tb.z; pj.w += tb.w;
     }
-    for (int v = 0; v < n; ++v) {
-      const float2 q = *reinterpret_cast<const float2*>(sNPj + v * kD + 2 * lane);
-      float4 gc[4];
+    *reinterpret_cast<float4*>(sNPj + row * kD + c4) = make_float4(-pj.x, -pj.y, -pj.z, -pj.w);
+  }
+#pragma unroll 4
+  for (int idx = threadIdx.x; idx < n * GU; idx += 256) {       // GU float4 per row
+    const int row = idx / GU, c = (idx - row * GU) * 4;
+    float4 gq = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < n) gq = __ldg(reinterpret_cast<const float4*>(gsd + (int64_t)row * npad + c));
+    if (c + 1 >= n) gq.y = 0.f;
+    if (c + 2 >= n) gq.z = 0.f;
+    if (c + 3 >= n) gq.w = 0.f;
+    *reinterpret_cast<float4*>(sGs + row * SG + c) = gq;
+  }
+  for (int row = threadIdx.x; row < n; row += 256) {
+    const int node = nodes[row];
+    sNode[row] = node;
+    sGv[row] = A.slope * __ldg(gsum_v + (int64_t)node * A.H + h);
+    sGu[row] = A.slope * __ldg(gsum_u + (int64_t)node * A.H + h);
+  }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dl = lane >> 2, ug = lane & 3;
+  const int d = warp * 8 + dl, col = hoff + d;
+  const int u0 = ug * GU;
+  const float c1 = 1.f - A.slope;
+  const float at = __ldg(A.attn + col);
+  float pi[GU], qu[GU];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) gc[k] = *reinterpret_cast<const float4*>(sGs + v * 16 + 4 * k);
-      float qa[4] = {0.f, 0.f, 0.f, 0.f}, qb[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const float4 g4 = gc[i >> 2];
-        const float gsv = (i & 3) == 0 ? g4.x : (i & 3) == 1 ? g4.y : (i & 3) == 2 ? g4.z : g4.w;
-        if (pi[i].x > q.x) { qu[i].x += gsv; qa[i & 3] += gsv; }
-        if (pi[i].y > q.y) { qu[i].y += gsv; qb[i & 3] += gsv; }
-      }
-      atomicAdd(sQv + v * kD + 2 * lane, (qa[0] + qa[1]) + (qa[2] + qa[3]));
-      atomicAdd(sQv + v * kD + 2 * lane + 1, (qb[0] + qb[1]) + (qb[2] + qb[3]));
-    }
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      if (i < nu) {
-        const int64_t node = nodes[ub + i];
-        const float su = A.slope * __ldg(gsum_u + node * A.H + h);
-        const float g0 = fmaf(c1, qu[i].x, su), g1 = fmaf(c1, qu[i].y, su);
-        gat0 = fmaf(pi[i].x, g0, gat0);
-        gat1 = fmaf(pi[i].y, g1, gat1);
-        float2* p = reinterpret_cast<float2*>(gPi + node * A.HD + hcol);
-        float2 o = *p;
-        *p = make_float2(fmaf(at.x, g0, o.x), fmaf(at.y, g1, o.y));
-      }
-    }
+  for (int j = 0; j < GU; ++j) {
+    qu[j] = 0.f;
+    pi[j] = (u0 + j < n) ? __ldg(Pi + (int64_t)nodes[u0 + j] * A.HD + col) : 0.f;
   }
   __syncthreads();
-  if (item_ok) {
-    float tab0 = 0.f, tab1 = 0.f;
-    for (int v = ut; v < n; v += A.tiles) {
-      const int64_t node = nodes[v];
-      const float sv = A.slope * __ldg(gsum_v + node * A.H + h);
-      const float2 qv = *reinterpret_cast<const float2*>(sQv + v * kD + 2 * lane);
-      const float2 q = *reinterpret_cast<const float2*>(sNPj + v * kD + 2 * lane);
-      const float g0 = fmaf(c1, qv.x, sv), g1 = fmaf(c1, qv.y, sv);
-      gat0 = fmaf(-q.x, g0, gat0);
-      gat1 = fmaf(-q.y, g1, gat1);
-      const float t0 = at.x * g0, t1 = at.y * g1;
-      tab0 += t0; tab1 += t1;
-      float2* p = reinterpret_cast<float2*>(gPj + node * A.HD + hcol);
-      float2 o = *p;
-      *p = make_float2(o.x + t0, o.y + t1);
+
+  float gat = 0.f, tab = 0.f;
+  // The cross-lane sum of Qv[v,d] (two shuffles over the four ug lanes) is software-pipelined: the shuffles of
+  // destination v-1 are issued between the two halves of destination v's compare/add block.
+  float qv_pend = 0.f, q_pend = 0.f;
+  auto finish = [&](int v, float qv, float q) {       // d Pj'[v,d], parked over the dead -Pj'[v,d]
+    if (ug == 0) {
+      const float gq = fmaf(c1, qv, sGv[v]);
+      gat = fmaf(-q, gq, gat);
+      const float t = at * gq;
+      tab += t;
+      sNPj[v * kD + d] = t;
     }
-    atomicAdd(sGat + 2 * lane, gat0);
-    atomicAdd(sGat + 2 * lane + 1, gat1);
-    atomicAdd(sTab + 2 * lane, tab0);
-    atomicAdd(sTab + 2 * lane + 1, tab1);
+  };
+  for (int v = 0; v < n; ++v) {
+    const float q = sNPj[v * kD + d];
+    float4 g4[GU / 4];
+#pragma unroll
+    for (int k = 0; k < GU / 4; ++k) g4[k] = *reinterpret_cast<const float4*>(sGs + v * SG + u0 + 4 * k);
+    float qa[4] = {0.f, 0.f, 0.f, 0.f};
+    const float r1 = __shfl_xor_sync(0xffffffffu, qv_pend, 1);
+#pragma unroll
+    for (int j = 0; j < GU / 2; ++j) {
+      const float4 g = g4[j >> 2];
+      const float gsv = (j & 3) == 0 ? g.x : (j & 3) == 1 ? g.y : (j & 3) == 2 ? g.z : g.w;
+      if (pi[j] > q) { qu[j] += gsv; qa[j & 3] += gsv; }
+    }
+    const float qv1 = qv_pend + r1;
+    const float r2 = __shfl_xor_sync(0xffffffffu, qv1, 2);
+#pragma unroll
+    for (int j = GU / 2; j < GU; ++j) {
+      const float4 g = g4[j >> 2];
+      const float gsv = (j & 3) == 0 ? g.x : (j & 3) == 1 ? g.y : (j & 3) == 2 ? g.z : g.w;
+      if (pi[j] > q) { qu[j] += gsv; qa[j & 3] += gsv; }
+    }
+    if (v > 0) finish(v - 1, qv1 + r2, q_pend);
+    qv_pend = (qa[0] + qa[1]) + (qa[2] + qa[3]);
+    q_pend = q;
+  }
+  {
+    float qv = qv_pend + __shfl_xor_sync(0xffffffffu, qv_pend, 1);
+    qv += __shfl_xor_sync(0xffffffffu, qv, 2);
+    if (n > 0) finish(n - 1, qv, q_pend);
+  }
+  __syncthreads();                 // every warp is done with the gs tile: reuse it for the d Pi rows [u][64]
+#pragma unroll
+  for (int j = 0; j < GU; ++j) {
+    if (u0 + j < n) {
+      const float g0 = fmaf(c1, qu[j], sGu[u0 + j]);
+      gat = fmaf(pi[j], g0, gat);
+      sGs[(u0 + j) * kD + d] = at * g0;
+    }
+  }
+  gat += __shfl_xor_sync(0xffffffffu, gat, 1);
+  gat += __shfl_xor_sync(0xffffffffu, gat, 2);
+  if (ug == 0) {
+    atomicAdd(g_attn + col, gat);
+    if (g_table) atomicAdd(g_table + (int64_t)type * A.HD + col, tab);
   }
   __syncthreads();
-  if (item_ok)
-    for (int i = tid; i < kD; i += nthr) {
-      atomicAdd(g_attn + h * kD + i, sGat[i]);
-      if (g_table) atomicAdd(g_table + (int64_t)type * A.HD + h * kD + i, sTab[i]);
-    }
+  for (int idx = threadIdx.x; idx < n * 16; idx += 256) {     // coalesced read-modify-write of the node rows
+    const int row = idx >> 4, c4 = (idx & 15) * 4;
+    const int64_t node = sNode[row];
+    float4* pj = reinterpret_cast<float4*>(gPj + node * A.HD + hoff + c4);
+    float4* pi4 = reinterpret_cast<float4*>(gPi + node * A.HD + hoff + c4);
+    const float4 aj = *reinterpret_cast<const float4*>(sNPj + row * kD + c4);
+    const float4 ai = *reinterpret_cast<const float4*>(sGs + row * kD + c4);
+    float4 oj = *pj, oi = *pi4;
+    oj.x += aj.x; oj.y += aj.y; oj.z += aj.z; oj.w += aj.w;
+    *pj = oj;
+    if (pi4 == pj) oi = oj;        // never: gPi and gPj are distinct tensors
+    oi.x += ai.x; oi.y += ai.y; oi.z += ai.z; oi.w += ai.w;
+    *pi4 = oi;
+  }
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -744,11 +782,19 @@ int clique_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
   }
   {
     ScopedTimer tm(B200GAT_TIMING_CLQ_BWD_ELEM, st);
-    A.item_floats = clique_bwd2_floats(A.rv, A.tiles);
-    const size_t smem = (size_t)A.ipc * A.item_floats * sizeof(float);
-    if ((rc = set_smem(k_clq_bwd_elem, smem, "k_clq_bwd_elem"))) return rc;
-    k_clq_bwd_elem<<<grid, block, smem, st>>>(A, Pi, Pj, gs_dense, gsum_u, gsum_v, gPi, gPj, g_attn,
-                                             A.table ? g_table : nullptr);
+    const int gu = (((g->cliques->max_block + 3) / 4) + 3) & ~3;          // sources per lane group, multiple of 4
+    const size_t smem = (size_t)clique_bwd2_floats(A.ru, gu) * sizeof(float);
+    float* gt = A.table ? g_table : nullptr;
+#define CLQ_BWD2(GU_)                                                                                         \
+  case GU_:                                                                                                   \
+    if ((rc = set_smem(k_clq_bwd_elem<GU_>, smem, "k_clq_bwd_elem"))) return rc;                              \
+    k_clq_bwd_elem<GU_><<<A.n_items, 256, smem, st>>>(A, Pi, Pj, gs_dense, gsum_u, gsum_v, gPi, gPj, g_attn, gt); \
+    break;
+    switch (gu) {
+      CLQ_BWD2(4) CLQ_BWD2(8) CLQ_BWD2(12) CLQ_BWD2(16) CLQ_BWD2(20) CLQ_BWD2(24) CLQ_BWD2(28) CLQ_BWD2(32)
+      default: set_error("k_clq_bwd_elem: block size %d not covered", g->cliques->max_block); return B200GAT_ERR_UNSUPPORTED;
+    }
+#undef CLQ_BWD2
     B200_CHECK_LAUNCH("k_clq_bwd_elem");
   }
   return B200GAT_OK;

@@ -131,9 +131,9 @@ __device__ __forceinline__ int hub_parts_of(const FastArgs& A, int n_hub) {
   return (A.hub_scratch && A.hub_parts > 1 && n_hub <= A.hub_cap) ? A.hub_parts : 1;
 }
 __device__ __forceinline__ WorkItem node_item(const FastArgs& A, const int32_t* __restrict__ ptr,
-                                              const int32_t* __restrict__ order, int wi) {
+                                              const int32_t* __restrict__ order, int wi, int group) {
   WorkItem it;
-  const int w = (blockIdx.x - A.hub_blocks) * kWarps + wi;
+  const int w = group * kWarps + wi;
   it.active = w < A.N;
   it.node = 0; it.seg_b = it.seg_e = 0;
   if (it.active) {
@@ -196,13 +196,15 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
   const int n_hub = hub_block ? *A.n_hub_dst : 0;
   const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
-  const int n_items = hub_block ? n_hub * P : 1;
+  const int n_items = hub_block ? n_hub * P : (A.N + kWarps - 1) / kWarps;      // node CTAs: groups of kWarps nodes
+  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
   float at[VPL];
   ldrow<VPL>(at, A.attn + c0);
 
-  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+  for (int item = item0; item < n_items; item += istep) {
     const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item / P], wi, item % P, P)
-                                  : node_item(A, A.in_ptr, A.dst_order, wi);
+                                  : node_item(A, A.in_ptr, A.dst_order, wi, item);
     const int v = it.node;
     float acc[VPL];
 #pragma unroll
@@ -365,15 +367,17 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
   const bool hub_block = (int)blockIdx.x < A.hub_blocks;
   const int n_hub = hub_block ? *A.n_hub_dst : 0;
   const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
-  const int n_items = hub_block ? n_hub * P : 1;
+  const int n_items = hub_block ? n_hub * P : (A.N + kWarps - 1) / kWarps;
+  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
   float at[VPL], gat[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
   for (int i = 0; i < VPL; ++i) gat[i] = 0.f;
 
-  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+  for (int item = item0; item < n_items; item += istep) {
     const WorkItem it = hub_block ? hub_item(A.in_ptr, A.hub_dst[item / P], wi, item % P, P)
-                                  : node_item(A, A.in_ptr, A.dst_order, wi);
+                                  : node_item(A, A.in_ptr, A.dst_order, wi, item);
     const int v = it.node;
     float gpj[VPL];
 #pragma unroll
@@ -530,15 +534,17 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_src_fast(
   const bool hub_block = (int)blockIdx.x < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
-  const int n_items = hub_block ? *A.n_hub_src : 1;
+  const int n_items = hub_block ? *A.n_hub_src : (A.N + kWarps - 1) / kWarps;
+  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
   float at[VPL], ats[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
   for (int i = 0; i < VPL; ++i) ats[i] = at[i] * A.slope;
 
-  for (int item = hub_block ? blockIdx.x : 0; item < n_items; item += hub_block ? A.hub_blocks : 1) {
+  for (int item = item0; item < n_items; item += istep) {
     const WorkItem it = hub_block ? hub_item(A.out_ptr, A.hub_src[item], wi)
-                                  : node_item(A, A.out_ptr, A.src_order, wi);
+                                  : node_item(A, A.out_ptr, A.src_order, wi, item);
     const int u = it.node;
     float gpi[VPL], gv[VPL];
 #pragma unroll
@@ -637,6 +643,13 @@ bool fast_supported(const b200gat_attn* a, const b200gat_edge_feats* ef) {
   return shape_of(a, vpl, lph);
 }
 
+// Node CTAs are persistent: at most two waves of the resident set (2 CTAs/SM), each looping over groups of
+// kWarps nodes, so the per-CTA flushes of d attn / d table stay few.
+static unsigned node_ctas(int64_t N) {
+  const int64_t need = ceil_div(N * 32, kFastThreads), cap = 4 * kNumSMs;
+  return (unsigned)(need < cap ? need : cap);
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_feats* ef) {
@@ -693,7 +706,7 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   if (A.N == 0) return B200GAT_OK;
   A.node_blk = node_blk;
   A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
-  const unsigned blocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads) + A.hub_blocks;
+  const unsigned blocks = node_ctas(A.N) + A.hub_blocks;
   const bool alias = (V == Pi);
   ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
   FAST_DISPATCH(vpl, lph, alias,
@@ -730,7 +743,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   if (A.emode == B200GAT_EDGE_AFFINE && A.K > 0) B200_CHECK_ARG(g_affine, "null g_affine");
   if (A.N == 0) return B200GAT_OK;
   const int HD = 32 * vpl;
-  const unsigned nblocks = (unsigned)ceil_div((int64_t)A.N * 32, kFastThreads);
+  const unsigned nblocks = node_ctas(A.N);
   const bool alias = (V == Pi);
   B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
   const int tab_in_smem = (A.emode != B200GAT_EDGE_NONE && (int64_t)A.T * HD * 4 <= 40 * 1024) ? 1 : 0;
