@@ -64,6 +64,12 @@ int64_t b200gat_launch_count(void);
 #define B200GAT_TIMING_CLASSES 12
 void b200gat_timing_enable(int on);
 int b200gat_timing_read(int cls, double* total_ms, int64_t* count);
+/* CUDA graphs: launches captured while timing is enabled record their event pairs as external event nodes of
+ * the graph.  After a replay has completed (synchronise first), b200gat_timing_collect_graph() adds the pairs'
+ * elapsed times to the accumulators (returns the number of pairs read); b200gat_timing_clear_graph() destroys
+ * the pairs (call it when the graph is destroyed). */
+int b200gat_timing_collect_graph(void);
+void b200gat_timing_clear_graph(void);
 
 /* ------------------------------------------------------------------ graph plan
  * Topology of one batched graph in both orders, built once per batch and reused by

@@ -23,6 +23,7 @@ SYMBOLS = (
     "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
     "b200gat_clique_scratch_elems", "b200gat_clique_build", "b200gat_conv_uses_cliques",
+    "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
 )
 MAX_CLIQUE = 128
 MIN_CLIQUE = 8        # smaller cliques stay on the sparse kernels
@@ -81,6 +82,9 @@ def _load():
     lib.b200gat_timing_enable.restype = None
     lib.b200gat_timing_enable.argtypes = [C.c_int]
     lib.b200gat_timing_read.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(i64)]
+    lib.b200gat_timing_collect_graph.argtypes = []
+    lib.b200gat_timing_clear_graph.argtypes = []
+    lib.b200gat_timing_clear_graph.restype = None
     lib.b200gat_plan_scratch_elems.restype = i64
     lib.b200gat_plan_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_plan_build.argtypes = [vp, vp, i64, i64] + [vp] * 9
@@ -106,7 +110,7 @@ def _load():
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
-                        "b200gat_clique_scratch_elems"):
+                        "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph"):
             fn.restype = C.c_int
     return lib
 

@@ -18,7 +18,7 @@ struct ScopedTimer {
   int cls_;
   cudaStream_t st_;
   cudaEvent_t e0_, e1_;
-  bool on_;
+  bool on_, capturing_;
 };
 
 #define B200_CHECK_ARG(cond, msg)                       \

@@ -21,6 +21,9 @@ static std::atomic<int> g_timing{0};
 static std::mutex g_tmu;
 struct EvPair { cudaEvent_t a, b; };
 static std::vector<EvPair> g_pending[B200GAT_TIMING_CLASSES];
+// Event pairs recorded as EXTERNAL event nodes of a CUDA graph under capture: they are re-recorded by every
+// replay and read (not destroyed) by b200gat_timing_collect_graph().
+static std::vector<EvPair> g_graph_pairs[B200GAT_TIMING_CLASSES];
 static double g_ms[B200GAT_TIMING_CLASSES];
 static int64_t g_cnt[B200GAT_TIMING_CLASSES];
 
@@ -28,13 +31,17 @@ ScopedTimer::ScopedTimer(int cls, cudaStream_t st) : cls_(cls), st_(st), on_(fal
   if (!g_timing.load(std::memory_order_relaxed) || cls < 0 || cls >= B200GAT_TIMING_CLASSES) return;
   if (cudaEventCreate(&e0_) != cudaSuccess || cudaEventCreate(&e1_) != cudaSuccess) return;
   on_ = true;
-  cudaEventRecord(e0_, st_);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  capturing_ = cudaStreamIsCapturing(st_, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusActive;
+  if (capturing_) cudaEventRecordWithFlags(e0_, st_, cudaEventRecordExternal);
+  else cudaEventRecord(e0_, st_);
 }
 ScopedTimer::~ScopedTimer() {
   if (!on_) return;
-  cudaEventRecord(e1_, st_);
+  if (capturing_) cudaEventRecordWithFlags(e1_, st_, cudaEventRecordExternal);
+  else cudaEventRecord(e1_, st_);
   std::lock_guard<std::mutex> lk(g_tmu);
-  g_pending[cls_].push_back({e0_, e1_});
+  (capturing_ ? g_graph_pairs : g_pending)[cls_].push_back({e0_, e1_});
 }
 
 static void drain() {
@@ -63,6 +70,31 @@ extern "C" void b200gat_timing_enable(int on) {
   drain();
   for (int c = 0; c < B200GAT_TIMING_CLASSES; ++c) { g_ms[c] = 0; g_cnt[c] = 0; }
   g_timing.store(on ? 1 : 0);
+}
+extern "C" int b200gat_timing_collect_graph(void) {
+  std::lock_guard<std::mutex> lk(g_tmu);
+  int n = 0;
+  for (int c = 0; c < B200GAT_TIMING_CLASSES; ++c)
+    for (auto& p : g_graph_pairs[c]) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+        g_ms[c] += ms;
+        g_cnt[c] += 1;
+        ++n;
+      }
+    }
+  cudaGetLastError();   // an unrecorded pair is not an error of the caller
+  return n;
+}
+extern "C" void b200gat_timing_clear_graph(void) {
+  std::lock_guard<std::mutex> lk(g_tmu);
+  for (int c = 0; c < B200GAT_TIMING_CLASSES; ++c) {
+    for (auto& p : g_graph_pairs[c]) {
+      cudaEventDestroy(p.a);
+      cudaEventDestroy(p.b);
+    }
+    g_graph_pairs[c].clear();
+  }
 }
 extern "C" int b200gat_timing_read(int cls, double* total_ms, int64_t* count) {
   B200_CHECK_ARG(cls >= 0 && cls < B200GAT_TIMING_CLASSES && total_ms && count, "bad timing class");

@@ -57,6 +57,21 @@ __device__ __forceinline__ void ldrow(float (&r)[VPL], const float* __restrict__
   }
 }
 template <int VPL>
+__device__ __forceinline__ void ldrow_s(float (&r)[VPL], const float* p) {     // plain (coherent) loads
+  if constexpr (VPL == 8) {
+    const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+  } else if constexpr (VPL == 4) {
+    const float4 a = reinterpret_cast<const float4*>(p)[0];
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+  } else if constexpr (VPL == 2) {
+    const float2 a = reinterpret_cast<const float2*>(p)[0];
+    r[0] = a.x; r[1] = a.y;
+  } else {
+    r[0] = p[0];
+  }
+}
+template <int VPL>
 __device__ __forceinline__ void strow(float* __restrict__ p, const float (&r)[VPL]) {
   if constexpr (VPL == 8) {
     reinterpret_cast<float4*>(p)[0] = make_float4(r[0], r[1], r[2], r[3]);
@@ -358,7 +373,9 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
   float* sh_tab = sh + HD;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
-  const int n_sh = HD + (tab_in_smem ? A.T * HD : 0);
+  // tab_in_smem: 0 = atomics on the global table, 1 = one shared table per CTA (shared fp32 atomics, which are
+  // CAS loops on sm_100), 2 = one private table per warp (plain read-modify-write: lane l owns its VPL columns)
+  const int n_sh = HD + (tab_in_smem == 2 ? kWarps * A.T * HD : tab_in_smem == 1 ? A.T * HD : 0);
   for (int i = threadIdx.x; i < n_sh; i += kFastThreads) sh[i] = 0.f;
   __syncthreads();
 
@@ -401,6 +418,15 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
       int t_cur = -1;
       auto flush_tab = [&]() {
         if (t_cur < 0) return;
+        if (tab_in_smem == 2) {
+          float* dst = sh_tab + ((wi * A.T + t_cur) * HD + c0);
+          float old[VPL];
+          ldrow_s<VPL>(old, dst);
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) { old[i] += gtab[i]; gtab[i] = 0.f; }
+          strow<VPL>(dst, old);
+          return;
+        }
         float* dst = tab_in_smem ? sh_tab + t_cur * HD + c0 : g_table + (int64_t)t_cur * HD + c0;
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
@@ -497,9 +523,17 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
   __syncthreads();
   for (int i = threadIdx.x; i < HD; i += kFastThreads)
     if (sh_gat[i] != 0.f) atomicAdd(g_attn + i, sh_gat[i]);
-  if (tab_in_smem)
+  if (tab_in_smem == 2) {
+    for (int i = threadIdx.x; i < A.T * HD; i += kFastThreads) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w2 = 0; w2 < kWarps; ++w2) sum += sh_tab[w2 * A.T * HD + i];
+      if (sum != 0.f) atomicAdd(g_table + i, sum);
+    }
+  } else if (tab_in_smem) {
     for (int i = threadIdx.x; i < A.T * HD; i += kFastThreads)
       if (sh_tab[i] != 0.f) atomicAdd(g_table + i, sh_tab[i]);
+  }
 }
 
 // Sum the partial d Pj rows of the slices of each split hub (in slice order).
@@ -746,13 +780,21 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   const unsigned nblocks = node_ctas(A.N);
   const bool alias = (V == Pi);
   B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
-  const int tab_in_smem = (A.emode != B200GAT_EDGE_NONE && (int64_t)A.T * HD * 4 <= 40 * 1024) ? 1 : 0;
-  const size_t smem = sizeof(float) * (HD + (tab_in_smem ? (size_t)A.T * HD : 0));
+  const int64_t tab_bytes = (int64_t)A.T * HD * 4;
+  const int tab_in_smem = A.emode == B200GAT_EDGE_NONE ? 0 : kWarps * tab_bytes <= 64 * 1024 ? 2
+                          : tab_bytes <= 40 * 1024 ? 1 : 0;
+  const size_t smem = sizeof(float) * (HD + (tab_in_smem == 2 ? (size_t)kWarps * A.T * HD
+                                             : tab_in_smem == 1 ? (size_t)A.T * HD : 0));
   float* alpha = gs + (n_pos > 0 ? n_pos : (int64_t)A.E) * A.H;   // edge positions may be those of the full graph
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
     A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
     const unsigned blocks = nblocks + A.hub_blocks;
+    if (smem > 48 * 1024) {
+      FAST_DISPATCH(vpl, lph, alias,
+                    (cudaFuncSetAttribute(k_bwd_dst_fast<VPL, LPH, ALIAS>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
+    }
     FAST_DISPATCH(vpl, lph, alias,
                   (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
                       A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
