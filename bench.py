@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--gemm", default=None, help="override WHEATLEY_B200_GEMM (cublas|tcgen05)")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="launch the resident-input step eagerly instead of replaying one captured CUDA graph")
     return ap.parse_args()
 
 
@@ -152,7 +154,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except OSError:
             pass
@@ -225,7 +227,7 @@ def run_b200(args):
     agent = JsspAgent(cfg["input_dim"], cfg["max_n_nodes"], cfg["n_m"], cfg["hidden"], cfg["layers"],
                       cfg["heads"]).to(dev)
     bucket = FlatGradAllReduce(list(agent.parameters()))
-    opt = torch.optim.Adam(agent.parameters(), lr=2e-4, fused=True)
+    opt = torch.optim.Adam(agent.parameters(), lr=2e-4, fused=True, capturable=True)
 
     hb = jssp_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress)
     masks, action, adv, ret = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
@@ -254,7 +256,9 @@ def run_b200(args):
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
-    def timed(fn, steps, warmup, sampler=False):
+    def timed(fn, steps, warmup, sampler=False, graphed=False):
+        # nvidia-smi needs ~100 ms to start: launch it before the warm-up so that it samples the timed region
+        smp = ClockSampler(local) if sampler and rank == 0 else None
         for _ in range(warmup):
             fn()
         torch.cuda.synchronize()
@@ -262,7 +266,6 @@ def run_b200(args):
             dist.barrier()
         if sampler:
             _lib.timing_enable(True)                       # per-kernel events over the timed steps only
-        smp = ClockSampler(local) if sampler and rank == 0 else None
         l0 = _lib.launch_count()
         total = 0.0
         evs = []
@@ -273,6 +276,9 @@ def run_b200(args):
             fn()
             e1.record()
             evs.append((e0, e1))
+            if graphed and sampler:                        # read the graph's per-kernel event pairs of this replay
+                torch.cuda.synchronize()
+                _lib.lib.b200gat_timing_collect_graph()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -288,7 +294,32 @@ def run_b200(args):
     d_res = to_dev()
     jb_res = make_batch(d_res)
     torch.cuda.synchronize()
-    ms_dev, launches, clocks = timed(lambda: train_step(jb_res, d_res), args.steps, args.warmup, sampler=True)
+    step_fn, graph, graph_note = (lambda: train_step(jb_res, d_res)), None, "eager launches"
+    if not args.no_graph:
+        # the whole step (fwd + head + loss + bwd + all-reduce + Adam) as ONE CUDA graph: shapes and the plan
+        # are fixed for resident inputs, so replaying it removes the per-launch host cost of ~350 kernels
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    train_step(jb_res, d_res)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            _lib.timing_enable(True)                       # captured launches carry external event pairs
+            l0 = _lib.launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, capture_error_mode="relaxed"):
+                train_step(jb_res, d_res)
+            captured = _lib.launch_count() - l0
+            step_fn, graph_note = graph.replay, "one CUDA graph replay per step"
+        except Exception as exc:                           # keep the eager path measurable
+            graph, graph_note = None, f"eager launches (graph capture failed: {type(exc).__name__}: {exc})"[:200]
+            _lib.lib.b200gat_timing_clear_graph()
+            torch.cuda.synchronize()
+    ms_dev, launches, clocks = timed(step_fn, args.steps, args.warmup, sampler=True, graphed=graph is not None)
+    if graph is not None:
+        launches = captured
     tm = _lib.timing_read()
     _lib.timing_enable(False)
 
@@ -316,14 +347,16 @@ def run_b200(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     HD, H = cfg["hidden"] * cfg["heads"], cfg["heads"]
-    fwd_ms, fwd_n = tm["conv_fwd"]
-    bd_ms, bd_n = tm["conv_bwd_dst"]
-    bs_ms, bs_n = tm["conv_bwd_src"]
+    # one "launch" of the conv pass = the sparse kernel(s) on the residual CSR + the dense clique kernel(s)
+    fwd_n, bd_n = tm["conv_fwd"][1], tm["conv_bwd_dst"][1]
+    fwd_ms = tm["conv_fwd"][0] + tm.get("clq_fwd", (0.0, 0))[0]
+    bwd_ms = (tm["conv_bwd_dst"][0] + tm["conv_bwd_src"][0] + tm.get("clq_bwd_mma", (0.0, 0))[0]
+              + tm.get("clq_bwd_elem", (0.0, 0))[0])
     per = {}
     if fwd_n:
         per["conv_fwd"] = (fwd_ms / fwd_n, algorithmic_bytes("conv_fwd", N, E, HD, H))
     if bd_n:
-        per["conv_bwd"] = ((bd_ms + bs_ms) / bd_n, algorithmic_bytes("conv_bwd", N, E, HD, H))
+        per["conv_bwd"] = (bwd_ms / bd_n, algorithmic_bytes("conv_bwd", N, E, HD, H))
     dom = max(per, key=lambda k: per[k][0] * (fwd_n if k == "conv_fwd" else bd_n)) if per else None
     roofline = None
     if dom:
@@ -343,7 +376,8 @@ def run_b200(args):
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
                            l2="flushed between timed steps (256 MiB write)",
                            parallelism=f"dp{world}", gemm=os.environ.get("WHEATLEY_B200_GEMM", "cublas"),
-                           step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam"),
+                           step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam",
+                           launch=graph_note),
             "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}

@@ -59,7 +59,9 @@ class AgentHeadMixin:
         node_features, graph_embedding = self.gnn(x)
         value = self.value_net(graph_embedding)
         logits = self.action_net(node_features).squeeze(-1)
-        unmasked_distrib = Categorical(logits=logits)          # generic/agent.py:197
+        # generic/agent.py:197.  validate_args=False: the default argument check reads a device flag back to the
+        # host (a sync per call, and illegal under CUDA-graph capture); the distribution itself is identical
+        unmasked_distrib = Categorical(logits=logits, validate_args=False)
         action, logprob, entropy = action_logprob_entropy(logits, action, action_masks, deterministic)
         return action, logprob, entropy, value, unmasked_distrib
 
