@@ -60,6 +60,20 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// Packed fp32x2 helpers (sm_100 FFMA2).
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float lo2(unsigned long long v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float hi2(unsigned long long v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
 // Shared-memory views of one item slot.
 struct ItemSmem {
   float *pi, *v, *npj, *ai, *aj, *at;
@@ -213,14 +227,22 @@ __device__ __forceinline__ void fwd_chunk(const CliqueArgs& A, const ItemSmem& S
     split_tf32(s0[2 * k + 1], ah[2], al[2]);
     split_tf32(s1[2 * k + 1], ah[3], al[3]);
     const float* vb = S.v + (ub + 8 * k + t) * kSP + g;
+    // four column blocks at a time; the three split products are issued product-major so that consecutive
+    // mma's target different accumulators (no back-to-back dependent tensor instructions)
 #pragma unroll
-    for (int nb = 0; nb < 8; ++nb) {
-      uint32_t bh0, bl0, bh1, bl1;
-      split_tf32(vb[nb * 8], bh0, bl0);
-      split_tf32(vb[4 * kSP + nb * 8], bh1, bl1);
-      mma_tf32(st.acc[nb], al[0], al[1], al[2], al[3], bh0, bh1);
-      mma_tf32(st.acc[nb], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
-      mma_tf32(st.acc[nb], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+    for (int nq = 0; nq < 8; nq += 4) {
+      uint32_t bh0[4], bl0[4], bh1[4], bl1[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        split_tf32(vb[(nq + j) * 8], bh0[j], bl0[j]);
+        split_tf32(vb[4 * kSP + (nq + j) * 8], bh1[j], bl1[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mma_tf32(st.acc[nq + j], al[0], al[1], al[2], al[3], bh0[j], bh1[j]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mma_tf32(st.acc[nq + j], ah[0], ah[1], ah[2], ah[3], bl0[j], bl1[j]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mma_tf32(st.acc[nq + j], ah[0], ah[1], ah[2], ah[3], bh0[j], bh1[j]);
     }
   }
 }
@@ -355,16 +377,19 @@ __device__ __forceinline__ void bwd1_chunk(const CliqueArgs& A, const BwdSmem& S
     split_tf32(S.v[u1 * kSB + k * 8 + t], ah[1], al[1]);
     split_tf32(S.v[u0 * kSB + k * 8 + t + 4], ah[2], al[2]);
     split_tf32(S.v[u1 * kSB + k * 8 + t + 4], ah[3], al[3]);
+    uint32_t bh0[VB], bl0[VB], bh1[VB], bl1[VB];
 #pragma unroll
     for (int j = 0; j < VB; ++j) {
       const float* gp = S.g + (vbase + 8 * j + g) * kSB + k * 8 + t;
-      uint32_t bh0, bl0, bh1, bl1;
-      split_tf32(gp[0], bh0, bl0);
-      split_tf32(gp[4], bh1, bl1);
-      mma_tf32(c[j], al[0], al[1], al[2], al[3], bh0, bh1);
-      mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
-      mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+      split_tf32(gp[0], bh0[j], bl0[j]);
+      split_tf32(gp[4], bh1[j], bl1[j]);
     }
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], al[0], al[1], al[2], al[3], bh0[j], bh1[j]);
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bl0[j], bl1[j]);
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bh0[j], bh1[j]);
   }
   // alpha / gs on the C fragments: c[j][0]=(u0,va) [1]=(u0,vb) [2]=(u1,va) [3]=(u1,vb)
 #pragma unroll
@@ -404,13 +429,19 @@ __device__ __forceinline__ void bwd1_chunk(const CliqueArgs& A, const BwdSmem& S
     split_tf32(al4[3], ah[3], al[3]);
     const float* ga = S.g + va * kSB + g;
 #pragma unroll
-    for (int nb = 0; nb < 8; ++nb) {
-      uint32_t bh0, bl0, bh1, bl1;
-      split_tf32(ga[nb * 8], bh0, bl0);
-      split_tf32(ga[kSB + nb * 8], bh1, bl1);
-      mma_tf32(acc[nb], al[0], al[1], al[2], al[3], bh0, bh1);
-      mma_tf32(acc[nb], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
-      mma_tf32(acc[nb], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+    for (int nq = 0; nq < 8; nq += 4) {
+      uint32_t bh0[4], bl0[4], bh1[4], bl1[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        split_tf32(ga[(nq + i) * 8], bh0[i], bl0[i]);
+        split_tf32(ga[kSB + (nq + i) * 8], bh1[i], bl1[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], al[0], al[1], al[2], al[3], bh0[i], bh1[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], ah[0], ah[1], ah[2], ah[3], bl0[i], bl1[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], ah[0], ah[1], ah[2], ah[3], bh0[i], bh1[i]);
     }
   }
 }
