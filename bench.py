@@ -221,6 +221,9 @@ def run_b200(args):
     from wheatley_b200.workload import jssp_batch
 
     torch.backends.cuda.matmul.allow_tf32 = True       # the reference's matmul precision (psp/train_psp.py:47)
+    from wheatley_b200 import dense as _dense
+    dense_backend = ("tcgen05 TF32 (b200gat_gemm_tf32; library GEMM for uncovered shapes)"
+                     if _dense.tf32_path_enabled() else "cublas TF32")
     cfg = model_config(args)
     B = cfg["graphs"]
     torch.manual_seed(0)                               # identical replicas on every rank
@@ -375,7 +378,7 @@ def run_b200(args):
             "data": "synthetic",
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
                            l2="flushed between timed steps (256 MiB write)",
-                           parallelism=f"dp{world}", gemm=os.environ.get("WHEATLEY_B200_GEMM", "cublas"),
+                           parallelism=f"dp{world}", gemm=dense_backend,
                            step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam",
                            launch=graph_note),
             "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,

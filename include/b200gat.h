@@ -276,6 +276,58 @@ int b200gat_mask_head_bwd(const float* logp, const uint8_t* mask, int64_t ld_mas
                           const float* g_entropy, int32_t batch, int32_t n, float* g_logits,
                           void* stream);
 
+/* ------------------------------------------------------------------ dense projections (tcgen05, TF32)
+ * Replaces the torch.nn.Linear GEMMs around every conv (generic/mlp.py:70-77; fc_ni / fc_nj /
+ * fc_node_src of generic/eegatconv.py:260-262,288; lin_l / lin_r of PyG GATv2Conv) at the matmul
+ * precision the reference runs them in (TF32, psp/train_psp.py:47):
+ *     D[m, n] = sum_k A(m, k) * B(n, k)  (+ bias[n])  -> epilogue
+ * a_major / b_major: 0 = the operand is stored [mn rows, k cols] (reduction index contiguous),
+ *                    1 = stored [k rows, mn cols].  So with row-major x [M,K], W [N,K], dy [M,N]:
+ *     y  = x W^T   : A = x  (0), B = W (0)
+ *     dx = dy W    : A = dy (0), B = W (1)            (reduction over N)
+ *     dW = dy^T x  : A = dy (1), B = x (1)            (reduction over the M rows, split-K + workspace)
+ * a_parts > 1: A is a_parts equally shaped matrices a_part_stride floats apart, concatenated along k
+ * (a_major 0) or along m (a_major 1); d_parts > 1: the output columns are split over d_parts matrices
+ * [M, N / d_parts] d_part_stride floats apart (the Pi | Pj | V projections in one launch).
+ * Epilogues: NONE: D = acc + bias (+ residual); GELU: D = acc + bias (pre-activation, may be NULL),
+ * D2 = gelu(D) (exact erf form, torch.nn.GELU default); DGELU: D = (acc + bias) * gelu'(Zin) (+ residual).
+ * Requirements: N per part a multiple of 64, leading dimensions multiples of 4 floats, 16-byte aligned
+ * pointers; b200gat_gemm_supported() tells whether a descriptor is covered (callers use the library
+ * GEMM otherwise, e.g. for the width-1 head outputs).                                               */
+#define B200GAT_EPI_NONE 0
+#define B200GAT_EPI_GELU 1
+#define B200GAT_EPI_DGELU 2
+typedef struct b200gat_gemm {
+  int32_t a_major, b_major;
+  int64_t M, N, K;
+  const float* A;
+  int64_t lda;
+  int32_t a_parts;
+  int64_t a_part_stride;
+  const float* B;
+  int64_t ldb;
+  float* D;
+  int64_t ldd;
+  int32_t d_parts;
+  int64_t d_part_stride;
+  const float* bias;
+  const float* residual;
+  int64_t ldr;
+  int32_t epilogue;
+  float* D2;
+  const float* Zin;
+  int64_t ld2;
+  float* workspace;         /* split-K partials (b200gat_gemm_workspace_elems floats) or NULL */
+  int64_t workspace_elems;
+} b200gat_gemm;
+int b200gat_gemm_supported(const b200gat_gemm* g);
+int64_t b200gat_gemm_workspace_elems(const b200gat_gemm* g);
+int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream);
+/* out[n] = sum_m X[m, n] (bias gradients), deterministic; scratch: b200gat_colsum_scratch_elems floats */
+int64_t b200gat_colsum_scratch_elems(int64_t M, int64_t N);
+int b200gat_colsum(const float* X, int64_t M, int64_t N, int64_t ld, float* out, float* scratch,
+                   void* stream);
+
 #ifdef __cplusplus
 }
 #endif

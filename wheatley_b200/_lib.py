@@ -24,7 +24,10 @@ SYMBOLS = (
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
     "b200gat_clique_scratch_elems", "b200gat_clique_build", "b200gat_conv_uses_cliques",
     "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
+    "b200gat_gemm_supported", "b200gat_gemm_workspace_elems", "b200gat_gemm_tf32",
+    "b200gat_colsum_scratch_elems", "b200gat_colsum",
 )
+EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
 MAX_CLIQUE = 128
 MIN_CLIQUE = 8        # smaller cliques stay on the sparse kernels
 
@@ -61,6 +64,18 @@ class EdgeFeats(C.Structure):
     _fields_ = [("mode", C.c_int32), ("n_types", C.c_int32),
                 ("table", C.c_void_p), ("etype", C.c_void_p), ("dense", C.c_void_p),
                 ("n_attr", C.c_int32), ("attr", C.c_void_p), ("affine", C.c_void_p)]
+
+
+class Gemm(C.Structure):
+    """``b200gat_gemm`` (include/b200gat.h)."""
+    _fields_ = [("a_major", C.c_int32), ("b_major", C.c_int32),
+                ("M", C.c_int64), ("N", C.c_int64), ("K", C.c_int64),
+                ("A", C.c_void_p), ("lda", C.c_int64), ("a_parts", C.c_int32), ("a_part_stride", C.c_int64),
+                ("B", C.c_void_p), ("ldb", C.c_int64),
+                ("D", C.c_void_p), ("ldd", C.c_int64), ("d_parts", C.c_int32), ("d_part_stride", C.c_int64),
+                ("bias", C.c_void_p), ("residual", C.c_void_p), ("ldr", C.c_int64),
+                ("epilogue", C.c_int32), ("D2", C.c_void_p), ("Zin", C.c_void_p), ("ld2", C.c_int64),
+                ("workspace", C.c_void_p), ("workspace_elems", C.c_int64)]
 
 
 class B200GatError(RuntimeError):
@@ -106,11 +121,20 @@ def _load():
     lib.b200gat_edge_out.argtypes = [gp, ap, ep, vp, vp, vp, vp]
     lib.b200gat_mask_head_fwd.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, vp, vp, vp]
     lib.b200gat_mask_head_bwd.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32, i32, vp, vp]
+    mp = C.POINTER(Gemm)
+    lib.b200gat_gemm_supported.argtypes = [mp]
+    lib.b200gat_gemm_workspace_elems.argtypes = [mp]
+    lib.b200gat_gemm_workspace_elems.restype = i64
+    lib.b200gat_gemm_tf32.argtypes = [mp, vp]
+    lib.b200gat_colsum_scratch_elems.argtypes = [i64, i64]
+    lib.b200gat_colsum_scratch_elems.restype = i64
+    lib.b200gat_colsum.argtypes = [vp, i64, i64, i64, vp, vp, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
-                        "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph"):
+                        "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
+                        "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems"):
             fn.restype = C.c_int
     return lib
 

@@ -10,6 +10,7 @@ from torch import nn
 from torch.nn import init
 
 from . import _lib
+from .dense import project3
 from .edge_feats import TypedEdgeFeats
 from .functional import (EdgeFeatures, attention_weights, edge_output, fused_gat_conv,
                          project_edge_feats)
@@ -137,9 +138,8 @@ class EEGATConv(nn.Module):
         H, De, Do = self._num_heads, self._out_edge_feats, self._out_node_feats
         if efeats_e is None:
             efeats_e = efeats.dense() if (self._edge_scoring and isinstance(efeats, TypedEdgeFeats)) else efeats
-        f_ni = self.fc_ni(nfeats)                                    # :260
-        f_nj = self.fc_nj(nfeats)                                    # :261
-        h_src = self.fc_node_src(nfeats)                             # :288
+        # :260, :261, :288 - the three bias-free projections, one tcgen05 launch when TF32 is allowed
+        f_ni, f_nj, h_src = project3(nfeats, self.fc_ni.weight, self.fc_nj.weight, self.fc_node_src.weight)
         ef = self._edge_features(plan, efeats, efeats_e)
         out, saved = fused_gat_conv(plan, f_ni, f_nj, h_src, self.attn, heads=H, dim=De,
                                     flavour=_lib.FLAVOUR_ADDITIVE, slope=0.01, eps=0.0, edge_feats=ef)

@@ -123,9 +123,10 @@ class _FusedGATConv(torch.autograd.Function):
         plan, view, cfg = ctx.plan, ctx.view, ctx.cfg
         H, D = cfg["heads"], cfg["dim"]
         g_out = _f32c(g_out)
-        gPi = torch.empty_like(Pi)
-        gPj = torch.empty_like(Pj)
-        gV = gPi if ctx.v_alias else torch.empty_like(Vt)
+        # one [3, N, HD] buffer: the projection backward (dense._Proj3) reads gPi | gPj | gV as one operand
+        g3 = torch.empty((2 if ctx.v_alias else 3,) + tuple(Pi.shape), dtype=Pi.dtype, device=Pi.device)
+        gPi, gPj = g3[0], g3[1]
+        gV = gPi if ctx.v_alias else g3[2]
         g_attn = torch.zeros_like(attn_c)
         g_attn_bias = torch.zeros_like(attn_bias_c) if attn_bias_c is not None else None
         g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None

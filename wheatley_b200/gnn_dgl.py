@@ -91,9 +91,9 @@ class GnnDGL(nn.Module):
         efeats = TypedEdgeFeats(b.etype, self.edge_embedder[0].weight)          # :364
         for layer in range(self.n_layers_features_extractor):
             h, _ = self.features_extractors[layer](b.plan, features, efeats)    # :374-376
-            features = self.mlps[layer](h.flatten(start_dim=-2, end_dim=-1))    # :377
-            if self.residual:
-                features = features + features_list[-1]                         # :395-396
+            # :377 and the residual add of :395-396 (fused into the MLP's last GEMM epilogue)
+            features = self.mlps[layer](h.flatten(start_dim=-2, end_dim=-1),
+                                        residual=features_list[-1] if self.residual else None)
             features_list.append(features)
         return torch.cat(features_list, dim=1)                                  # :401
 

@@ -2,15 +2,18 @@
 ``activation_layer`` attribute and parameter names, so ``state_dict`` keys match).
 
 Dense projections are the one GEMM-shaped part of the path (north_star item 4).
-``dense_linear`` dispatches each ``Linear`` to the library's tcgen05 TF32 GEMM
-(``b200gat_linear_tf32_*``, fp32 in / fp32 accumulate in TMEM / fp32 out - the precision the
-reference runs its matmuls in, ``torch.set_float32_matmul_precision("high")``,
-psp/train_psp.py:47) when the shape is covered and ``WHEATLEY_B200_GEMM`` is not ``cublas``;
-otherwise to cuBLAS through ``torch.nn.functional.linear`` (a plain library GEMM)."""
+A GELU MLP without LayerNorm (the default configuration, args.py:335-348) runs as
+``wheatley_b200.dense.gelu_mlp``: every ``Linear`` on the library's tcgen05 TF32 GEMM
+(``b200gat_gemm_tf32``, fp32 in / fp32 accumulate in TMEM / fp32 out - the precision the reference
+runs its matmuls in, ``torch.set_float32_matmul_precision("high")``, psp/train_psp.py:47) with bias,
+GELU, GELU' and the residual add fused into the epilogues, when TF32 matmuls are allowed and
+``WHEATLEY_B200_GEMM`` is not ``cublas``; otherwise cuBLAS through ``torch.nn.functional.linear``
+(a plain library GEMM).  ``forward(x, residual=None)``: the optional ``residual`` (an extension; the
+reference adds it right after the call, jssp/models/gnn_dgl.py:395-396) is fused into the last GEMM."""
 import torch
 from torch import nn
 
-from .dense import dense_linear
+from .dense import dense_linear, gelu_mlp, gelu_mlp_applicable
 
 _ACT = {
     "tanh": nn.Tanh,
@@ -43,7 +46,18 @@ class MLP(nn.Module):
             activation = _ACT[activation]
         self.activation_layer = activation()
 
-    def forward(self, x):
+    def forward(self, x, residual=None):
+        if (not self.norm and isinstance(self.activation_layer, nn.GELU)
+                and getattr(self.activation_layer, "approximate", "none") == "none"):
+            x2 = x.reshape(-1, x.shape[-1])
+            if gelu_mlp_applicable(x2, self.layers):
+                r2 = None if residual is None else residual.reshape(-1, residual.shape[-1])
+                y = gelu_mlp(x2, self.layers, r2)
+                return y.reshape(*x.shape[:-1], y.shape[-1])
+        y = self._forward_library(x)
+        return y if residual is None else y + residual
+
+    def _forward_library(self, x):
         for layer in range(self.n_layers - 1):
             x = dense_linear(x, self.layers[layer].weight, self.layers[layer].bias)
             if self.norm:
