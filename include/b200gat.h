@@ -58,9 +58,11 @@ int64_t b200gat_launch_count(void);
 #define B200GAT_TIMING_HEAD 4
 #define B200GAT_TIMING_GEMM 5
 #define B200GAT_TIMING_BATCH 6
+#define B200GAT_TIMING_GEMM_DX 7
 #define B200GAT_TIMING_CLQ_FWD 8
 #define B200GAT_TIMING_CLQ_BWD_MMA 9
 #define B200GAT_TIMING_CLQ_BWD_ELEM 10
+#define B200GAT_TIMING_GEMM_DW 11
 #define B200GAT_TIMING_CLASSES 12
 void b200gat_timing_enable(int on);
 int b200gat_timing_read(int cls, double* total_ms, int64_t* count);
@@ -290,7 +292,7 @@ int b200gat_mask_head_bwd(const float* logp, const uint8_t* mask, int64_t ld_mas
  * (a_major 0) or along m (a_major 1); d_parts > 1: the output columns are split over d_parts matrices
  * [M, N / d_parts] d_part_stride floats apart (the Pi | Pj | V projections in one launch).
  * Epilogues: NONE: D = acc + bias (+ residual); GELU: D = acc + bias (pre-activation, may be NULL),
- * D2 = gelu(D) (exact erf form, torch.nn.GELU default); DGELU: D = (acc + bias) * gelu'(Zin) (+ residual).
+ * D2 = gelu(D) (exact erf form, torch.nn.GELU default); DGELU: D = (acc + bias) * gelu'(Zin), no residual.
  * Requirements: N per part a multiple of 64, leading dimensions multiples of 4 floats, 16-byte aligned
  * pointers; b200gat_gemm_supported() tells whether a descriptor is covered (callers use the library
  * GEMM otherwise, e.g. for the width-1 head outputs).                                               */
@@ -319,6 +321,8 @@ typedef struct b200gat_gemm {
   int64_t ld2;
   float* workspace;         /* split-K partials (b200gat_gemm_workspace_elems floats) or NULL */
   int64_t workspace_elems;
+  float* a_rowsum;          /* optional [M]: sum_k A(m, k) - the bias gradient when A = dy^T (dW GEMM); */
+                            /* computed by the tensor core against an all-ones tile, no extra pass      */
 } b200gat_gemm;
 int b200gat_gemm_supported(const b200gat_gemm* g);
 int64_t b200gat_gemm_workspace_elems(const b200gat_gemm* g);

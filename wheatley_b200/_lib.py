@@ -75,7 +75,7 @@ class Gemm(C.Structure):
                 ("D", C.c_void_p), ("ldd", C.c_int64), ("d_parts", C.c_int32), ("d_part_stride", C.c_int64),
                 ("bias", C.c_void_p), ("residual", C.c_void_p), ("ldr", C.c_int64),
                 ("epilogue", C.c_int32), ("D2", C.c_void_p), ("Zin", C.c_void_p), ("ld2", C.c_int64),
-                ("workspace", C.c_void_p), ("workspace_elems", C.c_int64)]
+                ("workspace", C.c_void_p), ("workspace_elems", C.c_int64), ("a_rowsum", C.c_void_p)]
 
 
 class B200GatError(RuntimeError):
@@ -148,7 +148,7 @@ def check(rc, what):
 
 
 TIMING_CLASSES = {"conv_fwd": 0, "conv_bwd_dst": 1, "conv_bwd_src": 2, "plan": 3, "head": 4, "gemm": 5,
-                  "batch": 6, "clq_fwd": 8, "clq_bwd_mma": 9, "clq_bwd_elem": 10}
+                  "batch": 6, "gemm_dx": 7, "clq_fwd": 8, "clq_bwd_mma": 9, "clq_bwd_elem": 10, "gemm_dw": 11}
 
 
 def launch_count() -> int:

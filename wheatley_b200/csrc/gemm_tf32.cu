@@ -1,11 +1,11 @@
 // Dense projections of the path (north_star item 4) as a hand-written tcgen05 GEMM:
 //   D[m, n] = sum_k A(m, k) * B(n, k)      fp32 operands read as TF32 by the tensor core (kind::tf32),
 //                                           fp32 accumulators in TMEM, fused epilogue in registers.
-// One CTA = one 128 x BN output tile (x one K split).  Warp roles (192 threads):
-//   warps 0-3  epilogue: tcgen05.ld of the accumulator rows (thread = row), transposed through shared memory so
+// One CTA = one 128 x BN output tile (x one K split), BN in {64, 128, 256}.  Warp roles (320 threads):
+//   warps 0-7  epilogue (warp w: TMEM lanes 32 (w & 3).., column half w >> 2): tcgen05.ld of the accumulator rows (thread = row), transposed through shared memory so
 //              that bias / GELU / GELU' / residual run on coalesced 128-byte row segments
-//   warp  4    TMA producer: cp.async.bulk.tensor boxes (128-byte swizzle) into a 3-stage shared-memory ring
-//   warp  5    MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=8) x 4 per stage, tcgen05.commit
+//   warp  8    TMA producer: cp.async.bulk.tensor boxes (128-byte swizzle) into a 3-stage shared-memory ring
+//   warp  9    MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=8) x 4 per stage, tcgen05.commit
 //              releases the stage / signals the epilogue
 // Both operand majors are handled by descriptors, not by transposes:
 //   K-major  operand: stored [mn rows, k cols]  (forward: X and W; dX: dY)
@@ -41,6 +41,8 @@ struct GemmArgs {
   const float* Zin;           // EPI_DGELU: D = acc * gelu'(Zin)
   long long ld2;
   unsigned mn_lbo, mn_sbo, mn_layout, mn_kadv;   // MN-major descriptor fields (bytes; see smem_desc)
+  float* a_rowsum;            // [M] (+ split * rowsum_split_stride): sum_k A(m, k), or null
+  long long rowsum_split_stride;
 };
 
 // ------------------------------------------------------------------------------------------- PTX helpers
@@ -122,7 +124,7 @@ __device__ __forceinline__ float dgelu_f(float z) {
 
 // ------------------------------------------------------------------------------------------- the kernel
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __grid_constant__ CUtensorMap tmA,
                                                    const __grid_constant__ CUtensorMap tmB, GemmArgs p) {
   constexpr int B_STAGE_BYTES = BN * BK * 4;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -144,9 +146,19 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0) {      // TMEM: BN fp32 accumulator columns (power of two >= 32)
+  // Row sums of A (bias gradients in the weight-gradient GEMM) ride on the tensor core too: one extra
+  // N = 16 MMA per k-step against an all-ones B tile (2 KB behind the ring) into 16 more TMEM columns.
+  const bool rowsum = p.a_rowsum != nullptr && nt == 0;
+  const uint32_t ones_addr = base + STAGES * STAGE_BYTES;
+  if (rowsum) {
+    float* ones = reinterpret_cast<float*>(smem_raw + (ones_addr - smem_u32(smem_raw)));
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) ones[i] = 1.f;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  const uint32_t tmem_cols = p.a_rowsum ? 2u * BN : (uint32_t)BN;      // power of two >= 32
+  if (warp == 0) {      // TMEM: BN fp32 accumulator columns (+ the row-sum columns)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
-                 "r"((uint32_t)BN)
+                 "r"(tmem_cols)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -155,7 +167,7 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = tmem_base_s;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
@@ -183,11 +195,13 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
       }
       __syncwarp();
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ------------------------------------------------------------------ MMA issuer
     // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = TF32, majors, N >> 3, M >> 4
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    const uint32_t idesc_ones = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | (2u << 17) |
+                                ((uint32_t)(BM >> 4) << 24);             // N = 16, B (ones) K-major
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
       const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
@@ -202,6 +216,8 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
           const uint64_t bd = B_MN ? smem_desc(sb + k * p.mn_kadv, p.mn_lbo, p.mn_sbo, p.mn_layout)
                                    : smem_desc(sb + k * 32, 16, 1024, 2);
           umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          if (rowsum)
+            umma_tf32(tmem_base + BN, ad, smem_desc(ones_addr, 16, 1024, 2), idesc_ones, (i > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(empty0 + 8 * s);                 // frees the stage when these MMAs have read it
         if (i == nkb - 1) umma_commit(accum_bar);    // accumulator complete
@@ -216,29 +232,24 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
     // Zin / residual rows of a chunk are requested before the TMEM load is waited for.
     const int part = nt / p.n_tiles_per_part, col0 = (nt - part * p.n_tiles_per_part) * BN;
     const int ncol0 = nt * BN;                       // column in the un-parted output (bias / R / D2 / Zin index)
-    const int row_base = mt * BM + warp * 32;
+    const int lq = warp & 3, hf = warp >> 2;          // TMEM lane quarter, column half
+    const int row_base = mt * BM + lq * 32;
     const int sub = lane >> 3, cq = (lane & 7) * 4;  // coalesced mapping: rows 4*it + sub, columns cq..cq+3
-    float* stg = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + warp * (32 * 36);
+    float* stg = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + warp * (32 * 36);   // 8 x 4.5 KB <= the ring
     float* dbase = p.D ? p.D + (long long)blockIdx.z * p.d_split_stride + (long long)part * p.d_part_stride + col0
                        : nullptr;
     const bool dgelu = p.epi == B200GAT_EPI_DGELU, gelu = p.epi == B200GAT_EPI_GELU;
     bool waited = false;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
-      float4 zin[8], res[8];
-      if (dgelu) {
+    for (int c = hf * (BN / 2); c < (hf + 1) * (BN / 2); c += 32) {
+      float4 pre[8];                                 // Zin (DGELU) or residual rows of this chunk, never both
+      const float* pre_src = dgelu ? p.Zin : p.R;
+      const long long pre_ld = dgelu ? p.ld2 : p.ldr;
+      if (pre_src) {
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           const int row = row_base + 4 * it + sub;
-          zin[it] = row < p.M ? __ldg(reinterpret_cast<const float4*>(p.Zin + (long long)row * p.ld2 + ncol0 + c + cq))
-                              : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      }
-      if (p.R) {
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int row = row_base + 4 * it + sub;
-          res[it] = row < p.M ? __ldg(reinterpret_cast<const float4*>(p.R + (long long)row * p.ldr + ncol0 + c + cq))
+          pre[it] = row < p.M ? __ldg(reinterpret_cast<const float4*>(pre_src + (long long)row * pre_ld + ncol0 + c + cq))
                               : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
@@ -250,7 +261,7 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
         waited = true;
       }
       uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, r);
+      tmem_ld32(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)c, r);
 #pragma unroll
       for (int q = 0; q < 8; ++q)
         *reinterpret_cast<float4*>(stg + lane * 36 + 4 * q) =
@@ -263,9 +274,10 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
         float4 v = *reinterpret_cast<const float4*>(stg + rl * 36 + cq);
         v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
         if (dgelu) {
-          v.x *= dgelu_f(zin[it].x); v.y *= dgelu_f(zin[it].y); v.z *= dgelu_f(zin[it].z); v.w *= dgelu_f(zin[it].w);
+          v.x *= dgelu_f(pre[it].x); v.y *= dgelu_f(pre[it].y); v.z *= dgelu_f(pre[it].z); v.w *= dgelu_f(pre[it].w);
+        } else if (pre_src) {
+          v.x += pre[it].x; v.y += pre[it].y; v.z += pre[it].z; v.w += pre[it].w;
         }
-        if (p.R) { v.x += res[it].x; v.y += res[it].y; v.z += res[it].z; v.w += res[it].w; }
         if (row < p.M) {
           if (dbase) *reinterpret_cast<float4*>(dbase + (long long)row * p.ldd + c + cq) = v;
           if (gelu)
@@ -275,25 +287,63 @@ __global__ void __launch_bounds__(192, 2) k_gemm_tf32(const __grid_constant__ CU
       }
       __syncwarp();
     }
+    if (rowsum && hf == 0) {
+      if (!waited) {
+        mbar_wait(accum_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      }
+      uint32_t rs;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];"
+                   : "=r"(rs)
+                   : "r"(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)BN));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      const int row = row_base + lane;
+      if (row < p.M) p.a_rowsum[(long long)blockIdx.z * p.rowsum_split_stride + row] = __uint_as_float(rs);
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
 }
 
-// out[i] = sum_z ws[z * stride + i], fixed order (deterministic split-K)
-__global__ void k_splitk_reduce(const float* __restrict__ ws, int splits, long long stride, long long n4,
-                                float* __restrict__ out) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
-    float4 a = reinterpret_cast<const float4*>(ws)[i];
-    for (int z = 1; z < splits; ++z) {
-      const float4 b = reinterpret_cast<const float4*>(ws + z * stride)[i];
+// Deterministic split-K reduction: out[i] = sum_z ws[z * stride + i] for the n4 float4 of the output, and the same
+// for the r4 float4 of the row-sum partials behind them.  Block = 8 z-lanes x 32 float4 columns: z-lane j sums the
+// splits j, j+8, ... in order, the eight partials are added in lane order.
+__global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__ ws, int splits, long long stride,
+                                                       long long n4, float* __restrict__ out,
+                                                       const float* __restrict__ ws_rs, long long rs_stride,
+                                                       long long r4, float* __restrict__ out_rs) {
+  __shared__ float4 part[8][32];
+  const int lane = threadIdx.x & 31, zl = threadIdx.x >> 5;
+  const long long dblocks = (n4 + 31) / 32;
+  long long i = (long long)blockIdx.x * 32 + lane;
+  const float* src = ws;
+  float* dst = out;
+  long long st = stride, n = n4;
+  if (blockIdx.x >= dblocks) {         // the blocks behind the output handle the row sums
+    i -= dblocks * 32;
+    src = ws_rs; dst = out_rs; st = rs_stride; n = r4;
+  }
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < n) {
+#pragma unroll 4
+    for (int z = zl; z < splits; z += 8) {
+      const float4 b = reinterpret_cast<const float4*>(src + z * st)[i];
       a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
     }
-    reinterpret_cast<float4*>(out)[i] = a;
+  }
+  part[zl][lane] = a;
+  __syncthreads();
+  if (zl == 0 && i < n) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) {
+      const float4 b = part[j][lane];
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    reinterpret_cast<float4*>(dst)[i] = a;
   }
 }
 
@@ -316,11 +366,13 @@ __global__ void k_colsum_partial(const float* __restrict__ X, long long M, int N
   }
 }
 __global__ void k_colsum_finish(const float* __restrict__ partial, int slabs, int N, float* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per column: lanes stride over the slabs, fixed-order shuffle tree
+  const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (c >= N) return;
   float a = 0.f;
-  for (int s = 0; s < slabs; ++s) a += partial[(long long)s * N + c];
-  out[c] = a;
+  for (int s = lane; s < slabs; s += 32) a += partial[(long long)s * N + c];
+  a = warp_sum(a);
+  if (lane == 0) out[c] = a;
 }
 
 // ------------------------------------------------------------------------------------------- host side
@@ -379,7 +431,13 @@ int make_map(CUtensorMap* tm, const float* ptr, long long cols, long long rows, 
   return B200GAT_OK;
 }
 
-int pick_bn(long long n_per_part) {
+int pick_bn(long long n_per_part, bool a_mn) {
+  static const unsigned force = env_u("B200GAT_GEMM_BN", 0);      // development override
+  if (force == 64 && n_per_part % 64 == 0) return 64;
+  if (force == 128 && n_per_part % 128 == 0) return 128;
+  // 256-wide tiles read the weight operand once per 128 rows; weight gradients (split-K) keep 128 so that the
+  // partials stay small
+  if (!a_mn && n_per_part % 256 == 0) return 256;
   if (n_per_part % 128 == 0) return 128;
   if (n_per_part % 64 == 0) return 64;
   return 0;
@@ -404,9 +462,10 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   GEMM_REQ(g->M < (1ll << 31) && g->N <= 65535ll * 64 && g->K < (1ll << 31), "extent too large");
   const int ap = g->a_parts > 1 ? g->a_parts : 1, dp = g->d_parts > 1 ? g->d_parts : 1;
   GEMM_REQ(g->N % dp == 0, "N not divisible by d_parts");
-  s->bn = pick_bn(g->N / dp);
+  s->bn = pick_bn(g->N / dp, g->a_major != 0);
   GEMM_REQ(s->bn != 0, "N (per part) must be a multiple of 64");
   GEMM_REQ(g->lda % 4 == 0 && g->ldb % 4 == 0 && g->ldd % 4 == 0, "leading dimensions must be multiples of 4 floats");
+  if (g->a_rowsum) GEMM_REQ(g->d_parts <= 1, "row sums are not combined with parted outputs");
   GEMM_REQ(aligned16(g->A) && aligned16(g->B) && aligned16(g->D) && aligned16(g->bias) && aligned16(g->residual) &&
                aligned16(g->D2) && aligned16(g->Zin),
            "pointers must be 16-byte aligned");
@@ -419,7 +478,8 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   GEMM_REQ(g->epilogue == B200GAT_EPI_NONE || g->epilogue == B200GAT_EPI_GELU || g->epilogue == B200GAT_EPI_DGELU,
            "unknown epilogue");
   if (g->epilogue == B200GAT_EPI_GELU) GEMM_REQ(g->D2 && g->ld2 % 4 == 0, "EPI_GELU needs D2");
-  if (g->epilogue == B200GAT_EPI_DGELU) GEMM_REQ(g->Zin && g->ld2 % 4 == 0 && g->D, "EPI_DGELU needs Zin and D");
+  if (g->epilogue == B200GAT_EPI_DGELU)
+    GEMM_REQ(g->Zin && g->ld2 % 4 == 0 && g->D && !g->residual, "EPI_DGELU needs Zin and D and takes no residual");
   if (g->epilogue == B200GAT_EPI_NONE) GEMM_REQ(g->D != nullptr, "null D");
   if (g->residual) GEMM_REQ(g->ldr % 4 == 0, "ldr must be a multiple of 4");
   s->m_tiles = (int)ceil_div(g->M, BM);
@@ -439,8 +499,10 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   if (s->splits > 1) {
     GEMM_REQ(g->epilogue == B200GAT_EPI_NONE && !g->residual && !g->bias && dp == 1, "split-K takes a plain epilogue");
     GEMM_REQ(g->ldd == g->N, "split-K needs a contiguous output");
-    GEMM_REQ(g->workspace_elems >= (long long)s->splits * g->M * g->N, "workspace too small");
     GEMM_REQ(aligned16(g->workspace) && (g->M * g->N) % 4 == 0, "workspace alignment");
+    if (g->a_rowsum) GEMM_REQ(g->M % 4 == 0 && aligned16(g->a_rowsum), "row sums under split-K need M % 4 == 0");
+    GEMM_REQ(g->workspace_elems >= (long long)s->splits * (g->M * g->N + (g->a_rowsum ? g->M : 0)),
+             "workspace too small");
   }
   return B200GAT_OK;
 #undef GEMM_REQ
@@ -448,7 +510,7 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
 
 template <int BN, bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, dim3 grid, cudaStream_t st) {
-  constexpr size_t smem = (size_t)STAGES * (A_STAGE_BYTES + BN * BK * 4) + 1024;
+  constexpr size_t smem = (size_t)STAGES * (A_STAGE_BYTES + BN * BK * 4) + 1024 + 2048;   // + alignment + ones tile
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(k_gemm_tf32<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
@@ -458,7 +520,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, dim3
     }
     attr_set = true;
   }
-  k_gemm_tf32<BN, A_MN, B_MN><<<grid, 192, smem, st>>>(ta, tb, a);
+  k_gemm_tf32<BN, A_MN, B_MN><<<grid, 320, smem, st>>>(ta, tb, a);
   B200_CHECK_LAUNCH("k_gemm_tf32");
   return B200GAT_OK;
 }
@@ -482,7 +544,7 @@ extern "C" int64_t b200gat_gemm_workspace_elems(const b200gat_gemm* g) {
   probe.workspace_elems = INT64_MAX;
   Shape s;
   if (plan_gemm(&probe, &s, false) != B200GAT_OK || s.splits <= 1) return 0;
-  return (int64_t)s.splits * g->M * g->N;
+  return (int64_t)s.splits * (g->M * g->N + (g->a_rowsum ? g->M : 0));
 }
 
 extern "C" int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream) {
@@ -519,20 +581,26 @@ extern "C" int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream) {
   a.mn_sbo = env_u("B200GAT_MN_SBO", 512);
   a.mn_layout = env_u("B200GAT_MN_LAYOUT", 1);
   a.mn_kadv = env_u("B200GAT_MN_KADV", 1024);
+  a.a_rowsum = g->a_rowsum; a.rowsum_split_stride = 0;
+  if (s.splits > 1 && g->a_rowsum) {
+    a.a_rowsum = g->workspace + (long long)s.splits * g->M * g->N;
+    a.rowsum_split_stride = g->M;
+  }
   dim3 grid((unsigned)s.m_tiles, (unsigned)s.n_tiles, (unsigned)s.splits);
-  ScopedTimer tm(B200GAT_TIMING_GEMM, st);
+  ScopedTimer tm(a_mn ? B200GAT_TIMING_GEMM_DW : (b_mn ? B200GAT_TIMING_GEMM_DX : B200GAT_TIMING_GEMM), st);
 #define GEMM_LAUNCH(BN_)                                                           \
   (a_mn ? (b_mn ? launch<BN_, true, true>(ta, tb, a, grid, st)                     \
                 : launch<BN_, true, false>(ta, tb, a, grid, st))                   \
         : (b_mn ? launch<BN_, false, true>(ta, tb, a, grid, st)                    \
                 : launch<BN_, false, false>(ta, tb, a, grid, st)))
-  rc = s.bn == 128 ? GEMM_LAUNCH(128) : GEMM_LAUNCH(64);
+  rc = s.bn == 256 ? GEMM_LAUNCH(256) : (s.bn == 128 ? GEMM_LAUNCH(128) : GEMM_LAUNCH(64));
 #undef GEMM_LAUNCH
   if (rc) return rc;
   if (s.splits > 1) {
-    const long long n4 = g->M * g->N / 4;
-    const unsigned blocks = (unsigned)(ceil_div(n4, 256) < 4 * kNumSMs ? ceil_div(n4, 256) : 4 * kNumSMs);
-    k_splitk_reduce<<<blocks, 256, 0, st>>>(g->workspace, s.splits, g->M * g->N, n4, g->D);
+    const long long n4 = g->M * g->N / 4, r4 = g->a_rowsum ? g->M / 4 : 0;
+    const unsigned blocks = (unsigned)(ceil_div(n4, 32) + ceil_div(r4, 32));
+    k_splitk_reduce<<<blocks, 256, 0, st>>>(g->workspace, s.splits, g->M * g->N, n4, g->D, a.a_rowsum, g->M, r4,
+                                            g->a_rowsum);
     B200_CHECK_LAUNCH("k_splitk_reduce");
   }
   return B200GAT_OK;
@@ -558,7 +626,7 @@ extern "C" int b200gat_colsum(const float* X, int64_t M, int64_t N, int64_t ld, 
   const int slabs = (int)ceil_div(M, rows);
   ScopedTimer tm(B200GAT_TIMING_GEMM, st);
   k_colsum_partial<<<slabs, 256, 0, st>>>(X, M, (int)N, ld, rows, scratch);
-  k_colsum_finish<<<(unsigned)ceil_div(N, 128), 128, 0, st>>>(scratch, slabs, (int)N, out);
+  k_colsum_finish<<<(unsigned)ceil_div(N, 8), 256, 0, st>>>(scratch, slabs, (int)N, out);
   B200_CHECK_LAUNCHES("k_colsum", 2);
   return B200GAT_OK;
 }

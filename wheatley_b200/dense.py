@@ -29,7 +29,7 @@ def _ok(t):
 
 
 def _desc(a_major, b_major, M, N, K, A, lda, B, ldb, D, ldd, *, a_parts=1, a_part_stride=0, d_parts=1,
-          d_part_stride=0, bias=None, residual=None, epi=_lib.EPI_NONE, D2=None, Zin=None, ld2=0):
+          d_part_stride=0, bias=None, residual=None, epi=_lib.EPI_NONE, D2=None, Zin=None, ld2=0, a_rowsum=None):
     g = _lib.Gemm()
     g.a_major, g.b_major, g.M, g.N, g.K = a_major, b_major, M, N, K
     g.A, g.lda, g.a_parts, g.a_part_stride = _lib.ptr(A), lda, a_parts, a_part_stride
@@ -37,7 +37,7 @@ def _desc(a_major, b_major, M, N, K, A, lda, B, ldb, D, ldd, *, a_parts=1, a_par
     g.D, g.ldd, g.d_parts, g.d_part_stride = _lib.ptr(D), ldd, d_parts, d_part_stride
     g.bias, g.residual, g.ldr = _lib.ptr(bias), _lib.ptr(residual), (residual.stride(0) if residual is not None else 0)
     g.epilogue, g.D2, g.Zin, g.ld2 = epi, _lib.ptr(D2), _lib.ptr(Zin), ld2
-    g.workspace, g.workspace_elems = None, 0
+    g.workspace, g.workspace_elems, g.a_rowsum = None, 0, _lib.ptr(a_rowsum)
     return g
 
 
@@ -96,16 +96,19 @@ def linear_dx(dy, W, z_prev=None):
     return dx
 
 
-def linear_dw(dy, x):
-    """``dW = dy^T x``: dy [M, N], x [M, K] -> [N, K] (reduction over the M rows, split-K)."""
+def linear_dw(dy, x, want_bias=False):
+    """``dW = dy^T x``: dy [M, N], x [M, K] -> [N, K] (reduction over the M rows, split-K); with
+    ``want_bias`` also ``db = dy.sum(0)`` (row sums of the A operand, from the same launch).
+    Returns ``(dW, db or None)``."""
     M, N = dy.shape
     K = x.shape[1]
     if tf32_path_enabled() and _ok(dy) and _ok(x) and M > 0 and N % 4 == 0 and K % 64 == 0:
         dW = torch.empty((N, K), dtype=torch.float32, device=dy.device)
-        g = _desc(1, 1, N, K, M, dy, N, x, K, dW, K)
+        db = torch.empty(N, dtype=torch.float32, device=dy.device) if want_bias else None
+        g = _desc(1, 1, N, K, M, dy, N, x, K, dW, K, a_rowsum=db)
         _run(g, dy.device, "b200gat_gemm_tf32 (dW)")
-        return dW
-    return dy.t() @ x
+        return dW, db
+    return dy.t() @ x, (colsum(dy) if want_bias else None)
 
 
 def colsum(x):
@@ -154,8 +157,8 @@ class _GeluMLP(torch.autograd.Function):
         for i in range(n - 1, -1, -1):
             h_in = acts[2 * i]                      # input of layer i
             if ctx.needs_input_grad[2 + 2 * i]:
-                grads[2 * i] = linear_dw(dz, h_in)
-            if ctx.needs_input_grad[3 + 2 * i]:
+                grads[2 * i], grads[2 * i + 1] = linear_dw(dz, h_in, want_bias=ctx.needs_input_grad[3 + 2 * i])
+            elif ctx.needs_input_grad[3 + 2 * i]:
                 grads[2 * i + 1] = colsum(dz)
             if i > 0:
                 dz = linear_dx(dz, Ws[i], acts[2 * i - 1])      # * gelu'(z_{i-1})
