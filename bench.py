@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--gemm", default=None, help="override WHEATLEY_B200_GEMM (cublas|tcgen05)")
+    ap.add_argument("--max-seconds", type=float, default=900.0, help="watchdog: hard exit after this long")
     ap.add_argument("--no-graph", action="store_true",
                     help="launch the resident-input step eagerly instead of replaying one captured CUDA graph")
     return ap.parse_args()
@@ -349,9 +350,18 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(edges_all)
     edges_total = float(edges_all)
+    # tear the graphs down before anything else: a live CUDA graph holding captured NCCL kernels makes the
+    # communicator teardown block (seen at N=2: every rank printed / finished, then hung in shutdown)
+    step_fn = None
+    if graph is not None:
+        graph.reset()
+        tgraph.reset()
+        _lib.lib.b200gat_timing_clear_graph()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        finish(world)
         return
 
     import json as _json
@@ -405,12 +415,35 @@ def run_b200(args):
         cb, _, _ = time_cpu(cfg, args, 1000, 1, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)
+    finish(world)
+
+
+def finish(world):
+    """End of a rank's run.  Multi-rank runs leave through os._exit after flushing: the NCCL communicator
+    teardown at interpreter shutdown has nothing left to do for the bench and is the one place a finished run
+    could still block."""
+    sys.stdout.flush()
+    sys.stderr.flush()
     if world > 1:
-        dist.destroy_process_group()
+        os._exit(0)
+
+
+def start_watchdog(seconds):
+    """A bench run that has not finished after ``seconds`` is stuck: exit instead of holding the GPUs."""
+    import threading
+
+    def fire():
+        sys.stderr.write(f"bench.py: watchdog fired after {seconds} s, exiting\n")
+        sys.stderr.flush()
+        os._exit(3)
+    t = threading.Timer(seconds, fire)
+    t.daemon = True
+    t.start()
 
 
 def main():
     args = parse()
+    start_watchdog(args.max_seconds)
     # the workload generator is plain numpy: load it by path so the reference arm does not need
     # the CUDA library (wheatley_b200/__init__ refuses to import without it)
     import importlib.util

@@ -117,9 +117,30 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 
-__device__ __forceinline__ float gelu_f(float z) { return 0.5f * z * (1.f + erff(z * 0.70710678118654752f)); }
+// Exact-form GELU (torch.nn.GELU default, erf) and its derivative with one exp and one reciprocal per element:
+//   Phi(z) = 0.5 (1 + erf(z / sqrt 2)),  erf(x) = sign(x) (1 - (a1 t + ... + a5 t^5) exp(-x^2)),  t = 1 / (1 + p |x|)
+// (Abramowitz-Stegun 7.1.26, |error| <= 1.5e-7, i.e. fp32 rounding level); exp(-x^2) = exp(-z^2 / 2) is also the
+// Gaussian of the derivative: gelu'(z) = Phi(z) + z exp(-z^2 / 2) / sqrt(2 pi).
+__device__ __forceinline__ void phi_and_gauss(float z, float& phi, float& gauss) {
+  const float ax = fabsf(z) * 0.70710678118654752f;
+  const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+  gauss = __expf(-0.5f * z * z);
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_erfc = 0.5f * poly * t * gauss;          // 0.5 (1 - erf|x|)
+  phi = z >= 0.f ? 1.f - half_erfc : half_erfc;
+}
+__device__ __forceinline__ float gelu_f(float z) {
+  float phi, g;
+  phi_and_gauss(z, phi, g);
+  return z * phi;
+}
 __device__ __forceinline__ float dgelu_f(float z) {
-  return 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.39894228040143268f * __expf(-0.5f * z * z);
+  float phi, g;
+  phi_and_gauss(z, phi, g);
+  return fmaf(z * 0.39894228040143268f, g, phi);
 }
 
 // ------------------------------------------------------------------------------------------- the kernel
