@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200gat.so")
+LIB_PATH = os.environ.get("B200GAT_LIB") or os.path.join(_HERE, "libb200gat.so")   # env: development builds
 
 EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
 MAX_ATTR = 8

@@ -114,6 +114,9 @@ __device__ __forceinline__ void affine_add(const FastArgs& A, int64_t pos, int c
   }
 }
 
+#ifndef B200GAT_FAST_MINB
+#define B200GAT_FAST_MINB 2      // resident CTAs per SM the node kernels are compiled for (register cap)
+#endif
 constexpr int kFastThreads = 256;
 constexpr int kWarps = kFastThreads / 32;
 constexpr int kHubBlocks = 148;  // CTAs at the front of the grid that walk the hub list
@@ -197,7 +200,7 @@ __device__ __forceinline__ void fwd_finalize(const FastArgs& A, int v, bool any,
 
 // ------------------------------------------------------------------------------ forward
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, 2) k_fwd_fast(
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
     float* __restrict__ l_save, float* __restrict__ agg_save) {
@@ -359,7 +362,7 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, floa
 // Dynamic shared memory: sh_gat[HD] (d attn of the CTA) + sh_tab[T][HD] (d edge table of the CTA,
 // when it fits).  Static: per-warp partial d Pj rows for the hub merge.
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_fast(
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
     const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
@@ -558,7 +561,7 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, floa
 
 // ------------------------------------------------------------------------------ backward, by source
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, 2) k_bwd_src_fast(
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
     const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
     float* __restrict__ gV) {
