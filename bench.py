@@ -344,7 +344,7 @@ def run_b200(args):
         d = to_dev()
         jb = make_batch(d)
         return train_step(jb, d).item()                    # .item(): device->host read of the loss
-    ms_e2e, _, _ = timed(e2e_step, max(3, args.steps // 2), 3)
+    ms_e2e, _, _ = timed(e2e_step, max(3, args.steps), 5)
 
     edges_all = torch.tensor([E], device=dev, dtype=torch.float64)
     if world > 1:

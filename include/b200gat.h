@@ -293,7 +293,7 @@ int b200gat_mask_head_bwd(const float* logp, const uint8_t* mask, int64_t ld_mas
  * [M, N / d_parts] d_part_stride floats apart (the Pi | Pj | V projections in one launch).
  * Epilogues: NONE: D = acc + bias (+ residual); GELU: D = acc + bias (pre-activation, may be NULL),
  * D2 = gelu(D) (exact erf form, torch.nn.GELU default); DGELU: D = (acc + bias) * gelu'(Zin), no residual.
- * Requirements: N per part a multiple of 64, leading dimensions multiples of 4 floats, 16-byte aligned
+ * Requirements: N a multiple of 4 (64 per part when d_parts > 1), leading dimensions multiples of 4 floats, 16-byte aligned
  * pointers; b200gat_gemm_supported() tells whether a descriptor is covered (callers use the library
  * GEMM otherwise, e.g. for the width-1 head outputs).                                               */
 #define B200GAT_EPI_NONE 0

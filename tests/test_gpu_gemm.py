@@ -38,7 +38,7 @@ def launches():
 
 
 @pytest.mark.parametrize("M,K,N", [(128, 64, 64), (1000, 64, 256), (16008, 256, 256), (16008, 256, 64),
-                                   (333, 464, 64), (5, 32, 128), (4100, 36, 192)])
+                                   (333, 464, 64), (5, 32, 128), (4100, 36, 192), (1000, 64, 100), (300, 32, 332)])
 def test_linear_forward_variants(wb, tf32, M, K, N):
     from wheatley_b200 import dense
     g = torch.Generator().manual_seed(M + K + N)
@@ -63,7 +63,7 @@ def test_linear_forward_variants(wb, tf32, M, K, N):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (16008, 256, 256), (16008, 64, 256), (16008, 256, 64),
-                                   (777, 128, 192), (16000, 64, 464 - 464 % 64)])
+                                   (777, 128, 192), (16000, 64, 464), (900, 100, 36)])
 def test_linear_backward_variants(wb, tf32, M, N, K):
     """dx = dy W (MN-major B), dx * gelu'(z) epilogue, dW = dy^T x (both operands MN-major, split-K),
     bias gradient column sums."""
@@ -94,7 +94,7 @@ def test_linear_backward_variants(wb, tf32, M, N, K):
 
 def test_gemm_rejects_uncovered_shapes(wb, tf32):
     from wheatley_b200 import _lib, dense
-    x = torch.randn(10, 30).cuda()           # 30-wide rows: not 16-byte aligned -> library GEMM
+    x = torch.randn(10, 30).cuda()           # 30-wide rows: not 16-byte aligned -> library GEMM (MLPs pad instead)
     W = torch.randn(64, 30).cuda()
     l0 = launches()
     _, y = dense.linear_fwd(x, W, None)
@@ -102,7 +102,7 @@ def test_gemm_rejects_uncovered_shapes(wb, tf32):
     assert rel(y, x.double() @ W.double().t()) < TOL_GEMM
     g = dense._desc(0, 0, 10, 1, 64, x, 64, W, 64, y, 1)     # N = 1
     assert _lib.lib.b200gat_gemm_supported(g) == 0
-    assert _lib.lib.b200gat_gemm_tf32(g, None) != 0 and b"multiple of 64" in _lib.lib.b200gat_last_error()
+    assert _lib.lib.b200gat_gemm_tf32(g, None) != 0 and b"multiple of 4" in _lib.lib.b200gat_last_error()
 
 
 @pytest.mark.parametrize("dims,res", [((256, 256, 256, 64), True), ((30, 64, 64, 64), False),

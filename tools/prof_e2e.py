@@ -40,7 +40,7 @@ def main():
         opt.step()
         return loss.item()
 
-    for backend in ("tcgen05", "cublas"):
+    for backend in ("tcgen05",):
         os.environ["WHEATLEY_B200_GEMM"] = backend
         for _ in range(4):
             step()
@@ -70,8 +70,8 @@ def main():
         step()
         pr.disable()
         sio = io.StringIO()
-        pstats.Stats(pr, stream=sio).sort_stats("cumulative").print_stats(22)
-        print("\n".join(sio.getvalue().splitlines()[:45]))
+        pstats.Stats(pr, stream=sio).sort_stats("tottime").print_stats(28)
+        print("\n".join(sio.getvalue().splitlines()[:50]))
 
 
 if __name__ == "__main__":

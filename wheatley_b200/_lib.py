@@ -175,5 +175,28 @@ def ptr(t):
 
 
 def stream_ptr():
+    """Raw ``cudaStream_t`` of torch's current stream on the current device (the cheap accessor:
+    ``torch.cuda.current_stream()`` builds a Python object, ~10 us per call on the eager path)."""
     import torch
-    return torch.cuda.current_stream().cuda_stream
+    return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
+
+
+class _NoGuard:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def device_guard(device):
+    """``torch.cuda.device(device)`` only when ``device`` is not already current (the common case costs
+    two attribute reads instead of a context-manager round trip through the CUDA runtime)."""
+    import torch
+    idx = device.index
+    if idx is None or idx == torch._C._cuda_getDevice():
+        return _NO_GUARD
+    return torch.cuda.device(idx)

@@ -263,6 +263,8 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
     bool waited = false;
 #pragma unroll 1
     for (int c = hf * (BN / 2); c < (hf + 1) * (BN / 2); c += 32) {
+      if (ncol0 + c >= p.N) break;                   // ragged last column tile (N % 4 == 0): warp-uniform
+      const bool col_ok = ncol0 + c + cq < p.N;
       float4 pre[8];                                 // Zin (DGELU) or residual rows of this chunk, never both
       const float* pre_src = dgelu ? p.Zin : p.R;
       const long long pre_ld = dgelu ? p.ld2 : p.ldr;
@@ -270,12 +272,12 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           const int row = row_base + 4 * it + sub;
-          pre[it] = row < p.M ? __ldg(reinterpret_cast<const float4*>(pre_src + (long long)row * pre_ld + ncol0 + c + cq))
+          pre[it] = (row < p.M && col_ok) ? __ldg(reinterpret_cast<const float4*>(pre_src + (long long)row * pre_ld + ncol0 + c + cq))
                               : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
       float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (p.bias) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + ncol0 + c + cq));
+      if (p.bias && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + ncol0 + c + cq));
       if (!waited) {
         mbar_wait(accum_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -299,7 +301,7 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
         } else if (pre_src) {
           v.x += pre[it].x; v.y += pre[it].y; v.z += pre[it].z; v.w += pre[it].w;
         }
-        if (row < p.M) {
+        if (row < p.M && col_ok) {
           if (dbase) *reinterpret_cast<float4*>(dbase + (long long)row * p.ldd + c + cq) = v;
           if (gelu)
             *reinterpret_cast<float4*>(p.D2 + (long long)row * p.ld2 + ncol0 + c + cq) =
@@ -460,7 +462,7 @@ int pick_bn(long long n_per_part, bool a_mn) {
   // partials stay small
   if (!a_mn && n_per_part % 256 == 0) return 256;
   if (n_per_part % 128 == 0) return 128;
-  if (n_per_part % 64 == 0) return 64;
+  if (n_per_part % 4 == 0) return 64;       // ragged last tile: loads zero-filled by TMA, stores predicated
   return 0;
 }
 
@@ -484,7 +486,8 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   const int ap = g->a_parts > 1 ? g->a_parts : 1, dp = g->d_parts > 1 ? g->d_parts : 1;
   GEMM_REQ(g->N % dp == 0, "N not divisible by d_parts");
   s->bn = pick_bn(g->N / dp, g->a_major != 0);
-  GEMM_REQ(s->bn != 0, "N (per part) must be a multiple of 64");
+  GEMM_REQ(s->bn != 0, "N must be a multiple of 4");
+  GEMM_REQ(dp == 1 || (g->N / dp) % 64 == 0, "N per part must be a multiple of 64");
   GEMM_REQ(g->lda % 4 == 0 && g->ldb % 4 == 0 && g->ldd % 4 == 0, "leading dimensions must be multiples of 4 floats");
   if (g->a_rowsum) GEMM_REQ(g->d_parts <= 1, "row sums are not combined with parted outputs");
   GEMM_REQ(aligned16(g->A) && aligned16(g->B) && aligned16(g->D) && aligned16(g->bias) && aligned16(g->residual) &&
@@ -504,7 +507,7 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   if (g->epilogue == B200GAT_EPI_NONE) GEMM_REQ(g->D != nullptr, "null D");
   if (g->residual) GEMM_REQ(g->ldr % 4 == 0, "ldr must be a multiple of 4");
   s->m_tiles = (int)ceil_div(g->M, BM);
-  s->n_tiles = (int)(g->N / s->bn);
+  s->n_tiles = (int)ceil_div(g->N, s->bn);
   s->kb_total = (int)ceil_div(g->K, BK);
   // split the reduction when the tile grid alone cannot fill the machine (weight gradients: K = number of nodes)
   int splits = 1;

@@ -47,13 +47,13 @@ def _run(g, device, what):
     if ws_elems:
         ws = torch.empty(ws_elems, dtype=torch.float32, device=device)
         g.workspace, g.workspace_elems = ws.data_ptr(), ws_elems
-    with torch.cuda.device(device):
+    with _lib.device_guard(device):
         _lib.check(_lib.lib.b200gat_gemm_tf32(g, _lib.stream_ptr()), what)
 
 
 def _fwd_supported(x, W):
     return (_ok(x) and _ok(W) and x.dim() == 2 and x.shape[0] > 0 and x.shape[1] % 4 == 0
-            and W.shape[0] % 64 == 0)
+            and W.shape[0] % 4 == 0)
 
 
 def linear_fwd(x, W, b=None, gelu=False, residual=None, want_z=True):
@@ -83,7 +83,7 @@ def linear_dx(dy, W, z_prev=None):
     """``dx = dy W`` (``* gelu'(z_prev)`` when given).  dy [M, N], W [N, K] -> [M, K]."""
     M, N = dy.shape
     K = W.shape[1]
-    if tf32_path_enabled() and _ok(dy) and _ok(W) and M > 0 and N % 4 == 0 and K % 64 == 0:
+    if tf32_path_enabled() and _ok(dy) and _ok(W) and M > 0 and N % 4 == 0 and K % 4 == 0:
         W = W.contiguous()
         dx = torch.empty((M, K), dtype=torch.float32, device=dy.device)
         g = _desc(0, 1, M, K, N, dy, N, W, K, dx, K,
@@ -102,7 +102,7 @@ def linear_dw(dy, x, want_bias=False):
     Returns ``(dW, db or None)``."""
     M, N = dy.shape
     K = x.shape[1]
-    if tf32_path_enabled() and _ok(dy) and _ok(x) and M > 0 and N % 4 == 0 and K % 64 == 0:
+    if tf32_path_enabled() and _ok(dy) and _ok(x) and M > 0 and N % 4 == 0 and K % 4 == 0:
         dW = torch.empty((N, K), dtype=torch.float32, device=dy.device)
         db = torch.empty(N, dtype=torch.float32, device=dy.device) if want_bias else None
         g = _desc(1, 1, N, K, M, dy, N, x, K, dW, K, a_rowsum=db)
@@ -119,7 +119,7 @@ def colsum(x):
     out = torch.empty(N, dtype=torch.float32, device=x.device)
     scratch = torch.empty(max(1, int(_lib.lib.b200gat_colsum_scratch_elems(M, N))), dtype=torch.float32,
                           device=x.device)
-    with torch.cuda.device(x.device):
+    with _lib.device_guard(x.device):
         _lib.check(_lib.lib.b200gat_colsum(_lib.ptr(x), M, N, x.stride(0), _lib.ptr(out), _lib.ptr(scratch),
                                            _lib.stream_ptr()), "b200gat_colsum")
     return out
@@ -170,10 +170,16 @@ class _GeluMLP(torch.autograd.Function):
 
 
 def gelu_mlp(x, layers, residual=None):
-    """``layers``: the ``nn.Linear`` modules of a GELU MLP (bias required)."""
+    """``layers``: the ``nn.Linear`` modules of a GELU MLP (bias required).  An input width that is not a
+    multiple of 4 floats (the 30-wide JSSP node features) is zero-padded, with the first weight, to the next
+    multiple: TMA rows must be 16-byte aligned, and the zero columns change nothing."""
     params = []
     for lin in layers:
         params += [lin.weight, lin.bias]
+    pad = (-x.shape[1]) % 4
+    if pad:
+        x = torch.nn.functional.pad(x, (0, pad))
+        params[0] = torch.nn.functional.pad(params[0], (0, pad))
     return _GeluMLP.apply(x.contiguous(), None if residual is None else residual.contiguous(), *params)
 
 

@@ -99,11 +99,14 @@ class _FusedGATConv(torch.autograd.Function):
         s_dense = torch.empty(H * view.s_elems, dtype=torch.float32, device=Pi.device) if dense else None
         if dense and agg is None:           # the dense backward needs it; the forward writes it anyway
             agg = torch.empty((N, HD), dtype=torch.float32, device=Pi.device)
-        with torch.cuda.device(Pi.device):
+        with _lib.device_guard(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_fwd(view.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt),
                                                  _lib.ptr(out), _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
                                                  _lib.ptr(agg), _lib.ptr(s_dense), _lib.stream_ptr()),
                        "b200gat_conv_fwd")
+        # no zero-filled stand-ins for the gradients of the non-differentiable outputs (s, m, l, s_dense are
+        # 2 x 26 MB per layer at 8 x Taillard 100x20: materialising them was 4 memsets per layer)
+        ctx.set_materialize_grads(False)
         ctx.plan, ctx.view, ctx.cfg, ctx.mode, ctx.v_alias = plan, view, cfg, mode, v_alias
         ctx.dense = dense
         ctx.etype_sorted, ctx.attr_sorted = etype_sorted, attr_sorted
@@ -122,6 +125,8 @@ class _FusedGATConv(torch.autograd.Function):
          s_dense) = ctx.saved_tensors
         plan, view, cfg = ctx.plan, ctx.view, ctx.cfg
         H, D = cfg["heads"], cfg["dim"]
+        if g_out is None:
+            return (None,) * 14
         g_out = _f32c(g_out)
         # one [3, N, HD] buffer: the projection backward (dense._Proj3) reads gPi | gPj | gV as one operand
         g3 = torch.empty((2 if ctx.v_alias else 3,) + tuple(Pi.shape), dtype=Pi.dtype, device=Pi.device)
@@ -142,7 +147,7 @@ class _FusedGATConv(torch.autograd.Function):
                             _lib.ptr(e_table_c), _lib.ptr(ctx.etype_sorted), _lib.ptr(e_dense_c),
                             0 if e_affine_c is None else e_affine_c.shape[0], _lib.ptr(ctx.attr_sorted),
                             _lib.ptr(e_affine_c))
-        with torch.cuda.device(Pi.device):
+        with _lib.device_guard(Pi.device):
             _lib.check(_lib.lib.b200gat_conv_bwd(
                 view.c, a, ef, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(Vt), _lib.ptr(s), _lib.ptr(m),
                 _lib.ptr(l), _lib.ptr(agg), _lib.ptr(s_dense), _lib.ptr(g_out), _lib.ptr(gPi), _lib.ptr(gPj),
@@ -173,7 +178,7 @@ def attention_weights(plan: GraphPlan, saved, heads: int, eps: float) -> torch.T
     """alpha [E, H] in the original edge order from the logits saved by the forward."""
     s, m, l, s_dense, view = saved
     alpha = torch.empty((plan.n_edges, heads), dtype=torch.float32, device=s.device)
-    with torch.cuda.device(s.device):
+    with _lib.device_guard(s.device):
         _lib.check(_lib.lib.b200gat_attention(view.c, heads, eps, _lib.ptr(s), _lib.ptr(m), _lib.ptr(l),
                                               _lib.ptr(s_dense), _lib.ptr(alpha), _lib.stream_ptr()),
                    "b200gat_attention")
@@ -193,7 +198,7 @@ def edge_output(plan: GraphPlan, Pi, Pj, edge_feats: EdgeFeatures, *, heads, dim
                          _lib.ptr(ef.etype_sorted), _lib.ptr(dns), 0 if aff is None else aff.shape[0],
                          _lib.ptr(ef.attr_sorted), _lib.ptr(aff))
     f = torch.empty((plan.n_edges, heads, dim), dtype=torch.float32, device=Pi.device)
-    with torch.cuda.device(Pi.device):
+    with _lib.device_guard(Pi.device):
         _lib.check(_lib.lib.b200gat_edge_out(plan.c, a, efc, _lib.ptr(Pi), _lib.ptr(Pj), _lib.ptr(f),
                                              _lib.stream_ptr()), "b200gat_edge_out")
     return f
@@ -209,7 +214,7 @@ class _MaskedHead(torch.autograd.Function):
         logp = torch.empty_like(logits)
         ent = torch.empty(B, dtype=torch.float32, device=logits.device)
         amax = torch.empty(B, dtype=torch.int64, device=logits.device)
-        with torch.cuda.device(logits.device):
+        with _lib.device_guard(logits.device):
             _lib.check(_lib.lib.b200gat_mask_head_fwd(
                 _lib.ptr(logits), logits.stride(0), _lib.ptr(mask_u8),
                 0 if mask_u8 is None else mask_u8.stride(0), B, n, fill, _lib.ptr(logp), _lib.ptr(ent),
@@ -225,7 +230,7 @@ class _MaskedHead(torch.autograd.Function):
         # general path: logp is used through arbitrary downstream ops -> dense softmax backward
         # d logits = g_logp - p * sum(g_logp)  (masked entries get 0), entropy term via the kernel.
         g_logits = torch.empty_like(logp)
-        with torch.cuda.device(logp.device):
+        with _lib.device_guard(logp.device):
             _lib.check(_lib.lib.b200gat_mask_head_bwd(
                 _lib.ptr(logp), _lib.ptr(mask_u8), 0 if mask_u8 is None else mask_u8.stride(0), None,
                 _lib.ptr(ent), None, _lib.ptr(_f32c(g_ent)) if g_ent is not None else None, B, n,
@@ -249,7 +254,7 @@ class _MaskedHeadEval(torch.autograd.Function):
         B, n = logits.shape
         logp = torch.empty_like(logits)
         ent = torch.empty(B, dtype=torch.float32, device=logits.device)
-        with torch.cuda.device(logits.device):
+        with _lib.device_guard(logits.device):
             _lib.check(_lib.lib.b200gat_mask_head_fwd(
                 _lib.ptr(logits), logits.stride(0), _lib.ptr(mask_u8),
                 0 if mask_u8 is None else mask_u8.stride(0), B, n, fill, _lib.ptr(logp), _lib.ptr(ent),
@@ -264,7 +269,7 @@ class _MaskedHeadEval(torch.autograd.Function):
         logp, ent, mask_u8, action = ctx.saved_tensors
         B, n = logp.shape
         g_logits = torch.empty_like(logp)
-        with torch.cuda.device(logp.device):
+        with _lib.device_guard(logp.device):
             _lib.check(_lib.lib.b200gat_mask_head_bwd(
                 _lib.ptr(logp), _lib.ptr(mask_u8), 0 if mask_u8 is None else mask_u8.stride(0),
                 _lib.ptr(action), _lib.ptr(ent), _lib.ptr(_f32c(g_lp)) if g_lp is not None else None,

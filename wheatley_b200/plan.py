@@ -67,7 +67,7 @@ class CliqueView:
         self.c = plan.c
         if N == 0 or E == 0:
             return
-        with torch.cuda.device(dev):
+        with _lib.device_guard(dev):
             self.node_blk, self.node_run, self.node_rank = (torch.empty(N, **i32) for _ in range(3))
             self.blk_ptr, self.blk_soff = torch.empty(N + 1, **i32), torch.empty(N + 1, **i32)
             self.blk_nodes, self.blk_type = torch.empty(N, **i32), torch.empty(N, **i32)
@@ -127,7 +127,7 @@ class GraphPlan:
         self.out_pos = torch.empty(E, **i32)
         self.stats = torch.empty(4, **i32)
         scratch = torch.empty(_lib.lib.b200gat_plan_scratch_elems(N, E), **i32)
-        with torch.cuda.device(dev):
+        with _lib.device_guard(dev):
             _lib.check(_lib.lib.b200gat_plan_build(
                 _lib.ptr(src), _lib.ptr(dst), E, N, _lib.ptr(self.in_ptr), _lib.ptr(self.in_src),
                 _lib.ptr(self.in_eid), _lib.ptr(self.out_ptr), _lib.ptr(self.out_dst),
