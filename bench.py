@@ -346,6 +346,26 @@ def run_b200(args):
         return train_step(jb, d).item()                    # .item(): device->host read of the loss
     ms_e2e, _, _ = timed(e2e_step, max(3, args.steps), 5)
 
+    # ---- PPO env-steps/sec (BASELINE.json metric, second half): the learner side of one PPO iteration
+    # (alg/ppo.py:196-206 rollout inference, :547-727 update) on this workload, per rank:
+    #   rollout step  = host observation of `num_envs` graphs -> device, plan, trunk + head forward under
+    #                   no_grad, sampled action read back to the host (the env needs it, alg/ppo.py:206)
+    #   update        = n_epochs passes over the rollout in minibatches of `batch` graphs = the e2e step above
+    # env-steps/s = num_envs / (t_rollout + n_epochs * (num_envs / batch) * t_update); the CPU simulators
+    # (jssp/env, psp/env) are out of scope and not in the figure.
+    def rollout_step():
+        d = to_dev()
+        jb = make_batch(d)
+        with torch.no_grad():
+            action, _, _, _, _ = agent.get_action_and_value(jb, None, d["masks"])
+        return action.cpu()
+    ms_roll, _, _ = timed(rollout_step, max(3, args.steps), 5)
+    n_epochs = 10                                           # args.py:113-117 default
+    ppo_rate = B / ((ms_roll + n_epochs * ms_e2e) * 1e-3)
+    ppo_all = torch.tensor([ppo_rate], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ppo_all)
+
     edges_all = torch.tensor([E], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(edges_all)
@@ -410,12 +430,23 @@ def run_b200(args):
                            launch=graph_note),
             "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,
+                    "minibatch_graphs": B, "n_epochs": n_epochs, "rollout_ms_per_step": ms_roll,
+                    "update_ms_per_minibatch": ms_e2e,
+                    "definition": "num_envs / (t_rollout + n_epochs * t_update), learner side only: host "
+                                  "observation in, sampled action out per rollout step; env simulators excluded",
+                    "rollout_graph_edges_per_sec": edges_per_rank_note(E, ms_roll, world)}}
     if world == 1 and not args.no_cpu_baseline:
         cb, _, _ = time_cpu(cfg, args, 1000, 1, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)
     finish(world)
+
+
+def edges_per_rank_note(edges, ms, world):
+    """Forward-only (inference) throughput of the rollout step, all ranks (same shard size on every rank)."""
+    return world * edges / (ms * 1e-3)
 
 
 def finish(world):
