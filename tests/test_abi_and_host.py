@@ -177,3 +177,41 @@ def test_flat_gradient_allreduce_world_size_2_gloo(built, tmp_path):
     outs = [p.communicate(timeout=240)[0].decode() for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_gemm_descriptor_validation_without_gpu(built):
+    """b200gat_gemm_supported / workspace sizing are host-only: shapes the tcgen05 GEMM covers, the ones it
+    hands to the library GEMM, and the split-K workspace of a weight-gradient GEMM (include/b200gat.h)."""
+    from wheatley_b200 import _lib
+    P = 1 << 20                      # fake, 16-byte aligned device addresses (never dereferenced on the host)
+
+    def desc(a_major, b_major, M, N, K, lda, ldb, ldd, **kw):
+        g = _lib.Gemm()
+        g.a_major, g.b_major, g.M, g.N, g.K = a_major, b_major, M, N, K
+        g.A, g.lda, g.B, g.ldb, g.D, g.ldd = P, lda, 2 * P, ldb, 3 * P, ldd
+        g.a_parts, g.d_parts = kw.get("a_parts", 1), kw.get("d_parts", 1)
+        g.a_part_stride, g.d_part_stride = kw.get("a_part_stride", 0), kw.get("d_part_stride", 0)
+        g.epilogue = kw.get("epilogue", _lib.EPI_NONE)
+        g.D2, g.Zin, g.ld2 = kw.get("D2"), kw.get("Zin"), kw.get("ld2", 0)
+        return g
+
+    sup = _lib.lib.b200gat_gemm_supported
+    assert sup(desc(0, 0, 16008, 256, 256, 256, 256, 256)) == 1            # MLP layer forward
+    assert sup(desc(0, 0, 16000, 64, 464, 464, 464, 64)) == 1              # head layer 1 (K = 464)
+    assert sup(desc(0, 1, 16000, 464, 64, 64, 464, 464)) == 1              # its dx: ragged 464-wide output
+    assert sup(desc(0, 0, 16008, 768, 64, 64, 64, 256, d_parts=3, d_part_stride=16008 * 256)) == 1
+    assert sup(desc(0, 0, 10, 1, 64, 64, 64, 1)) == 0                      # width-1 head output
+    assert sup(desc(0, 0, 10, 64, 30, 30, 30, 64)) == 0                    # 30-wide rows: not 16-byte aligned
+    assert sup(desc(0, 0, 10, 64, 64, 64, 64, 64, epilogue=_lib.EPI_GELU)) == 0       # GELU needs D2
+    assert sup(desc(0, 0, 10, 64, 64, 64, 64, 64, epilogue=_lib.EPI_GELU, D2=4 * P, ld2=64)) == 1
+    g = desc(0, 0, 10, 64, 64, 64, 64, 64)
+    g.A = P + 4                                                             # misaligned operand
+    assert sup(g) == 0
+    # weight gradient dW[256, 256] = dy^T x over 16,008 rows: split-K, partials + row sums in the workspace
+    g = desc(1, 1, 256, 256, 16008, 256, 256, 256)
+    ws = _lib.lib.b200gat_gemm_workspace_elems(g)
+    assert ws > 0 and ws % (256 * 256) == 0 and ws // (256 * 256) >= 16
+    g.a_rowsum = 5 * P
+    assert _lib.lib.b200gat_gemm_workspace_elems(g) == ws // (256 * 256) * (256 * 256 + 256)
+    assert _lib.lib.b200gat_gemm_workspace_elems(desc(0, 0, 16008, 256, 256, 256, 256, 256)) == 0
+    assert _lib.launch_count() == 0

@@ -211,3 +211,41 @@ def test_trunk_with_tf32_dense_path_matches_oracle(wb, tf32):
         if refp[k].grad is None:
             continue
         assert rel(p.grad, refp[k].grad) < 5e-2, k
+
+
+def test_graphconv_pyg_flavour_with_tf32_projections(wb, tf32):
+    """GraphConv(pyg=True) -> GATv2Conv: lin_l / lin_r run on the tcgen05 GEMM when TF32 is allowed; outputs
+    and gradients against the fp64 oracle (psp/graph/graph_conv.py:33-40,51-53)."""
+    from oracle import gat_oracle
+    from wheatley_b200 import _lib
+    N, E, Fin, D, H = 3000, 20000, 64, 64, 4
+    gen = torch.Generator().manual_seed(11)
+    src = torch.randint(0, N, (E,), generator=gen)
+    dst = torch.randint(0, N, (E,), generator=gen)
+    ei = torch.stack([torch.cat([src, torch.arange(N)]), torch.cat([dst, torch.arange(N)])])
+    ref = gat_oracle.OracleGATv2Conv(Fin, D, H, edge_dim=Fin).double()
+    with torch.no_grad():
+        for p_ in ref.parameters():
+            p_.add_(0.05 * torch.randn(p_.shape, generator=gen, dtype=torch.float64))
+    layer = wb.GraphConv(Fin, D, H, pyg=True, edge_dim=Fin).cuda()
+    layer.conv.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64)
+    ea = torch.randn(ei.shape[1], Fin, generator=gen, dtype=torch.float64)
+    R = torch.randn(N, H * D, generator=gen, dtype=torch.float64)
+    xr = x.clone().requires_grad_(True)
+    out_ref, _ = gat_oracle.gatv2_forward(xr, ei, ea, ref.lin_l.weight, ref.lin_l.bias, ref.lin_r.weight,
+                                          ref.lin_r.bias, ref.lin_edge.weight, ref.att, ref.bias)
+    (out_ref * R).sum().backward()
+    xg = x.float().cuda().requires_grad_(True)
+    _lib.timing_enable(True)
+    out, _ = layer.forward_nog(xg, ei.cuda(), ea.float().cuda())
+    (out * R.float().cuda()).sum().backward()
+    torch.cuda.synchronize()
+    tm = _lib.timing_read()
+    _lib.timing_enable(False)
+    assert tm["gemm"][1] >= 2 and tm["gemm_dx"][1] >= 2 and tm["gemm_dw"][1] >= 2, tm
+    assert rel(out, out_ref) < 1e-2
+    assert rel(xg.grad, xr.grad) < 5e-2          # TF32 logits through the softmax: same bound as the trunk test
+    for k, p_ in layer.conv.named_parameters():
+        q = dict(ref.named_parameters())[k]
+        assert rel(p_.grad, q.grad) < 5e-2, k

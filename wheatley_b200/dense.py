@@ -241,6 +241,10 @@ def project3(x, w_i, w_j, w_v):
 
 
 def dense_linear(x, weight, bias=None):
-    """Single ``Linear`` (no fused activation): library GEMM; the MLP / projection entry points above
-    are the fused tcgen05 paths."""
+    """Single ``Linear`` (``lin_l`` / ``lin_r`` of the PyG-flavour layers, psp/graph/graph_conv.py:33-40):
+    the one-layer case of the fused path (forward, dx and dW + bias row sums on ``b200gat_gemm_tf32``) when
+    TF32 matmuls are allowed and the shape is covered, the library GEMM otherwise."""
+    if (tf32_path_enabled() and _ok(x) and _ok(weight) and x.dim() == 2 and x.shape[0] > 0
+            and x.shape[1] % 4 == 0 and weight.shape[0] % 4 == 0):
+        return _GeluMLP.apply(x.contiguous(), None, weight, bias)
     return torch.nn.functional.linear(x, weight, bias)

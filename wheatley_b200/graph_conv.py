@@ -12,6 +12,7 @@ import torch
 from torch import nn
 
 from . import _lib
+from .dense import dense_linear
 from .edge_feats import TypedEdgeFeats
 from .eegatconv import EEGATConv
 from .functional import attention_weights, fused_gat_conv, project_edge_feats
@@ -32,6 +33,9 @@ class _PygLinear(nn.Linear):
         _glorot(self.weight)
         if self.bias is not None:
             nn.init.zeros_(self.bias)
+
+    def forward(self, x):
+        return dense_linear(x, self.weight, self.bias)
 
 
 def _resolve(edge_index, n_nodes):
