@@ -289,7 +289,9 @@ def run_b200(args):
         if world > 1:
             dist.barrier()
         clocks = smp.stop() if smp else None
-        total = sum(a.elapsed_time(b) for a, b in evs)
+        per_step = sorted(a.elapsed_time(b) for a, b in evs)
+        timed.last_spread = {"min": per_step[0], "median": per_step[len(per_step) // 2], "max": per_step[-1]}
+        total = sum(per_step)
         launches = _lib.launch_count() - l0
         t = torch.tensor([total], device=dev, dtype=torch.float64)
         if world > 1:
@@ -341,12 +343,27 @@ def run_b200(args):
     tm = _lib.timing_read()
     _lib.timing_enable(False)
 
+    # The eager legs below are host-bound (~350 launches per step): a full cyclic-GC pass over the ~10^6 long-lived
+    # objects of torch + this process costs 10-40 ms and showed up as 2-4 outlier steps in 20.  Freeze what exists
+    # (standard practice for latency-sensitive loops); objects created from here on are still collected.
+    import gc
+    gc.collect()
+    gc.freeze()
+
     # ---- e2e: host buffers in, loss out, through the public module API, every step
     def e2e_step():
         d = to_dev()
         jb = make_batch(d)
         return train_step(jb, d).item()                    # .item(): device->host read of the loss
-    ms_e2e, _, _ = timed(e2e_step, max(3, args.steps), 5)
+    ms_e2e_mean, _, _ = timed(e2e_step, max(3, args.steps), 5)
+    e2e_spread = dict(timed.last_spread)
+    # every step is bracketed by its own event pair; the median is reported because single steps of this
+    # host-bound loop occasionally stall for 20-200 ms on the shared box (seen with identical inputs and a frozen
+    # GC; mean, min and max are kept beside it).  Multi-rank: the slowest rank's median.
+    t_med = torch.tensor([e2e_spread["median"]], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_med, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t_med)
 
     # ---- PPO env-steps/sec (BASELINE.json metric, second half): the learner side of one PPO iteration
     # (alg/ppo.py:196-206 rollout inference, :547-727 update) on this workload, per rank:
@@ -361,7 +378,8 @@ def run_b200(args):
         with torch.no_grad():
             action, _, _, _, _ = agent.get_action_and_value(jb, None, d["masks"])
         return action.cpu()
-    ms_roll, _, _ = timed(rollout_step, max(3, args.steps), 5)
+    timed(rollout_step, max(3, args.steps), 5)
+    ms_roll = timed.last_spread["median"]
     n_epochs = 10                                           # args.py:113-117 default
     ppo_rate = B / ((ms_roll + n_epochs * ms_e2e) * 1e-3)
     ppo_all = torch.tensor([ppo_rate], device=dev, dtype=torch.float64)
@@ -431,6 +449,8 @@ def run_b200(args):
                            step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam",
                            launch=graph_note),
             "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "ms_per_step_mean": ms_e2e_mean, "ms_per_step_spread": e2e_spread,
+                    "statistic": "median of the per-step CUDA-event times (rank 0 spread shown; max over ranks)",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,

@@ -321,8 +321,8 @@ typedef struct b200gat_gemm {
   int64_t ld2;
   float* workspace;         /* split-K partials (b200gat_gemm_workspace_elems floats) or NULL */
   int64_t workspace_elems;
-  float* a_rowsum;          /* optional [M]: sum_k A(m, k) - the bias gradient when A = dy^T (dW GEMM); */
-                            /* computed by the tensor core against an all-ones tile, no extra pass      */
+  float* a_rowsum;          /* optional [M], a_major 1 only: sum_k A(m, k) - the bias gradient when A = dy  */
+                            /* (dW GEMM); exact fp32 sums of the staged tiles by the idle epilogue warps */
 } b200gat_gemm;
 int b200gat_gemm_supported(const b200gat_gemm* g);
 int64_t b200gat_gemm_workspace_elems(const b200gat_gemm* g);
@@ -331,6 +331,41 @@ int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream);
 int64_t b200gat_colsum_scratch_elems(int64_t M, int64_t N);
 int b200gat_colsum(const float* X, int64_t M, int64_t N, int64_t ld, float* out, float* scratch,
                    void* stream);
+
+/* ------------------------------------------------------------------ fused GELU MLP (one call per pass)
+ * generic/mlp.py:70-77 with activation GELU and no LayerNorm (the default configuration, args.py:335-348):
+ *     h_0 = x ; z_i = h_i W_i^T + b_i ; h_{i+1} = gelu(z_i) (i < n-1) ; y = z_{n-1} (+ residual)
+ * b200gat_mlp_fwd issues the n GEMMs of the forward pass, b200gat_mlp_bwd the 2n - 1 (or 2n) GEMMs of the
+ * backward pass (dW_i = dz_i^T h_i with the bias row sums, dz_{i-1} = (dz_i W_i) * gelu'(z_{i-1}), dx = dz_0 W_0)
+ * on b200gat_gemm_tf32, from ONE host call each: the eager PPO step is host-bound, and one binding call per
+ * pass instead of one per GEMM is what the host mirror needs.  Every width must be a multiple of 4 floats
+ * (the mirror zero-pads the 30-wide JSSP input and the width-1 head outputs).  z / h may be NULL in b200gat_mlp
+ * for inference (no pre-activations kept); h is always needed as the next layer's input.                  */
+#define B200GAT_MLP_MAX_LAYERS 8
+typedef struct b200gat_mlp {
+  int32_t n_layers;
+  int64_t M;
+  int32_t dims[B200GAT_MLP_MAX_LAYERS + 1]; /* dims[0] input width ... dims[n] output width               */
+  const float* W[B200GAT_MLP_MAX_LAYERS];   /* [dims[i+1], dims[i]] row-major                             */
+  const float* b[B200GAT_MLP_MAX_LAYERS];   /* [dims[i+1]] or NULL                                        */
+  const float* x;                           /* [M, dims[0]]                                               */
+  const float* residual;                    /* [M, dims[n]] or NULL                                       */
+  float* z[B200GAT_MLP_MAX_LAYERS];         /* i < n-1: pre-activations [M, dims[i+1]], NULL = not kept   */
+  float* h[B200GAT_MLP_MAX_LAYERS];         /* i < n-1: gelu(z_i)       [M, dims[i+1]]                    */
+  float* y;                                 /* [M, dims[n]]                                               */
+} b200gat_mlp;
+typedef struct b200gat_mlp_grads {
+  const float* gy;                          /* [M, dims[n]]                                               */
+  float* dx;                                /* [M, dims[0]] or NULL                                       */
+  float* dW[B200GAT_MLP_MAX_LAYERS];        /* [dims[i+1], dims[i]] or NULL                               */
+  float* db[B200GAT_MLP_MAX_LAYERS];        /* [dims[i+1]] or NULL (needs dW[i])                          */
+  float* dz[B200GAT_MLP_MAX_LAYERS];        /* i < n-1: scratch [M, dims[i+1]]                            */
+  float* workspace;                         /* b200gat_mlp_bwd_workspace_elems floats                     */
+  int64_t workspace_elems;
+} b200gat_mlp_grads;
+int b200gat_mlp_fwd(const b200gat_mlp* m, void* stream);
+int64_t b200gat_mlp_bwd_workspace_elems(const b200gat_mlp* m, const b200gat_mlp_grads* g);
+int b200gat_mlp_bwd(const b200gat_mlp* m, const b200gat_mlp_grads* g, void* stream);
 
 #ifdef __cplusplus
 }

@@ -85,7 +85,7 @@ def test_linear_backward_variants(wb, tf32, M, N, K):
     dW, db = dense.linear_dw(dy, x, want_bias=True)
     ref_dw = dy.double().t() @ x.double()
     assert rel(dW, ref_dw) < TOL_GEMM
-    assert rel(db, dy.double().sum(0)) < TOL_GEMM          # row sums ride on the tensor core (TF32 operands)
+    assert rel(db, dy.double().sum(0)) < 1e-5              # exact fp32 row sums of the staged dy tiles
     dW2, db2 = dense.linear_dw(dy, x, want_bias=True)
     assert torch.equal(dW, dW2) and torch.equal(db, db2), "split-K must be deterministic"
     assert torch.equal(dense.linear_dw(dy, x)[0], dW)

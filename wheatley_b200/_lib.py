@@ -26,7 +26,9 @@ SYMBOLS = (
     "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
     "b200gat_gemm_supported", "b200gat_gemm_workspace_elems", "b200gat_gemm_tf32",
     "b200gat_colsum_scratch_elems", "b200gat_colsum",
+    "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
 )
+MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
 MAX_CLIQUE = 128
 MIN_CLIQUE = 8        # smaller cliques stay on the sparse kernels
@@ -76,6 +78,19 @@ class Gemm(C.Structure):
                 ("bias", C.c_void_p), ("residual", C.c_void_p), ("ldr", C.c_int64),
                 ("epilogue", C.c_int32), ("D2", C.c_void_p), ("Zin", C.c_void_p), ("ld2", C.c_int64),
                 ("workspace", C.c_void_p), ("workspace_elems", C.c_int64), ("a_rowsum", C.c_void_p)]
+
+
+class Mlp(C.Structure):
+    """``b200gat_mlp`` (include/b200gat.h)."""
+    _fields_ = [("n_layers", C.c_int32), ("M", C.c_int64), ("dims", C.c_int32 * 9),
+                ("W", C.c_void_p * 8), ("b", C.c_void_p * 8), ("x", C.c_void_p), ("residual", C.c_void_p),
+                ("z", C.c_void_p * 8), ("h", C.c_void_p * 8), ("y", C.c_void_p)]
+
+
+class MlpGrads(C.Structure):
+    """``b200gat_mlp_grads`` (include/b200gat.h)."""
+    _fields_ = [("gy", C.c_void_p), ("dx", C.c_void_p), ("dW", C.c_void_p * 8), ("db", C.c_void_p * 8),
+                ("dz", C.c_void_p * 8), ("workspace", C.c_void_p), ("workspace_elems", C.c_int64)]
 
 
 class B200GatError(RuntimeError):
@@ -129,12 +144,18 @@ def _load():
     lib.b200gat_colsum_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_colsum_scratch_elems.restype = i64
     lib.b200gat_colsum.argtypes = [vp, i64, i64, i64, vp, vp, vp]
+    lp, lg = C.POINTER(Mlp), C.POINTER(MlpGrads)
+    lib.b200gat_mlp_fwd.argtypes = [lp, vp]
+    lib.b200gat_mlp_bwd_workspace_elems.argtypes = [lp, lg]
+    lib.b200gat_mlp_bwd_workspace_elems.restype = i64
+    lib.b200gat_mlp_bwd.argtypes = [lp, lg, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
                         "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
-                        "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems"):
+                        "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
+                        "b200gat_mlp_bwd_workspace_elems"):
             fn.restype = C.c_int
     return lib
 

@@ -159,25 +159,21 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int nkb = min(p.kb_per_split, p.kb_total - kb0);
 
+  // Row sums of A (the bias gradient inside the weight-gradient GEMM, A = dy stored MN-major): epilogue warps
+  // 0-3 are idle during the main loop, so they add up the staged A tiles in exact fp32 (thread = one of the 128
+  // mn columns, k ascending: deterministic) before the stage is released - the stage's "empty" barrier then counts
+  // the MMA commit plus these 128 readers.
+  const bool rowsum = A_MN && p.a_rowsum != nullptr && nt == 0;
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, rowsum ? 129 : 1);
     }
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  // Row sums of A (bias gradients in the weight-gradient GEMM) ride on the tensor core too: one extra
-  // N = 16 MMA per k-step against an all-ones B tile (2 KB behind the ring) into 16 more TMEM columns.
-  const bool rowsum = p.a_rowsum != nullptr && nt == 0;
-  const uint32_t ones_addr = base + STAGES * STAGE_BYTES;
-  if (rowsum) {
-    float* ones = reinterpret_cast<float*>(smem_raw + (ones_addr - smem_u32(smem_raw)));
-    for (int i = threadIdx.x; i < 512; i += blockDim.x) ones[i] = 1.f;
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  }
-  const uint32_t tmem_cols = p.a_rowsum ? 2u * BN : (uint32_t)BN;      // power of two >= 32
-  if (warp == 0) {      // TMEM: BN fp32 accumulator columns (+ the row-sum columns)
+  const uint32_t tmem_cols = (uint32_t)BN;          // power of two >= 32
+  if (warp == 0) {      // TMEM: BN fp32 accumulator columns
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
                  "r"(tmem_cols)
                  : "memory");
@@ -221,8 +217,6 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
     // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = TF32, majors, N >> 3, M >> 4
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    const uint32_t idesc_ones = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | (2u << 17) |
-                                ((uint32_t)(BM >> 4) << 24);             // N = 16, B (ones) K-major
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
       const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
@@ -237,8 +231,6 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
           const uint64_t bd = B_MN ? smem_desc(sb + k * p.mn_kadv, p.mn_lbo, p.mn_sbo, p.mn_layout)
                                    : smem_desc(sb + k * 32, 16, 1024, 2);
           umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          if (rowsum)
-            umma_tf32(tmem_base + BN, ad, smem_desc(ones_addr, 16, 1024, 2), idesc_ones, (i > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(empty0 + 8 * s);                 // frees the stage when these MMAs have read it
         if (i == nkb - 1) umma_commit(accum_bar);    // accumulator complete
@@ -261,6 +253,23 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
                        : nullptr;
     const bool dgelu = p.epi == B200GAT_EPI_DGELU, gelu = p.epi == B200GAT_EPI_GELU;
     bool waited = false;
+    if (rowsum && warp < 4) {
+      // MN-major A stage: 4 boxes of 32 mn columns x 32 k rows (128 B per row, 32-byte chunks xor-ed with row & 3)
+      const int t = threadIdx.x, c = t & 31;
+      const uint8_t* a_tile = smem_raw + (base - smem_u32(smem_raw)) + (t >> 5) * 4096 + (c & 7) * 4;
+      float sum = 0.f;
+      for (int i = 0; i < nkb; ++i) {
+        const int s2 = i % STAGES;
+        mbar_wait(full0 + 8 * s2, (uint32_t)(i / STAGES) & 1u);
+        const uint8_t* st_base = a_tile + s2 * STAGE_BYTES;
+#pragma unroll 8
+        for (int row = 0; row < BK; ++row)
+          sum += *reinterpret_cast<const float*>(st_base + row * 128 + (((c >> 3) ^ (row & 3)) << 5));
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s2) : "memory");
+      }
+      const int row = mt * BM + t;
+      if (row < p.M) p.a_rowsum[(long long)blockIdx.z * p.rowsum_split_stride + row] = sum;
+    }
 #pragma unroll 1
     for (int c = hf * (BN / 2); c < (hf + 1) * (BN / 2); c += 32) {
       if (ncol0 + c >= p.N) break;                   // ragged last column tile (N % 4 == 0): warp-uniform
@@ -309,19 +318,6 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
         }
       }
       __syncwarp();
-    }
-    if (rowsum && hf == 0) {
-      if (!waited) {
-        mbar_wait(accum_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      }
-      uint32_t rs;
-      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];"
-                   : "=r"(rs)
-                   : "r"(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)BN));
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      const int row = row_base + lane;
-      if (row < p.M) p.a_rowsum[(long long)blockIdx.z * p.rowsum_split_stride + row] = __uint_as_float(rs);
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -489,7 +485,9 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
   GEMM_REQ(s->bn != 0, "N must be a multiple of 4");
   GEMM_REQ(dp == 1 || (g->N / dp) % 64 == 0, "N per part must be a multiple of 64");
   GEMM_REQ(g->lda % 4 == 0 && g->ldb % 4 == 0 && g->ldd % 4 == 0, "leading dimensions must be multiples of 4 floats");
-  if (g->a_rowsum) GEMM_REQ(g->d_parts <= 1, "row sums are not combined with parted outputs");
+  if (g->a_rowsum)
+    GEMM_REQ(g->d_parts <= 1 && g->a_major == 1 && g->a_parts <= 1,
+             "row sums need an MN-major, un-parted A (A = dy of a weight-gradient GEMM) and an un-parted output");
   GEMM_REQ(aligned16(g->A) && aligned16(g->B) && aligned16(g->D) && aligned16(g->bias) && aligned16(g->residual) &&
                aligned16(g->D2) && aligned16(g->Zin),
            "pointers must be 16-byte aligned");

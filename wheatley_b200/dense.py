@@ -169,23 +169,114 @@ class _GeluMLP(torch.autograd.Function):
         return (dz, gy if ctx.has_res and ctx.needs_input_grad[1] else None, *grads)
 
 
+def _mlp_desc(x, Ws, bs, residual, zs, hs, y):
+    m = _lib.Mlp()
+    n = len(Ws)
+    m.n_layers, m.M = n, x.shape[0]
+    m.dims[0] = x.shape[1]
+    for i in range(n):
+        m.dims[i + 1] = Ws[i].shape[0]
+        m.W[i] = Ws[i].data_ptr()
+        m.b[i] = None if bs[i] is None else bs[i].data_ptr()
+    for i in range(n - 1):
+        m.z[i] = None if zs is None else zs[i].data_ptr()
+        m.h[i] = hs[i].data_ptr()
+    m.x, m.residual, m.y = x.data_ptr(), _lib.ptr(residual), y.data_ptr()
+    return m
+
+
+class _GeluMLPFused(torch.autograd.Function):
+    """The whole ``Linear -> GELU -> ... -> Linear (+ residual)`` stack with ONE binding call per pass
+    (``b200gat_mlp_fwd`` / ``b200gat_mlp_bwd``, which issue the tcgen05 GEMMs of ``_GeluMLP`` from C): the eager
+    PPO step is host-bound and an MLP's forward + backward cost ~400 us of host time call by call."""
+
+    @staticmethod
+    def forward(ctx, x, residual, *params):
+        n = len(params) // 2
+        Ws = [w.contiguous() for w in params[0::2]]
+        bs = list(params[1::2])
+        need = any(ctx.needs_input_grad)
+        M, dev = x.shape[0], x.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        hs = [torch.empty((M, Ws[i].shape[0]), **f32) for i in range(n - 1)]
+        zs = [torch.empty((M, Ws[i].shape[0]), **f32) for i in range(n - 1)] if need else None
+        y = torch.empty((M, Ws[-1].shape[0]), **f32)
+        m = _mlp_desc(x, Ws, bs, residual, zs, hs, y)
+        with _lib.device_guard(dev):
+            _lib.check(_lib.lib.b200gat_mlp_fwd(m, _lib.stream_ptr()), "b200gat_mlp_fwd")
+        ctx.n, ctx.has_res = n, residual is not None
+        ctx.has_bias = [b is not None for b in bs]
+        if need:
+            ctx.save_for_backward(x, *Ws, *zs, *hs)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        n = ctx.n
+        saved = ctx.saved_tensors
+        x, Ws = saved[0], list(saved[1: 1 + n])
+        rest = saved[1 + n:]
+        zs, hs = list(rest[: n - 1]), list(rest[n - 1:])
+        gy = gy.contiguous()
+        M, dev = x.shape[0], x.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        need = ctx.needs_input_grad
+        g = _lib.MlpGrads()
+        g.gy = gy.data_ptr()
+        dWs, dbs = [None] * n, [None] * n
+        for i in range(n):
+            if need[2 + 2 * i] or need[3 + 2 * i]:           # a bias gradient rides on its weight-gradient GEMM
+                dWs[i] = torch.empty_like(Ws[i])
+                g.dW[i] = dWs[i].data_ptr()
+                if need[3 + 2 * i] and ctx.has_bias[i]:
+                    dbs[i] = torch.empty(Ws[i].shape[0], **f32)
+                    g.db[i] = dbs[i].data_ptr()
+        dzs = [torch.empty_like(z) for z in zs]
+        for i in range(n - 1):
+            g.dz[i] = dzs[i].data_ptr()
+        dx = torch.empty_like(x) if need[0] else None
+        g.dx = _lib.ptr(dx)
+        m = _mlp_desc(x, Ws, [None] * n, None, zs, hs, gy)       # biases / residual / y are not read backward
+        ws_elems = int(_lib.lib.b200gat_mlp_bwd_workspace_elems(m, g))
+        ws = torch.empty(max(ws_elems, 4), **f32)
+        g.workspace, g.workspace_elems = ws.data_ptr(), ws_elems
+        with _lib.device_guard(dev):
+            _lib.check(_lib.lib.b200gat_mlp_bwd(m, g, _lib.stream_ptr()), "b200gat_mlp_bwd")
+        grads = []
+        for i in range(n):
+            grads += [dWs[i] if need[2 + 2 * i] else None, dbs[i] if need[3 + 2 * i] else None]
+        return (dx, gy if ctx.has_res and need[1] else None, *grads)
+
+
 def gelu_mlp(x, layers, residual=None):
-    """``layers``: the ``nn.Linear`` modules of a GELU MLP (bias required).  An input width that is not a
-    multiple of 4 floats (the 30-wide JSSP node features) is zero-padded, with the first weight, to the next
-    multiple: TMA rows must be 16-byte aligned, and the zero columns change nothing."""
+    """``layers``: the ``nn.Linear`` modules of a GELU MLP.  Widths that are not multiples of 4 floats are
+    zero-padded around the fused call (TMA rows must be 16-byte aligned): the 30-wide JSSP node features with
+    the first weight's columns, the width-1 head outputs with the last weight's rows; the padding changes
+    nothing and autograd slices the gradients back."""
     params = []
     for lin in layers:
         params += [lin.weight, lin.bias]
-    pad = (-x.shape[1]) % 4
-    if pad:
-        x = torch.nn.functional.pad(x, (0, pad))
-        params[0] = torch.nn.functional.pad(params[0], (0, pad))
-    return _GeluMLP.apply(x.contiguous(), None if residual is None else residual.contiguous(), *params)
+    pad_in = (-x.shape[1]) % 4
+    if pad_in:
+        x = torch.nn.functional.pad(x, (0, pad_in))
+        params[0] = torch.nn.functional.pad(params[0], (0, pad_in))
+    n_out = params[-2].shape[0]
+    pad_out = (-n_out) % 4
+    if pad_out:
+        params[-2] = torch.nn.functional.pad(params[-2], (0, 0, 0, pad_out))
+        if params[-1] is not None:
+            params[-1] = torch.nn.functional.pad(params[-1], (0, pad_out))
+        if residual is not None:
+            residual = torch.nn.functional.pad(residual, (0, pad_out))
+    hidden_ok = all(p.shape[0] % 4 == 0 for p in params[0:-2:2])
+    fn = _GeluMLPFused if (hidden_ok and len(layers) <= _lib.MLP_MAX_LAYERS
+                           and os.environ.get("WHEATLEY_B200_MLP_CALLS", "fused") == "fused") else _GeluMLP
+    y = fn.apply(x.contiguous(), None if residual is None else residual.contiguous(), *params)
+    return y[:, :n_out] if pad_out else y
 
 
 def gelu_mlp_applicable(x, layers) -> bool:
-    return (tf32_path_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
-            and all(lin.bias is not None for lin in layers))
+    return (tf32_path_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.shape[0] > 0)
 
 
 class _Proj3(torch.autograd.Function):
