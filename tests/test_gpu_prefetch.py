@@ -1,0 +1,100 @@
+"""BatchPrefetcher / deferred plan build: the pipelined batches must be the same plans, and give the same losses
+(to the bit) and gradients, as batches built directly on the current stream."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def wb():
+    import wheatley_b200
+    return wheatley_b200
+
+
+def _host_batch(n_j, n_m, B, seed):
+    from wheatley_b200.workload import jssp_batch
+    hb = jssp_batch(n_j, n_m, B, seed0=seed, progress=0.25)
+    g = torch.Generator().manual_seed(seed)
+    masks = torch.rand(B, n_j * n_m, generator=g) < 0.4
+    masks[:, 0] = True
+    action = torch.multinomial(masks.float(), 1, generator=g).squeeze(1)
+    host = dict(src=hb["src"], dst=hb["dst"], etype=hb["etype"], feat=hb["feat"], masks=masks, action=action,
+                adv=torch.randn(B, generator=g), ret=torch.randn(B, generator=g))
+    return {k: v.contiguous().pin_memory() for k, v in host.items()}, hb["n_nodes"], hb["n_task_nodes"]
+
+
+def _step(agent, plan, d, B, n, NT):
+    from wheatley_b200.gnn_dgl import JsspBatch
+    from wheatley_b200.ppo import ppo_like_loss
+    jb = JsspBatch(plan, d["etype"], d["feat"], B, n, NT, poolnodes=torch.arange(NT, NT + B, device="cuda"))
+    for p in agent.parameters():
+        p.grad = None
+    _, lp, ent, val, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
+    loss = ppo_like_loss(lp, ent, val, d["adv"], d["ret"])
+    loss.backward()
+    return loss.detach().clone(), [p.grad.detach().clone() for p in agent.parameters() if p.grad is not None]
+
+
+def test_deferred_prepare_builds_the_same_view(wb):
+    host, N, _ = _host_batch(10, 5, 3, seed=2)
+    d = {k: v.cuda() for k, v in host.items()}
+    a = wb.GraphPlan(d["src"], d["dst"], N).prepare(d["etype"])
+    b = wb.GraphPlan(d["src"], d["dst"], N)
+    b.prepare(d["etype"], defer=True)
+    vb = next(iter(b._clique_views.values()))
+    assert vb._pending is not None and vb.n_blocks == 0          # queued, counts not read yet
+    b.finish()
+    va = next(iter(a._clique_views.values()))
+    assert vb._pending is None and va.n_blocks == vb.n_blocks > 0
+    assert (va.max_block, va.n_res_edges, va.n_members, va.s_elems) == \
+           (vb.max_block, vb.n_res_edges, vb.n_members, vb.s_elems)
+    assert a.stats_host() == b.stats_host()
+    for name in ("node_blk", "node_run", "node_rank", "blk_type"):
+        assert torch.equal(getattr(va, name), getattr(vb, name)), name
+    for x, y in zip(va.r, vb.r):
+        assert torch.equal(x, y)
+    assert len(b.tensors()) >= 20
+
+
+def test_prefetched_batches_train_identically(wb):
+    """Four different minibatches through the pipeline (next batch queued while the current one trains) against
+    the same four built directly, on the bench's dense path (tcgen05 TF32): the forward is deterministic, so the
+    losses must agree to the bit; the backward accumulates a few small gradients with atomics (order-dependent
+    rounding), so gradients are compared to 1e-5 of their scale."""
+    from wheatley_b200.agent import JsspAgent
+    from wheatley_b200.prefetch import BatchPrefetcher
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n_j, n_m, B = 15, 8, 4
+        batches = [_host_batch(n_j, n_m, B, seed=s) for s in range(4)]
+        torch.manual_seed(0)
+        agent = JsspAgent(batches[0][0]["feat"].shape[1], n_j * n_m, n_m, 64, 3, 4).cuda()
+        direct = []
+        for host, N, NT in batches:
+            d = {k: v.cuda() for k, v in host.items()}
+            direct.append(_step(agent, wb.GraphPlan(d["src"], d["dst"], N), d, B, n_j * n_m, NT))
+        torch.cuda.synchronize()
+        pf = BatchPrefetcher("cuda:0")
+        pf.submit(batches[0][0], batches[0][1])
+        piped = []
+        for i, (host, N, NT) in enumerate(batches):
+            d, plan = pf.get()
+            if i + 1 < len(batches):
+                pf.submit(batches[i + 1][0], batches[i + 1][1])
+            piped.append(_step(agent, plan, d, B, n_j * n_m, NT))    # no sync: the next get() overlaps with this
+        torch.cuda.synchronize()
+        for (l0, g0), (l1, g1) in zip(direct, piped):
+            assert torch.equal(l0, l1)
+            assert len(g0) == len(g1)
+            for a, b in zip(g0, g1):
+                assert float((a - b).abs().max()) <= 1e-5 * max(float(a.abs().max()), 1e-6)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def test_prefetcher_get_without_submit_raises(wb):
+    from wheatley_b200.prefetch import BatchPrefetcher
+    with pytest.raises(wb.B200GatError):
+        BatchPrefetcher("cuda:0").get()

@@ -18,6 +18,7 @@
 //   P.V     : numerators stay in registers as A fragments; out[v] += P[v,u] V[u] on the tensor cores,
 //             3xTF32 split operands (a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) for fp32-level accuracy
 //   final   : normalise, write out / agg_save / m_save / l_save; raw logits go to s_dense[h][v][u]
+#include <atomic>
 #include <math.h>
 #include "common.cuh"
 #include "gat_kernels.cuh"
@@ -745,16 +746,21 @@ static int fill_clique(CliqueArgs& A, const b200gat_cliques* c, const b200gat_at
   return B200GAT_OK;
 }
 
-template <typename K>
-static int set_smem(K kernel, size_t bytes, const char* name) {
+template <auto Kernel>
+static int set_smem(size_t bytes, const char* name) {
   if (bytes > 227 * 1024) {
     set_error("%s: %zu bytes of shared memory needed", name, bytes);
     return B200GAT_ERR_UNSUPPORTED;
   }
-  if (bytes > 48 * 1024 &&
-      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) {
-    set_error("%s: cudaFuncSetAttribute(%zu) failed", name, bytes);
-    return B200GAT_ERR_CUDA;
+  // one instantiation of this function (and of `granted`) per kernel: the attribute is raised only when a
+  // launch needs more than any before it (the call costs a few microseconds on a host-bound step)
+  static std::atomic<size_t> granted{48 * 1024};
+  if (bytes > granted.load(std::memory_order_relaxed)) {
+    if (cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) {
+      set_error("%s: cudaFuncSetAttribute(%zu) failed", name, bytes);
+      return B200GAT_ERR_CUDA;
+    }
+    granted.store(bytes, std::memory_order_relaxed);
   }
   return B200GAT_OK;
 }
@@ -775,10 +781,10 @@ int clique_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
   const unsigned grid = (unsigned)ceil_div(A.n_items, A.ipc), block = 32u * A.ipc * A.tiles;
   ScopedTimer tm(B200GAT_TIMING_CLQ_FWD, st);
   if (alias) {
-    if ((rc = set_smem(k_clq_fwd<true>, smem, "k_clq_fwd"))) return rc;
+    if ((rc = set_smem<k_clq_fwd<true>>(smem, "k_clq_fwd"))) return rc;
     k_clq_fwd<true><<<grid, block, smem, st>>>(A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
   } else {
-    if ((rc = set_smem(k_clq_fwd<false>, smem, "k_clq_fwd"))) return rc;
+    if ((rc = set_smem<k_clq_fwd<false>>(smem, "k_clq_fwd"))) return rc;
     k_clq_fwd<false><<<grid, block, smem, st>>>(A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
   }
   B200_CHECK_LAUNCH("k_clq_fwd");
@@ -806,7 +812,7 @@ int clique_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
     ScopedTimer tm(B200GAT_TIMING_CLQ_BWD_MMA, st);
     A.item_floats = clique_bwd1_floats(A.rv);
     const size_t smem = (size_t)A.ipc * A.item_floats * sizeof(float);
-    if ((rc = set_smem(k_clq_bwd_mma, smem, "k_clq_bwd_mma"))) return rc;
+    if ((rc = set_smem<k_clq_bwd_mma>(smem, "k_clq_bwd_mma"))) return rc;
     k_clq_bwd_mma<<<grid, block, smem, st>>>(A, V, g_out, agg_save, s_dense, m_save, l_save, gs_dense, gsum_u,
                                             gsum_v, gV);
     B200_CHECK_LAUNCH("k_clq_bwd_mma");
@@ -818,7 +824,7 @@ int clique_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
     float* gt = A.table ? g_table : nullptr;
 #define CLQ_BWD2(GU_)                                                                                         \
   case GU_:                                                                                                   \
-    if ((rc = set_smem(k_clq_bwd_elem<GU_>, smem, "k_clq_bwd_elem"))) return rc;                              \
+    if ((rc = set_smem<k_clq_bwd_elem<GU_>>(smem, "k_clq_bwd_elem"))) return rc;                              \
     k_clq_bwd_elem<GU_><<<A.n_items, 256, smem, st>>>(A, Pi, Pj, gs_dense, gsum_u, gsum_v, gPi, gPj, g_attn, gt); \
     break;
     switch (gu) {

@@ -29,6 +29,8 @@ class JsspBatch:
         self.plan, self.etype, self.feat = plan, etype, feat
         self.batch_size, self.n_nodes, self.num_task_nodes = batch_size, n_nodes, num_task_nodes
         self.poolnodes, self.machinenodes = poolnodes, machinenodes
+        if hasattr(plan, "prepare"):
+            plan.prepare(etype)         # clique view + host counts with one device->host copy, before the trunk
 
 
 class GnnDGL(nn.Module):

@@ -59,12 +59,13 @@ class CliqueView:
     (``b200gat_clique_build``): block tables + the residual CSR of the edges outside the blocks.
     ``c`` is what ``b200gat_conv_fwd/bwd`` take; it equals the plain plan when no block was found."""
 
-    def __init__(self, plan, etype_sorted):
+    def __init__(self, plan, etype_sorted, defer=False):
         N, E, dev = plan.n_nodes, plan.n_edges, plan.device
         i32 = dict(dtype=torch.int32, device=dev)
         self.plan, self.etype_sorted = plan, etype_sorted
         self.n_blocks = self.max_block = self.n_members = self.s_elems = self.n_res_edges = 0
-        self.c = plan.c
+        self.c = plan._c                     # same struct as plan.c; the host counts are attached below
+        self._pending = None
         if N == 0 or E == 0:
             return
         with _lib.device_guard(dev):
@@ -73,27 +74,56 @@ class CliqueView:
             self.blk_nodes, self.blk_type = torch.empty(N, **i32), torch.empty(N, **i32)
             r_in_ptr, r_out_ptr = torch.empty(N + 1, **i32), torch.empty(N + 1, **i32)
             r_in_src, r_in_pos, r_out_dst, r_out_pos = (torch.empty(E, **i32) for _ in range(4))
+            self._r_full = (r_in_ptr, r_in_src, r_in_pos, r_out_ptr, r_out_dst, r_out_pos)
             counts = torch.empty(8, **i32)
             scratch = torch.empty(_lib.lib.b200gat_clique_scratch_elems(N, E) + 2, **i32)
             off = (-scratch.data_ptr() // 4) % 2          # 8-byte alignment
+            # plan._c: the build reads the CSR only, so it need not wait for the plan's own host counts
             _lib.check(_lib.lib.b200gat_clique_build(
-                plan.c, _lib.ptr(etype_sorted), _lib.MIN_CLIQUE, _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
+                plan._c, _lib.ptr(etype_sorted), _lib.MIN_CLIQUE, _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
                 _lib.ptr(self.node_rank), _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes),
                 _lib.ptr(self.blk_type), _lib.ptr(self.blk_soff), _lib.ptr(r_in_ptr), _lib.ptr(r_in_src),
                 _lib.ptr(r_in_pos), _lib.ptr(r_out_ptr), _lib.ptr(r_out_dst), _lib.ptr(r_out_pos),
                 _lib.ptr(counts), scratch.data_ptr() + 4 * off, _lib.stream_ptr()), "b200gat_clique_build")
             self.r_aux = _orders_and_hubs(r_in_ptr, r_in_src, r_out_ptr, r_out_dst, N, dev)
-            host = torch.cat([counts, self.r_aux[4]]).tolist()          # the one device->host copy
-            self.n_blocks, self.max_block, self.n_res_edges, self.n_members, self.s_elems = host[:5]
-            n_hub_dst = host[8]
-            if self.n_blocks == 0:
+            # the one device->host copy (it also carries the plan's own counts if they were not read yet)
+            first = plan._stats_host is None
+            dev_counts = torch.cat([counts, self.r_aux[4]] + ([plan.stats, plan.n_hub] if first else []))
+            if defer:       # asynchronous copy into pinned memory; finish() waits for the event, not the stream
+                host_counts = torch.empty(dev_counts.numel(), dtype=torch.int32, pin_memory=True)
+                host_counts.copy_(dev_counts, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                self._pending = (host_counts, ev, first)
                 return
-            Er = self.n_res_edges
-            self.r = (r_in_ptr, r_in_src[:Er], r_in_pos[:Er], r_out_ptr, r_out_dst[:Er], r_out_pos[:Er])
+            self._finish(dev_counts.tolist(), first)
+
+    def finish(self):
+        """Second half of a deferred build: wait for the counts, then the host-side structures."""
+        if self._pending is not None:
+            host_counts, ev, first = self._pending
+            self._pending = None
+            ev.synchronize()
+            self._finish(host_counts.tolist(), first)
+        return self
+
+    def _finish(self, host, first):
+        plan = self.plan
+        N, dev = plan.n_nodes, plan.device
+        if first and plan._stats_host is None:
+            plan._set_stats_host(host[10:16])
+        self.n_blocks, self.max_block, self.n_res_edges, self.n_members, self.s_elems = host[:5]
+        n_hub_dst = host[8]
+        if self.n_blocks == 0:
+            return
+        Er = self.n_res_edges
+        r_in_ptr, r_in_src, r_in_pos, r_out_ptr, r_out_dst, r_out_pos = self._r_full
+        self.r = (r_in_ptr, r_in_src[:Er], r_in_pos[:Er], r_out_ptr, r_out_dst[:Er], r_out_pos[:Er])
         dst_order, src_order, hub_dst, hub_src, n_hub = self.r_aux
         self._res_c = _graph_struct(N, Er, r_in_ptr, r_in_src, None, r_out_ptr, r_out_dst, r_out_pos, dst_order,
                                     src_order, hub_dst, hub_src, n_hub, in_pos=r_in_pos)
-        self._hub_scratch = _attach_hub_scratch(self._res_c, n_hub_dst, dev)
+        with _lib.device_guard(dev):
+            self._hub_scratch = _attach_hub_scratch(self._res_c, n_hub_dst, dev)
         self._cl = _lib.Cliques(self.n_blocks, self.max_block, self.n_members, self.s_elems,
                                 _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes), _lib.ptr(self.blk_type),
                                 _lib.ptr(self.blk_soff), _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
@@ -155,28 +185,71 @@ class GraphPlan:
         self.stats_host()                  # first use: one device->host copy, sizes the hub scratch
         return self._c
 
-    def clique_view(self, etype_sorted=None) -> CliqueView:
+    def clique_view(self, etype_sorted=None, defer=False) -> CliqueView:
         """Dense clique blocks for one edge typing (``None`` = untyped), built once and cached.
-        One small device->host copy (block counts) per (plan, typing)."""
+        One small device->host copy (block counts) per (plan, typing); ``defer=True`` only queues the build and
+        the copy (``CliqueView.finish`` / ``GraphPlan.finish`` complete it)."""
         key = None if etype_sorted is None else (etype_sorted.data_ptr(), etype_sorted._version)
         view = self._clique_views.get(key)
         if view is None:
             if os.environ.get("WHEATLEY_B200_CLIQUES", "1") == "0":
                 view = CliqueView.__new__(CliqueView)
-                view.plan, view.c, view.n_blocks, view.s_elems = self, self.c, 0, 0
+                view.plan, view.c, view.n_blocks, view.s_elems, view._pending = self, self.c, 0, 0, None
             else:
-                view = CliqueView(self, etype_sorted)
+                view = CliqueView(self, etype_sorted, defer=defer)
             self._clique_views[key] = view
+        elif not defer:
+            view.finish()
         return view
 
     def stats_host(self):
         """(n_zero_in_degree, max_in_degree, n_bad_edges, max_out_degree); one device sync,
         cached."""
         if self._stats_host is None:
-            host = torch.cat([self.stats, self.n_hub]).tolist()
-            self._stats_host = tuple(int(x) for x in host[:4])
-            self._hub_scratch = _attach_hub_scratch(self._c, int(host[4]), self.device)
+            self._set_stats_host(torch.cat([self.stats, self.n_hub]).tolist())
         return self._stats_host
+
+    def _set_stats_host(self, host):
+        self._stats_host = tuple(int(x) for x in host[:4])
+        self._hub_scratch = _attach_hub_scratch(self._c, int(host[4]), self.device)
+
+    def prepare(self, etype=None, defer=False):
+        """Build everything the layers will ask for (host counts, the clique view of this edge typing) now, with
+        ONE device->host copy, instead of lazily inside the first layer (two copies, each waiting on whatever
+        was queued before it).  ``defer=True`` queues the device work and an asynchronous copy of the counts and
+        returns without waiting; ``finish()`` completes it (``wheatley_b200.prefetch`` overlaps the two with the
+        previous training step).  Returns ``self``."""
+        if self.n_nodes and self.n_edges:
+            self.clique_view(None if etype is None else self.sort_edge_ints(etype), defer=defer)
+        if not defer:
+            self.stats_host()
+        return self
+
+    def finish(self):
+        for view in self._clique_views.values():
+            view.finish()
+        self.stats_host()
+        return self
+
+    def tensors(self):
+        """Every device tensor the plan and its views hold (for ``Tensor.record_stream`` when the plan was
+        built on another stream than the one that uses it)."""
+        seen, out, stack = set(), [], [self]
+        while stack:
+            o = stack.pop()
+            if id(o) in seen:
+                continue
+            seen.add(id(o))
+            if isinstance(o, torch.Tensor):
+                if o.is_cuda:
+                    out.append(o)
+            elif isinstance(o, (list, tuple)):
+                stack.extend(o)
+            elif isinstance(o, dict):
+                stack.extend(o.values())
+            elif isinstance(o, (GraphPlan, CliqueView)):
+                stack.extend(vars(o).values())
+        return out
 
     def validate(self):
         bad = self.stats_host()[2]
