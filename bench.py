@@ -240,7 +240,16 @@ def run_b200(args):
     host = dict(src=hb["src"], dst=hb["dst"], etype=hb["etype"], feat=hb["feat"], masks=masks,
                 action=action, adv=adv, ret=ret)
     host = {k: v.contiguous().pin_memory() for k, v in host.items()}
-    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+    # the e2e / rollout legs start from the padded gym observation (what the reference's batching receives,
+    # jssp/models/agent_observation.py:127-131): the batched graph is built on the device (wheatley_b200.batch)
+    from wheatley_b200.workload import jssp_observation_batch
+    from wheatley_b200.batch import jssp_batch_from_observation
+    obs = {k: v.contiguous().pin_memory() for k, v in
+           jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress).items()}
+    extras = {k: host[k] for k in ("masks", "action", "adv", "ret")}
+    builder_kw = dict(conflicts="clique", graph_pooling="learn")
+    h2d_bytes = (sum(v.numel() * v.element_size() for v in obs.values())
+                 + sum(v.numel() * v.element_size() for v in extras.values()) + 4 * (B + 1) * 8)
     N, E, NT = hb["n_nodes"], hb["n_edges"], hb["n_task_nodes"]
 
     def to_dev():
@@ -352,8 +361,8 @@ def run_b200(args):
 
     # ---- e2e: host buffers in, loss out, through the public module API, every step
     def e2e_step_serial():
-        d = to_dev()
-        jb = make_batch(d)
+        d = {k: v.to(dev, non_blocking=True) for k, v in extras.items()}
+        jb, _ = jssp_batch_from_observation(obs, dev, cfg["max_n_nodes"], **builder_kw)
         return train_step(jb, d).item()                    # .item(): device->host read of the loss
     timed(e2e_step_serial, max(3, args.steps), 5)
     ms_e2e_serial = timed.last_spread["median"]
@@ -364,14 +373,12 @@ def run_b200(args):
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
     from wheatley_b200.prefetch import BatchPrefetcher
     pf = BatchPrefetcher(dev)
-    pf.submit(host, N)
+    pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)
 
     def e2e_step():
-        d, plan = pf.get()
-        pf.submit(host, N)                                 # next step's inputs
-        pool = torch.arange(NT, NT + B, device=dev)
-        jb = JsspBatch(plan, d["etype"], d["feat"], B, cfg["max_n_nodes"], NT, poolnodes=pool)
-        return train_step(jb, d).item()
+        d, _ = pf.get()
+        pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)     # next step's inputs
+        return train_step(d["batch"], d).item()
     ms_e2e_mean, _, _ = timed(e2e_step, max(3, args.steps), 5)
     e2e_spread = dict(timed.last_spread)
     pf.get()                                               # drain the last (unused) prefetch
@@ -392,10 +399,10 @@ def run_b200(args):
     # env-steps/s = num_envs / (t_rollout + n_epochs * (num_envs / batch) * t_update); the CPU simulators
     # (jssp/env, psp/env) are out of scope and not in the figure.
     def rollout_step():
-        d = to_dev()
-        jb = make_batch(d)
+        masks_d = extras["masks"].to(dev, non_blocking=True)
+        jb, _ = jssp_batch_from_observation(obs, dev, cfg["max_n_nodes"], **builder_kw)
         with torch.no_grad():
-            action, _, _, _, _ = agent.get_action_and_value(jb, None, d["masks"])
+            action, _, _, _, _ = agent.get_action_and_value(jb, None, masks_d)
         return action.cpu()
     timed(rollout_step, max(3, args.steps), 5)
     ms_roll = timed.last_spread["median"]
@@ -471,9 +478,12 @@ def run_b200(args):
                     "ms_per_step_mean": ms_e2e_mean, "ms_per_step_spread": e2e_spread,
                     "statistic": "median of the per-step CUDA-event times (rank 0 spread shown; max over ranks)",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
-                    "pipeline": "wheatley_b200.prefetch.BatchPrefetcher: step i+1's host->device copy and plan "
-                                "build are queued on a side stream while step i trains; every timed step copies "
-                                "its inputs from pinned host memory and reads its loss back",
+                    "input": "padded gym observation (features, precedence edge_index, n_nodes, n_edges) + masks / "
+                             "actions / advantages / returns in pinned host memory; the batched graph (clique "
+                             "conflict edges, pool wiring) is built on the device by b200gat_jssp_batch_build",
+                    "pipeline": "wheatley_b200.prefetch.BatchPrefetcher: step i+1's host->device copy, batch and "
+                                "plan build are queued on a side stream while step i trains; every timed step "
+                                "copies its inputs from pinned host memory and reads its loss back",
                     "ms_per_step_no_prefetch": ms_e2e_serial},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,

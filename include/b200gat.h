@@ -189,6 +189,44 @@ int b200gat_gather_rows_f32(const float* table, const int32_t* idx, int64_t n, i
 /* out[i] = (int32) in[i]  (int64 -> int32 narrowing with 16-byte loads). */
 int b200gat_narrow_i64(const int64_t* in, int64_t n, int32_t* out, void* stream);
 
+/* ------------------------------------------------------------------ batch builder
+ * Device-side replacement of the host batching of JSSP observations:
+ *   jssp/models/agent_observation.py:110-229 (per-graph DGL graphs: precedence edges forward (type 1) and
+ *   reversed (type 2) :53-72, machine-clique conflict edges :81-88,160-176 = jssp/utils/utils.py:460-478
+ *   (type 5, or machine id + 5 with mid_in_edges), self loops (type 0) :210-211, `dgl.batch` :223, the
+ *   feature fix-up feat[:,1] = (feat[:,1] == -1 ? -1 : feat[:,4]) :133-135 and no_tct :138-139)
+ *   + jssp/models/gnn_dgl.py:263-286 (one pool node per graph appended after all graph nodes: pool self
+ *   loops (type 0), [pool -> node (type 3) for "learninv"], node -> pool (type 4)).
+ * The reference does this with Python loops over the graphs on the CPU and copies the batched graph; here
+ * the padded observation arrays are copied as they are and the COO (same edge ORDER, bit-exact) is written
+ * by two kernels.  Per-graph sizes are host knowledge (the observation carries n_nodes / n_edges, and the
+ * clique edge counts follow from a histogram of the machine ids), so no device->host read is needed.
+ *   features   [B, max_nodes, n_feat] fp32 (column 6 = machine id, -1 = unaffected)
+ *   edge_index [B, 2, max_edges] int64 (precedence edges, node ids local to the graph)
+ *   meta       [4, B+1] int64, device: row 0 node offsets (exclusive prefix of n_nodes, [B] = total),
+ *              row 1 edge offsets of the per-graph segments (prefix of per-graph edge counts),
+ *              row 2 n_edges per graph (precedence edges), row 3 clique edges per graph
+ * Outputs: src / dst / etype [E_total] int64, feat [N_total (+ B pool rows), n_feat] fp32. */
+#define B200GAT_POOL_NONE 0
+#define B200GAT_POOL_LEARN 1
+#define B200GAT_POOL_LEARNINV 2
+typedef struct {
+  int32_t n_graphs, max_nodes, n_feat, max_edges;
+  const float* features;
+  const int64_t* edge_index;
+  const int64_t* meta;
+  int32_t clique_conflicts; /* 1: conflicts == "clique"; 0: no conflict edges ("att")      */
+  int32_t mid_in_edges, bidir, self_loops, no_tct;
+  int32_t pooling;          /* B200GAT_POOL_*                                               */
+  int32_t n_machine_ids;    /* machine ids are in [-1, n_machine_ids)                       */
+  int64_t n_nodes_total;    /* meta[0][B]                                                   */
+  int64_t n_edges_graphs;   /* meta[1][B]                                                   */
+} b200gat_jssp_obs;
+/* Total edge count of the batch (graph segments + pool wiring). */
+int64_t b200gat_jssp_batch_edges(const b200gat_jssp_obs* o);
+int b200gat_jssp_batch_build(const b200gat_jssp_obs* o, int64_t* src, int64_t* dst, int64_t* etype,
+                             float* feat, void* stream);
+
 /* ------------------------------------------------------------------ attention layer */
 typedef struct {
   int32_t flavour; /* B200GAT_FLAVOUR_*                                                  */

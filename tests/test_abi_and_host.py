@@ -126,6 +126,32 @@ def test_workload_batch_matches_oracle_batching(built):
     assert np.array_equal(ob["type"], wbat["etype"].numpy())
 
 
+def test_batch_sizes_from_observation_match_oracle(built):
+    """Host half of the device batch builder: per-graph node / edge offsets and clique edge counts computed from
+    the observation alone (no device work) equal what the oracle's builder produces."""
+    import torch
+    from oracle import batch_oracle
+    from wheatley_b200.batch import jssp_sizes
+    rng = np.random.default_rng(5)
+    B, n, F = 4, 23, 9
+    nn = np.array([23, 1, 17, 9])
+    ne = np.array([5, 0, 30, 2])
+    feat = rng.standard_normal((B, n, F)).astype(np.float32)
+    mid = rng.integers(0, 4, (B, n)).astype(np.float32)
+    mid[rng.random((B, n)) < 0.3] = -1
+    feat[:, :, 6] = mid
+    ei = np.zeros((B, 2, 30), np.int64)
+    for conflicts in ("att", "clique"):
+        ob = batch_oracle.jssp_batch(feat, ei, nn, ne, conflicts=conflicts)
+        meta, n_mid = jssp_sizes(torch.from_numpy(feat), nn, ne, conflicts)
+        assert meta[0].tolist() == [0] + np.cumsum(nn).tolist()
+        assert meta[1].tolist() == [0] + np.cumsum(ob["batch_num_edges"]).tolist()
+        assert meta[2, :B].tolist() == ne.tolist()
+        if conflicts == "clique":
+            assert n_mid == int(mid[np.arange(n)[None, :] < nn[:, None]].max()) + 1
+            assert meta[3, :B].tolist() == (ob["batch_num_edges"] - 2 * ne - nn).tolist()
+
+
 def test_sharding(built):
     from wheatley_b200.ppo import shard_by_edges, shard_range
     for n, w in [(10, 4), (3, 8), (128, 8), (7, 1)]:

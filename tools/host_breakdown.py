@@ -55,7 +55,51 @@ def main():
     wrap(GnnDGL, "node_embeddings", "M.trunk")
     wrap(_lib.lib, "b200gat_mlp_fwd", "C.mlp_fwd") if False else None
 
+    from wheatley_b200.prefetch import BatchPrefetcher
+    from wheatley_b200.workload import jssp_observation_batch
+    obs = {k: v.contiguous().pin_memory() for k, v in jssp_observation_batch(n_j, n_m, B).items()}
+    extras = {k: host[k] for k in ("masks", "action", "adv", "ret")}
+    pf = BatchPrefetcher(dev)
+    mode = os.environ.get("HB_MODE", "serial").replace("bg", "")
+    if mode == "obs":
+        pf.submit_observation(obs, n_j * n_m, extras, conflicts="clique", graph_pooling="learn")
+    elif mode == "coo":
+        pf.submit(host, N)
+
+    def step_pf(rec):
+        t0 = time.perf_counter()
+        d, plan = pf.get()
+        t1 = time.perf_counter()
+        if mode == "obs":
+            pf.submit_observation(obs, n_j * n_m, extras, conflicts="clique", graph_pooling="learn")
+            jb = d["batch"]
+        else:
+            pf.submit(host, N)
+            jb = JsspBatch(plan, d["etype"], d["feat"], B, n_j * n_m, NT, poolnodes=torch.arange(NT, NT + B, device=dev))
+        t2 = time.perf_counter()
+        bucket.zero()
+        _, lp, ent, val, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
+        t3 = time.perf_counter()
+        loss = ppo_like_loss(lp, ent, val, d["adv"], d["ret"])
+        t4 = time.perf_counter()
+        loss.backward()
+        t5 = time.perf_counter()
+        bucket.reduce()
+        opt.step()
+        t6 = time.perf_counter()
+        v = loss.item()
+        t7 = time.perf_counter()
+        if rec:
+            for k, a, b in (("pf.get", t0, t1), ("pf.submit", t1, t2), ("forward", t2, t3), ("loss", t3, t4),
+                            ("backward", t4, t5), ("reduce+adam", t5, t6), ("drain(item)", t6, t7),
+                            ("TOTAL", t0, t7)):
+                T["S." + k] += b - a
+                C["S." + k] += 1
+        return v
+
     def step(rec):
+        if mode != "serial":
+            return step_pf(rec)
         t0 = time.perf_counter()
         d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
         t1 = time.perf_counter()
@@ -91,7 +135,6 @@ def main():
     n = 30
     for _ in range(n):
         step(True)
-        torch.cuda.synchronize()
     for k in sorted(T):
         print(f"{k:22s} {1e6 * T[k] / n:9.1f} us/step  ({C[k] / n:.0f} calls/step, {1e6 * T[k] / max(C[k], 1):7.1f} us/call)")
 

@@ -27,6 +27,7 @@ SYMBOLS = (
     "b200gat_gemm_supported", "b200gat_gemm_workspace_elems", "b200gat_gemm_tf32",
     "b200gat_colsum_scratch_elems", "b200gat_colsum",
     "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
+    "b200gat_jssp_batch_edges", "b200gat_jssp_batch_build",
 )
 MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
@@ -85,6 +86,18 @@ class Mlp(C.Structure):
     _fields_ = [("n_layers", C.c_int32), ("M", C.c_int64), ("dims", C.c_int32 * 9),
                 ("W", C.c_void_p * 8), ("b", C.c_void_p * 8), ("x", C.c_void_p), ("residual", C.c_void_p),
                 ("z", C.c_void_p * 8), ("h", C.c_void_p * 8), ("y", C.c_void_p)]
+
+
+class JsspObs(C.Structure):
+    """``b200gat_jssp_obs`` (include/b200gat.h)."""
+    _fields_ = [("n_graphs", C.c_int32), ("max_nodes", C.c_int32), ("n_feat", C.c_int32), ("max_edges", C.c_int32),
+                ("features", C.c_void_p), ("edge_index", C.c_void_p), ("meta", C.c_void_p),
+                ("clique_conflicts", C.c_int32), ("mid_in_edges", C.c_int32), ("bidir", C.c_int32),
+                ("self_loops", C.c_int32), ("no_tct", C.c_int32), ("pooling", C.c_int32),
+                ("n_machine_ids", C.c_int32), ("n_nodes_total", C.c_int64), ("n_edges_graphs", C.c_int64)]
+
+
+POOLING = {None: 0, "learn": 1, "learninv": 2}
 
 
 class MlpGrads(C.Structure):
@@ -149,13 +162,17 @@ def _load():
     lib.b200gat_mlp_bwd_workspace_elems.argtypes = [lp, lg]
     lib.b200gat_mlp_bwd_workspace_elems.restype = i64
     lib.b200gat_mlp_bwd.argtypes = [lp, lg, vp]
+    jp = C.POINTER(JsspObs)
+    lib.b200gat_jssp_batch_edges.argtypes = [jp]
+    lib.b200gat_jssp_batch_edges.restype = i64
+    lib.b200gat_jssp_batch_build.argtypes = [jp, vp, vp, vp, vp, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
                         "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
                         "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
-                        "b200gat_mlp_bwd_workspace_elems"):
+                        "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges"):
             fn.restype = C.c_int
     return lib
 

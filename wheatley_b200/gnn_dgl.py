@@ -25,11 +25,11 @@ class JsspBatch:
     """What ``GnnDGL.forward`` needs from one batched observation."""
 
     def __init__(self, plan, etype, feat, batch_size, n_nodes, num_task_nodes, poolnodes=None,
-                 machinenodes=None):
+                 machinenodes=None, prepare=True):
         self.plan, self.etype, self.feat = plan, etype, feat
         self.batch_size, self.n_nodes, self.num_task_nodes = batch_size, n_nodes, num_task_nodes
         self.poolnodes, self.machinenodes = poolnodes, machinenodes
-        if hasattr(plan, "prepare"):
+        if prepare and hasattr(plan, "prepare"):
             plan.prepare(etype)         # clique view + host counts with one device->host copy, before the trunk
 
 

@@ -22,6 +22,8 @@ from .plan import GraphPlan
 
 class BatchPrefetcher:
     def __init__(self, device, src_key="src", dst_key="dst", etype_key="etype"):
+        # (a worker thread for the submissions was tried: the step's own launches and the worker's contend for
+        # the GIL and the step got 50 % slower; the submissions stay on the caller's thread)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _lib.B200GatError("BatchPrefetcher needs a CUDA device: wheatley_b200 has no CPU path")
@@ -29,16 +31,39 @@ class BatchPrefetcher:
         self.keys = (src_key, dst_key, etype_key)
         self._pending = []
 
+    def _enqueue(self, job):
+        self._pending.append(job())
+
     def submit(self, host: dict, n_nodes: int):
         """Queue the copies of ``host`` (a dict of pinned CPU tensors) and the plan build on the side stream."""
         ks, kd, kt = self.keys
-        with torch.cuda.stream(self.side):
-            d = {k: v.to(self.device, non_blocking=True) for k, v in host.items()}
-            plan = GraphPlan(d[ks], d[kd], n_nodes)
-            plan.prepare(d.get(kt), defer=True)
-            done = torch.cuda.Event()
-            done.record()
-        self._pending.append((d, plan, done))
+
+        def job():
+            with torch.cuda.stream(self.side):
+                d = {k: v.to(self.device, non_blocking=True) for k, v in host.items()}
+                plan = GraphPlan(d[ks], d[kd], n_nodes)
+                plan.prepare(d.get(kt), defer=True)
+                done = torch.cuda.Event()
+                done.record()
+            return d, plan, done
+        self._enqueue(job)
+
+    def submit_observation(self, obs: dict, max_n_nodes: int, extras: dict = None, **builder_kw):
+        """Queue a raw JSSP gym observation: copies of the padded arrays, the device-side batch builder
+        (``wheatley_b200.batch``), the plan and its clique view.  ``extras``: other pinned host tensors of the
+        minibatch (masks, actions, advantages ...) copied alongside.  ``get()`` returns them with the built
+        ``JsspBatch`` under key ``"batch"``."""
+        from .batch import jssp_batch_from_observation
+
+        def job():
+            with torch.cuda.stream(self.side):
+                d = {k: v.to(self.device, non_blocking=True) for k, v in (extras or {}).items()}
+                jb, built = jssp_batch_from_observation(obs, self.device, max_n_nodes, defer=True, **builder_kw)
+                d.update(batch=jb, **{k: built[k] for k in ("src", "dst", "etype", "feat", "poolnodes")})
+                done = torch.cuda.Event()
+                done.record()
+            return d, jb.plan, done
+        self._enqueue(job)
 
     def get(self):
         """``(device_tensors, plan)`` of the oldest submitted batch, usable on the current stream."""
@@ -51,5 +76,6 @@ class BatchPrefetcher:
         main.wait_event(done)
         # the tensors were allocated on the side stream's pool and are used (and eventually freed) on `main`
         for t in list(d.values()) + plan.tensors():
-            t.record_stream(main)
+            if isinstance(t, torch.Tensor) and t.is_cuda:
+                t.record_stream(main)
         return d, plan

@@ -132,3 +132,18 @@ def jssp_clique_graph(n_j, n_m, seed=0):
     """One full-size graph (tasks + pool node): ``(src, dst, etype, n_nodes)``."""
     b = jssp_batch(n_j, n_m, 1, seed)
     return b["src"], b["dst"], b["etype"], b["n_nodes"]
+
+
+def jssp_observation_batch(n_j, n_m, batch, seed0=0, progress=0.0, n_features=None):
+    """The padded gym observation of ``batch`` graphs, as ``AgentObservation.from_gym_observation`` receives it
+    (jssp/models/agent_observation.py:127-131): ``features [B, max_nodes, F]``, ``edge_index [B, 2, max_edges]``
+    (zero-padded), ``n_nodes [B]``, ``n_edges [B]`` - CPU torch tensors."""
+    obs = [jssp_observation(n_j, n_m, seed0 + b, n_features, progress) for b in range(batch)]
+    max_e = max(o["n_edges"] for o in obs)
+    ei = np.zeros((batch, 2, max_e), np.int64)
+    for i, o in enumerate(obs):
+        ei[i, :, : o["n_edges"]] = o["edge_index"]
+    return dict(features=torch.from_numpy(np.stack([o["features"] for o in obs])),
+                edge_index=torch.from_numpy(ei),
+                n_nodes=torch.tensor([o["n_nodes"] for o in obs], dtype=torch.int64),
+                n_edges=torch.tensor([o["n_edges"] for o in obs], dtype=torch.int64))
