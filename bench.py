@@ -132,7 +132,7 @@ def run_reference(args):
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 def workload_config(args, cfg, graphs, note=None):
@@ -495,13 +495,31 @@ def run_b200(args):
     if world == 1 and not args.no_cpu_baseline:
         cb, _, _ = time_cpu(cfg, args, 1000, 1, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = cb
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
     finish(world)
 
 
 def edges_per_rank_note(edges, ms, world):
     """Forward-only (inference) throughput of the rollout step, all ranks (same shard size on every rank)."""
     return world * edges / (ms * 1e-3)
+
+
+_JSON_FD = None
+
+
+def guard_stdout():
+    """stdout carries exactly one JSON line.  Libraries write there behind Python's back (NCCL prints its version
+    line to fd 1 on some boxes whatever NCCL_DEBUG_FILE says): point fd 1 at stderr for the run and keep the
+    real stdout for emit()."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(text):
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (text + "\n").encode())
 
 
 def finish(world):
@@ -529,6 +547,7 @@ def start_watchdog(seconds):
 
 def main():
     args = parse()
+    guard_stdout()
     start_watchdog(args.max_seconds)
     # the workload generator is plain numpy: load it by path so the reference arm does not need
     # the CUDA library (wheatley_b200/__init__ refuses to import without it)
