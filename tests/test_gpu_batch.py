@@ -133,14 +133,15 @@ def test_batch_bench_size_and_trunk(wb):
     assert torch.equal(a, b)
 
 
-def test_prefetcher_observation_path(wb):
+@pytest.mark.parametrize("side_stream", [False, True])
+def test_prefetcher_observation_path(wb, side_stream):
     from wheatley_b200.batch import jssp_batch_from_observation
     from wheatley_b200.prefetch import BatchPrefetcher
     from wheatley_b200.workload import jssp_observation_batch
     n_j, n_m, B = 12, 5, 3
     obs = {k: v.pin_memory() for k, v in jssp_observation_batch(n_j, n_m, B, seed0=4, progress=0.4).items()}
     extras = dict(adv=torch.randn(B).pin_memory())
-    pf = BatchPrefetcher("cuda:0")
+    pf = BatchPrefetcher("cuda:0", side_stream=side_stream)
     pf.submit_observation(obs, n_j * n_m, extras, conflicts="clique", graph_pooling="learn")
     d, plan = pf.get()
     jb, ref = jssp_batch_from_observation(obs, "cuda:0", n_j * n_m, conflicts="clique", graph_pooling="learn")

@@ -57,7 +57,8 @@ def test_deferred_prepare_builds_the_same_view(wb):
     assert len(b.tensors()) >= 20
 
 
-def test_prefetched_batches_train_identically(wb):
+@pytest.mark.parametrize("side_stream", [False, True])
+def test_prefetched_batches_train_identically(wb, side_stream):
     """Four different minibatches through the pipeline (next batch queued while the current one trains) against
     the same four built directly, on the bench's dense path (tcgen05 TF32): the forward is deterministic, so the
     losses must agree to the bit; the backward accumulates a few small gradients with atomics (order-dependent
@@ -76,7 +77,7 @@ def test_prefetched_batches_train_identically(wb):
             d = {k: v.cuda() for k, v in host.items()}
             direct.append(_step(agent, wb.GraphPlan(d["src"], d["dst"], N), d, B, n_j * n_m, NT))
         torch.cuda.synchronize()
-        pf = BatchPrefetcher("cuda:0")
+        pf = BatchPrefetcher("cuda:0", side_stream=side_stream)
         pf.submit(batches[0][0], batches[0][1])
         piped = []
         for i, (host, N, NT) in enumerate(batches):

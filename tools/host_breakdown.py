@@ -59,7 +59,7 @@ def main():
     from wheatley_b200.workload import jssp_observation_batch
     obs = {k: v.contiguous().pin_memory() for k, v in jssp_observation_batch(n_j, n_m, B).items()}
     extras = {k: host[k] for k in ("masks", "action", "adv", "ret")}
-    pf = BatchPrefetcher(dev)
+    pf = BatchPrefetcher(dev, side_stream=os.environ.get("HB_SIDE", "0") == "1")
     mode = os.environ.get("HB_MODE", "serial").replace("bg", "")
     if mode == "obs":
         pf.submit_observation(obs, n_j * n_m, extras, conflicts="clique", graph_pooling="learn")

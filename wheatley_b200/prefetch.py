@@ -1,19 +1,33 @@
-"""Batch prefetch for the PPO update loop: the NEXT minibatch's host->device copies, graph plan and clique view
-are queued on a side stream while the CURRENT minibatch trains, so the copy (tens of MB of int64 edge index per
-minibatch at Taillard 100x20) runs on the copy engine under the step's kernels and the plan's one device->host
-read of its counts no longer stalls the host with an empty GPU behind it.
+"""Batch prefetch for the PPO update loop: the NEXT minibatch's host->device copies, batch build, graph plan and
+clique view are queued BEFORE the current minibatch's training step instead of at the start of its own step, and
+the plan's one device->host read of its counts is asynchronous (``GraphPlan.prepare(defer=True)``), so by the
+time the next step asks for them (``get()``) they have long arrived: the host never waits on a GPU that has only
+the plan build to do (~1 ms at 8 x Taillard 100x20), and in the host-bound regime the build runs on the GPU while
+the host is still launching the forward.
+
+Two placements:
+
+* ``side_stream=False`` (default): everything on the caller's stream, ahead of the step's kernels.  No
+  cross-stream bookkeeping; right for raw observations (``submit_observation``: 2 MB of copies per minibatch).
+* ``side_stream=True``: copies and kernels on a side stream, so that a LARGE copy (the 41 MB int64 COO of an
+  already batched graph, ``submit``) runs on the copy engine under the step's kernels; tensors change streams
+  through ``record_stream``, which costs ~0.3 ms of host time per step in allocator events - worth it only for
+  copies of that size (measured: 8.5 -> 7.75 ms with the COO, slower than the default with observations).
 
 The reference builds each minibatch on the host inside the update loop (alg/ppo.py:547-727 ->
 jssp/models/agent_observation / gnn_dgl.py:272-286) with nothing overlapped; this is the B200-side counterpart
 of a pinned-memory DataLoader with ``non_blocking`` copies.
 
     pf = BatchPrefetcher(device)
-    pf.submit(host_batch, n_nodes)              # pinned host tensors: src, dst, etype, ... (any other keys ride along)
-    for next_host in batches:
-        d, plan = pf.get()                      # ready on the current stream
-        pf.submit(next_host, n_nodes)           # overlaps with the step below
-        step(d, plan)
+    pf.submit_observation(obs[0], max_n_nodes, extras[0], conflicts="clique")
+    for i in range(n_minibatches):
+        d, plan = pf.get()                      # ready on the current stream; d["batch"] is the JsspBatch
+        if i + 1 < n_minibatches:
+            pf.submit_observation(obs[i + 1], max_n_nodes, extras[i + 1], conflicts="clique")
+        step(d)
 """
+import contextlib
+
 import torch
 
 from . import _lib
@@ -21,25 +35,28 @@ from .plan import GraphPlan
 
 
 class BatchPrefetcher:
-    def __init__(self, device, src_key="src", dst_key="dst", etype_key="etype"):
+    def __init__(self, device, src_key="src", dst_key="dst", etype_key="etype", side_stream=False):
         # (a worker thread for the submissions was tried: the step's own launches and the worker's contend for
         # the GIL and the step got 50 % slower; the submissions stay on the caller's thread)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _lib.B200GatError("BatchPrefetcher needs a CUDA device: wheatley_b200 has no CPU path")
-        self.side = torch.cuda.Stream(self.device)
+        self.side = torch.cuda.Stream(self.device) if side_stream else None
         self.keys = (src_key, dst_key, etype_key)
         self._pending = []
 
     def _enqueue(self, job):
         self._pending.append(job())
 
+    def _stream(self):
+        return torch.cuda.stream(self.side) if self.side is not None else contextlib.nullcontext()
+
     def submit(self, host: dict, n_nodes: int):
         """Queue the copies of ``host`` (a dict of pinned CPU tensors) and the plan build on the side stream."""
         ks, kd, kt = self.keys
 
         def job():
-            with torch.cuda.stream(self.side):
+            with self._stream():
                 d = {k: v.to(self.device, non_blocking=True) for k, v in host.items()}
                 plan = GraphPlan(d[ks], d[kd], n_nodes)
                 plan.prepare(d.get(kt), defer=True)
@@ -56,7 +73,7 @@ class BatchPrefetcher:
         from .batch import jssp_batch_from_observation
 
         def job():
-            with torch.cuda.stream(self.side):
+            with self._stream():
                 d = {k: v.to(self.device, non_blocking=True) for k, v in (extras or {}).items()}
                 jb, built = jssp_batch_from_observation(obs, self.device, max_n_nodes, defer=True, **builder_kw)
                 d.update(batch=jb, **{k: built[k] for k in ("src", "dst", "etype", "feat", "poolnodes")})
@@ -70,9 +87,12 @@ class BatchPrefetcher:
         if not self._pending:
             raise _lib.B200GatError("BatchPrefetcher.get() without a submitted batch")
         d, plan, done = self._pending.pop(0)
+        if self.side is None:
+            plan.finish()               # waits for the counts' event only (queued ahead of the previous step)
+            return d, plan
         main = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self.side):
-            plan.finish()               # waits for the counts' event only; allocations stay on the side pool
+            plan.finish()               # allocations stay on the side pool
         main.wait_event(done)
         # the tensors were allocated on the side stream's pool and are used (and eventually freed) on `main`
         for t in list(d.values()) + plan.tensors():
