@@ -241,3 +241,54 @@ def test_gemm_descriptor_validation_without_gpu(built):
     assert _lib.lib.b200gat_gemm_workspace_elems(g) == ws // (256 * 256) * (256 * 256 + 256)
     assert _lib.lib.b200gat_gemm_workspace_elems(desc(0, 0, 16008, 256, 256, 256, 256, 256)) == 0
     assert _lib.launch_count() == 0
+
+
+def test_batched_edge_tables_match_per_layer_linear(built):
+    """edge_feats.edge_tables (one GEMM for all layers' projected edge-type tables) against the per-layer
+    ``fc_fij(Embedding.weight) + bias`` it replaces: values and every gradient (pure torch: runs on the CPU)."""
+    import torch
+    from wheatley_b200.edge_feats import edge_tables
+    torch.manual_seed(0)
+    T, F, HD, L = 6, 16, 24, 3
+    for with_bias in (True, False):
+        emb = torch.randn(T, F, dtype=torch.float64, requires_grad=True)
+        Ws = [torch.randn(HD, F, dtype=torch.float64, requires_grad=True) for _ in range(L)]
+        bs = [torch.randn(HD, dtype=torch.float64, requires_grad=True) if with_bias else None for _ in range(L)]
+        tabs = edge_tables(emb, Ws, bs)
+        coef = [torch.randn(T, HD, dtype=torch.float64) for _ in range(L)]
+        # layer 1's table is left unused: its gradient arrives as None
+        loss = sum((tabs[id(Ws[l])] * coef[l]).sum() for l in (0, 2))
+        loss.backward()
+        got = [emb.grad.clone()] + [w.grad for w in Ws] + [b.grad if with_bias else None for b in bs]
+        emb.grad = None
+        for w in Ws:
+            w.grad = None
+        for b in bs:
+            if b is not None:
+                b.grad = None
+        ref_tabs = [torch.nn.functional.linear(emb, Ws[l], bs[l]) for l in range(L)]
+        for l in range(L):
+            assert torch.allclose(tabs[id(Ws[l])], ref_tabs[l], rtol=1e-12, atol=1e-12)
+        sum((ref_tabs[l] * coef[l]).sum() for l in (0, 2)).backward()
+        ref = [emb.grad] + [w.grad for w in Ws] + [b.grad if with_bias else None for b in bs]
+        for g, r in zip(got, ref):
+            if r is None:
+                assert g is None or float(g.abs().max()) == 0.0
+            else:
+                assert torch.allclose(g, r, rtol=1e-12, atol=1e-12)
+    assert edge_tables(emb, [], []) is None
+    assert edge_tables(emb, Ws, [bs[0], None, None]) is None or not with_bias
+
+
+def test_split_rows_backward_is_a_concatenation(built):
+    import torch
+    from wheatley_b200.gnn_dgl import _SplitRows
+    x = torch.randn(7, 3, dtype=torch.float64, requires_grad=True)
+    a, b = _SplitRows.apply(x, 5)
+    assert torch.equal(a, x[:5]) and torch.equal(b, x[5:])
+    (a * 2).sum().backward()
+    assert torch.equal(x.grad, torch.cat([torch.full((5, 3), 2.0, dtype=torch.float64), torch.zeros(2, 3, dtype=torch.float64)]))
+    x.grad = None
+    a, b = _SplitRows.apply(x, 5)
+    ((a * 2).sum() + (b * 3).sum()).backward()
+    assert torch.equal(x.grad[:5], torch.full((5, 3), 2.0, dtype=torch.float64)) and float(x.grad[5:].min()) == 3.0

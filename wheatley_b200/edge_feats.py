@@ -17,6 +17,7 @@ class TypedEdgeFeats:
         self.etype, self.weight = etype, weight
         self.attrs = None
         self.attr_weight = None
+        self.tables = None          # optional {id(layer weight): projected [T, H*D] table} (edge_tables)
 
     @property
     def shape(self):
@@ -24,6 +25,59 @@ class TypedEdgeFeats:
 
     def dense(self) -> torch.Tensor:
         return torch.nn.functional.embedding(self.etype.long(), self.weight)
+
+
+class _EdgeTables(torch.autograd.Function):
+    """Projected edge-type tables of ALL layers at once: ``table_l = weight @ W_l.T + b_l`` ([T, H*D] each).
+    Per layer this is ``fc_fij(Embedding.weight) + bias`` (jssp/models/gnn_dgl.py:364 + generic/eegatconv.py:262,
+    271-275 on the T distinct rows); layer by layer it costs one 6-row GEMM forward and two backward plus a bias
+    sum - 30 launches of ~3 us of GPU and ~8 us of host time each for 6 layers.  Here: 4 launches forward, 4
+    backward, same arithmetic (one GEMM over the concatenated weights)."""
+
+    @staticmethod
+    def forward(ctx, weight, n_layers, *params):
+        Ws, bs = params[:n_layers], params[n_layers:]
+        T, HD = weight.shape[0], Ws[0].shape[0]
+        Wcat = torch.cat(Ws, 0)                                           # [L*HD, F]
+        if bs[0] is not None:
+            out = torch.addmm(torch.cat(bs, 0), weight, Wcat.t())         # [T, L*HD]
+        else:
+            out = weight @ Wcat.t()
+        tabs = out.view(T, n_layers, HD).transpose(0, 1).contiguous()     # [L, T, HD]
+        ctx.save_for_backward(weight, Wcat)
+        ctx.n_layers, ctx.has_bias, ctx.HD = n_layers, bs[0] is not None, HD
+        ctx.set_materialize_grads(False)
+        return tabs.unbind(0)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        weight, Wcat = ctx.saved_tensors
+        L, HD = ctx.n_layers, ctx.HD
+        if all(g is None for g in gs):
+            return (None,) * (2 + 2 * L)
+        gs = [g if g is not None else torch.zeros((weight.shape[0], HD), dtype=weight.dtype, device=weight.device)
+              for g in gs]
+        g2 = torch.cat(gs, 1)                                             # [T, L*HD]
+        need = ctx.needs_input_grad
+        d_weight = g2 @ Wcat if need[0] else None                         # [T, F]
+        dWcat = g2.t() @ weight                                           # [L*HD, F]
+        dWs = tuple(dWcat[l * HD:(l + 1) * HD] if need[2 + l] else None for l in range(L))
+        if ctx.has_bias:
+            dbcat = g2.sum(0)
+            dbs = tuple(dbcat[l * HD:(l + 1) * HD] if need[2 + L + l] else None for l in range(L))
+        else:
+            dbs = (None,) * L
+        return (d_weight, None) + dWs + dbs
+
+
+def edge_tables(weight, layer_weights, layer_biases):
+    """``{id(W_l): table_l}`` for ``TypedEdgeFeats.tables`` (looked up by ``functional.project_edge_feats``)."""
+    L = len(layer_weights)
+    has_b = [b is not None for b in layer_biases]
+    if L == 0 or (any(has_b) and not all(has_b)) or len({tuple(w.shape) for w in layer_weights}) != 1:
+        return None
+    tabs = _EdgeTables.apply(weight, L, *layer_weights, *layer_biases)
+    return {id(w): t for w, t in zip(layer_weights, tabs)}
 
 
 class AffineEdgeFeats(TypedEdgeFeats):

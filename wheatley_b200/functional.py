@@ -41,7 +41,9 @@ def project_edge_feats(plan: GraphPlan, efeats, weight, pre_bias=None) -> EdgeFe
     if efeats is None:
         return EdgeFeatures.none()
     if isinstance(efeats, TypedEdgeFeats):
-        table = torch.nn.functional.linear(efeats.weight, weight, pre_bias)     # [T, H*D]
+        table = efeats.tables.get(id(weight)) if getattr(efeats, "tables", None) else None
+        if table is None or efeats.attrs is not None:
+            table = torch.nn.functional.linear(efeats.weight, weight, pre_bias)  # [T, H*D]
         etype_sorted = plan.sort_edge_ints(efeats.etype)
         if efeats.attrs is not None and efeats.attrs.shape[1] <= _lib.MAX_ATTR:
             affine = (weight @ efeats.attr_weight).t()                            # [K, H*D]
@@ -132,11 +134,15 @@ class _FusedGATConv(torch.autograd.Function):
         g3 = torch.empty((2 if ctx.v_alias else 3,) + tuple(Pi.shape), dtype=Pi.dtype, device=Pi.device)
         gPi, gPj = g3[0], g3[1]
         gV = gPi if ctx.v_alias else g3[2]
-        g_attn = torch.zeros_like(attn_c)
-        g_attn_bias = torch.zeros_like(attn_bias_c) if attn_bias_c is not None else None
-        g_table = torch.zeros_like(e_table_c) if e_table_c is not None else None
+        # the small gradients the kernels accumulate into with atomics: one zero-filled buffer, carved up
+        # (16-byte aligned pieces)
+        acc = [attn_c, attn_bias_c, e_table_c, e_affine_c]
+        sizes = [0 if t is None else (t.numel() + 3) // 4 * 4 for t in acc]
+        zbuf = torch.zeros(sum(sizes), dtype=attn_c.dtype, device=attn_c.device)
+        offs = [sum(sizes[:i]) for i in range(4)]
+        g_attn, g_attn_bias, g_table, g_affine = (
+            None if t is None else zbuf[o:o + t.numel()].view(t.shape) for t, o in zip(acc, offs))
         g_dense = torch.empty_like(e_dense_c) if e_dense_c is not None else None
-        g_affine = torch.zeros_like(e_affine_c) if e_affine_c is not None else None
         n_gs = 2 * s.numel()
         if ctx.dense:       # + gs_dense [H*s_elems] + gsum_u / gsum_v [N*H]   (include/b200gat.h)
             n_gs += ((H * view.s_elems + 3) // 4) * 4 + 2 * plan.n_nodes * H

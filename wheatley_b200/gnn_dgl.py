@@ -16,9 +16,31 @@ checkpoints.  Differences, all inside the boundary:
 import torch
 from torch import nn
 
-from .edge_feats import TypedEdgeFeats
+from .edge_feats import TypedEdgeFeats, edge_tables
 from .eegatconv import EGATConv
 from .mlp import MLP
+
+
+class _SplitRows(torch.autograd.Function):
+    """``(x[:n], x[n:])`` as views; backward = one ``cat`` of the two gradients."""
+
+    @staticmethod
+    def forward(ctx, x, n):
+        ctx.n, ctx.shape = n, x.shape
+        ctx.set_materialize_grads(False)
+        return x[:n], x[n:]
+
+    @staticmethod
+    def backward(ctx, ga, gb):
+        if ga is None and gb is None:
+            return None, None
+        n, shape = ctx.n, ctx.shape
+        ref = ga if ga is not None else gb
+        if ga is None:
+            ga = ref.new_zeros((n,) + tuple(shape[1:]))
+        if gb is None:
+            gb = ref.new_zeros((shape[0] - n,) + tuple(shape[1:]))
+        return torch.cat((ga, gb), 0), None
 
 
 class JsspBatch:
@@ -91,6 +113,10 @@ class GnnDGL(nn.Module):
         features = self.embedder(features)                                      # :355
         features_list.append(features)
         efeats = TypedEdgeFeats(b.etype, self.edge_embedder[0].weight)          # :364
+        # all layers' projected edge-type tables with one GEMM (each layer would do its own 6-row one)
+        efeats.tables = edge_tables(self.edge_embedder[0].weight,
+                                    [fe.fc_fij.weight for fe in self.features_extractors],
+                                    [fe.bias for fe in self.features_extractors])
         for layer in range(self.n_layers_features_extractor):
             h, _ = self.features_extractors[layer](b.plan, features, efeats)    # :374-376
             # :377 and the residual add of :395-396 (fused into the MLP's last GEMM epilogue)
@@ -103,16 +129,25 @@ class GnnDGL(nn.Module):
         """``(node_features [B, max_n_nodes, F], graph_embedding [B, 1, F])`` - the pair the generic
         ``Agent`` unpacks (generic/agent.py:193)."""
         features = self.node_embeddings(b)
-        node_features = features[: b.num_task_nodes].reshape(b.batch_size, b.n_nodes, -1)   # :402-405
-        if self.graph_pooling == "max":
-            graph_embedding = node_features.max(dim=1)[0]
-        elif self.graph_pooling == "avg":
-            graph_embedding = node_features.mean(dim=1)
-        elif self.graph_pooling in ("learn", "learninv"):
-            graph_embedding = features[b.num_task_nodes: b.num_task_nodes + b.batch_size]
+        NT = b.num_task_nodes
+        if self.graph_pooling in ("learn", "learninv"):
+            # the two row ranges of one tensor: split with one backward (a concatenation) instead of two
+            # slice backwards (each a zero-filled [N, F] tensor + a copy) and their sum
+            if features.shape[0] == NT + b.batch_size:
+                node_rows, graph_embedding = _SplitRows.apply(features, NT)
+            else:
+                node_rows, graph_embedding = features[:NT], features[NT: NT + b.batch_size]
+            node_features = node_rows.reshape(b.batch_size, b.n_nodes, -1)                  # :402-405
         else:
-            raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
-        node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - node_features.shape[1]))
+            node_features = features[:NT].reshape(b.batch_size, b.n_nodes, -1)
+            if self.graph_pooling == "max":
+                graph_embedding = node_features.max(dim=1)[0]
+            elif self.graph_pooling == "avg":
+                graph_embedding = node_features.mean(dim=1)
+            else:
+                raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
+        if self.max_n_nodes != node_features.shape[1]:       # (F.pad with nothing to pad still copies)
+            node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - node_features.shape[1]))
         return node_features, graph_embedding.reshape(b.batch_size, 1, -1)
 
     def forward(self, b: JsspBatch):
