@@ -220,7 +220,7 @@ def run_b200(args):
     from wheatley_b200 import _lib
     from wheatley_b200.agent import JsspAgent
     from wheatley_b200.gnn_dgl import JsspBatch
-    from wheatley_b200.ppo import FlatGradAllReduce, ppo_like_loss
+    from wheatley_b200.ppo import FlatAdam, FlatGradAllReduce, ppo_like_loss
     from wheatley_b200.workload import jssp_batch
 
     torch.backends.cuda.matmul.allow_tf32 = True       # the reference's matmul precision (psp/train_psp.py:47)
@@ -233,7 +233,8 @@ def run_b200(args):
     agent = JsspAgent(cfg["input_dim"], cfg["max_n_nodes"], cfg["n_m"], cfg["hidden"], cfg["layers"],
                       cfg["heads"]).to(dev)
     bucket = FlatGradAllReduce(list(agent.parameters()))
-    opt = torch.optim.Adam(agent.parameters(), lr=2e-4, fused=True, capturable=True)
+    # Adam of alg/ppo.py on ONE flat parameter / the all-reduced flat gradient (ppo.FlatAdam)
+    opt = FlatAdam(agent.parameters(), lr=2e-4, bucket=bucket)
 
     hb = jssp_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress)
     masks, action, adv, ret = synth_targets(B, cfg["max_n_nodes"], 1 + rank)

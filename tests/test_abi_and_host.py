@@ -189,6 +189,21 @@ ref.load_state_dict(model.state_dict())
 for p, q in zip(model.parameters(), ref.parameters()):
     assert p.grad.data_ptr() >= bucket.flat.data_ptr()
     assert torch.allclose(p.grad, q.grad, atol=1e-6), (p.grad - q.grad).abs().max()
+# FlatAdam on the all-reduced bucket == torch.optim.Adam on the global-batch gradients, for 3 steps
+from wheatley_b200.ppo import FlatAdam
+ref_opt = torch.optim.Adam(ref.parameters(), lr=1e-2)
+opt = FlatAdam(model.parameters(), lr=1e-2, bucket=bucket)
+for it in range(3):
+    if it:
+        opt.zero_grad()
+        (model(x[lo:hi]).sum() / 10 * world).backward()
+        bucket.reduce()
+        ref_opt.zero_grad()
+        (ref(x).sum() / 10).backward()
+    opt.step()
+    ref_opt.step()
+    for p, q in zip(model.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, atol=1e-6), (it, (p - q).abs().max())
 dist.destroy_process_group()
 print("ok", rank)
 '''
@@ -203,6 +218,37 @@ def test_flat_gradient_allreduce_world_size_2_gloo(built, tmp_path):
     outs = [p.communicate(timeout=240)[0].decode() for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_flat_adam_matches_torch_adam(built):
+    """ppo.FlatAdam (one flat parameter, one concatenated gradient) against torch.optim.Adam parameter by
+    parameter, including a parameter that never receives a gradient and the state dict round trip."""
+    import torch
+    import wheatley_b200
+    from wheatley_b200.ppo import FlatAdam
+    torch.manual_seed(0)
+    a = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+    a.unused = torch.nn.Parameter(torch.randn(5))
+    b = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+    b.unused = torch.nn.Parameter(a.unused.detach().clone())
+    b.load_state_dict(a.state_dict())
+    oa = FlatAdam(a.parameters(), lr=3e-3, weight_decay=0.0)
+    ob = torch.optim.Adam(b.parameters(), lr=3e-3)
+    assert all(p.data_ptr() >= oa.flat.data_ptr() for p in a.parameters())      # parameters live in the flat buffer
+    x = torch.randn(12, 6)
+    for it in range(4):
+        oa.zero_grad()
+        ob.zero_grad()
+        a(x).square().mean().backward()
+        b(x).square().mean().backward()
+        oa.step()
+        ob.step()
+        for (k, p), q in zip(a.named_parameters(), b.parameters()):
+            assert torch.allclose(p, q, atol=1e-7, rtol=1e-6), (it, k)
+    assert torch.equal(a.unused, b.unused)
+    sd = oa.state_dict()
+    oa.load_state_dict(sd)
+    assert set(a.state_dict()) == set(b.state_dict())
 
 
 def test_gemm_descriptor_validation_without_gpu(built):

@@ -99,3 +99,35 @@ def test_prefetcher_get_without_submit_raises(wb):
     from wheatley_b200.prefetch import BatchPrefetcher
     with pytest.raises(wb.B200GatError):
         BatchPrefetcher("cuda:0").get()
+
+
+def test_flat_adam_on_the_agent_matches_torch_adam(wb):
+    """ppo.FlatAdam (fused Adam on one flat parameter) against torch.optim.Adam(fused) on the whole agent,
+    three training steps on the same batch and the same gradients: same parameters."""
+    from wheatley_b200.agent import JsspAgent
+    from wheatley_b200.ppo import FlatAdam
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n_j, n_m, B = 10, 5, 3
+        host, N, NT = _host_batch(n_j, n_m, B, seed=1)
+        d = {k: v.cuda() for k, v in host.items()}
+        torch.manual_seed(0)
+        a = JsspAgent(host["feat"].shape[1], n_j * n_m, n_m, 64, 2, 4).cuda()
+        b = JsspAgent(host["feat"].shape[1], n_j * n_m, n_m, 64, 2, 4).cuda()
+        b.load_state_dict(a.state_dict())
+        oa = FlatAdam(a.parameters(), lr=1e-3)
+        ob = torch.optim.Adam(b.parameters(), lr=1e-3, fused=True, capturable=True)
+        plan = wb.GraphPlan(d["src"], d["dst"], N)
+        for it in range(3):
+            _step(a, plan, d, B, n_j * n_m, NT)
+            # the same gradients for both optimizers (Adam turns the rounding noise of a theoretically zero
+            # gradient into +-lr steps, so two separately computed backward passes may not be compared)
+            for pa, pb in zip(a.parameters(), b.parameters()):
+                pb.grad = None if pa.grad is None else pa.grad.clone()
+            oa.step()
+            ob.step()
+            for (k, p), q in zip(a.named_parameters(), b.parameters()):
+                assert float((p - q).abs().max()) <= 1e-6 * max(float(q.abs().max()), 1e-3), (it, k)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
