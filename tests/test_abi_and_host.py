@@ -338,3 +338,20 @@ def test_split_rows_backward_is_a_concatenation(built):
     a, b = _SplitRows.apply(x, 5)
     ((a * 2).sum() + (b * 3).sum()).backward()
     assert torch.equal(x.grad[:5], torch.full((5, 3), 2.0, dtype=torch.float64)) and float(x.grad[5:].min()) == 3.0
+
+
+def test_lazy_categorical_is_the_reference_distribution(built):
+    import torch
+    from torch.distributions.categorical import Categorical
+    from wheatley_b200.agent_head import LazyCategorical
+    logits = torch.randn(4, 9, requires_grad=True)
+    lazy, ref = LazyCategorical(logits), Categorical(logits=logits)
+    assert lazy._d is None
+    assert torch.equal(lazy.probs, ref.probs) and torch.equal(lazy.logits, ref.logits)
+    assert torch.equal(lazy.entropy(), ref.entropy())
+    a = torch.tensor([0, 3, 8, 2])
+    assert torch.equal(lazy.log_prob(a), ref.log_prob(a))
+    lazy.probs.sum().backward()                  # stays in the autograd graph of the logits
+    assert logits.grad is not None
+    with __import__("pytest").raises(AttributeError):
+        lazy._missing

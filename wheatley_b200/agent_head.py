@@ -10,6 +10,28 @@ from torch.distributions.categorical import Categorical
 
 from .functional import masked_log_softmax, masked_logprob_entropy
 
+class LazyCategorical:
+    """``Categorical(logits=logits)`` of generic/agent.py:197, built on first use.  The update loop reads it only
+    for the optional uniform-target KL term (alg/ppo.py:694-699); constructing it costs a log-sum-exp and a
+    subtraction over ``[B, n]`` plus their autograd nodes every minibatch.  Attribute access (``.probs``,
+    ``.logits``, ``.entropy()``, ``.log_prob()``, ``.sample()`` ...) is forwarded to the real distribution.
+    ``validate_args=False``: the default argument check reads a device flag back to the host (a sync per call,
+    illegal under CUDA-graph capture); the distribution itself is identical."""
+
+    def __init__(self, logits):
+        self._logits, self._d = logits, None
+
+    def materialize(self) -> Categorical:
+        if self._d is None:
+            self._d = Categorical(logits=self._logits, validate_args=False)
+        return self._d
+
+    def __getattr__(self, name):
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self.materialize(), name)
+
+
 HUGE_NEG = -1e20          # generic/agent.py:206, :270
 HUGE_NEG_PRETRAIN = -1e10  # generic/agent.py:245-247
 
@@ -59,9 +81,7 @@ class AgentHeadMixin:
         node_features, graph_embedding = self.gnn(x)
         value = self.value_net(graph_embedding)
         logits = self.action_net(node_features).squeeze(-1)
-        # generic/agent.py:197.  validate_args=False: the default argument check reads a device flag back to the
-        # host (a sync per call, and illegal under CUDA-graph capture); the distribution itself is identical
-        unmasked_distrib = Categorical(logits=logits, validate_args=False)
+        unmasked_distrib = LazyCategorical(logits)                  # generic/agent.py:197
         action, logprob, entropy = action_logprob_entropy(logits, action, action_masks, deterministic)
         return action, logprob, entropy, value, unmasked_distrib
 
