@@ -455,11 +455,22 @@ def run_b200(args):
                   "the event nodes serialise launches, `value` is timed on the plain graph)"
                   if graph is not None else "per-kernel CUDA events in the timed eager steps")
     roofline = None
+    # DRAM traffic of the kernel class per launch, from the committed ncu --set full capture of this workload
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1m_traffic.json")) as f:
+            tr = json.load(f)
+        if (tr["workload"], tr["graphs_per_gpu"], tr["hidden"], tr["heads"]) == (args.workload, B, cfg["hidden"],
+                                                                              cfg["heads"]) and dom in tr:
+            traffic, traffic_src = tr[dom], tr["source"]
+    except (OSError, KeyError, ValueError):
+        pass
     if dom:
         ms, byt = per[dom]
         ach = byt / (ms * 1e-3) / 1e9
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ach / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "frac": ach / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": byt, "avg_launch_ms": ms,
                     "kernels": {k: {"avg_ms": v[0], "algorithmic_bytes": v[1],
                                     "gbps": v[1] / (v[0] * 1e-3) / 1e9} for k, v in per.items()},
