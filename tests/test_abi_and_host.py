@@ -355,3 +355,24 @@ def test_lazy_categorical_is_the_reference_distribution(built):
     assert logits.grad is not None
     with __import__("pytest").raises(AttributeError):
         lazy._missing
+
+
+def test_batch_builder_refuses_cpu_and_unknown_modes(built):
+    """The device batch builder has no CPU path and says so; option validation happens before any device work."""
+    import torch
+    import wheatley_b200 as wb
+    from wheatley_b200.batch import jssp_batch_on_device
+    from wheatley_b200.prefetch import BatchPrefetcher
+    obs = dict(features=torch.zeros(1, 2, 8), edge_index=torch.zeros(1, 2, 1, dtype=torch.int64),
+               n_nodes=torch.tensor([2]), n_edges=torch.tensor([1]))
+    with pytest.raises(wb.B200GatError):
+        jssp_batch_on_device(obs, "cpu", conflicts="clique")
+    with pytest.raises(wb.B200GatError):
+        BatchPrefetcher("cpu")
+    if torch.cuda.is_available():
+        return
+    # without a GPU the mode checks still run first when the device is a CUDA device name
+    with pytest.raises(NotImplementedError):
+        jssp_batch_on_device(obs, "cuda:0", conflicts="node")
+    with pytest.raises(ValueError):
+        jssp_batch_on_device(obs, "cuda:0", conflicts="bogus")
