@@ -206,7 +206,7 @@ int b200gat_narrow_i64(const int64_t* in, int64_t n, int32_t* out, void* stream)
  *   meta       [4, B+1] int64, device: row 0 node offsets (exclusive prefix of n_nodes, [B] = total),
  *              row 1 edge offsets of the per-graph segments (prefix of per-graph edge counts),
  *              row 2 n_edges per graph (precedence edges), row 3 clique edges per graph
- * Outputs: src / dst / etype [E_total] int64, feat [N_total (+ B pool rows), n_feat] fp32. */
+ * Outputs: src / dst / etype [E_total] int64, feat [N_total (+ B pool rows) (+ B*M machine rows), n_feat] fp32. */
 #define B200GAT_POOL_NONE 0
 #define B200GAT_POOL_LEARN 1
 #define B200GAT_POOL_LEARNINV 2
@@ -221,6 +221,14 @@ typedef struct {
   int32_t n_machine_ids;    /* machine ids are in [-1, n_machine_ids)                       */
   int64_t n_nodes_total;    /* meta[0][B]                                                   */
   int64_t n_edges_graphs;   /* meta[1][B]                                                   */
+  /* conflicts == "node" (jssp/models/gnn_dgl.py:288-335): max_n_machines machine nodes per graph appended after
+   * the pool nodes, wired in this order after the pool edges: machine self loops (type 0), task -> machine
+   * (type mid+5) and machine -> task (type mid+5+M) for every affected task in ascending node order,
+   * machine -> pool (type 5+2M, "learn" pooling only).  meta row 3 then holds the exclusive prefix of the
+   * per-graph affected-task counts ([B] = n_affected) instead of clique edge counts. */
+  int32_t node_conflicts;
+  int32_t max_n_machines;
+  int64_t n_affected;
 } b200gat_jssp_obs;
 /* Total edge count of the batch (graph segments + pool wiring). */
 int64_t b200gat_jssp_batch_edges(const b200gat_jssp_obs* o);

@@ -372,7 +372,7 @@ def test_batch_builder_refuses_cpu_and_unknown_modes(built):
     if torch.cuda.is_available():
         return
     # without a GPU the mode checks still run first when the device is a CUDA device name
-    with pytest.raises(NotImplementedError):
-        jssp_batch_on_device(obs, "cuda:0", conflicts="node")
+    with pytest.raises(ValueError):
+        jssp_batch_on_device(obs, "cuda:0", conflicts="node")            # needs max_n_machines
     with pytest.raises(ValueError):
         jssp_batch_on_device(obs, "cuda:0", conflicts="bogus")

@@ -78,6 +78,27 @@ def test_batch_matches_oracle_option_space(wb, conflicts, pooling, opts):
         assert dev["n_task_nodes"] == ref["num_task_nodes"]
 
 
+@pytest.mark.parametrize("pooling", [None, "learn", "learninv"])
+@pytest.mark.parametrize("M", [6, 9])
+def test_batch_node_conflicts_match_oracle(wb, pooling, M):
+    """conflicts="node" (jssp/models/gnn_dgl.py:288-335): machine nodes after the pool nodes, self loops, task ->
+    machine, machine -> task (ascending affected task order), machine -> pool for "learn"."""
+    from oracle import batch_oracle
+    from wheatley_b200.batch import jssp_batch_on_device
+    rng = np.random.default_rng(100 + M + len(str(pooling)))
+    feat, ei, nn, ne = _random_obs(rng, B=4, max_nodes=70, F=9, n_mach=6, p_unaffected=0.3)
+    ref = batch_oracle.jssp_batch(feat, ei, nn, ne, conflicts="node")
+    ref = batch_oracle.jssp_add_pool_and_machine_nodes(ref, pooling, "node", max_n_machines=M)
+    dev = jssp_batch_on_device(_obs_t(feat, ei, nn, ne), "cuda:0", conflicts="node", graph_pooling=pooling,
+                               max_n_machines=M)
+    _same(dev, ref["src"], ref["dst"], ref["type"], ref["feat"])
+    assert np.array_equal(dev["machinenodes"].cpu().numpy(), ref["machinenodes"])
+    assert dev["n_nodes"] == ref["feat"].shape[0]
+    with pytest.raises(wb.B200GatError):
+        jssp_batch_on_device(_obs_t(feat, ei, nn, ne), "cuda:0", conflicts="node", graph_pooling=pooling,
+                             max_n_machines=3)
+
+
 def test_batch_edge_cases(wb):
     from oracle import batch_oracle
     from wheatley_b200.batch import jssp_batch_on_device
@@ -99,8 +120,8 @@ def test_batch_edge_cases(wb):
                                graph_pooling=None)
     _same(dev, ref["src"], ref["dst"], ref["type"], ref["feat"])
     assert dev["n_edges"] == 2 * 47 + 300 * 299 + 299 * 298 + 599
-    with pytest.raises(NotImplementedError):
-        jssp_batch_on_device(_obs_t(feat, ei, [300, 299], [40, 7]), "cuda:0", conflicts="node")
+    with pytest.raises(ValueError):
+        jssp_batch_on_device(_obs_t(feat, ei, [300, 299], [40, 7]), "cuda:0", conflicts="node")     # no max_n_machines
     with pytest.raises(wb.B200GatError):
         jssp_batch_on_device(_obs_t(feat, ei, [301, 299], [40, 7]), "cuda:0", conflicts="clique")
 

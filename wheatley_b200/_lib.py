@@ -94,7 +94,8 @@ class JsspObs(C.Structure):
                 ("features", C.c_void_p), ("edge_index", C.c_void_p), ("meta", C.c_void_p),
                 ("clique_conflicts", C.c_int32), ("mid_in_edges", C.c_int32), ("bidir", C.c_int32),
                 ("self_loops", C.c_int32), ("no_tct", C.c_int32), ("pooling", C.c_int32),
-                ("n_machine_ids", C.c_int32), ("n_nodes_total", C.c_int64), ("n_edges_graphs", C.c_int64)]
+                ("n_machine_ids", C.c_int32), ("n_nodes_total", C.c_int64), ("n_edges_graphs", C.c_int64),
+                ("node_conflicts", C.c_int32), ("max_n_machines", C.c_int32), ("n_affected", C.c_int64)]
 
 
 POOLING = {None: 0, "learn": 1, "learninv": 2}

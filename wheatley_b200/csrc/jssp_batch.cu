@@ -27,6 +27,8 @@ struct ObsArgs {
   const int64_t* meta;
   int clique, mid_in_edges, bidir, self_loops, no_tct, pooling, n_mid;
   int64_t N, Eg;
+  int node_mode, M;
+  int64_t A;
 };
 
 __global__ void __launch_bounds__(kThreads)
@@ -63,13 +65,14 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
   const int r0 = blockIdx.x * kRowsPerCta;
   if (r0 >= nn && !(r0 == 0)) return;                       // (an empty graph still owns its pool node)
   const int64_t ne = a.meta[2 * (a.B + 1) + g];
-  const int64_t K = a.meta[3 * (a.B + 1) + g];
+  const int64_t K = a.clique ? a.meta[3 * (a.B + 1) + g] : 0;
   const int64_t ebase = a.meta[(a.B + 1) + g];
   const int64_t clq_base = ebase + (a.bidir ? 2 : 1) * ne;
   const int64_t self_base = clq_base + K;
   const float* fg = a.features + (int64_t)g * a.max_nodes * a.F;
 
-  if (a.clique) {
+  const bool need_mid = a.clique || a.node_mode;
+  if (need_mid) {
     for (int i = t; i < a.n_mid; i += kThreads) hist[i] = 0;
     __syncthreads();
     for (int i = t; i < nn; i += kThreads) {
@@ -82,7 +85,7 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
     int part = 0;
     for (int i = t; i < r0 && i < nn; i += kThreads) {
       const int m = mid[i];
-      part += (m >= 0 && m < a.n_mid) ? hist[m] - 1 : 0;
+      part += (m >= 0 && m < a.n_mid) ? (a.clique ? hist[m] - 1 : 1) : 0;
     }
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
     if (lane == 0) red[warp] = part;
@@ -95,7 +98,7 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
         const int r = r0 + k;
         if (r < nn) {
           const int m = mid[r];
-          acc += (m >= 0 && m < a.n_mid) ? hist[m] - 1 : 0;
+          acc += (m >= 0 && m < a.n_mid) ? (a.clique ? hist[m] - 1 : 1) : 0;
         }
       }
       rowoff[kRowsPerCta] = acc;
@@ -107,6 +110,10 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
   const int64_t pool_to_node = a.Eg + a.B;                            // [N] (learninv)
   const int64_t node_to_pool = pool_to_node + (a.pooling == B200GAT_POOL_LEARNINV ? a.N : 0);
   const int64_t pool_id = a.N + g;
+  // machine-node block (conflicts == "node"), after the pool wiring
+  const int64_t mach_blk = a.pooling != B200GAT_POOL_NONE ? node_to_pool + a.N : a.Eg;
+  const int64_t MB = (int64_t)a.M * a.B;
+  const int64_t mach_node0 = a.N + (a.pooling != B200GAT_POOL_NONE ? a.B : 0) + (int64_t)g * a.M;
 
   for (int k = warp; k < kRowsPerCta; k += kThreads / 32) {
     const int r = r0 + k;
@@ -129,6 +136,18 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
           }
           pos += __popc(bal);
         }
+      }
+    }
+    if (lane == 0 && a.node_mode) {
+      const int m = mid[r];
+      if (m >= 0 && m < a.n_mid) {
+        const int64_t p = mach_blk + MB + a.meta[3 * (a.B + 1) + g] + rowoff[k];
+        src[p] = gid;
+        dst[p] = mach_node0 + m;
+        et[p] = (int64_t)m + 5;
+        src[p + a.A] = mach_node0 + m;
+        dst[p + a.A] = gid;
+        et[p + a.A] = (int64_t)m + 5 + a.M;
       }
     }
     if (lane == 0) {
@@ -167,6 +186,21 @@ k_jssp_nodes(ObsArgs a, int64_t* __restrict__ src, int64_t* __restrict__ dst, in
     }
     for (int c = t; c < a.F; c += kThreads) feat[pool_id * a.F + c] = 0.f;   // zero row (gnn_dgl.py:266-270)
   }
+  if (blockIdx.x == 0 && a.node_mode) {
+    for (int j = t; j < a.M; j += kThreads) {
+      const int64_t mn = mach_node0 + j, e = mach_blk + (int64_t)g * a.M + j;
+      src[e] = mn;
+      dst[e] = mn;
+      et[e] = 0;
+      if (a.pooling == B200GAT_POOL_LEARN) {
+        const int64_t q = mach_blk + MB + 2 * a.A + (int64_t)g * a.M + j;
+        src[q] = mn;
+        dst[q] = pool_id;
+        et[q] = 5 + 2 * (int64_t)a.M;
+      }
+    }
+    for (int i = t; i < a.M * a.F; i += kThreads) feat[mach_node0 * a.F + i] = 0.f;
+  }
 }
 
 int fill(ObsArgs& a, const b200gat_jssp_obs* o) {
@@ -180,6 +214,9 @@ int fill(ObsArgs& a, const b200gat_jssp_obs* o) {
   a.self_loops = o->self_loops != 0; a.no_tct = o->no_tct != 0; a.pooling = o->pooling;
   a.n_mid = o->n_machine_ids > 0 ? o->n_machine_ids : 0;
   a.N = o->n_nodes_total; a.Eg = o->n_edges_graphs;
+  a.node_mode = o->node_conflicts != 0; a.M = a.node_mode ? o->max_n_machines : 0; a.A = a.node_mode ? o->n_affected : 0;
+  B200_CHECK_ARG(!(a.clique && a.node_mode), "clique and node conflicts are exclusive");
+  B200_CHECK_ARG(!a.node_mode || (a.M >= a.n_mid && a.A >= 0), "machine ids exceed max_n_machines");
   return B200GAT_OK;
 }
 
@@ -193,6 +230,10 @@ extern "C" int64_t b200gat_jssp_batch_edges(const b200gat_jssp_obs* o) {
   int64_t e = o->n_edges_graphs;
   if (o->pooling != B200GAT_POOL_NONE) e += o->n_graphs + o->n_nodes_total;
   if (o->pooling == B200GAT_POOL_LEARNINV) e += o->n_nodes_total;
+  if (o->node_conflicts) {
+    const int64_t MB = (int64_t)o->max_n_machines * o->n_graphs;
+    e += MB + 2 * o->n_affected + (o->pooling == B200GAT_POOL_LEARN ? MB : 0);
+  }
   return e;
 }
 
@@ -203,7 +244,7 @@ extern "C" int b200gat_jssp_batch_build(const b200gat_jssp_obs* o, int64_t* src,
   if (rc) return rc;
   if (a.B == 0) return B200GAT_OK;
   B200_CHECK_ARG(a.features && a.meta && feat, "null pointer");
-  B200_CHECK_ARG(a.F >= 7 || !a.clique, "clique conflicts need the machine id in feature column 6");
+  B200_CHECK_ARG(a.F >= 7 || !(a.clique || a.node_mode), "conflicts need the machine id in feature column 6");
   B200_CHECK_ARG(a.F >= 5, "the feature fix-up reads columns 1 and 4");
   B200_CHECK_ARG(b200gat_jssp_batch_edges(o) == 0 || (src && dst && etype), "null edge output");
   B200_CHECK_ARG(a.max_edges == 0 || a.edge_index, "null edge_index");
@@ -214,7 +255,7 @@ extern "C" int b200gat_jssp_batch_build(const b200gat_jssp_obs* o, int64_t* src,
     k_jssp_prec<<<grid, kThreads, 0, st>>>(a, src, dst, etype);
     B200_CHECK_LAUNCH("k_jssp_prec");
   }
-  const size_t smem = sizeof(int) * ((size_t)(a.clique ? a.max_nodes + a.n_mid : 0) + kRowsPerCta + 1);
+  const size_t smem = sizeof(int) * ((size_t)((a.clique || a.node_mode) ? a.max_nodes + a.n_mid : 0) + kRowsPerCta + 1);
   if (smem > 200 * 1024) {
     set_error("b200gat_jssp_batch_build: %d nodes per graph + %d machine ids do not fit in shared memory",
               a.max_nodes, a.n_mid);
