@@ -183,6 +183,13 @@ int b200gat_hub_list(const int32_t* ptr, int64_t n_nodes, int32_t hub_degree, in
 /* out[i] = table[idx[i]] for int32 (permute per-edge attributes into dst-sorted order). */
 int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
                        void* stream);
+/* Same, and range[0] = min, range[1] = max of the gathered values (device int32[2]; n == 0 leaves
+ * INT_MAX / INT_MIN).  The host mirror checks edge types against the rows of the edge-type table before the
+ * first layer uses them: the reference's nn.Embedding raises IndexError on an out-of-range type
+ * (jssp/models/gnn_dgl.py:364, psp/models/edge_embedder.py:131), the kernels would read / accumulate out of
+ * bounds. */
+int b200gat_gather_i32_range(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
+                             int32_t* range, void* stream);
 /* out[i, :] = table[idx[i], :] for fp32 rows of `width` elements (per-edge attributes). */
 int b200gat_gather_rows_f32(const float* table, const int32_t* idx, int64_t n, int32_t width,
                             float* out, void* stream);

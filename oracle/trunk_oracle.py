@@ -45,12 +45,16 @@ class OracleMLP(nn.Module):
 
 
 class OracleGnnDGL(nn.Module):
-    """gat/gatv2 branch of jssp/models/gnn_dgl.py with residual=True, normalize=False."""
+    """gat/gatv2 branch of jssp/models/gnn_dgl.py with residual=True, normalize=False.  Pinned by
+    tests/golden/gnn_dgl.npz: the reference's own ``GnnDGL.forward`` (:245-431) executed on the DGL shim
+    (tests/golden/make_golden.py::golden_gnn_dgl)."""
 
     def __init__(self, input_dim, graph_pooling, max_n_nodes, max_n_machines, n_mlp_layers, n_layers,
-                 hidden_dim, activation, n_heads, n_edge_types=6):
+                 hidden_dim, activation, n_heads, n_edge_types=6, conflicts="clique", checkpoint=False):
         super().__init__()
+        self.checkpoint = checkpoint        # recompute each layer in backward (one layer's [E, H*D] tensors live)
         self.graph_pooling, self.max_n_nodes, self.n_layers = graph_pooling, max_n_nodes, n_layers
+        self.conflicts, self.max_n_machines = conflicts, max_n_machines
         self.node_embedder = nn.Embedding(1 + max_n_machines, input_dim)
         self.edge_embedder = nn.ModuleList([nn.Embedding(n_edge_types, hidden_dim)])
         self.embedder = OracleMLP(n_mlp_layers, input_dim, hidden_dim, hidden_dim, False, activation)
@@ -63,24 +67,49 @@ class OracleGnnDGL(nn.Module):
                                        hidden_dim, False, activation))
 
     def forward(self, src, dst, etype, feat, batch_size, n_nodes, num_task_nodes):
+        """``n_nodes`` = nodes per graph (``num_task_nodes / batch_size``, agent_observation.py:47-51)."""
         features = feat
+        node_offset = num_task_nodes
+        if self.graph_pooling in ("learn", "learninv"):
+            node_offset += batch_size
         if self.graph_pooling == "learn":                                   # gnn_dgl.py:341-344
             features = features.clone()
             features[num_task_nodes: num_task_nodes + batch_size] = self.node_embedder.weight[0]
+        if self.conflicts == "node":                                        # :346-351
+            M = self.max_n_machines
+            features = features.clone()
+            features[node_offset: node_offset + M * batch_size] = self.node_embedder(
+                torch.arange(M).repeat(batch_size) + 1)
         fl = [features]
         features = self.embedder(features)                                  # :355
         fl.append(features)
         emb = self.edge_embedder[0](etype)                                  # :364
         for l in range(self.n_layers):
-            h, _ = self.features_extractors[l](src, dst, features, emb)     # :374-376
-            features = self.mlps[l](h.flatten(start_dim=-2, end_dim=-1))    # :377
+            def layer_fn(features, emb, l=l):
+                h, _ = self.features_extractors[l](src, dst, features, emb)     # :374-376
+                return self.mlps[l](h.flatten(start_dim=-2, end_dim=-1))        # :377
+            if self.checkpoint and torch.is_grad_enabled():
+                from torch.utils.checkpoint import checkpoint
+                features = checkpoint(layer_fn, features, emb, use_reentrant=False)
+            else:
+                features = layer_fn(features, emb)
             features = features + fl[-1]                                    # :395-396
             fl.append(features)
         features = torch.cat(fl, dim=1)                                     # :401
-        node_features = features[:num_task_nodes].reshape(batch_size, n_nodes, -1)
-        graph_embedding = features[num_task_nodes: num_task_nodes + batch_size]   # 'learn' pooling :415
-        node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - n_nodes))
+        node_features = features[:num_task_nodes].reshape(batch_size, n_nodes, -1)      # :402-405
+        if self.graph_pooling == "max":                                     # :407-409
+            graph_embedding = node_features.max(dim=1)[0]
+        elif self.graph_pooling == "avg":                                   # :410-412
+            graph_embedding = node_features.mean(dim=1)
+        else:                                                               # 'learn' / 'learninv' :413-415
+            graph_embedding = features[num_task_nodes: num_task_nodes + batch_size]
+        node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - n_nodes))   # :420-425
         return node_features, graph_embedding.reshape(batch_size, 1, -1)
+
+    def forward_cat(self, *a):
+        """The reference's return value (:427-431): node features next to the repeated graph embedding."""
+        node_features, graph_embedding = self.forward(*a)
+        return torch.cat((node_features, graph_embedding.expand(node_features.shape)), dim=2)
 
 
 class OracleAgent(nn.Module):

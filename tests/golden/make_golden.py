@@ -13,6 +13,8 @@ What is executed verbatim from the reference tree:
   * psp/models/edge_embedder.py PspEdgeEmbedder.forward
   * jssp/utils/utils.py   compute_conflicts_cliques
   * jssp/models/agent_observation.py AgentObservation.from_gym_observation (DGL shim)
+  * jssp/models/gnn_dgl.py GnnDGL.forward (DGL shim, dgl.nn.EGATConv := generic/eegatconv.py EEGATConv)
+  * psp/graph/graph_conv.py GraphConv.forward / forward_nog (PyG shim; GATv2Conv itself is a restatement)
 
 Outputs: small .npz files (float64 for the layers so that the comparison with
 the oracle is tight; float32 where the reference module is float32-only).
@@ -351,6 +353,115 @@ def golden_jssp_batch(fname: str, seed: int):
     np.savez_compressed(os.path.join(HERE, fname), **d)
 
 
+# ---------------------------------------------------------------- trunk: jssp/models/gnn_dgl.py GnnDGL.forward
+def _install_dgl_trunk_shim():
+    """What ``jssp/models/gnn_dgl.py`` needs on top of the batching shim: ``dgl.nn.EGATConv`` (:= the in-repo
+    restatement ``generic/eegatconv.py`` EEGATConv with ``edge_scoring=False``, SURVEY F3: same math as DGL's
+    layer), ``DGLGraph.add_nodes`` (published DGL semantics: new nodes get ids after the existing ones, the
+    given node features are appended, missing ones zero-filled), and placeholders for the layer classes the
+    file imports but the gat/gatv2 branch never instantiates."""
+    import dgl
+    from generic.eegatconv import EEGATConv
+
+    class EGATConv(EEGATConv):
+        def __init__(self, in_node_feats, in_edge_feats, out_node_feats, out_edge_feats, num_heads, bias=True):
+            super().__init__(in_node_feats, in_edge_feats, out_node_feats, out_edge_feats, num_heads, bias=bias,
+                             edge_scoring=False)
+
+        def forward(self, graph, nfeats, efeats, edge_weight=None, get_attention=False):
+            return super().forward(graph, nfeats, efeats, None, edge_weight, get_attention)
+
+    def add_nodes(self, num, data=None):
+        self._n += num
+        for k in list(self.ndata.keys()):
+            new = data[k] if (data is not None and k in data) else torch.zeros(
+                (num,) + tuple(self.ndata[k].shape[1:]), dtype=self.ndata[k].dtype)
+            self.ndata[k] = torch.cat([self.ndata[k], torch.as_tensor(new).to(self.ndata[k].dtype)])
+
+    dgl.DGLGraph.add_nodes = add_nodes
+    dgl.nn.EGATConv = EGATConv
+    for name in ("DGNConv", "GCN2Conv", "GINEConv", "PNAConv"):
+        setattr(dgl.nn, name, type(name, (), {}))
+    dgl.LaplacianPE = type("LaplacianPE", (), {})
+
+
+def golden_gnn_dgl(fname: str, seed: int):
+    """The reference's own ``GnnDGL.forward`` (jssp/models/gnn_dgl.py:245-431) executed on the padded gym
+    observation: batching, pool / machine node wiring, embedder, L x (EGATConv -> MLP, residual), concat, pool
+    slice, pad, final cat.  float32 (the reference module's dtype)."""
+    _install_dgl_batching_shim()
+    _install_dgl_trunk_shim()
+    from jssp.models.gnn_dgl import GnnDGL
+
+    d = {}
+    n_j, n_m, B, Fdim, Hd, H, L = 4, 3, 3, 10, 8, 2, 2
+    for tag, conflicts, pooling, mie, pad_nodes in [("clique", "clique", "learn", False, 0),
+                                                   ("cliquepad", "clique", "learn", True, 3),
+                                                   ("node", "node", "learn", True, 0),
+                                                   ("att_max", "att", "max", False, 2)]:
+        obs = synthetic_jssp_obs(n_j, n_m, B, seed, scheduled_frac=0.5, feat_dim=Fdim, pad_nodes=2, pad_edges=3)
+        torch.manual_seed(seed)
+        gnn = GnnDGL(Fdim, "gatv2", pooling, False, n_j * n_m + pad_nodes, n_m, 3, L, Hd, "gelu", H,
+                     residual=True, normalize=False, conflicts=conflicts, no_tct=False, mid_in_edges=mie)
+        with torch.no_grad():
+            for fe in gnn.features_extractors:
+                fe.bias.copy_(torch.randn(fe.bias.shape) * 0.1)
+        ret = gnn(obs)
+        gen = torch.Generator().manual_seed(seed + 1)
+        R = torch.randn(ret.shape, generator=gen)
+        names = [k for k, _ in gnn.named_parameters()]
+        params = [p for _, p in gnn.named_parameters()]
+        gr = grads_of((ret * R).sum(), params)
+        for k, v in obs.items():
+            d[f"{tag}.obs.{k}"] = np_(v)
+        d[f"{tag}.ret"], d[f"{tag}.R"] = np_(ret), np_(R)
+        d[f"{tag}.cfg"] = np.array([n_j, n_m, B, Fdim, Hd, H, L, n_j * n_m + pad_nodes, int(mie)])
+        d[f"{tag}.conflicts"], d[f"{tag}.pooling"] = np.array(conflicts), np.array(pooling)
+        for k, p, g_ in zip(names, params, gr):
+            d[f"{tag}.p.{k}"] = np_(p)
+            d[f"{tag}.g.{k}"] = np_(g_)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
+# ---------------------------------------------------------------- a2: GraphConv -> PyG GATv2Conv
+def golden_gatv2(fname: str, seed: int):
+    """``psp/graph/graph_conv.py`` GraphConv(pyg=True) executed verbatim: its constructor call (:33-40), ``forward``
+    (:51-53) and ``forward_nog`` (:59-60) - on ``oracle/shims/torch_geometric`` GATv2Conv, a RESTATEMENT of the
+    third-party layer (parity unpinned for the layer itself, see the class docstring)."""
+    from psp.graph.graph_conv import GraphConv
+
+    gen = torch.Generator().manual_seed(seed)
+    N, E0, Fin, C, H = 12, 36, 6, 5, 3
+    src, dst = rand_graph(gen, N, E0, self_loops=False)
+    dst[dst == 7] = 3                                   # node 7 has no in-edge: output = bias
+    ei = torch.stack([src, dst])
+    torch.manual_seed(seed)
+    layer = GraphConv(Fin, C, H, pyg=True).double()
+    assert layer.gatv3 is False
+    with torch.no_grad():
+        for p_ in (layer.conv.lin_l.bias, layer.conv.lin_r.bias, layer.conv.bias):
+            p_.copy_(torch.randn(p_.shape, generator=gen, dtype=torch.float64) * 0.1)
+    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64, requires_grad=True)
+    ea = torch.randn(E0, Fin, generator=gen, dtype=torch.float64, requires_grad=True)
+    g = types.SimpleNamespace(edge_index=ei)
+    out, none_ = layer(g, x, ea)
+    assert none_ is None
+    out_nog, _ = layer.forward_nog(x, ei, ea)
+    assert torch.equal(out, out_nog)
+    out_noedge, _ = layer.forward_nog(x, ei, None)      # psp/models/gnn_hier.py:69,115
+    _, (_, alpha) = layer.conv(x, ei, ea, return_attention_weights=True)
+    R = torch.randn(out.shape, generator=gen, dtype=torch.float64)
+    names = [k for k, _ in layer.named_parameters()]
+    params = [p_ for _, p_ in layer.named_parameters()]
+    gr = grads_of((out * R).sum(), params + [x, ea])
+    d = dict(edge_index=np_(ei), x=np_(x), ea=np_(ea), R=np_(R), out=np_(out), out_noedge=np_(out_noedge),
+             alpha=np_(alpha), gx=np_(gr[-2]), gea=np_(gr[-1]), heads=np.int64(H))
+    for k, p_, gp in zip(names, params, gr):
+        d["p." + k] = np_(p_)
+        d["g." + k] = np_(gp)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
 if __name__ == "__main__":
     golden_eegat(False, "eegat.npz", 11)
     golden_eegat(True, "eegat_edge_scoring.npz", 12)
@@ -359,4 +470,6 @@ if __name__ == "__main__":
     golden_mlp("mlp.npz", 15)
     golden_edge_embedder("edge_embedder.npz", 16)
     golden_jssp_batch("jssp_batch.npz", 17)
+    golden_gnn_dgl("gnn_dgl.npz", 18)
+    golden_gatv2("gatv2.npz", 19)
     print("golden fixtures written to", HERE)

@@ -201,7 +201,9 @@ def _egat_case(wb, hb, H, D, gen, no_grad=False, typed=True):
 
 
 @pytest.mark.parametrize("n_j,n_m,batch,progress", [(10, 10, 3, 0.5), (15, 15, 2, 0.0), (30, 20, 1, 0.5),
-                                                    (20, 5, 2, 1.0), (9, 3, 4, 0.0)])
+                                                    (20, 5, 2, 1.0), (9, 3, 4, 0.0),
+                                                    (100, 20, 1, 0.0),     # the bench regime: 100-member blocks
+                                                    (128, 2, 1, 0.3), (77, 3, 2, 1.0)])
 def test_egat_clique_path_matches_oracle(wb, n_j, n_m, batch, progress):
     from wheatley_b200.workload import jssp_batch
     hb = jssp_batch(n_j, n_m, batch, seed0=11, progress=progress)

@@ -156,3 +156,57 @@ def test_jssp_batch_matches_reference(golden_dir):
         assert np.array_equal(b["feat"], g[f"{tag}.feat"]), tag
         assert np.array_equal(b["batch_num_nodes"], g[f"{tag}.bnn"])
         assert np.array_equal(b["batch_num_edges"], g[f"{tag}.bne"])
+
+
+@pytest.mark.parametrize("tag", ["clique", "cliquepad", "node", "att_max"])
+def test_trunk_oracle_matches_reference_gnn_dgl(golden_dir, tag):
+    """oracle.trunk_oracle.OracleGnnDGL + oracle.batch_oracle against the reference's own GnnDGL.forward
+    (jssp/models/gnn_dgl.py:245-431 executed on the DGL shim): output and every parameter gradient."""
+    from oracle import trunk_oracle
+    g = load(golden_dir, "gnn_dgl.npz")
+    n_j, n_m, B, Fdim, Hd, H, L, max_n_nodes, mie = (int(v) for v in g[f"{tag}.cfg"])
+    conflicts, pooling = str(g[f"{tag}.conflicts"]), str(g[f"{tag}.pooling"])
+    obs = {k: g[f"{tag}.obs.{k}"] for k in ("features", "edge_index", "n_nodes", "n_edges")}
+    b = batch_oracle.jssp_batch(obs["features"], obs["edge_index"], obs["n_nodes"], obs["n_edges"],
+                                conflicts=conflicts, mid_in_edges=bool(mie))
+    b = batch_oracle.jssp_add_pool_and_machine_nodes(b, pooling, conflicts, n_m)
+    P = {k[len(tag) + 3:]: T(g[k]) for k in g.files if k.startswith(tag + ".p.")}
+    gnn = trunk_oracle.OracleGnnDGL(Fdim, pooling, max_n_nodes, n_m, 3, L, Hd, "gelu", H,
+                                    n_edge_types=P["edge_embedder.0.weight"].shape[0], conflicts=conflicts)
+    gnn.load_state_dict(P)
+    NT = int(b["num_task_nodes"])
+    ret = gnn.forward_cat(T(b["src"]), T(b["dst"]), T(b["type"]), T(b["feat"]), B, NT // B, NT)
+    np.testing.assert_allclose(ret.detach().numpy(), g[f"{tag}.ret"], rtol=2e-5, atol=2e-6)
+    (ret * T(g[f"{tag}.R"])).sum().backward()
+    for k, p in gnn.named_parameters():
+        ref = g[f"{tag}.g.{k}"]
+        got = np.zeros_like(ref) if p.grad is None else p.grad.numpy()
+        np.testing.assert_allclose(got, ref, rtol=2e-4, atol=2e-5 * max(1.0, np.abs(ref).max()), err_msg=k)
+
+
+def test_gatv2_oracle_matches_graphconv_golden(golden_dir):
+    """oracle.gat_oracle.gatv2_forward against psp/graph/graph_conv.py GraphConv(pyg=True) executed on the PyG
+    shim (gatv2.npz).  The shim's GATv2Conv is itself a restatement of the third-party layer: this pins the
+    adapter (constructor arguments, return conventions, parameter names) and keeps the two restatements honest
+    against each other; the layer's parity stays "unpinned (third-party layer)"."""
+    g = load(golden_dir, "gatv2.npz")
+    P = {k[2:]: T(g[k]).requires_grad_(True) for k in g.files if k.startswith("p.")}
+    assert set(P) == {"conv.att", "conv.bias", "conv.lin_l.weight", "conv.lin_l.bias", "conv.lin_r.weight",
+                      "conv.lin_r.bias", "conv.lin_edge.weight"}
+    x = T(g["x"]).requires_grad_(True)
+    ea = T(g["ea"]).requires_grad_(True)
+    ei = T(g["edge_index"])
+    args_ = (P["conv.lin_l.weight"], P["conv.lin_l.bias"], P["conv.lin_r.weight"], P["conv.lin_r.bias"],
+             P["conv.lin_edge.weight"], P["conv.att"], P["conv.bias"])
+    out, alpha = gat_oracle.gatv2_forward(x, ei, ea, *args_)
+    np.testing.assert_allclose(out.detach().numpy(), g["out"], rtol=1e-12, atol=1e-13)
+    np.testing.assert_allclose(alpha.detach().numpy(), g["alpha"], rtol=1e-12, atol=1e-13)
+    np.testing.assert_allclose(out[7].detach().numpy(), g["p.conv.bias"], rtol=0, atol=0)   # isolated target
+    out_ne, _ = gat_oracle.gatv2_forward(x, ei, None, *args_)
+    np.testing.assert_allclose(out_ne.detach().numpy(), g["out_noedge"], rtol=1e-12, atol=1e-13)
+    names = list(P)
+    grads = torch.autograd.grad((out * T(g["R"])).sum(), [P[k] for k in names] + [x, ea])
+    for k, gr in zip(names, grads):
+        np.testing.assert_allclose(gr.numpy(), g["g." + k], rtol=1e-10, atol=1e-12, err_msg=k)
+    np.testing.assert_allclose(grads[-2].numpy(), g["gx"], rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(grads[-1].numpy(), g["gea"], rtol=1e-10, atol=1e-12)

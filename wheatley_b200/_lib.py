@@ -20,7 +20,7 @@ SYMBOLS = (
     "b200gat_last_error", "b200gat_version", "b200gat_launch_count", "b200gat_timing_enable",
     "b200gat_timing_read", "b200gat_plan_scratch_elems", "b200gat_plan_build",
     "b200gat_node_order_scratch_elems", "b200gat_node_order", "b200gat_hub_list",
-    "b200gat_gather_i32", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
+    "b200gat_gather_i32", "b200gat_gather_i32_range", "b200gat_gather_rows_f32", "b200gat_narrow_i64", "b200gat_conv_fwd", "b200gat_conv_bwd",
     "b200gat_attention", "b200gat_edge_out", "b200gat_mask_head_fwd", "b200gat_mask_head_bwd",
     "b200gat_clique_scratch_elems", "b200gat_clique_build", "b200gat_conv_uses_cliques",
     "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
@@ -137,6 +137,7 @@ def _load():
     lib.b200gat_node_order.argtypes = [vp, vp, i64, vp, vp, vp]
     lib.b200gat_hub_list.argtypes = [vp, i64, i32, vp, vp, vp]
     lib.b200gat_gather_i32.argtypes = [vp, vp, i64, vp, vp]
+    lib.b200gat_gather_i32_range.argtypes = [vp, vp, i64, vp, vp, vp]
     lib.b200gat_gather_rows_f32.argtypes = [vp, vp, i64, i32, vp, vp]
     lib.b200gat_narrow_i64.argtypes = [vp, i64, vp, vp]
     gp, ap, ep = C.POINTER(Graph), C.POINTER(Attn), C.POINTER(EdgeFeats)

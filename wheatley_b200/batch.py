@@ -114,7 +114,16 @@ def jssp_batch_from_observation(obs, device, max_n_nodes, conflicts="att", graph
     ``defer=True`` leaves the plan's host counts pending (``JsspBatch.plan.finish()``, used by the prefetcher)."""
     from .gnn_dgl import JsspBatch
     d = jssp_batch_on_device(obs, device, conflicts, graph_pooling, **kw)
+    bnn = d["batch_num_nodes"]
+    # nodes per graph = num_nodes / batch_size (jssp/models/agent_observation.py:47-51); the trunk reshapes the task
+    # rows to [B, n_nodes, F] (gnn_dgl.py:402-405: equal-sized graphs) and THEN pads to max_n_nodes (:420-425)
+    if len(set(bnn)) > 1:
+        raise _lib.B200GatError(f"graphs of one batch must have the same number of nodes (got {sorted(set(bnn))}): "
+                                "GnnDGL reshapes the node rows to [B, n_nodes, F] (jssp/models/gnn_dgl.py:402-405)")
+    n_nodes = int(bnn[0]) if bnn else 0
+    if n_nodes > max_n_nodes:
+        raise _lib.B200GatError(f"graphs have {n_nodes} nodes, max_n_nodes is {max_n_nodes}")
     plan = GraphPlan(d["src"], d["dst"], d["n_nodes"])
     plan.prepare(d["etype"], defer=defer)
-    return JsspBatch(plan, d["etype"], d["feat"], len(d["batch_num_nodes"]), max_n_nodes, d["n_task_nodes"],
+    return JsspBatch(plan, d["etype"], d["feat"], len(bnn), n_nodes, d["n_task_nodes"],
                      poolnodes=d["poolnodes"], machinenodes=d["machinenodes"], prepare=not defer), d

@@ -260,6 +260,30 @@ __global__ void k_gather_i32(const int32_t* __restrict__ table, const int32_t* _
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) out[i] = table[idx[i]];
 }
+// gather + range of the gathered values: range[0] = min, range[1] = max (caller initialises INT_MAX / INT_MIN)
+__global__ void k_gather_i32_range(const int32_t* __restrict__ table, const int32_t* __restrict__ idx,
+                                   int64_t n, int32_t* __restrict__ out, int32_t* __restrict__ range) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int lo = 0x7fffffff, hi = (int)0x80000000;
+  if (i < n) {
+    const int v = table[idx[i]];
+    out[i] = v;
+    lo = v; hi = v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0 && lo <= hi) {
+    atomicMin(range, lo);
+    atomicMax(range + 1, hi);
+  }
+}
+__global__ void k_init_range(int32_t* range) {
+  range[0] = 0x7fffffff;
+  range[1] = (int)0x80000000;
+}
 __global__ void k_gather_rows_f32(const float* __restrict__ table, const int32_t* __restrict__ idx,
                                   int64_t n, int width, float* __restrict__ out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -414,6 +438,21 @@ extern "C" int b200gat_gather_i32(const int32_t* table, const int32_t* idx, int6
   B200_CHECK_ARG(table && idx && out, "null pointer");
   k_gather_i32<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, out);
   B200_CHECK_LAUNCH("k_gather_i32");
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_gather_i32_range(const int32_t* table, const int32_t* idx, int64_t n, int32_t* out,
+                                        int32_t* range, void* stream) {
+  B200_CHECK_ARG(n >= 0, "negative size");
+  B200_CHECK_ARG(range, "null range");
+  k_init_range<<<1, 1, 0, (cudaStream_t)stream>>>(range);
+  if (n == 0) {
+    B200_CHECK_LAUNCH("k_init_range");
+    return B200GAT_OK;
+  }
+  B200_CHECK_ARG(table && idx && out, "null pointer");
+  k_gather_i32_range<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, out, range);
+  B200_CHECK_LAUNCHES("k_gather_i32_range", 2);
   return B200GAT_OK;
 }
 

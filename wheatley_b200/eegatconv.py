@@ -52,7 +52,7 @@ def resolve_plan(graph):
     if isinstance(plan, GraphPlan):
         return plan
     cached = getattr(graph, "_b200gat_plan", None)
-    if cached is not None:
+    if isinstance(cached, GraphPlan):
         return cached
     if isinstance(graph, tuple):
         src, dst, n = graph

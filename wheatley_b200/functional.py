@@ -3,7 +3,7 @@ called from).  No PyTorch fallback exists: CPU tensors raise."""
 import torch
 
 from . import _lib
-from .plan import GraphPlan
+from .plan import GraphPlan, check_edge_types
 
 
 class EdgeFeatures:
@@ -85,6 +85,8 @@ class _FusedGATConv(torch.autograd.Function):
         if e_affine is not None:
             mode = _lib.EDGE_AFFINE
         n_attr = 0 if e_affine_c is None else e_affine_c.shape[0]
+        if e_table_c is not None:           # IndexError like nn.Embedding, instead of an out-of-bounds gather
+            check_edge_types(etype_sorted, e_table_c.shape[0])
         assert Pi.shape == (N, HD) and Pj.shape == (N, HD) and Vt.shape == (N, HD)
         out = torch.empty((N, HD), dtype=torch.float32, device=Pi.device)
         s = torch.empty((E, H), dtype=torch.float32, device=Pi.device)

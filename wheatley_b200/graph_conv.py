@@ -131,13 +131,14 @@ class GATv3Conv(nn.Module):
         self._loop_cache = None
 
     def _with_self_loops(self, edge_index, n):
-        tag = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape), n)
-        if self._loop_cache is not None and self._loop_cache[0] == tag:
+        tag = (edge_index._version, tuple(edge_index.shape), n)
+        if (self._loop_cache is not None and self._loop_cache[2] is edge_index
+                and self._loop_cache[0] == tag):            # the same tensor object, unchanged
             return self._loop_cache[1]
         keep = edge_index[0] != edge_index[1]            # remove_self_loops keeps edge order
         loop = torch.arange(n, dtype=edge_index.dtype, device=edge_index.device)
         ei = torch.cat([edge_index[:, keep], torch.stack([loop, loop])], dim=1)   # add_self_loops appends
-        self._loop_cache = (tag, ei)
+        self._loop_cache = (tag, ei, edge_index)
         return ei
 
     def forward(self, x, edge_index, edge_attr=None, *, return_attention_weights=None):

@@ -88,7 +88,10 @@ class CliqueView:
             self.r_aux = _orders_and_hubs(r_in_ptr, r_in_src, r_out_ptr, r_out_dst, N, dev)
             # the one device->host copy (it also carries the plan's own counts if they were not read yet)
             first = plan._stats_host is None
-            dev_counts = torch.cat([counts, self.r_aux[4]] + ([plan.stats, plan.n_hub] if first else []))
+            rng = getattr(etype_sorted, "_b200_range_dev", None) if etype_sorted is not None else None
+            self._has_range = rng is not None and getattr(etype_sorted, "_b200_range_host", None) is None
+            dev_counts = torch.cat([counts, self.r_aux[4]] + ([plan.stats, plan.n_hub] if first else [])
+                                   + ([rng] if self._has_range else []))
             if defer:       # asynchronous copy into pinned memory; finish() waits for the event, not the stream
                 host_counts = torch.empty(dev_counts.numel(), dtype=torch.int32, pin_memory=True)
                 host_counts.copy_(dev_counts, non_blocking=True)
@@ -112,6 +115,8 @@ class CliqueView:
         N, dev = plan.n_nodes, plan.device
         if first and plan._stats_host is None:
             plan._set_stats_host(host[10:16])
+        if getattr(self, "_has_range", False):        # the edge types' (min, max): last two ints of the copy
+            self.etype_sorted._b200_range_host = (int(host[-2]), int(host[-1]))
         self.n_blocks, self.max_block, self.n_res_edges, self.n_members, self.s_elems = host[:5]
         n_hub_dst = host[8]
         if self.n_blocks == 0:
@@ -189,12 +194,15 @@ class GraphPlan:
         """Dense clique blocks for one edge typing (``None`` = untyped), built once and cached.
         One small device->host copy (block counts) per (plan, typing); ``defer=True`` only queues the build and
         the copy (``CliqueView.finish`` / ``GraphPlan.finish`` complete it)."""
-        key = None if etype_sorted is None else (etype_sorted.data_ptr(), etype_sorted._version)
+        key = None if etype_sorted is None else id(etype_sorted)
         view = self._clique_views.get(key)
+        if view is not None and view.etype_sorted is not etype_sorted:
+            view = None                      # id() of a dead tensor re-used
         if view is None:
             if os.environ.get("WHEATLEY_B200_CLIQUES", "1") == "0":
                 view = CliqueView.__new__(CliqueView)
                 view.plan, view.c, view.n_blocks, view.s_elems, view._pending = self, self.c, 0, 0, None
+                view.etype_sorted = etype_sorted
             else:
                 view = CliqueView(self, etype_sorted, defer=defer)
             self._clique_views[key] = view
@@ -256,14 +264,27 @@ class GraphPlan:
         if bad:
             raise _lib.B200GatError(f"{bad} edges have an endpoint outside [0, {self.n_nodes})")
 
+    def _cache_get(self, key, src):
+        """Cache entries hold the SOURCE tensor: a hit needs the same tensor object at the same version (a
+        ``data_ptr`` alone is not an identity - the caching allocator hands a freed block to the next tensor of
+        that size)."""
+        hit = self._sorted_cache.get(key)
+        if hit is not None and (src is None or (hit[0] is src and hit[1] == src._version)):
+            return hit[2]
+        return None
+
     def sort_edge_ints(self, per_edge: torch.Tensor, key=None) -> torch.Tensor:
         """Permute an int per-edge attribute (e.g. edge type) from the original edge order
-        into the plan's destination-sorted order (int32)."""
-        key = key if key is not None else (per_edge.data_ptr(), per_edge._version)
-        hit = self._sorted_cache.get(key)
+        into the plan's destination-sorted order (int32).  The result carries the device-side range of its
+        values (``_b200_range_dev`` int32[2] = min, max), read by :func:`edge_type_range`."""
+        explicit = key is not None
+        key = key if explicit else ("ints", id(per_edge))
+        hit = self._cache_get(key, None if explicit else per_edge)
         if hit is not None:
             return hit
         t = per_edge
+        if t.numel() != self.n_edges:
+            raise _lib.B200GatError(f"per-edge attribute has {t.numel()} entries, the graph {self.n_edges} edges")
         if t.dtype != torch.int32:
             t32 = torch.empty(t.numel(), dtype=torch.int32, device=t.device)
             if t.dtype == torch.int64 and t.is_contiguous() and t.data_ptr() % 16 == 0:
@@ -273,17 +294,19 @@ class GraphPlan:
                 t32.copy_(t)
             t = t32
         out = torch.empty(self.n_edges, dtype=torch.int32, device=self.device)
-        _lib.check(_lib.lib.b200gat_gather_i32(_lib.ptr(t.contiguous()), _lib.ptr(self.in_eid),
-                                               self.n_edges, _lib.ptr(out), _lib.stream_ptr()),
-                   "b200gat_gather_i32")
-        self._sorted_cache[key] = out
+        rng = torch.empty(2, dtype=torch.int32, device=self.device)
+        _lib.check(_lib.lib.b200gat_gather_i32_range(_lib.ptr(t.contiguous()), _lib.ptr(self.in_eid),
+                                                     self.n_edges, _lib.ptr(out), _lib.ptr(rng),
+                                                     _lib.stream_ptr()), "b200gat_gather_i32_range")
+        out._b200_range_dev, out._b200_range_host = rng, None
+        self._sorted_cache[key] = (per_edge, per_edge._version, out)
         return out
-
 
     def sort_edge_rows(self, per_edge: torch.Tensor, key=None) -> torch.Tensor:
         """Permute fp32 per-edge attribute rows ``[E, K]`` into destination-sorted order."""
-        key = key if key is not None else ("rows", per_edge.data_ptr(), per_edge._version)
-        hit = self._sorted_cache.get(key)
+        explicit = key is not None
+        key = key if explicit else ("rows", id(per_edge))
+        hit = self._cache_get(key, None if explicit else per_edge)
         if hit is not None:
             return hit
         t = per_edge.detach()
@@ -294,21 +317,47 @@ class GraphPlan:
         _lib.check(_lib.lib.b200gat_gather_rows_f32(_lib.ptr(t), _lib.ptr(self.in_eid), self.n_edges,
                                                     t.shape[1], _lib.ptr(out), _lib.stream_ptr()),
                    "b200gat_gather_rows_f32")
-        self._sorted_cache[key] = out
+        self._sorted_cache[key] = (per_edge, per_edge._version, out)
         return out
+
+
+def edge_type_range(etype_sorted: torch.Tensor):
+    """``(min, max)`` of a tensor produced by :meth:`GraphPlan.sort_edge_ints` (host ints).  The first call reads
+    two ints back from the device (``GraphPlan.prepare`` folds that read into the plan's one count copy); the
+    result is cached on the tensor."""
+    host = getattr(etype_sorted, "_b200_range_host", None)
+    if host is None:
+        dev = getattr(etype_sorted, "_b200_range_dev", None)
+        if dev is None:
+            lo, hi = (int(etype_sorted.min()), int(etype_sorted.max())) if etype_sorted.numel() else (0, -1)
+        else:
+            lo, hi = dev.tolist()
+        host = etype_sorted._b200_range_host = (int(lo), int(hi))
+    return host
+
+
+def check_edge_types(etype_sorted: torch.Tensor, n_types: int):
+    """The reference's ``nn.Embedding`` raises IndexError on an edge type outside the table
+    (jssp/models/gnn_dgl.py:364, psp/models/edge_embedder.py:131); the kernels would read - and their backward
+    accumulate - out of bounds.  Same error here, before any kernel runs."""
+    if etype_sorted is None or etype_sorted.numel() == 0:
+        return
+    lo, hi = edge_type_range(etype_sorted)
+    if lo < 0 or hi >= n_types:
+        raise IndexError(f"edge type out of range: types span [{lo}, {hi}], the edge-type table has {n_types} rows")
 
 
 def plan_for_edge_index(edge_index: torch.Tensor, n_nodes: int, holder=None) -> GraphPlan:
     """Plan cache: the plan is stored on ``holder`` (the graph object the reference passes
-    around, or the edge_index tensor itself) and reused while the tensor is unchanged."""
+    around, or the edge_index tensor itself) and reused while it is the SAME tensor object, unchanged."""
     holder = edge_index if holder is None else holder
-    tag = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape), int(n_nodes))
+    tag = (edge_index._version, tuple(edge_index.shape), int(n_nodes))
     cached = getattr(holder, "_b200gat_plan", None)
-    if cached is not None and cached[0] == tag:
-        return cached[1]
+    if cached is not None and cached[0] is edge_index and cached[1] == tag:
+        return cached[2]
     plan = GraphPlan.from_edge_index(edge_index, n_nodes)
     try:
-        holder._b200gat_plan = (tag, plan)
+        holder._b200gat_plan = (edge_index, tag, plan)
     except AttributeError:
         pass
     return plan
