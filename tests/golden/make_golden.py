@@ -15,6 +15,8 @@ What is executed verbatim from the reference tree:
   * jssp/models/agent_observation.py AgentObservation.from_gym_observation (DGL shim)
   * jssp/models/gnn_dgl.py GnnDGL.forward (DGL shim, dgl.nn.EGATConv := generic/eegatconv.py EEGATConv)
   * psp/graph/graph_conv.py GraphConv.forward / forward_nog (PyG shim; GATv2Conv itself is a restatement)
+  * psp/models/agent.py Agent._obs_as_tensor_graph / Agent.preprocess + psp/models/rewiring.py +
+    psp/models/agent_graph_observation.py (on oracle/shims/psp_graph.py, a stand-in for the HeteroData container)
 
 Outputs: small .npz files (float64 for the layers so that the comparison with
 the oracle is tight; float32 where the reference module is float32-only).
@@ -462,6 +464,135 @@ def golden_gatv2(fname: str, seed: int):
     np.savez_compressed(os.path.join(HERE, fname), **d)
 
 
+# ---------------------------------------------------------------- a5: PSP / PyG-flavour batching (Agent.preprocess)
+def _install_psp_stubs():
+    """Modules psp/models/agent.py imports that need third-party wheels absent here and are NOT on the path
+    exercised (hierarchical / TokenGT extractors, the HeteroData graph factory): empty placeholders."""
+    for name, attrs in (("psp.models.gnn_hier", ["GnnHier"]), ("generic.tokenGT", ["TokenGT"]),
+                        ("psp.graph.graph_factory", ["GraphFactory"])):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            for a in attrs:
+                setattr(m, a, type(a, (), {}))
+            sys.modules[name] = m
+
+
+def synthetic_psp_env_graph(problem, rng, n_rp=0, with_rp_store=False):
+    """The graph an env worker hands over (psp/env/gstate.py:169-183,544-546 on the stand-in container): ``prec``
+    edges in ``problem_edges`` order (gstate.py:98-103), the node fields ``rewire_internal`` concatenates
+    (agent_graph_observation.py:66-86) with seeded random values, ``resources`` normalised by availability
+    (gstate.py:260-277), ``res_cal`` (:332-341), optionally ``n_rp`` resource-priority edges with their 4 attributes
+    (gstate.py:891-934)."""
+    from psp_graph import StandInGraph
+    job_modes, m = [], 0
+    for j in problem.n_modes_per_job:
+        job_modes.append(list(range(m, m + j)))
+        m += j
+    n = m
+    edges = [(o, d) for k, succ in enumerate(problem.successors_id) for sj in succ
+             for o in job_modes[k] for d in job_modes[sj]]
+    g = StandInGraph(edges, n)
+    f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32)   # noqa: E731
+    g.set_ndata("job", torch.tensor([k for k, jm in enumerate(job_modes) for _ in jm], dtype=torch.int32))
+    g.set_ndata("durations", f32(rng.random((n, 3))))
+    g.set_ndata("affected", f32(rng.random(n) < 0.3))
+    g.set_ndata("selectable", f32(rng.random(n) < 0.3))
+    typ = np.zeros(n, np.float32)
+    typ[0], typ[-1] = -1, 1
+    g.set_ndata("type", f32(typ))
+    g.set_ndata("normalized_durations", f32(rng.random((n, 3))))
+    g.set_ndata("normalized_tct", f32(rng.random((n, 3))))
+    g.set_ndata("normalized_tardiness", f32(rng.random((n, 3))))
+    g.set_ndata("has_due_date", f32(rng.random(n) < 0.2))
+    g.set_ndata("normalized_due_dates", f32(rng.random(n)))
+    g.set_ndata("past", torch.tensor(rng.random(n) < 0.2))
+    res = np.array([c for per_job in problem.resource_cons for c in per_job], dtype=np.float32)
+    res = res / np.array(problem.resource_availabilities, dtype=np.float32)[None, :]
+    g.set_ndata("resources", f32(res))
+    g.set_global_data("res_cal", torch.tensor([(0, 0, 0)] * problem.n_resources, dtype=torch.float32))
+    if n_rp:
+        s = torch.tensor(rng.integers(0, n, n_rp))
+        d = torch.tensor(rng.integers(0, n, n_rp))
+        r = f32(np.concatenate([rng.integers(0, problem.n_resources, (n_rp, 1)), rng.random((n_rp, 3))], axis=1))
+        g.add_edges(s, d, etype="rp", data={"r": r})
+    elif with_rp_store:
+        g.num_edges("rp")
+    return g
+
+
+def golden_psp_batch(fname: str, seed: int):
+    """``Agent._obs_as_tensor_graph`` (rewire_internal) and ``Agent.preprocess`` of psp/models/agent.py EXECUTED
+    VERBATIM (unbound, on a namespace carrying the specification fields they read) together with everything they
+    call - AgentGraphObservation, rewire, node_conflicts, learned_graph_pool, vnode, homogeneous_edges,
+    compute_resources_graph_torch - on the stand-in graph container (oracle/shims/psp_graph.py)."""
+    _install_psp_stubs()
+    from psp.models.agent import Agent as PspAgent
+    from psp.utils.loaders import PSPLoader
+    from psp.utils.taillard_rcpsp import TaillardRcpsp
+    import contextlib
+    import io
+
+    with contextlib.redirect_stdout(io.StringIO()):
+        p272 = PSPLoader().load_single("/root/reference/instances/psp/272/272.sm")
+    tai43 = TaillardRcpsp(0, 4, 3, seed=3)
+    tai33 = TaillardRcpsp(1, 3, 3, seed=4)
+    d = {}
+    cases = [
+        # tag, conflicts, pooling, vnode, self loops, [(problem, n_rp, with_rp_store)]
+        ("node272", "node", "learn", False, True, [(p272, 0, False), (p272, 5, False), (p272, 2, False)]),
+        ("clique272", "clique", "learn", False, True, [(p272, 3, False), (p272, 0, False)]),
+        # vnode=True is not runnable in the reference: rewiring.py:288-290 hands Python lists to add_edges, whose
+        # torch.stack (pyg_graph.py:168) raises TypeError
+        ("nodeinv", "node", "learninv", False, True, [(tai43, 0, True), (tai43, 4, False)]),
+        ("ragged", "node", "learn", False, True, [(p272, 2, False), (tai33, 0, False), (tai43, 3, False)]),
+        ("clique_noself", "clique", "max", False, False, [(tai43, 0, False), (tai33, 2, False)]),
+        ("single", "node", "learn", False, True, [(tai33, 1, False)]),
+    ]
+    for tag, conflicts, pooling, vnode, self_loops, graphs in cases:
+        rng = np.random.default_rng(seed)
+        env_graphs = [synthetic_psp_env_graph(pb, rng, n_rp, st) for pb, n_rp, st in graphs]
+        ns = types.SimpleNamespace(
+            agent_specification=types.SimpleNamespace(conflicts=conflicts, graph_pooling=pooling, vnode=vnode,
+                                                      rwpe_k=0),
+            env_specification=types.SimpleNamespace(factored_rp=False, add_rp_edges="frontier_strict",
+                                                    max_n_resources=max(pb.n_resources for pb, _, _ in graphs),
+                                                    remove_past_prec=self_loops, observe_subgraph=False,
+                                                    n_features=16),
+            graphobs=True, rwpe_cache=None)
+        # wire-level inputs: what the env worker's graph holds (before rewire_internal)
+        d[f"{tag}.n_graphs"] = np.int64(len(env_graphs))
+        d[f"{tag}.opts"] = np.array([conflicts, pooling, str(int(vnode)), str(int(self_loops))])
+        for i, g in enumerate(env_graphs):
+            d[f"{tag}.g{i}.prec"] = np_(g._graph.edges["prec"]["edge_index"])
+            d[f"{tag}.g{i}.resources"] = np_(g.ndata("resources"))
+            d[f"{tag}.g{i}.res_cal"] = np_(g.global_data("res_cal"))
+            rp = g._graph.edges.get("rp")
+            has = rp is not None and "edge_index" in rp
+            d[f"{tag}.g{i}.rp"] = np_(rp["edge_index"]) if has else np.zeros((2, 0), np.int64)
+            d[f"{tag}.g{i}.rp_r"] = np_(rp["r"]) if has else np.zeros((0, 4), np.float32)
+            d[f"{tag}.g{i}.stores_env"] = np.array(list(g._graph.edges.keys()))
+        obs = PspAgent._obs_as_tensor_graph(ns, [g.clone() for g in env_graphs])      # alg/ppo.py:144,236
+        for i, g in enumerate(obs):
+            d[f"{tag}.g{i}.feat"] = np_(g.ndata("feat"))                               # [n, 16]
+            d[f"{tag}.g{i}.stores"] = np.array(list(g._graph.edges.keys()))
+        (g, batch_size, num_nodes, n_nodes, poolnodes, resource_nodes, vnodes, res_cal_id, pe) = \
+            PspAgent.preprocess(ns, obs)
+        assert pe is None
+        h = g._graph
+        d[f"{tag}.out.edge_index"] = np_(h["edge_index"])
+        for k in ("type", "rid", "att_rc", "att_rp", "feat"):
+            d[f"{tag}.out.{k}"] = np_(h[k])
+        d[f"{tag}.out.store_order"] = np.array(h.store_order)
+        d[f"{tag}.out.batch_size"], d[f"{tag}.out.num_nodes"] = np.int64(batch_size), np.int64(num_nodes)
+        d[f"{tag}.out.n_nodes"] = np.atleast_1d(np.asarray(n_nodes, dtype=np.int64))
+        d[f"{tag}.out.poolnodes"] = np.asarray([] if poolnodes is None else poolnodes, dtype=np.int64)
+        d[f"{tag}.out.resource_nodes"] = (np.zeros(0, np.int64) if resource_nodes is None
+                                          else np_(resource_nodes).astype(np.int64))
+        d[f"{tag}.out.vnodes"] = np.asarray([] if vnodes is None else vnodes, dtype=np.int64)
+        d[f"{tag}.out.res_cal_id"] = np_(res_cal_id)
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
 if __name__ == "__main__":
     golden_eegat(False, "eegat.npz", 11)
     golden_eegat(True, "eegat_edge_scoring.npz", 12)
@@ -472,4 +603,5 @@ if __name__ == "__main__":
     golden_jssp_batch("jssp_batch.npz", 17)
     golden_gnn_dgl("gnn_dgl.npz", 18)
     golden_gatv2("gatv2.npz", 19)
+    golden_psp_batch("psp_batch.npz", 20)
     print("golden fixtures written to", HERE)

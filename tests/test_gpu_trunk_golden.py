@@ -190,4 +190,5 @@ def test_trunk_at_bench_shape_matches_oracle(wb, bench_shape_case, dense):
     assert errs[gk] < grad_tol, errs
 
 
-TF32_OUT_TOL, TF32_GRAD_TOL = 2e-2, 5e-2
+# measured on B200 (r2a): outputs 3.0e-4, worst gradient 7.4e-3 (embedder first-layer weight)
+TF32_OUT_TOL, TF32_GRAD_TOL = 2e-3, 2e-2

@@ -210,3 +210,41 @@ def test_gatv2_oracle_matches_graphconv_golden(golden_dir):
         np.testing.assert_allclose(gr.numpy(), g["g." + k], rtol=1e-10, atol=1e-12, err_msg=k)
     np.testing.assert_allclose(grads[-2].numpy(), g["gx"], rtol=1e-10, atol=1e-12)
     np.testing.assert_allclose(grads[-1].numpy(), g["gea"], rtol=1e-10, atol=1e-12)
+
+
+PSP_TAGS = ["node272", "clique272", "nodeinv", "ragged", "clique_noself", "single"]
+
+
+def psp_golden_case(g, tag):
+    """(graphs, options, store order of the base edge types) of one psp_batch.npz case."""
+    conflicts, pooling, _vnode, self_loops = (str(x) for x in g[f"{tag}.opts"])
+    B = int(g[f"{tag}.n_graphs"])
+    graphs = [dict(feat=g[f"{tag}.g{i}.feat"], resources=g[f"{tag}.g{i}.resources"],
+                   res_cal=g[f"{tag}.g{i}.res_cal"], prec=g[f"{tag}.g{i}.prec"], rp=g[f"{tag}.g{i}.rp"],
+                   rp_r=g[f"{tag}.g{i}.rp_r"]) for i in range(B)]
+    return graphs, conflicts, pooling, self_loops == "1", [str(x) for x in g[f"{tag}.g0.stores_env"]]
+
+
+@pytest.mark.parametrize("tag", PSP_TAGS)
+def test_psp_batch_oracle_matches_reference_preprocess(golden_dir, tag):
+    """oracle.psp_batch_oracle against psp/models/agent.py Agent.preprocess (+ rewire_internal, rewire,
+    homogeneous_edges) executed on the stand-in container: every integer / attribute array bit for bit."""
+    from oracle import psp_batch_oracle as pbo
+    g = load(golden_dir, "psp_batch.npz")
+    graphs, conflicts, pooling, self_loops, env_stores = psp_golden_case(g, tag)
+    order = pbo.base_store_order(conflicts, env_stores)
+    assert order == [str(x) for x in g[f"{tag}.g0.stores"]][:len(order)]
+    out = pbo.psp_batch(graphs, conflicts, pooling, self_loops, store_order=order)
+    for k in ("edge_index", "type", "rid", "att_rc", "att_rp", "res_cal_id"):
+        ref = g[f"{tag}.out.{k}"]
+        assert out[k].dtype == ref.dtype and out[k].shape == ref.shape, (k, out[k].dtype, ref.dtype)
+        assert np.array_equal(out[k], ref), k
+    assert out["batch_size"] == int(g[f"{tag}.out.batch_size"]) and out["num_nodes"] == int(g[f"{tag}.out.num_nodes"])
+    assert np.array_equal(out["n_nodes"], g[f"{tag}.out.n_nodes"])
+    assert np.array_equal(out["poolnodes"], g[f"{tag}.out.poolnodes"])
+    assert np.array_equal(out["resource_nodes"], g[f"{tag}.out.resource_nodes"])
+    ref_feat = g[f"{tag}.out.feat"]
+    assert out["feat"].shape == ref_feat.shape
+    keep = np.ones(ref_feat.shape[0], bool)
+    keep[out["resource_nodes"]] = False                 # torch.empty rows in the reference (rewiring.py:132-141)
+    assert np.array_equal(out["feat"][keep], ref_feat[keep])
