@@ -242,6 +242,69 @@ int64_t b200gat_jssp_batch_edges(const b200gat_jssp_obs* o);
 int b200gat_jssp_batch_build(const b200gat_jssp_obs* o, int64_t* src, int64_t* dst, int64_t* etype,
                              float* feat, void* stream);
 
+/* ------------------------------------------------------------------ PSP observation wire format + batch builder
+ * (SURVEY rows a5, 8f N1 and N2).
+ *
+ * Wire format.  The reference ships every observation from an env worker to the learner as a torch.save pickle of
+ * a HeteroData dict through a shared byte array (psp/graph/pyg_graph.py:240-283,
+ * psp/env/graphgym/async_vector_env.py:59-103) and rebuilds tensors from it per step.  Here an observation is ONE
+ * fixed-layout slot of 4-byte little-endian words, written in place by the worker and copied to the device as it is:
+ *     int32 header[16]: [0] magic 'PSP1', [1] n_nodes, [2] n_resources, [3] n_prec, [4] n_rp, [5] 16, rest 0
+ *     fp32  feat      [max_nodes][16]   the 16 columns AgentGraphObservation.rewire_internal concatenates
+ *                                       (psp/models/agent_graph_observation.py:66-86), rows >= n_nodes zero
+ *     fp32  resources [max_nodes][max_res]   normalised consumptions (psp/env/gstate.py:260-277), zero padded
+ *     fp32  res_cal   [max_res][3]           calendar ids (gstate.py:332-341)
+ *     int32 prec      [2][max_prec]          precedence edges, node ids local to the graph (row 0 = source)
+ *     int32 rp        [2][max_rp]            resource-priority edges (gstate.py:891-934)
+ *     fp32  rp_r      [max_rp][4]            their attributes "r"
+ * rprec / rrp (reversed copies) and, in clique mode, the rc conflict edges are functions of these fields
+ * (agent_graph_observation.py:88-118) and are generated on the device.  slot_words is rounded up to 16 bytes.
+ *
+ * Builder.  b200gat_psp_batch_build replaces psp/models/agent.py:298-406 Agent.preprocess (AgentGraphObservation
+ * batching :300-309 = Batch.from_data_list per edge type, add_self_loops :339-344, rewire :353-368 =
+ * psp/models/rewiring.py:27-363, homogeneous_edges :371-378 = rewiring.py:366-440, to_homogeneous) and the
+ * rewire_internal edge additions before it: same node order (task nodes of all graphs, resource nodes, pool
+ * nodes), same EDGE ORDER, same per-edge type / rid / att_rc / att_rp, bit-exact.  The reference runs this in
+ * Python on the CPU per minibatch (6 DataLoader workers, alg/ppo.py:547-555) and per rollout step.
+ *   meta [5][B+1] int64, device: exclusive prefixes over the graphs of n_nodes, n_prec, n_rp, rc edges
+ *        (sum_r c_r (c_r - 1), clique mode), resource users (non-zeros of resources, node mode); host knowledge.
+ *   base_order: the batch's store order of the base edge types, codes 0 prec, 1 rprec, 2 rp, 3 rrp, 4 rc
+ *        (-1 = skip): the order in which the FIRST graph got its edge stores (Batch.from_data_list inherits it).
+ * Outputs: edge_index [2][E] int64, type [E] int64, rid [E] int32, attr [E][5] fp32 (att_rc | att_rp),
+ *          feat [n_total][16] fp32 (resource-node rows zero: uninitialised in the reference, rewiring.py:132-141),
+ *          res_cal_id [B * n_res][3] fp32 (agent_graph_observation.py:264-269). */
+#define B200GAT_PSP_MAGIC 0x31505350
+#define B200GAT_PSP_HEADER_WORDS 16
+#define B200GAT_PSP_N_FEAT 16
+#define B200GAT_PSP_MAX_RES 32
+#define B200GAT_CONFLICTS_NONE 0
+#define B200GAT_CONFLICTS_CLIQUE 1
+#define B200GAT_CONFLICTS_NODE 2
+typedef struct {
+  int32_t max_nodes, max_res, max_prec, max_rp;
+  int64_t slot_words;
+} b200gat_psp_layout;
+typedef struct {
+  b200gat_psp_layout layout;
+  int32_t n_graphs;
+  const int32_t* arena;       /* device: n_graphs consecutive slots */
+  const int64_t* meta;        /* device [5][B+1] */
+  int32_t conflicts;          /* B200GAT_CONFLICTS_* */
+  int32_t pooling;            /* B200GAT_POOL_* */
+  int32_t self_loops;
+  int32_t base_order[5];
+  int32_t n_res;              /* resources per graph after padding = max over the batch (pyg_graph.py:203-215) */
+  uint32_t unused_res_mask;   /* bit r: no graph of the batch uses resource r (rewiring.py:218-228) */
+  /* filled by b200gat_psp_batch_sizes: first edge of each segment by edge-type id (agent_graph_observation.py:36-53;
+   * -1 = absent), totals */
+  int64_t seg_start[16];
+  int64_t n_edges, n_task_nodes, n_total_nodes;
+} b200gat_psp_obs;
+int64_t b200gat_psp_slot_words(const b200gat_psp_layout* l);
+int b200gat_psp_batch_sizes(b200gat_psp_obs* o, const int64_t* meta_host);
+int b200gat_psp_batch_build(const b200gat_psp_obs* o, int64_t* edge_index, int64_t* type, int32_t* rid,
+                            float* attr, float* feat, float* res_cal_id, void* stream);
+
 /* ------------------------------------------------------------------ attention layer */
 typedef struct {
   int32_t flavour; /* B200GAT_FLAVOUR_*                                                  */

@@ -17,6 +17,7 @@ What is executed verbatim from the reference tree:
   * psp/graph/graph_conv.py GraphConv.forward / forward_nog (PyG shim; GATv2Conv itself is a restatement)
   * psp/models/agent.py Agent._obs_as_tensor_graph / Agent.preprocess + psp/models/rewiring.py +
     psp/models/agent_graph_observation.py (on oracle/shims/psp_graph.py, a stand-in for the HeteroData container)
+  * psp/models/gnn_mp.py GnnMP.forward + psp/models/gnn_flat.py GnnFlat.forward (torch.compile on the eager backend)
 
 Outputs: small .npz files (float64 for the layers so that the comparison with
 the oracle is tight; float32 where the reference module is float32-only).
@@ -593,6 +594,93 @@ def golden_psp_batch(fname: str, seed: int):
     np.savez_compressed(os.path.join(HERE, fname), **d)
 
 
+# ---------------------------------------------------------------- N3: GnnMP / GnnFlat trunk (PyG flavour)
+def golden_gnn_mp(fname: str, seed: int):
+    """psp/models/gnn_mp.py GnnMP.forward (:318-507) and psp/models/gnn_flat.py GnnFlat.forward (:151-259) EXECUTED
+    VERBATIM on the batches ``Agent.preprocess`` builds (stand-in container) with the layer stack on the PyG shim
+    (GraphConv -> GATv2Conv restatement, PspEdgeEmbedder and MLP are the reference's own).  ``torch.compile`` is
+    kept (so the ``_orig_mod.`` infix of the state-dict keys is the reference's) but pointed at the ``eager``
+    backend: no Inductor / Triton in this container, same arithmetic."""
+    _install_psp_stubs()
+    from psp.models.agent import Agent as PspAgent
+    from psp.models.gnn_mp import GnnMP
+    from psp.utils.loaders import PSPLoader
+    from psp.utils.taillard_rcpsp import TaillardRcpsp
+    import contextlib
+    import io
+
+    with contextlib.redirect_stdout(io.StringIO()):
+        p272 = PSPLoader().load_single("/root/reference/instances/psp/272/272.sm")
+    tai33 = TaillardRcpsp(1, 3, 3, seed=4)
+    orig_compile = torch.compile
+    torch.compile = lambda m, **kw: orig_compile(m, backend="eager", dynamic=kw.get("dynamic"))
+    d = {}
+    try:
+        for tag, conflicts, pooling, graphs, max_n_nodes in [
+                ("node272", "node", "learn", [(p272, 0), (p272, 5), (p272, 2)], 20),
+                ("clique272", "clique", "learn", [(p272, 3), (p272, 0)], 18),
+                ("ragged_max", "node", "max", [(p272, 2), (tai33, 0)], 19),
+                ("single", "node", "learn", [(tai33, 1)], 13)]:
+            rng = np.random.default_rng(seed)
+            env_graphs = [synthetic_psp_env_graph(pb, rng, n_rp, False) for pb, n_rp in graphs]
+            max_res = max(pb.n_resources for pb, _ in graphs)
+            ns = types.SimpleNamespace(
+                agent_specification=types.SimpleNamespace(conflicts=conflicts, graph_pooling=pooling, vnode=False,
+                                                          rwpe_k=0),
+                env_specification=types.SimpleNamespace(factored_rp=False, add_rp_edges="frontier_strict",
+                                                        max_n_resources=max_res, remove_past_prec=True,
+                                                        observe_subgraph=False, n_features=16),
+                graphobs=True, rwpe_cache=None)
+            d[f"{tag}.n_graphs"] = np.int64(len(env_graphs))
+            d[f"{tag}.opts"] = np.array([conflicts, pooling, "0", "1"])
+            obs = PspAgent._obs_as_tensor_graph(ns, [g.clone() for g in env_graphs])
+            for i, (g, ge) in enumerate(zip(obs, env_graphs)):
+                d[f"{tag}.g{i}.feat"] = np_(g.ndata("feat"))
+                d[f"{tag}.g{i}.prec"] = np_(ge._graph.edges["prec"]["edge_index"])
+                d[f"{tag}.g{i}.resources"] = np_(ge.ndata("resources"))
+                d[f"{tag}.g{i}.res_cal"] = np_(ge.global_data("res_cal")) + 1.0 + i   # non-trivial calendar ids
+                ge.set_global_data("res_cal", torch.tensor(d[f"{tag}.g{i}.res_cal"]))
+                g.set_global_data("res_cal", torch.tensor(d[f"{tag}.g{i}.res_cal"]))
+                rp = ge._graph.edges.get("rp")
+                has = rp is not None and "edge_index" in rp
+                d[f"{tag}.g{i}.rp"] = np_(rp["edge_index"]) if has else np.zeros((2, 0), np.int64)
+                d[f"{tag}.g{i}.rp_r"] = np_(rp["r"]) if has else np.zeros((0, 4), np.float32)
+                d[f"{tag}.g{i}.stores_env"] = np.array(list(ge._graph.edges.keys()))
+            pre = PspAgent.preprocess(ns, obs)
+            Hd, H, L = 8, 2, 2
+            torch.manual_seed(seed)
+            gnn = GnnMP(input_dim_features_extractor=16, graph_pooling=pooling, max_n_nodes=max_n_nodes,
+                        max_n_resources=max_res, n_mlp_layers_features_extractor=3, n_layers_features_extractor=L,
+                        hidden_dim_features_extractor=Hd, activation_features_extractor="gelu",
+                        n_attention_heads=H, residual=True, normalize=False, conflicts=conflicts,
+                        edge_embedding_flavor="sum", layer_pooling="all", factored_rp=False,
+                        add_rp_edges="frontier_strict", add_self_loops=True, vnode=False,
+                        update_edge_features=False, update_edge_features_pe=False, rwpe_k=0, rwpe_h=0,
+                        rwpe_cache=None, graphobs=True, shared_conv=False, pyg=True, hierarchical=False,
+                        tokengt=False, checkpoint=1, dual_net=False)
+            with torch.no_grad():
+                for fe in gnn.gnn._orig_mod.features_extractors:
+                    for p_ in (fe.conv.lin_l.bias, fe.conv.lin_r.bias, fe.conv.bias):
+                        p_.copy_(torch.randn(p_.shape) * 0.1)
+            node_features, graph_embedding = gnn(pre)
+            gen = torch.Generator().manual_seed(seed + 1)
+            R1 = torch.randn(node_features.shape, generator=gen)
+            R2 = torch.randn(graph_embedding.shape, generator=gen)
+            names = [k for k, _ in gnn.named_parameters()]
+            params = [p_ for _, p_ in gnn.named_parameters()]
+            gr = grads_of((node_features * R1).sum() + (graph_embedding * R2).sum(), params)
+            d[f"{tag}.node_features"], d[f"{tag}.graph_embedding"] = np_(node_features), np_(graph_embedding)
+            d[f"{tag}.R1"], d[f"{tag}.R2"] = np_(R1), np_(R2)
+            d[f"{tag}.cfg"] = np.array([Hd, H, L, max_n_nodes, max_res])
+            d[f"{tag}.state_keys"] = np.array(list(gnn.state_dict().keys()))
+            for k, p_, g_ in zip(names, params, gr):
+                d[f"{tag}.p.{k}"] = np_(p_)
+                d[f"{tag}.g.{k}"] = np_(g_)
+    finally:
+        torch.compile = orig_compile
+    np.savez_compressed(os.path.join(HERE, fname), **d)
+
+
 if __name__ == "__main__":
     golden_eegat(False, "eegat.npz", 11)
     golden_eegat(True, "eegat_edge_scoring.npz", 12)
@@ -604,4 +692,5 @@ if __name__ == "__main__":
     golden_gnn_dgl("gnn_dgl.npz", 18)
     golden_gatv2("gatv2.npz", 19)
     golden_psp_batch("psp_batch.npz", 20)
+    golden_gnn_mp("gnn_mp.npz", 21)
     print("golden fixtures written to", HERE)

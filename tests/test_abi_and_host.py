@@ -376,3 +376,70 @@ def test_batch_builder_refuses_cpu_and_unknown_modes(built):
         jssp_batch_on_device(obs, "cuda:0", conflicts="node")            # needs max_n_machines
     with pytest.raises(ValueError):
         jssp_batch_on_device(obs, "cuda:0", conflicts="bogus")
+
+
+def test_wire_format_round_trip_and_gather(built):
+    """Observation wire format: encode -> decode is the identity on every field, slots are
+    independent, capacities are enforced, and a minibatch gather is a plain copy of whole slots."""
+    import numpy as np
+    from wheatley_b200.wire import PspArena, PspObsLayout
+    from wheatley_b200.workload import psp_taillard_graph
+    graphs = [psp_taillard_graph(4, 4, 1, n_rp=3), psp_taillard_graph(3, 2, 2), psp_taillard_graph(5, 3, 3, n_rp=1)]
+    layout = PspObsLayout.for_graphs(graphs)
+    assert layout.slot_words % 4 == 0
+    arena = PspArena(layout, 5, pin=False)
+    for i, g in enumerate(graphs):
+        arena.write(i + 1, g)
+    for i, g in enumerate(graphs):
+        back = arena.read(i + 1)
+        for k in ("feat", "resources", "res_cal", "prec", "rp", "rp_r"):
+            assert np.array_equal(back[k], g[k]), k
+    arena.write(1, graphs[1])                                   # overwrite with a smaller graph: no stale rows
+    back = arena.read(1)
+    assert back["feat"].shape == graphs[1]["feat"].shape and np.array_equal(back["prec"], graphs[1]["prec"])
+    assert not arena.words[1, layout.off_res: layout.off_cal].view(np.float32).reshape(
+        layout.max_nodes, layout.max_res)[graphs[1]["feat"].shape[0]:].any()
+    mb = arena.gather([3, 2, 3])
+    assert np.array_equal(mb.words[0], arena.words[3]) and np.array_equal(mb.words[1], arena.words[2])
+    with pytest.raises(ValueError):
+        PspObsLayout(4, 2, 4, 0).encode(np.zeros(1000, np.int32), **{k: graphs[0][k] for k in
+                                                                  ("feat", "resources", "res_cal", "prec")})
+    with pytest.raises(ValueError):
+        layout.decode(np.zeros(layout.slot_words, np.int32))
+    # a shared-memory buffer (what a worker process maps) works as the backing store
+    import multiprocessing as mp
+    shm = mp.RawArray("i", 2 * layout.slot_words)
+    shared = PspArena(layout, 2, buffer=shm)
+    shared.write(0, graphs[0])
+    assert np.array_equal(np.frombuffer(shm, dtype=np.int32, count=layout.slot_words), shared.words[0])
+
+
+def test_psp_sizes_and_oracle_agree_on_survey_table(built):
+    """PyG-flavour node / edge counts per graph at t = 0 from the numpy oracle on generated graphs."""
+    from oracle import psp_batch_oracle as pbo
+    from wheatley_b200.workload import psp_sizes_expected, psp_taillard_graph
+    for (n_j, n_m), (n_node, e_node) in {(10, 10): (113, 635), (15, 15): (243, 1400), (30, 20): (623, 3685),
+                                         (4, 4): (23, 113)}.items():
+        out = pbo.psp_batch([psp_taillard_graph(n_j, n_m, 0)], "node", "learn", True)
+        assert (out["n_total"], out["edge_index"].shape[1]) == (n_node, e_node) == psp_sizes_expected(n_j, n_m)
+    out = pbo.psp_batch([psp_taillard_graph(10, 10, 0)], "clique", "learn", True)
+    assert out["n_total"] == 103 and out["edge_index"].shape[1] == psp_sizes_expected(10, 10, "clique")[1]
+
+
+def test_gnn_mp_state_dict_names_match_reference_golden(built, golden_dir):
+    """State-dict keys of wheatley_b200.GnnMP == the reference GnnMP's (gnn_mp.npz, incl. torch.compile's
+    ``_orig_mod.`` infix, psp/models/gnn_mp.py:139,145,183,266,300), shapes included."""
+    import numpy as np
+    import os
+    from wheatley_b200.gnn_mp import GnnMP
+    g = np.load(os.path.join(golden_dir, "gnn_mp.npz"))
+    for tag in ("node272", "clique272"):
+        conflicts, pooling = (str(x) for x in g[f"{tag}.opts"][:2])
+        Hd, H, L, max_n_nodes, max_res = (int(v) for v in g[f"{tag}.cfg"])
+        gnn = GnnMP(16, pooling, max_n_nodes, max_res, 3, L, Hd, "gelu", H, conflicts=conflicts, rwpe_k=0,
+                    shared_conv=False, pyg=True, graphobs=True, add_rp_edges="frontier_strict")
+        sd = gnn.state_dict()
+        assert sorted(sd) == sorted(str(k) for k in g[f"{tag}.state_keys"])
+        for k, v in sd.items():
+            assert tuple(v.shape) == g[f"{tag}.p.{k}"].shape, k
+        assert gnn.features_dim == g[f"{tag}.node_features"].shape[2]

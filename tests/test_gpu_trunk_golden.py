@@ -192,3 +192,83 @@ def test_trunk_at_bench_shape_matches_oracle(wb, bench_shape_case, dense):
 
 # measured on B200 (r2a): outputs 3.0e-4, worst gradient 7.4e-3 (embedder first-layer weight)
 TF32_OUT_TOL, TF32_GRAD_TOL = 2e-3, 2e-2
+
+
+@pytest.mark.parametrize("tag", ["node272", "clique272", "ragged_max", "single"])
+def test_gnn_mp_matches_reference_trunk_golden(wb, golden_dir, fp32_dense, tag):
+    """wheatley_b200.GnnMP fed by the device PSP batch builder (wire-format arena) against the reference's own
+    GnnMP.forward / GnnFlat.forward on the same observations and weights (gnn_mp.npz): ``node_features
+    [B, max_n_nodes, F]``, ``graph_embedding [B, 1, F]`` and every parameter gradient, reference state-dict keys
+    (``_orig_mod.`` infix) loaded as they are."""
+    from wheatley_b200.gnn_mp import GnnMP
+    from wheatley_b200.psp_batch import preprocess
+    from wheatley_b200.wire import PspArena
+    g = np.load(os.path.join(golden_dir, "gnn_mp.npz"))
+    conflicts, pooling, _v, _s = (str(x) for x in g[f"{tag}.opts"])
+    B = int(g[f"{tag}.n_graphs"])
+    graphs = [dict(feat=g[f"{tag}.g{i}.feat"], resources=g[f"{tag}.g{i}.resources"],
+                   res_cal=g[f"{tag}.g{i}.res_cal"], prec=g[f"{tag}.g{i}.prec"], rp=g[f"{tag}.g{i}.rp"],
+                   rp_r=g[f"{tag}.g{i}.rp_r"]) for i in range(B)]
+    env_stores = [str(x) for x in g[f"{tag}.g0.stores_env"]]
+    Hd, H, L, max_n_nodes, max_res = (int(v) for v in g[f"{tag}.cfg"])
+    gnn = GnnMP(16, pooling, max_n_nodes, max_res, 3, L, Hd, "gelu", H, residual=True, normalize=False,
+                conflicts=conflicts, layer_pooling="all", add_rp_edges="frontier_strict", rwpe_k=0, rwpe_h=0,
+                graphobs=True, shared_conv=False, pyg=True).cuda()
+    P = {k[len(tag) + 3:]: T(g[k]) for k in g.files if k.startswith(tag + ".p.")}
+    assert sorted(gnn.state_dict()) == sorted(str(k) for k in g[f"{tag}.state_keys"])
+    gnn.load_state_dict(P)
+    obs = preprocess(PspArena.from_graphs(graphs), "cuda", conflicts=conflicts, graph_pooling=pooling,
+                     first_graph_env_stores=env_stores)
+    nf, ge = gnn(obs)
+    assert rel(nf, g[f"{tag}.node_features"]) < 1e-4 and rel(ge, g[f"{tag}.graph_embedding"]) < 1e-4
+    ((nf * T(g[f"{tag}.R1"]).cuda()).sum() + (ge * T(g[f"{tag}.R2"]).cuda()).sum()).backward()
+    for k, p in gnn.named_parameters():
+        ref = g[f"{tag}.g.{k}"]
+        got = torch.zeros_like(p) if p.grad is None else p.grad
+        assert rel(got, ref) < 3e-4, k
+
+
+def test_psp_agent_step_and_checkpoint_layout(wb, fp32_dense):
+    """PspAgent end to end on a 272-shaped batch (hidden 32, 4 layers: 272.sh:1): preprocess -> get_action_and_value
+    -> loss -> backward against the fp64 oracle trunk + head; checkpoint dict layout of generic/agent.py:158-172."""
+    from oracle import head_oracle, psp_batch_oracle as pbo, trunk_oracle
+    from wheatley_b200.agent import PspAgent
+    from wheatley_b200.ppo import ppo_like_loss
+    from wheatley_b200.wire import PspArena
+    from wheatley_b200.workload import psp_taillard_graph
+    B, Hd, L, H = 6, 32, 4, 4
+    graphs = [psp_taillard_graph(4, 4, 3 + b, n_rp=b % 3, progress=0.1 * b) for b in range(B)]
+    torch.manual_seed(0)
+    agent = PspAgent(18, 4, hidden_dim=Hd, n_layers=L, n_heads=H, conflicts="node").cuda()
+    obs = agent.preprocess(PspArena.from_graphs(graphs))
+    gen = torch.Generator().manual_seed(5)
+    masks = torch.rand(B, 18, generator=gen) < 0.4
+    masks[:, 0] = True
+    action = torch.multinomial(masks.float(), 1, generator=gen).squeeze(1)
+    adv, ret = torch.randn(B, generator=gen), torch.randn(B, generator=gen)
+    _, lp, ent, val, _ = agent.get_action_and_value(obs, action.cuda(), masks.cuda())
+    loss = ppo_like_loss(lp, ent, val, adv.cuda(), ret.cuda())
+    loss.backward()
+    # oracle
+    b = pbo.psp_batch(graphs, "node", "learn", True)
+    ognn = trunk_oracle.OracleGnnMP(16, "learn", 18, 3, L, Hd, "gelu", H, conflicts="node").double()
+    ognn.load_state_dict({k: v.double().cpu() for k, v in agent.gnn.state_dict().items()})
+    ovn = trunk_oracle.OracleMLP(3, agent.gnn.features_dim, 64, 1, False, "gelu").double()
+    oan = trunk_oracle.OracleMLP(3, agent.gnn.features_dim, 64, 1, False, "gelu").double()
+    ovn.load_state_dict({k.replace("_orig_mod.", ""): v.double().cpu() for k, v in agent.value_net.state_dict().items()})
+    oan.load_state_dict({k.replace("_orig_mod.", ""): v.double().cpu() for k, v in agent.action_net.state_dict().items()})
+    nf, ge = ognn(T(b["edge_index"]), T(b["type"]), T(b["att_rc"]).double(), T(b["att_rp"]).double(),
+                  T(b["feat"]).double(), B, b["num_nodes"], b["n_nodes"].tolist(), b["poolnodes"].tolist(),
+                  b["resource_nodes"].tolist(), T(b["res_cal_id"]).double())
+    _, lp_r, ent_r, _ = head_oracle.action_and_logprob(oan(nf).squeeze(-1), action, masks)
+    val_r = ovn(ge)
+    loss_r = trunk_oracle.ppo_like_loss(lp_r, ent_r, val_r, adv.double(), ret.double())
+    loss_r.backward()
+    assert rel(lp, lp_r) < 1e-4 and rel(ent, ent_r) < 1e-4 and rel(val, val_r) < 1e-4 and rel(loss, loss_r) < 1e-4
+    og = dict(ognn.named_parameters())
+    for k, p in agent.gnn.named_parameters():
+        if og[k].grad is not None:
+            assert rel(p.grad, og[k].grad) < 3e-4, k
+    d = agent.save_dict()
+    assert set(d) == {"gnn", "value_net", "action_net"} and "_orig_mod.layers.0.weight" in d["value_net"]
+    agent.load_dict(d)

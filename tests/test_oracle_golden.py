@@ -248,3 +248,31 @@ def test_psp_batch_oracle_matches_reference_preprocess(golden_dir, tag):
     keep = np.ones(ref_feat.shape[0], bool)
     keep[out["resource_nodes"]] = False                 # torch.empty rows in the reference (rewiring.py:132-141)
     assert np.array_equal(out["feat"][keep], ref_feat[keep])
+
+
+@pytest.mark.parametrize("tag", ["node272", "clique272", "ragged_max", "single"])
+def test_gnn_mp_oracle_matches_reference_trunk(golden_dir, tag):
+    """oracle.trunk_oracle.OracleGnnMP (+ psp_batch_oracle) against the reference's GnnMP.forward / GnnFlat.forward
+    executed on the shims (gnn_mp.npz): both outputs and every parameter gradient, reference state-dict keys."""
+    from oracle import psp_batch_oracle as pbo
+    from oracle import trunk_oracle
+    g = load(golden_dir, "gnn_mp.npz")
+    graphs, conflicts, pooling, self_loops, env_stores = psp_golden_case(g, tag)
+    Hd, H, L, max_n_nodes, _max_res = (int(v) for v in g[f"{tag}.cfg"])
+    b = pbo.psp_batch(graphs, conflicts, pooling, self_loops, store_order=pbo.base_store_order(conflicts, env_stores))
+    gnn = trunk_oracle.OracleGnnMP(16, pooling, max_n_nodes, 3, L, Hd, "gelu", H, conflicts=conflicts)
+    P = {k[len(tag) + 3:]: T(g[k]) for k in g.files if k.startswith(tag + ".p.")}
+    assert sorted(P) == sorted(str(k) for k in g[f"{tag}.state_keys"])
+    missing = gnn.load_state_dict(P, strict=False)
+    assert not missing.missing_keys, missing
+    n_nodes = b["n_nodes"].tolist()
+    nf, ge = gnn(T(b["edge_index"]), T(b["type"]), T(b["att_rc"]), T(b["att_rp"]), T(b["feat"]), b["batch_size"],
+                 b["num_nodes"], n_nodes[0] if len(n_nodes) == 1 else n_nodes, b["poolnodes"].tolist(),
+                 b["resource_nodes"].tolist(), T(b["res_cal_id"]))
+    np.testing.assert_allclose(nf.detach().numpy(), g[f"{tag}.node_features"], rtol=2e-5, atol=2e-6)
+    np.testing.assert_allclose(ge.detach().numpy(), g[f"{tag}.graph_embedding"], rtol=2e-5, atol=2e-6)
+    ((nf * T(g[f"{tag}.R1"])).sum() + (ge * T(g[f"{tag}.R2"])).sum()).backward()
+    for k, p in gnn.named_parameters():
+        ref = g[f"{tag}.g.{k}"]
+        got = np.zeros_like(ref) if p.grad is None else p.grad.numpy()
+        np.testing.assert_allclose(got, ref, rtol=3e-4, atol=3e-5 * max(1.0, np.abs(ref).max()), err_msg=k)

@@ -14,6 +14,9 @@ GraphConv         wheatley_b200.GraphConv         (psp/graph/graph_conv.py:8)
 GATv2Conv (PyG)   wheatley_b200.GATv2Conv         (psp/graph/graph_conv.py:33)
 GATv3Conv         wheatley_b200.GATv3Conv         (generic/gatv3_conv.py:16)
 MLP               wheatley_b200.MLP               (generic/mlp.py:29)
+GnnMP / GnnFlat   wheatley_b200.GnnMP / GnnFlat   (psp/models/gnn_mp.py:38, gnn_flat.py:7)
+Agent.preprocess  wheatley_b200.psp_batch         (psp/models/agent.py:298-406)
+obs wire format   wheatley_b200.wire              (psp/graph/pyg_graph.py:240-283)
 Agent head        wheatley_b200.agent_head        (generic/agent.py:190-277)
 ================  ==========================================================
 """
@@ -26,11 +29,12 @@ from .functional import (EdgeFeatures, fused_gat_conv, attention_weights, edge_o
 from .eegatconv import EGATConv, EEGATConv, DGLError
 from .graph_conv import GraphConv, GATv2Conv, GATv3Conv
 from .mlp import MLP
+from .gnn_mp import GnnFlat, GnnMP
 from . import agent_head
 
 __all__ = [
     "B200GatError", "GraphPlan", "plan_for_edge_index", "TypedEdgeFeats", "AffineEdgeFeats",
     "EdgeFeatures", "fused_gat_conv", "attention_weights", "edge_output", "masked_log_softmax",
     "masked_logprob_entropy", "EGATConv", "EEGATConv", "DGLError", "GraphConv", "GATv2Conv",
-    "GATv3Conv", "MLP", "agent_head",
+    "GATv3Conv", "MLP", "GnnMP", "GnnFlat", "agent_head",
 ]

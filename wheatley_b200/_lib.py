@@ -28,6 +28,7 @@ SYMBOLS = (
     "b200gat_colsum_scratch_elems", "b200gat_colsum",
     "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
     "b200gat_jssp_batch_edges", "b200gat_jssp_batch_build",
+    "b200gat_psp_slot_words", "b200gat_psp_batch_sizes", "b200gat_psp_batch_build",
 )
 MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
@@ -99,6 +100,24 @@ class JsspObs(C.Structure):
 
 
 POOLING = {None: 0, "learn": 1, "learninv": 2}
+CONFLICTS = {"att": 0, "clique": 1, "node": 2}
+PSP_MAGIC, PSP_HEADER_WORDS, PSP_N_FEAT, PSP_MAX_RES = 0x31505350, 16, 16, 32
+PSP_BASE_CODES = {"prec": 0, "rprec": 1, "rp": 2, "rrp": 3, "rc": 4}
+
+
+class PspLayout(C.Structure):
+    """``b200gat_psp_layout`` (include/b200gat.h)."""
+    _fields_ = [("max_nodes", C.c_int32), ("max_res", C.c_int32), ("max_prec", C.c_int32), ("max_rp", C.c_int32),
+                ("slot_words", C.c_int64)]
+
+
+class PspObs(C.Structure):
+    """``b200gat_psp_obs`` (include/b200gat.h)."""
+    _fields_ = [("layout", PspLayout), ("n_graphs", C.c_int32), ("arena", C.c_void_p), ("meta", C.c_void_p),
+                ("conflicts", C.c_int32), ("pooling", C.c_int32), ("self_loops", C.c_int32),
+                ("base_order", C.c_int32 * 5), ("n_res", C.c_int32), ("unused_res_mask", C.c_uint32),
+                ("seg_start", C.c_int64 * 16), ("n_edges", C.c_int64), ("n_task_nodes", C.c_int64),
+                ("n_total_nodes", C.c_int64)]
 
 
 class MlpGrads(C.Structure):
@@ -168,13 +187,18 @@ def _load():
     lib.b200gat_jssp_batch_edges.argtypes = [jp]
     lib.b200gat_jssp_batch_edges.restype = i64
     lib.b200gat_jssp_batch_build.argtypes = [jp, vp, vp, vp, vp, vp]
+    pl, po = C.POINTER(PspLayout), C.POINTER(PspObs)
+    lib.b200gat_psp_slot_words.argtypes = [pl]
+    lib.b200gat_psp_slot_words.restype = i64
+    lib.b200gat_psp_batch_sizes.argtypes = [po, vp]
+    lib.b200gat_psp_batch_build.argtypes = [po, vp, vp, vp, vp, vp, vp, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
                         "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
                         "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
-                        "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges"):
+                        "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges", "b200gat_psp_slot_words"):
             fn.restype = C.c_int
     return lib
 

@@ -139,4 +139,9 @@ class PspEdgeEmbedder(nn.Module):
                 return g.edata(None, key)
             except KeyError:
                 return None
+        a5 = get("attr5")       # the device batch builder's [E, 5] = att_rc | att_rp (one tensor for every layer)
+        if a5 is not None and self.add_rp_edges != "none":
+            table = self.edge_type_embedder.weight + self.rc_att_embedder.bias + self.rp_att_embedder.bias
+            return AffineEdgeFeats(g.edata(None, "type"), table, a5,
+                                   torch.cat([self.rc_att_embedder.weight, self.rp_att_embedder.weight], dim=1))
         return self.factor(g.edata(None, "type"), get("att_rc"), get("att_rp"))

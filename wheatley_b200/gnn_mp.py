@@ -1,0 +1,217 @@
+"""GnnMP / GnnFlat - the LIVE trunk of the reference (psp/models/gnn_mp.py:38-507, psp/models/gnn_flat.py:7-259;
+every JSSP / PSP config runs through it today) on the fused CUDA attention layer.
+
+Same constructor arguments, sub-module / parameter names - including the ``_orig_mod.`` infix ``torch.compile``
+puts into the reference's state-dict keys (``gnn._orig_mod.features_extractors.<l>.conv.lin_l.weight`` ...,
+SURVEY section 5 "Checkpoint") - and return values, so ``Agent.save`` / ``load_state_dict`` round-trip with
+reference checkpoints.  Covered configuration = the only one that runs upstream:
+``normalize=False, rwpe_k=0, update_edge_features=False, shared_conv=False, hierarchical=False, tokengt=False,
+dual_net=False, layer_pooling="all"``; anything else raises like the reference does (AttributeError on the
+attributes it never creates) or NotImplementedError.
+
+Differences, all inside the boundary:
+* the batched graph arrives as the 9-tuple of ``wheatley_b200.psp_batch.preprocess`` (built on the device);
+* edge features stay factored (``PspEdgeEmbedder`` -> ``AffineEdgeFeats``): ``lin_edge`` projects a 16-row table
+  and a 5-row affine map instead of ``[E, hidden]`` (psp/models/edge_embedder.py:130-143);
+* the residual add (gnn_flat.py:228-230) rides in the MLP's last GEMM epilogue; the per-graph pad to
+  ``max_n_nodes`` (gnn_mp.py:459-470: a Python loop of ``F.pad`` + ``stack``) is one indexed copy."""
+import numpy as np
+import torch
+from torch import nn
+
+from . import _lib
+from .edge_feats import PspEdgeEmbedder
+from .graph_conv import GraphConv
+from .mlp import MLP
+
+
+class Compiled(nn.Module):
+    """Name-compatible stand-in for ``torch.compile(module)``: the wrapped module's parameters appear under
+    ``_orig_mod.`` exactly as in the reference's OptimizedModule; calls are forwarded (the hot ops are hand-written
+    kernels: there is nothing for a tracing compiler to fuse)."""
+
+    def __init__(self, mod):
+        super().__init__()
+        self._orig_mod = mod
+
+    def forward(self, *a, **k):
+        return self._orig_mod(*a, **k)
+
+    def __getattr__(self, name):
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            return getattr(super().__getattr__("_orig_mod"), name)
+
+
+class GnnFlat(nn.Module):
+    def __init__(self, input_dim_features_extractor, hidden_dim_features_extractor, n_layers_features_extractor,
+                 n_mlp_layers_features_extractor, layer_pooling, n_attention_heads, normalize,
+                 activation_features_extractor, residual, rwpe_k, rwpe_h, update_edge_features,
+                 update_edge_features_pe, shared_conv, edge_embedding_flavor, max_n_resources, add_rp_edges,
+                 factored_rp, pyg, checkpoint):
+        super().__init__()
+        if normalize or rwpe_k != 0 or update_edge_features or shared_conv or not pyg:
+            raise NotImplementedError("only the live GnnFlat configuration is on the hot path (SURVEY F13: the other "
+                                      "branches reference attributes the reference never creates)")
+        self.hidden_dim = hidden_dim_features_extractor
+        self.layer_pooling = layer_pooling
+        self.rwpe_k, self.rwpe_h = rwpe_k, rwpe_h
+        self.update_edge_features, self.update_edge_features_pe = update_edge_features, update_edge_features_pe
+        self.n_layers_features_extractor = n_layers_features_extractor
+        self.shared_conv, self.pyg, self.normalize, self.residual = shared_conv, pyg, normalize, residual
+        self.input_dim_features_extractor = input_dim_features_extractor
+        self.checkpoint = checkpoint
+        self.features_extractors = nn.ModuleList()
+        self.mlps = nn.ModuleList()
+        self.edge_embedders = nn.ModuleList()
+        for _ in range(n_layers_features_extractor):                          # gnn_flat.py:96-125
+            self.features_extractors.append(GraphConv(self.hidden_dim, self.hidden_dim,
+                                                      num_heads=n_attention_heads, edge_scoring=False, pyg=True))
+            self.mlps.append(MLP(n_layers=n_mlp_layers_features_extractor,
+                                 input_dim=self.hidden_dim * n_attention_heads,
+                                 hidden_dim=self.hidden_dim * n_attention_heads, output_dim=self.hidden_dim,
+                                 norm=False, activation=activation_features_extractor))
+            self.edge_embedders.append(PspEdgeEmbedder(edge_embedding_flavor, max_n_resources, self.hidden_dim,
+                                                       add_rp_edges, factored_rp, n_mlp_layers_features_extractor,
+                                                       activation_features_extractor))
+
+    def _layer(self, layer, g, features, prev):
+        h, _ = self.features_extractors[layer](g._graph, features, self.edge_embedders[layer](g))   # :204-208
+        # :209 and the residual add of :228-230, fused into the MLP's last GEMM epilogue
+        return self.mlps[layer](h, residual=prev if self.residual else None)
+
+    def forward(self, g, features, pe):
+        features_list = [features]                                            # :155-161
+        previous = features
+        for layer in range(self.n_layers_features_extractor):
+            if layer % self.checkpoint:                                       # :192-202 activation checkpointing
+                from torch.utils.checkpoint import checkpoint
+                features = checkpoint(self._layer, layer, g, features, previous, use_reentrant=False)
+            else:
+                features = self._layer(layer, g, features, previous)
+            previous = features
+            if self.layer_pooling == "all":
+                features_list.append(features)                                # :249-253
+        return features_list if self.layer_pooling == "all" else features
+
+
+def _pad_rows_index(counts, max_n_nodes, device):
+    """Row of the ``[B * max_n_nodes]`` padded layout each task node goes to (host arithmetic, one small copy)."""
+    counts = np.asarray(counts, dtype=np.int64)
+    if counts.size and int(counts.max()) > max_n_nodes:
+        raise _lib.B200GatError(f"a graph has {int(counts.max())} nodes, max_n_nodes is {max_n_nodes}")
+    starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
+    local = np.arange(int(counts.sum())) - np.repeat(starts, counts)
+    dest = np.repeat(np.arange(len(counts)) * max_n_nodes, counts) + local
+    return torch.from_numpy(dest).to(device, non_blocking=True)
+
+
+class GnnMP(nn.Module):
+    def __init__(self, input_dim_features_extractor, graph_pooling, max_n_nodes, max_n_resources,
+                 n_mlp_layers_features_extractor, n_layers_features_extractor, hidden_dim_features_extractor,
+                 activation_features_extractor, n_attention_heads, residual=True, normalize=False, conflicts="att",
+                 edge_embedding_flavor="sum", layer_pooling="all", factored_rp=False, add_rp_edges="all",
+                 add_self_loops=False, vnode=False, update_edge_features=False, update_edge_features_pe=False,
+                 rwpe_k=16, rwpe_h=16, rwpe_cache=None, graphobs=False, shared_conv=True, pyg=True,
+                 hierarchical=False, tokengt=False, checkpoint=1, dual_net=False):
+        super().__init__()
+        if hierarchical or tokengt or dual_net or vnode or graph_pooling == "gap" or normalize:
+            raise NotImplementedError("hierarchical / TokenGT / dual-net / vnode / gap / normalised trunks are not "
+                                      "the graph-attention hot path (SURVEY section 2)")
+        self.pyg, self.conflicts, self.residual, self.normalize = pyg, conflicts, residual, normalize
+        self.max_n_nodes = max_n_nodes
+        self.input_dim_features_extractor = input_dim_features_extractor
+        self.layer_pooling = layer_pooling
+        self.rwpe_k = rwpe_k
+        self.rwpe_h = 0 if rwpe_k == 0 else rwpe_h
+        self.hierarchical, self.tokengt, self.dual_net = hierarchical, tokengt, dual_net
+        self.node_type_size = 2
+        if layer_pooling == "all":                                            # gnn_mp.py:100-105
+            self.features_dim = (input_dim_features_extractor
+                                 + (hidden_dim_features_extractor + self.rwpe_h) * (n_layers_features_extractor + 1)
+                                 + self.rwpe_h)
+        else:
+            self.features_dim = hidden_dim_features_extractor + self.rwpe_h
+        self.graphobs, self.factored_rp, self.add_rp_edges = graphobs, factored_rp, add_rp_edges
+        self.max_n_resources = max_n_resources
+        self.add_self_loops = True
+        self.hidden_dim = hidden_dim_features_extractor
+        self.graph_pooling = graph_pooling
+        self.n_layers_features_extractor = n_layers_features_extractor
+        self.vnode, self.shared_conv, self.checkpoint = vnode, shared_conv, checkpoint
+        self.edge_embedding_flavor = edge_embedding_flavor
+        H2 = hidden_dim_features_extractor - self.node_type_size
+        self.node_type_embedder = Compiled(nn.Embedding(4, self.node_type_size))          # :135-139
+        self.pool_node_embedder = Compiled(nn.Embedding(1, H2))                           # :141-145
+        if conflicts == "node":
+            self.resource_node_embedder = Compiled(nn.Linear(3, H2))                      # :178-183
+        self.gnn = Compiled(GnnFlat(input_dim_features_extractor, hidden_dim_features_extractor,
+                                    n_layers_features_extractor, n_mlp_layers_features_extractor, layer_pooling,
+                                    n_attention_heads, normalize, activation_features_extractor, residual, rwpe_k,
+                                    self.rwpe_h, update_edge_features, update_edge_features_pe, shared_conv,
+                                    edge_embedding_flavor, max_n_resources, add_rp_edges, factored_rp, pyg,
+                                    checkpoint))                                          # :246-266
+        self.features_embedder = Compiled(MLP(n_layers=n_mlp_layers_features_extractor,
+                                              input_dim=input_dim_features_extractor, hidden_dim=H2,
+                                              output_dim=H2, norm=normalize,
+                                              activation=activation_features_extractor))  # :292-300
+
+    def embed_nodes(self, orig_features, num_nodes, poolnodes, resource_nodes, res_cal_id):
+        """gnn_mp.py:342-398: the ``[N_total, hidden]`` input of the first layer, assembled with ONE
+        concatenation per node class (the reference fills a ``torch.empty`` buffer slice by slice)."""
+        dev, dt = orig_features.device, orig_features.dtype
+        nte = self.node_type_embedder._orig_mod.weight
+        emb = self.features_embedder(orig_features[:num_nodes])                            # :349-351
+        parts = [torch.cat((nte[2].expand(num_nodes, -1), emb), dim=1)]                   # :346-351
+        n_res = 0 if resource_nodes is None else len(resource_nodes)
+        n_pool = 0 if poolnodes is None else len(poolnodes)
+        # node order of the builder: tasks | resource nodes | pool nodes (rewiring.py:314-361)
+        if self.conflicts == "node" and n_res:                                             # :392-398
+            r = self.resource_node_embedder(res_cal_id.to(device=dev, dtype=dt))
+            parts.append(torch.cat((nte[1].expand(n_res, -1), r), dim=1))
+        if n_pool:                                                                         # :353-359
+            p = self.pool_node_embedder._orig_mod.weight[0]
+            parts.append(torch.cat((nte[0], p)).expand(n_pool, -1))
+        return torch.cat(parts, dim=0) if len(parts) > 1 else parts[0]
+
+    def forward(self, obs):
+        (g, batch_size, num_nodes, n_nodes, poolnodes, resource_nodes, vnodes, res_cal_id, pe) = obs
+        g = g.to(next(self.parameters()).device)                                           # :331
+        features = g.ndata("feat")
+        features[:, 2:4] = 0                                                               # :337 (in place, like the reference)
+        orig_features = features
+        n_total = orig_features.shape[0]
+        n_res = 0 if resource_nodes is None else len(resource_nodes)
+        n_pool = 0 if poolnodes is None else len(poolnodes)
+        if num_nodes + n_res + n_pool != n_total:
+            raise _lib.B200GatError("node layout is not tasks | resource nodes | pool nodes")
+        if self.graph_pooling == "learninv" and n_pool == 0:
+            raise _lib.B200GatError("learned pooling without pool nodes")
+        features = self.embed_nodes(orig_features, num_nodes, poolnodes, resource_nodes, res_cal_id)
+        features = self.gnn(g, features, pe)                                               # :414
+        if self.layer_pooling == "all":
+            features = torch.cat([orig_features] + features, dim=-1)                       # :419-425
+        node_features = features[:num_nodes]
+        counts = [n_nodes] * batch_size if isinstance(n_nodes, int) else list(n_nodes)
+        equal = len(set(counts)) <= 1
+        F = node_features.shape[1]
+        if self.graph_pooling in ("learn", "learninv"):                                    # :453-457, :485-489
+            graph_embedding = features[num_nodes + n_res: num_nodes + n_res + n_pool]
+        elif self.graph_pooling in ("max", "avg"):                                         # :430-452, :475-482
+            if equal:
+                nf3 = node_features.reshape(batch_size, counts[0], F)
+                graph_embedding = nf3.max(dim=1)[0] if self.graph_pooling == "max" else nf3.mean(dim=1)
+            else:
+                lengths = torch.tensor(counts, device=node_features.device)
+                graph_embedding = torch.segment_reduce(node_features, "max" if self.graph_pooling == "max" else "mean",
+                                                       lengths=lengths, axis=0)
+        else:
+            raise Exception(f"Graph pooling {self.graph_pooling} not recognized. Only accepted pooling are max and avg")
+        if equal and counts and counts[0] == self.max_n_nodes:
+            node_features = node_features.reshape(batch_size, self.max_n_nodes, F)
+        else:                                                                              # :459-470, :495-500
+            dest = _pad_rows_index(counts, self.max_n_nodes, node_features.device)
+            node_features = node_features.new_zeros((batch_size * self.max_n_nodes, F)).index_copy(
+                0, dest, node_features).reshape(batch_size, self.max_n_nodes, F)
+        return node_features, graph_embedding.reshape(batch_size, 1, -1)

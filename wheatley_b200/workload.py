@@ -147,3 +147,65 @@ def jssp_observation_batch(n_j, n_m, batch, seed0=0, progress=0.0, n_features=No
                 edge_index=torch.from_numpy(ei),
                 n_nodes=torch.tensor([o["n_nodes"] for o in obs], dtype=torch.int64),
                 n_edges=torch.tensor([o["n_edges"] for o in obs], dtype=torch.int64))
+
+
+# ------------------------------------------------------------------------- PSP / PyG flavour
+def psp_taillard_graph(n_j: int, n_m: int, seed: int, n_rp: int = 0, progress: float = 0.0):
+    """One env-side observation of a Taillard JSSP modelled as an RCPSP the way ``psp/utils/taillard_rcpsp.py:46-160``
+    does (how every JSSP config runs today): node 0 = source, node 1 + j*n_m + i = operation i of job j,
+    last node = sink; ``prec`` edges in ``problem_edges`` order (psp/env/gstate.py:98-103: by source node, the
+    source's n_j successors first); one renewable resource per machine with capacity 1, so
+    ``resources[node, machine] = 1`` (gstate.py:260-277).  ``feat [N, 16]``: the columns of
+    agent_graph_observation.py:66-86 with seeded values (only the numerics depend on them); ``n_rp``
+    resource-priority edges between operations of one machine with 4 attributes (gstate.py:891-934).
+    Returns the dict ``wheatley_b200.wire.PspObsLayout.encode`` takes.  ``psp_taillard_graph(4, 4, s)`` has the
+    shape of ``instances/psp/272/272.sm`` (18 jobs incl. source / sink, 4 resources)."""
+    _, machines = taillard_instance(n_j, n_m, seed)
+    N = n_j * n_m + 2
+    ids = 1 + np.arange(n_j * n_m).reshape(n_j, n_m)
+    nxt = np.concatenate([ids[:, 1:], np.full((n_j, 1), N - 1)], axis=1)
+    prec = np.concatenate([np.stack([np.zeros(n_j, np.int64), ids[:, 0]]),
+                           np.stack([ids.reshape(-1), nxt.reshape(-1)])], axis=1).astype(np.int64)
+    resources = np.zeros((N, n_m), np.float32)
+    resources[ids.reshape(-1), machines.reshape(-1)] = 1.0
+    rng = np.random.default_rng(seed + 104729)
+    feat = rng.random((N, 16), dtype=np.float32)
+    n_aff = int(round(progress * N))
+    feat[:, 0] = 0.0
+    feat[:n_aff, 0] = 1.0                                  # affected
+    feat[:, 1] = (rng.random(N) < 0.3).astype(np.float32)  # selectable
+    feat[:, 2] = np.concatenate([[0], 1 + np.arange(n_j * n_m), [N - 1]]).astype(np.float32)   # job id
+    feat[:, 3] = 0.0
+    feat[0, 3], feat[-1, 3] = -1.0, 1.0                    # type: source / sink
+    feat[:, 13] = 0.0                                      # has_due_date
+    feat[:, 15] = (np.arange(N) < n_aff).astype(np.float32)   # past
+    rp = np.zeros((2, 0), np.int64)
+    rp_r = np.zeros((0, 4), np.float32)
+    if n_rp:
+        m = rng.integers(0, n_m, n_rp)
+        flat_m = machines.reshape(-1)
+        s, d = [], []
+        for mm in m:
+            users = ids.reshape(-1)[flat_m == mm]
+            a, b = rng.choice(users, 2, replace=False)
+            s.append(a); d.append(b)
+        rp = np.array([s, d], dtype=np.int64)
+        rp_r = np.concatenate([m[:, None].astype(np.float32), rng.random((n_rp, 3), dtype=np.float32)], axis=1)
+    return dict(feat=feat, resources=resources, res_cal=np.zeros((n_m, 3), np.float32), prec=prec, rp=rp, rp_r=rp_r)
+
+
+def psp_sizes_expected(n_j, n_m, conflicts="node", pooling=True):
+    """(nodes, edges) per graph at t = 0, SURVEY 8d table (PyG flavour)."""
+    N = n_j * n_m + 2
+    prec = n_j * (n_m + 1)
+    e = 2 * prec + N
+    n = N
+    if conflicts == "node":
+        n += n_m
+        e += 2 * n_j * n_m
+    elif conflicts == "clique":
+        e += n_m * n_j * (n_j - 1)
+    if pooling:
+        n += 1
+        e += N + (n_m if conflicts == "node" else 0) + 1
+    return n, e
