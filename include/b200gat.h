@@ -483,6 +483,84 @@ int b200gat_mlp_fwd(const b200gat_mlp* m, void* stream);
 int64_t b200gat_mlp_bwd_workspace_elems(const b200gat_mlp* m, const b200gat_mlp_grads* g);
 int b200gat_mlp_bwd(const b200gat_mlp* m, const b200gat_mlp_grads* g, void* stream);
 
+/* ------------------------------------------------------------------ trunk readout
+ * Replaces the tail of the reference's trunks: torch.cat over the per-layer node tensors
+ * (psp/models/gnn_mp.py:419-425, jssp/models/gnn_dgl.py:401), the per-graph Python loop that slices, pools
+ * (torch.max(dim=0) / matmul with 1/n / the learned pool node's row) and F.pad's every graph to max_n_nodes
+ * followed by torch.stack (gnn_mp.py:429-470,472-500; gnn_dgl.py:402-425).  The sources are read where they lie:
+ *   node_features  [B, max_n_nodes, F] = rows row_start[b] .. row_start[b+1]-1 of concat_i src_i, zero rows after
+ *   graph_embedding[B, F]              = max / mean over the graph's rows, or row pool_row0 + b of the concat
+ *   argmax         [B, F] int32        = first maximal row (local index) per column, kept for the backward
+ * (the reference's gradient follows torch.max's index, the first maximum on the CPU).
+ * Backward writes every source's gradient [n_rows_total, width_i] completely (rows nothing reads get zeros);
+ * g_src[i] == NULL skips a source (the raw input features need no gradient). */
+#define B200GAT_READOUT_MAX_SRC 16
+#define B200GAT_READOUT_NONE 0
+#define B200GAT_READOUT_MAX 1
+#define B200GAT_READOUT_AVG 2
+#define B200GAT_READOUT_ROWS 3 /* graph_embedding[b] = row pool_row0 + b ("learn" / "learninv" pool nodes) */
+typedef struct b200gat_readout {
+  int32_t n_src;
+  const float* src[B200GAT_READOUT_MAX_SRC]; /* [rows, width[i]], row stride ld[i]                          */
+  int32_t width[B200GAT_READOUT_MAX_SRC];
+  int64_t ld[B200GAT_READOUT_MAX_SRC];
+  int32_t n_graphs, max_n_nodes;
+  const int32_t* row_start;                  /* device [B+1]: exclusive prefix of the graphs' task-node counts */
+  int64_t n_task_rows;                       /* host copy of row_start[B]                                     */
+  int32_t pooling;                           /* B200GAT_READOUT_*                                             */
+  int64_t pool_row0;                         /* ROWS: pool node of graph b is row pool_row0 + b               */
+} b200gat_readout;
+int b200gat_readout_fwd(const b200gat_readout* r, float* node_features, float* graph_embedding, int32_t* argmax,
+                        void* stream);
+int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node_features, const float* g_graph_embedding,
+                        const int32_t* argmax, float* const* g_src, int64_t n_rows_total, void* stream);
+
+/* ------------------------------------------------------------------ PPO update tail
+ * b200gat_gae replaces the Python loop over the rollout steps of alg/ppo.py:276-299:
+ *   delta_t = (r_t + gamma * V_{t+1} * nonterminal_{t+1} - V_t) / sigma
+ *   A_t     = delta_t + gamma * lambda * nonterminal_{t+1} * A_{t+1} ;  returns = A + V
+ * rewards / values / advantages / returns [T, E, R] (steps, envs, reward components), dones [T, E],
+ * next_value [E, R], next_done [E]; same operation order as the reference, no fused multiply-adds: bit-exact
+ * against the fp32 torch loop. */
+int b200gat_gae(const float* rewards, const float* values, const float* dones, const float* next_value,
+                const float* next_done, int32_t n_steps, int32_t n_envs, int32_t reward_dim, float gamma,
+                float gae_lambda, float sigma, float* advantages, float* returns, void* stream);
+
+/* Clipped-PPO minibatch loss of alg/ppo.py:582-705 and its gradient in ONE launch:
+ *   ratio = exp(logprob - old_logprob) ; a = norm_adv ? (adv - mean) / (std + 1e-8) : adv   (:602-605, unbiased std)
+ *   pg_loss = mean(max(-a ratio, -a clamp(ratio, 1 - clip, 1 + clip)))   (:608-620; clip_coef < 0: mean(-a ratio))
+ *   v_loss  = mse / l1 of (value, returns)  (:632-641);  clip_vloss: mean(max(v_loss_unclipped (the scalar mean),
+ *             per-sample loss of old_value + clamp(value - old_value, -clip, clip)))  (:665-690; the reference
+ *             hard-codes clip_vloss = False, alg/ppo.py:89)
+ *   loss    = pg_loss - ent_coef * mean(entropy) + vf_coef * v_loss      (:701-705, update > 0)
+ * stats [8] = {pg_loss, v_loss, entropy_loss, approx_kl (:588-590), clipfrac (:591-597), mean |ratio - 1| (:616),
+ *              advantage mean, advantage std}: the values the reference reads back with .item() one by one.
+ * g_logprob / g_entropy / g_value [n] = d loss / d input (the loss is a scalar: the autograd backward is a scale).
+ * Sharded minibatch: `moments` = device double[3] {count, sum, sum of squares} of the advantages of the
+ * GLOBAL minibatch (b200gat_ppo_adv_moments on every rank, all-reduced): normalisation then uses the global mean /
+ * std, and loss, stats and gradients are this rank's share sum_local / count_global, so a SUM all-reduce of the
+ * gradients (and of loss / stats) gives exactly the single-process values. */
+#define B200GAT_CRITIC_L2 0
+#define B200GAT_CRITIC_L1 1
+#define B200GAT_CRITIC_SL1 2 /* clipped value loss only (:679-684) */
+typedef struct b200gat_ppo_loss_args {
+  int32_t n;
+  const float* logprob;     /* [n] new log-probabilities of the taken actions          */
+  const float* old_logprob; /* [n]                                                     */
+  const float* advantages;  /* [n] aggregated over reward components                   */
+  const float* entropy;     /* [n] or NULL                                             */
+  const float* value;       /* [n] new values                                          */
+  const float* returns;     /* [n]                                                     */
+  const float* old_values;  /* [n], clip_vloss only                                    */
+  float clip_coef;          /* < 0: None                                               */
+  int32_t norm_adv, clip_vloss, critic_loss;
+  float ent_coef, vf_coef;
+  const double* moments;    /* device double[3] or NULL (local statistics)             */
+} b200gat_ppo_loss_args;
+int b200gat_ppo_adv_moments(const float* advantages, int32_t n, double* moments, void* stream);
+int b200gat_ppo_loss(const b200gat_ppo_loss_args* p, float* loss, float* stats, float* g_logprob, float* g_entropy,
+                     float* g_value, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

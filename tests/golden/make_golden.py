@@ -18,6 +18,7 @@ What is executed verbatim from the reference tree:
   * psp/models/agent.py Agent._obs_as_tensor_graph / Agent.preprocess + psp/models/rewiring.py +
     psp/models/agent_graph_observation.py (on oracle/shims/psp_graph.py, a stand-in for the HeteroData container)
   * psp/models/gnn_mp.py GnnMP.forward + psp/models/gnn_flat.py GnnFlat.forward (torch.compile on the eager backend)
+  * alg/ppo.py:276-299 (GAE loop) and :582-705 (minibatch loss): the source lines themselves, exec'ed
 
 Outputs: small .npz files (float64 for the layers so that the comparison with
 the oracle is tight; float32 where the reference module is float32-only).
@@ -681,7 +682,98 @@ def golden_gnn_mp(fname: str, seed: int):
     np.savez_compressed(os.path.join(HERE, fname), **d)
 
 
+# ---------------------------------------------------------------- N4: GAE + PPO minibatch loss
+def _reference_lines(path, first, last):
+    """Source lines first..last (1-based, inclusive) of a reference file, dedented: code that sits in the middle
+    of a long method (PPO.collect_rollouts / PPO.train, module not importable without gymnasium) is executed from
+    the reference tree itself, in a namespace that supplies the variables the method has in scope."""
+    import textwrap
+    with open(os.path.join("/root/reference", path)) as f:
+        lines = f.readlines()[first - 1:last]
+    return textwrap.dedent("".join(lines))
+
+
+def golden_ppo(fname: str, seed: int):
+    gen = torch.Generator().manual_seed(seed)
+    out = {}
+    # ---- GAE: alg/ppo.py:276-299
+    src = _reference_lines("alg/ppo.py", 276, 299)
+    assert src.startswith("with torch.no_grad():") and "lastgaelam" in src and "returns = advantages + values" in src
+    code = compile(src, "/root/reference/alg/ppo.py:276-299", "exec")
+    for tag, (T, E, R, gamma, lam, sigma) in dict(a=(7, 3, 1, 1.0, 1.0, 1.0), b=(40, 5, 2, 0.99, 0.95, 1.7),
+                                                  c=(1, 4, 1, 0.9, 0.8, 1.0)).items():
+        rewards, values = torch.randn(T, E, R, generator=gen), torch.randn(T, E, R, generator=gen)
+        dones = (torch.rand(T, E, generator=gen) < 0.2).float()
+        next_value, next_done = torch.randn(E, R, generator=gen), (torch.rand(E, generator=gen) < 0.3).float()
+        ns = dict(torch=torch, rewards=rewards, values=values, dones=dones, next_value=next_value,
+                  next_done=next_done, sigma=sigma,
+                  self=types.SimpleNamespace(num_steps=T, gamma=gamma, gae_lambda=lam))
+        exec(code, ns)
+        out.update({f"gae.{tag}.rewards": np_(rewards), f"gae.{tag}.values": np_(values), f"gae.{tag}.dones": np_(dones),
+                    f"gae.{tag}.next_value": np_(next_value), f"gae.{tag}.next_done": np_(next_done),
+                    f"gae.{tag}.cfg": np.array([gamma, lam, sigma]), f"gae.{tag}.advantages": np_(ns["advantages"]),
+                    f"gae.{tag}.returns": np_(ns["returns"])})
+    # ---- minibatch loss: alg/ppo.py:582-705
+    src = _reference_lines("alg/ppo.py", 582, 705)
+    assert src.startswith("logratio = newlogprob") and src.rstrip().endswith(")") and "uniform_loss" in src
+    code = compile(src, "/root/reference/alg/ppo.py:582-705", "exec")
+    cases = dict(
+        default=dict(B=64, clip_coef=0.2, norm_adv=True, clip_vloss=False, critic_loss="l2", ent_coef=0.0, vf_coef=0.5, update=3),
+        entropy_l1=dict(B=37, clip_coef=0.1, norm_adv=True, clip_vloss=False, critic_loss="l1", ent_coef=0.05, vf_coef=2.0, update=2),
+        no_norm=dict(B=16, clip_coef=0.3, norm_adv=False, clip_vloss=False, critic_loss="l2", ent_coef=0.01, vf_coef=1.0, update=1),
+        espo=dict(B=33, clip_coef=None, norm_adv=True, clip_vloss=False, critic_loss="l2", ent_coef=0.02, vf_coef=0.5, update=5),
+        vclip_l2=dict(B=50, clip_coef=0.2, norm_adv=True, clip_vloss=True, critic_loss="l2", ent_coef=0.0, vf_coef=0.5, update=2),
+        vclip_sl1=dict(B=41, clip_coef=0.15, norm_adv=True, clip_vloss=True, critic_loss="sl1", ent_coef=0.03, vf_coef=0.7, update=2),
+        warmup=dict(B=24, clip_coef=0.2, norm_adv=True, clip_vloss=False, critic_loss="l2", ent_coef=0.0, vf_coef=0.5, update=0),
+        single=dict(B=1, clip_coef=0.2, norm_adv=True, clip_vloss=False, critic_loss="l2", ent_coef=0.1, vf_coef=0.5, update=4),
+    )
+    for tag, c in cases.items():
+        B, n_act = c["B"], 9
+        newlogprob = (-torch.rand(B, generator=gen) * 3).requires_grad_(True)
+        old = (newlogprob.detach() + 0.4 * torch.randn(B, generator=gen))
+        entropy = torch.rand(B, generator=gen).requires_grad_(True)
+        newvalue = torch.randn(B, 1, generator=gen).requires_grad_(True)
+        returns, old_values = torch.randn(B, 1, generator=gen), torch.randn(B, 1, generator=gen)
+        adv = torch.randn(B, 1, generator=gen)
+        logits = torch.randn(B, n_act, generator=gen).requires_grad_(True)
+        unmasked = torch.distributions.Categorical(logits=logits)
+        spec = types.SimpleNamespace(two_hot=None, hl_gauss=None, symlog=False)
+        agent = types.SimpleNamespace(agent_specification=spec, aggregate_reward=lambda r: r.squeeze(1) * 1.0)
+        self_ = types.SimpleNamespace(clip_coef=c["clip_coef"], target_kl=0.04, norm_adv=c["norm_adv"],
+                                      critic_loss=c["critic_loss"], clip_vloss=c["clip_vloss"],
+                                      ent_coef=c["ent_coef"], vf_coef=c["vf_coef"])
+        ns = dict(torch=torch, nn=torch.nn, np=np, self=self_, agent=agent, newlogprob=newlogprob,
+                  batched_logprobs=old, train_device="cpu", approx_kl_divs=[], clipfracs=[],
+                  approx_kl_divs_on_epoch=[], batched_advantages=adv, max_espo_dev=0, newvalue=newvalue,
+                  batched_returns=returns, batched_values=old_values, entropy=entropy, update=c["update"],
+                  unmasked_distrib=unmasked)
+        if c["critic_loss"] == "sl1":
+            # :632-641 define the unclipped term for l2 / l1 only; give it the value :679-684 use for the clipped one
+            ns["v_loss_unclipped"] = torch.nn.functional.smooth_l1_loss(newvalue, returns)
+        exec(code, ns)
+        loss = ns["loss"]
+        g = torch.autograd.grad(loss, [newlogprob, entropy, newvalue, logits], allow_unused=True)
+        z = lambda t, like: np_(torch.zeros_like(like) if t is None else t)
+        out.update({f"loss.{tag}.logprob": np_(newlogprob), f"loss.{tag}.old_logprob": np_(old),
+                    f"loss.{tag}.entropy": np_(entropy), f"loss.{tag}.value": np_(newvalue),
+                    f"loss.{tag}.returns": np_(returns), f"loss.{tag}.old_values": np_(old_values),
+                    f"loss.{tag}.advantages": np_(adv), f"loss.{tag}.logits": np_(logits),
+                    f"loss.{tag}.cfg": np.array([str(c[k]) for k in ("clip_coef", "norm_adv", "clip_vloss", "critic_loss",
+                                                                     "ent_coef", "vf_coef", "update")]),
+                    f"loss.{tag}.loss": np_(loss), f"loss.{tag}.pg_loss": np_(ns["pg_loss"]),
+                    f"loss.{tag}.v_loss": np_(ns["v_loss"]), f"loss.{tag}.entropy_loss": np_(ns["entropy_loss"]),
+                    f"loss.{tag}.approx_kl": np.array(ns["approx_kl_divs"][-1]),
+                    f"loss.{tag}.clipfrac": np.array(ns["clipfracs"][-1] if ns["clipfracs"] else 0.0),
+                    f"loss.{tag}.g_logprob": z(g[0], newlogprob), f"loss.{tag}.g_entropy": z(g[1], entropy),
+                    f"loss.{tag}.g_value": z(g[2], newvalue), f"loss.{tag}.g_logits": z(g[3], logits)})
+    out["loss.tags"] = np.array(list(cases))
+    np.savez_compressed(os.path.join(HERE, fname), **out)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "ppo":
+        golden_ppo("ppo.npz", 22)
+        sys.exit(0)
     golden_eegat(False, "eegat.npz", 11)
     golden_eegat(True, "eegat_edge_scoring.npz", 12)
     golden_gatv3("gatv3.npz", 13)
@@ -693,4 +785,5 @@ if __name__ == "__main__":
     golden_gatv2("gatv2.npz", 19)
     golden_psp_batch("psp_batch.npz", 20)
     golden_gnn_mp("gnn_mp.npz", 21)
+    golden_ppo("ppo.npz", 22)
     print("golden fixtures written to", HERE)

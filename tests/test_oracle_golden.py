@@ -276,3 +276,32 @@ def test_gnn_mp_oracle_matches_reference_trunk(golden_dir, tag):
         ref = g[f"{tag}.g.{k}"]
         got = np.zeros_like(ref) if p.grad is None else p.grad.numpy()
         np.testing.assert_allclose(got, ref, rtol=3e-4, atol=3e-5 * max(1.0, np.abs(ref).max()), err_msg=k)
+
+
+def test_ppo_oracle_matches_reference_lines(golden_dir):
+    """oracle/ppo_oracle.py against ppo.npz = the reference's own source lines alg/ppo.py:276-299 (GAE) and
+    :582-705 (minibatch loss) exec'ed by make_golden.py: bit-exact (same torch ops in the same order)."""
+    from oracle import ppo_oracle as po
+    g = np.load(os.path.join(golden_dir, "ppo.npz"))
+    T = lambda a: torch.from_numpy(np.asarray(a))
+    for tag in "abc":
+        gamma, lam, sigma = (float(x) for x in g[f"gae.{tag}.cfg"])
+        a, r = po.gae(T(g[f"gae.{tag}.rewards"]), T(g[f"gae.{tag}.values"]), T(g[f"gae.{tag}.dones"]),
+                      T(g[f"gae.{tag}.next_value"]), T(g[f"gae.{tag}.next_done"]), gamma, lam, sigma)
+        assert torch.equal(a, T(g[f"gae.{tag}.advantages"])) and torch.equal(r, T(g[f"gae.{tag}.returns"]))
+    for tag in g["loss.tags"]:
+        c = g[f"loss.{tag}.cfg"]
+        lp, ent, v, logits = (T(g[f"loss.{tag}.{k}"]).requires_grad_(True) for k in ("logprob", "entropy", "value", "logits"))
+        loss, st = po.ppo_loss(lp, ent, v, T(g[f"loss.{tag}.old_logprob"]), T(g[f"loss.{tag}.advantages"]).squeeze(1),
+                               T(g[f"loss.{tag}.returns"]), T(g[f"loss.{tag}.old_values"]),
+                               clip_coef=None if c[0] == "None" else float(c[0]), norm_adv=c[1] == "True",
+                               clip_vloss=c[2] == "True", critic_loss=str(c[3]), ent_coef=float(c[4]),
+                               vf_coef=float(c[5]), update=int(c[6]),
+                               unmasked_probs=torch.distributions.Categorical(logits=logits).probs)
+        assert torch.equal(loss.detach(), T(g[f"loss.{tag}.loss"])), tag
+        for k in ("pg_loss", "v_loss", "entropy_loss", "approx_kl", "clipfrac"):
+            assert torch.allclose(st[k].detach().float(), T(g[f"loss.{tag}.{k}"]).float(), rtol=0, atol=0), (tag, k)
+        gs = torch.autograd.grad(loss, [lp, ent, v, logits], allow_unused=True)
+        for got, like, k in zip(gs, (lp, ent, v, logits), ("g_logprob", "g_entropy", "g_value", "g_logits")):
+            got = torch.zeros_like(like) if got is None else got
+            assert torch.equal(got, T(g[f"loss.{tag}.{k}"])), (tag, k)

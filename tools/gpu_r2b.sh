@@ -1,5 +1,10 @@
 #!/bin/bash
+# Round-2 second visit: whole GPU suite incl. the PSP flavour (a5 builder, GnnMP trunk), smoke, bench line.
 TAG=${1:-r2b}
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -q -x -k "psp or gnn_mp or trunk_golden or batch" > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${TAG}_pytest.log
-tail -25 gpurun_out/${TAG}_pytest.log
+timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${TAG}_pytest.log
+tail -30 gpurun_out/${TAG}_pytest.log
+timeout 300 python __graft_entry__.py smoke > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -4 gpurun_out/${TAG}_smoke.log
+timeout 600 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?"
+tail -3 gpurun_out/${TAG}_bench.err
+cat gpurun_out/${TAG}_bench.json | head -c 3000

@@ -29,6 +29,8 @@ SYMBOLS = (
     "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
     "b200gat_jssp_batch_edges", "b200gat_jssp_batch_build",
     "b200gat_psp_slot_words", "b200gat_psp_batch_sizes", "b200gat_psp_batch_build",
+    "b200gat_readout_fwd", "b200gat_readout_bwd",
+    "b200gat_gae", "b200gat_ppo_adv_moments", "b200gat_ppo_loss",
 )
 MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
@@ -126,6 +128,28 @@ class MlpGrads(C.Structure):
                 ("dz", C.c_void_p * 8), ("workspace", C.c_void_p), ("workspace_elems", C.c_int64)]
 
 
+READOUT_MAX_SRC = 16
+READOUT_NONE, READOUT_MAX, READOUT_AVG, READOUT_ROWS = 0, 1, 2, 3
+
+
+class Readout(C.Structure):
+    """``b200gat_readout`` (include/b200gat.h)."""
+    _fields_ = [("n_src", C.c_int32), ("src", C.c_void_p * 16), ("width", C.c_int32 * 16), ("ld", C.c_int64 * 16),
+                ("n_graphs", C.c_int32), ("max_n_nodes", C.c_int32), ("row_start", C.c_void_p),
+                ("n_task_rows", C.c_int64), ("pooling", C.c_int32), ("pool_row0", C.c_int64)]
+
+
+CRITIC = {"l2": 0, "l1": 1, "sl1": 2}
+
+
+class PpoLossArgs(C.Structure):
+    """``b200gat_ppo_loss_args`` (include/b200gat.h)."""
+    _fields_ = [("n", C.c_int32), ("logprob", C.c_void_p), ("old_logprob", C.c_void_p), ("advantages", C.c_void_p),
+                ("entropy", C.c_void_p), ("value", C.c_void_p), ("returns", C.c_void_p), ("old_values", C.c_void_p),
+                ("clip_coef", C.c_float), ("norm_adv", C.c_int32), ("clip_vloss", C.c_int32),
+                ("critic_loss", C.c_int32), ("ent_coef", C.c_float), ("vf_coef", C.c_float), ("moments", C.c_void_p)]
+
+
 class B200GatError(RuntimeError):
     pass
 
@@ -192,6 +216,12 @@ def _load():
     lib.b200gat_psp_slot_words.restype = i64
     lib.b200gat_psp_batch_sizes.argtypes = [po, vp]
     lib.b200gat_psp_batch_build.argtypes = [po, vp, vp, vp, vp, vp, vp, vp]
+    lib.b200gat_gae.argtypes = [vp] * 5 + [i32, i32, i32, f32, f32, f32, vp, vp, vp]
+    lib.b200gat_ppo_adv_moments.argtypes = [vp, i32, vp, vp]
+    lib.b200gat_ppo_loss.argtypes = [C.POINTER(PpoLossArgs), vp, vp, vp, vp, vp, vp]
+    rp = C.POINTER(Readout)
+    lib.b200gat_readout_fwd.argtypes = [rp, vp, vp, vp, vp]
+    lib.b200gat_readout_bwd.argtypes = [rp, vp, vp, vp, C.POINTER(C.c_void_p), i64, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",

@@ -18,7 +18,9 @@ from torch import nn
 
 from .edge_feats import TypedEdgeFeats, edge_tables
 from .eegatconv import EGATConv
+from ._lib import B200GatError
 from .mlp import MLP
+from .readout import readout
 
 
 class _SplitRows(torch.autograd.Function):
@@ -101,6 +103,10 @@ class GnnDGL(nn.Module):
 
     def node_embeddings(self, b: JsspBatch):
         """Concatenation of all layers' node embeddings ``[N_total, F]`` (gnn_dgl.py:339-401)."""
+        return torch.cat(self.layer_embeddings(b), dim=1)                       # :401
+
+    def layer_embeddings(self, b: JsspBatch):
+        """The list the reference concatenates at :401: input features, embedder output, every layer's output."""
         features = b.feat
         if self.graph_pooling == "learn" and b.poolnodes is not None:           # :341-344
             features = features.clone()
@@ -123,31 +129,19 @@ class GnnDGL(nn.Module):
             features = self.mlps[layer](h.flatten(start_dim=-2, end_dim=-1),
                                         residual=features_list[-1] if self.residual else None)
             features_list.append(features)
-        return torch.cat(features_list, dim=1)                                  # :401
+        return features_list
 
     def forward_split(self, b: JsspBatch):
         """``(node_features [B, max_n_nodes, F], graph_embedding [B, 1, F])`` - the pair the generic
         ``Agent`` unpacks (generic/agent.py:193)."""
-        features = self.node_embeddings(b)
-        NT = b.num_task_nodes
-        if self.graph_pooling in ("learn", "learninv"):
-            # the two row ranges of one tensor: split with one backward (a concatenation) instead of two
-            # slice backwards (each a zero-filled [N, F] tensor + a copy) and their sum
-            if features.shape[0] == NT + b.batch_size:
-                node_rows, graph_embedding = _SplitRows.apply(features, NT)
-            else:
-                node_rows, graph_embedding = features[:NT], features[NT: NT + b.batch_size]
-            node_features = node_rows.reshape(b.batch_size, b.n_nodes, -1)                  # :402-405
-        else:
-            node_features = features[:NT].reshape(b.batch_size, b.n_nodes, -1)
-            if self.graph_pooling == "max":
-                graph_embedding = node_features.max(dim=1)[0]
-            elif self.graph_pooling == "avg":
-                graph_embedding = node_features.mean(dim=1)
-            else:
-                raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
-        if self.max_n_nodes != node_features.shape[1]:       # (F.pad with nothing to pad still copies)
-            node_features = nn.functional.pad(node_features, (0, 0, 0, self.max_n_nodes - node_features.shape[1]))
+        # :401-425 in one pass (b200gat_readout_fwd, SURVEY 8f N3): no [N, F] concatenation, no row split, no pad
+        # copy - the per-layer tensors are read where they lie and every graph's rows land in their padded slot
+        if self.graph_pooling not in ("learn", "learninv", "max", "avg"):
+            raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
+        if b.num_task_nodes != b.batch_size * b.n_nodes:
+            raise B200GatError("GnnDGL needs equal-sized graphs (the reference reshapes to [B, n_nodes, F], :405)")
+        node_features, graph_embedding = readout(self.layer_embeddings(b), [b.n_nodes] * b.batch_size,
+                                                 self.max_n_nodes, self.graph_pooling, pool_row0=b.num_task_nodes)
         return node_features, graph_embedding.reshape(b.batch_size, 1, -1)
 
     def forward(self, b: JsspBatch):

@@ -15,7 +15,6 @@ Differences, all inside the boundary:
   and a 5-row affine map instead of ``[E, hidden]`` (psp/models/edge_embedder.py:130-143, SURVEY section 7);
 * the residual add (gnn_flat.py:228-230) rides in the MLP's last GEMM epilogue; the per-graph pad to
   ``max_n_nodes`` (gnn_mp.py:459-470: a Python loop of ``F.pad`` + ``stack``) is one indexed copy."""
-import numpy as np
 import torch
 from torch import nn
 
@@ -23,6 +22,7 @@ from . import _lib
 from .edge_feats import PspEdgeEmbedder
 from .graph_conv import GraphConv
 from .mlp import MLP
+from .readout import readout
 
 
 class Compiled(nn.Module):
@@ -94,17 +94,6 @@ class GnnFlat(nn.Module):
             if self.layer_pooling == "all":
                 features_list.append(features)                                # :249-253
         return features_list if self.layer_pooling == "all" else features
-
-
-def _pad_rows_index(counts, max_n_nodes, device):
-    """Row of the ``[B * max_n_nodes]`` padded layout each task node goes to (host arithmetic, one small copy)."""
-    counts = np.asarray(counts, dtype=np.int64)
-    if counts.size and int(counts.max()) > max_n_nodes:
-        raise _lib.B200GatError(f"a graph has {int(counts.max())} nodes, max_n_nodes is {max_n_nodes}")
-    starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
-    local = np.arange(int(counts.sum())) - np.repeat(starts, counts)
-    dest = np.repeat(np.arange(len(counts)) * max_n_nodes, counts) + local
-    return torch.from_numpy(dest).to(device, non_blocking=True)
 
 
 class GnnMP(nn.Module):
@@ -186,32 +175,17 @@ class GnnMP(nn.Module):
         n_pool = 0 if poolnodes is None else len(poolnodes)
         if num_nodes + n_res + n_pool != n_total:
             raise _lib.B200GatError("node layout is not tasks | resource nodes | pool nodes")
-        if self.graph_pooling == "learninv" and n_pool == 0:
+        if self.graph_pooling in ("learn", "learninv") and n_pool == 0:
             raise _lib.B200GatError("learned pooling without pool nodes")
         features = self.embed_nodes(orig_features, num_nodes, poolnodes, resource_nodes, res_cal_id)
         features = self.gnn(g, features, pe)                                               # :414
-        if self.layer_pooling == "all":
-            features = torch.cat([orig_features] + features, dim=-1)                       # :419-425
-        node_features = features[:num_nodes]
+        # :419-500 in one pass (b200gat_readout_fwd): the concatenation of all layers is never materialised, every
+        # graph's rows land in their padded slot, max / avg pooling (first-maximum gradient like torch.max on the
+        # CPU) or the learned pool node's row becomes the graph embedding
+        sources = [orig_features] + features if self.layer_pooling == "all" else [features]
         counts = [n_nodes] * batch_size if isinstance(n_nodes, int) else list(n_nodes)
-        equal = len(set(counts)) <= 1
-        F = node_features.shape[1]
-        if self.graph_pooling in ("learn", "learninv"):                                    # :453-457, :485-489
-            graph_embedding = features[num_nodes + n_res: num_nodes + n_res + n_pool]
-        elif self.graph_pooling in ("max", "avg"):                                         # :430-452, :475-482
-            if equal:
-                nf3 = node_features.reshape(batch_size, counts[0], F)
-                graph_embedding = nf3.max(dim=1)[0] if self.graph_pooling == "max" else nf3.mean(dim=1)
-            else:
-                lengths = torch.tensor(counts, device=node_features.device)
-                graph_embedding = torch.segment_reduce(node_features, "max" if self.graph_pooling == "max" else "mean",
-                                                       lengths=lengths, axis=0)
-        else:
+        if self.graph_pooling not in ("learn", "learninv", "max", "avg"):
             raise Exception(f"Graph pooling {self.graph_pooling} not recognized. Only accepted pooling are max and avg")
-        if equal and counts and counts[0] == self.max_n_nodes:
-            node_features = node_features.reshape(batch_size, self.max_n_nodes, F)
-        else:                                                                              # :459-470, :495-500
-            dest = _pad_rows_index(counts, self.max_n_nodes, node_features.device)
-            node_features = node_features.new_zeros((batch_size * self.max_n_nodes, F)).index_copy(
-                0, dest, node_features).reshape(batch_size, self.max_n_nodes, F)
+        node_features, graph_embedding = readout(sources, counts, self.max_n_nodes, self.graph_pooling,
+                                                 pool_row0=num_nodes + n_res)
         return node_features, graph_embedding.reshape(batch_size, 1, -1)
