@@ -31,6 +31,8 @@ SYMBOLS = (
     "b200gat_psp_slot_words", "b200gat_psp_batch_sizes", "b200gat_psp_batch_build",
     "b200gat_readout_fwd", "b200gat_readout_bwd",
     "b200gat_gae", "b200gat_ppo_adv_moments", "b200gat_ppo_loss",
+    "b200gat_trunk_supported", "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems",
+    "b200gat_trunk_fwd", "b200gat_trunk_bwd",
 )
 MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
@@ -139,6 +141,38 @@ class Readout(C.Structure):
                 ("n_task_rows", C.c_int64), ("pooling", C.c_int32), ("pool_row0", C.c_int64)]
 
 
+TRUNK_MAX_LAYERS = 16
+
+
+class TrunkLayer(C.Structure):
+    """``b200gat_trunk_layer`` (include/b200gat.h)."""
+    _fields_ = [("n_proj", C.c_int32), ("Wp", C.c_void_p * 3), ("bp", C.c_void_p * 3), ("attn", Attn),
+                ("ef", EdgeFeats), ("n_mlp", C.c_int32), ("dims", C.c_int32 * 9), ("W", C.c_void_p * 8),
+                ("b", C.c_void_p * 8), ("P", C.c_void_p), ("conv_out", C.c_void_p), ("s_save", C.c_void_p),
+                ("m_save", C.c_void_p), ("l_save", C.c_void_p), ("agg_save", C.c_void_p), ("s_dense", C.c_void_p),
+                ("z", C.c_void_p * 8), ("h", C.c_void_p * 8), ("y", C.c_void_p)]
+
+
+class Trunk(C.Structure):
+    """``b200gat_trunk`` (include/b200gat.h)."""
+    _fields_ = [("n_layers", C.c_int32), ("in_dim", C.c_int32), ("residual", C.c_int32), ("n_nodes", C.c_int64),
+                ("graph", C.POINTER(Graph)), ("x0", C.c_void_p), ("wcat", C.c_void_p),
+                ("layer", TrunkLayer * TRUNK_MAX_LAYERS)]
+
+
+class TrunkLayerGrads(C.Structure):
+    """``b200gat_trunk_layer_grads`` (include/b200gat.h)."""
+    _fields_ = [("g_y", C.c_void_p), ("dWp", C.c_void_p), ("dbp", C.c_void_p), ("g_attn", C.c_void_p),
+                ("g_table", C.c_void_p), ("g_affine", C.c_void_p), ("g_out_bias", C.c_void_p),
+                ("dW", C.c_void_p * 8), ("db", C.c_void_p * 8)]
+
+
+class TrunkGrads(C.Structure):
+    """``b200gat_trunk_grads`` (include/b200gat.h)."""
+    _fields_ = [("g_x0", C.c_void_p), ("workspace", C.c_void_p), ("workspace_elems", C.c_int64),
+                ("layer", TrunkLayerGrads * TRUNK_MAX_LAYERS)]
+
+
 CRITIC = {"l2": 0, "l1": 1, "sl1": 2}
 
 
@@ -219,6 +253,14 @@ def _load():
     lib.b200gat_gae.argtypes = [vp] * 5 + [i32, i32, i32, f32, f32, f32, vp, vp, vp]
     lib.b200gat_ppo_adv_moments.argtypes = [vp, i32, vp, vp]
     lib.b200gat_ppo_loss.argtypes = [C.POINTER(PpoLossArgs), vp, vp, vp, vp, vp, vp]
+    tp, tg = C.POINTER(Trunk), C.POINTER(TrunkGrads)
+    lib.b200gat_trunk_supported.argtypes = [tp]
+    lib.b200gat_trunk_wcat_elems.argtypes = [tp]
+    lib.b200gat_trunk_wcat_elems.restype = i64
+    lib.b200gat_trunk_bwd_workspace_elems.argtypes = [tp]
+    lib.b200gat_trunk_bwd_workspace_elems.restype = i64
+    lib.b200gat_trunk_fwd.argtypes = [tp, vp]
+    lib.b200gat_trunk_bwd.argtypes = [tp, tg, vp]
     rp = C.POINTER(Readout)
     lib.b200gat_readout_fwd.argtypes = [rp, vp, vp, vp, vp]
     lib.b200gat_readout_bwd.argtypes = [rp, vp, vp, vp, C.POINTER(C.c_void_p), i64, vp]
@@ -228,7 +270,8 @@ def _load():
                         "b200gat_timing_enable", "b200gat_node_order_scratch_elems",
                         "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
                         "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
-                        "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges", "b200gat_psp_slot_words"):
+                        "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges", "b200gat_psp_slot_words",
+                        "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems"):
             fn.restype = C.c_int
     return lib
 

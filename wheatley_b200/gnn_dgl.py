@@ -17,10 +17,11 @@ import torch
 from torch import nn
 
 from .edge_feats import TypedEdgeFeats, edge_tables
-from .eegatconv import EGATConv
+from .eegatconv import DGLError, EGATConv
 from ._lib import B200GatError
 from .mlp import MLP
 from .readout import readout
+from .trunk import LayerSpec, fused_trunk, trunk_applicable
 
 
 class _SplitRows(torch.autograd.Function):
@@ -123,6 +124,19 @@ class GnnDGL(nn.Module):
         efeats.tables = edge_tables(self.edge_embedder[0].weight,
                                     [fe.fc_fij.weight for fe in self.features_extractors],
                                     [fe.bias for fe in self.features_extractors])
+        specs = self._trunk_specs(efeats)
+        if specs is not None and trunk_applicable(features, specs, self.features_extractors[0]._num_heads, self.hidden_dim):
+            # all L layers behind one autograd node / one C-ABI call per pass (wheatley_b200.trunk)
+            plan = b.plan
+            if plan.stats_host()[0] > 0:                                        # generic/eegatconv.py:238-247
+                raise DGLError("There are 0-in-degree nodes in the graph, output for those nodes will be invalid. "
+                               "Adding self-loop on the input graph by calling `g = dgl.add_self_loop(g)` will "
+                               "resolve the issue.")
+            etype_sorted = plan.sort_edge_ints(b.etype)
+            outs = fused_trunk(plan.clique_view(etype_sorted), etype_sorted, None, features, specs,
+                               heads=self.features_extractors[0]._num_heads, dim=self.hidden_dim, slope=0.01, eps=0.0,
+                               residual=self.residual)
+            return features_list + outs
         for layer in range(self.n_layers_features_extractor):
             h, _ = self.features_extractors[layer](b.plan, features, efeats)    # :374-376
             # :377 and the residual add of :395-396 (fused into the MLP's last GEMM epilogue)
@@ -130,6 +144,21 @@ class GnnDGL(nn.Module):
                                         residual=features_list[-1] if self.residual else None)
             features_list.append(features)
         return features_list
+
+    def _trunk_specs(self, efeats):
+        """Per-layer parameter lists for ``wheatley_b200.trunk`` (None when a layer is not the GELU / no-LayerNorm
+        configuration or the projected edge tables are missing)."""
+        if efeats.tables is None:
+            return None
+        specs = []
+        for fe, mlp in zip(self.features_extractors, self.mlps):
+            if (mlp.norm or not isinstance(mlp.activation_layer, nn.GELU)
+                    or getattr(mlp.activation_layer, "approximate", "none") != "none" or fe._edge_scoring):
+                return None
+            specs.append(LayerSpec([fe.fc_ni.weight, fe.fc_nj.weight, fe.fc_node_src.weight], None, fe.attn, None,
+                                   efeats.tables[id(fe.fc_fij.weight)], None,
+                                   [lin.weight for lin in mlp.layers], [lin.bias for lin in mlp.layers]))
+        return specs
 
     def forward_split(self, b: JsspBatch):
         """``(node_features [B, max_n_nodes, F], graph_embedding [B, 1, F])`` - the pair the generic

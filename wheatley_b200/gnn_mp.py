@@ -20,9 +20,11 @@ from torch import nn
 
 from . import _lib
 from .edge_feats import PspEdgeEmbedder
-from .graph_conv import GraphConv
+from .graph_conv import GATv2Conv, GraphConv
 from .mlp import MLP
+from .plan import GraphPlan
 from .readout import readout
+from .trunk import LayerSpec, fused_trunk, trunk_applicable, trunk_enabled
 
 
 class Compiled(nn.Module):
@@ -81,7 +83,39 @@ class GnnFlat(nn.Module):
         # :209 and the residual add of :228-230, fused into the MLP's last GEMM epilogue
         return self.mlps[layer](h, residual=prev if self.residual else None)
 
+    def _trunk_specs(self, g):
+        """Per-layer parameter lists for ``wheatley_b200.trunk``: ``lin_l | lin_r`` (+ biases), ``att``, the output
+        ``bias``, and the layer's edge embedder folded through ``lin_edge`` into a 16-row table and a 5-row affine
+        map (psp/models/edge_embedder.py:130-143)."""
+        specs, ef0 = [], None
+        for fe, mlp, emb in zip(self.features_extractors, self.mlps, self.edge_embedders):
+            conv = fe.conv
+            if (mlp.norm or not isinstance(mlp.activation_layer, nn.GELU)
+                    or getattr(mlp.activation_layer, "approximate", "none") != "none"
+                    or not isinstance(conv, GATv2Conv) or conv.lin_edge is None or conv.lin_l.bias is None):
+                return None, None
+            ef = emb(g)
+            if ef.attrs is None or ef.attrs.shape[1] > _lib.MAX_ATTR:
+                return None, None
+            ef0 = ef0 or ef
+            W = conv.lin_edge.weight
+            specs.append(LayerSpec([conv.lin_l.weight, conv.lin_r.weight], [conv.lin_l.bias, conv.lin_r.bias],
+                                   conv.att, conv.bias, nn.functional.linear(ef.weight, W),
+                                   (W @ ef.attr_weight).t(), [lin.weight for lin in mlp.layers],
+                                   [lin.bias for lin in mlp.layers]))
+        return specs, ef0
+
     def forward(self, g, features, pe):
+        plan = getattr(g._graph, "plan", None)
+        if self.checkpoint == 1 and isinstance(plan, GraphPlan) and trunk_enabled():
+            specs, ef0 = self._trunk_specs(g)
+            H = self.features_extractors[0].conv.heads
+            if specs is not None and trunk_applicable(features, specs, H, self.hidden_dim):
+                # all L layers behind one autograd node / one C-ABI call per pass (wheatley_b200.trunk)
+                outs = fused_trunk(plan, plan.sort_edge_ints(ef0.etype), plan.sort_edge_rows(ef0.attrs), features,
+                                   specs, heads=H, dim=self.hidden_dim, slope=0.2, eps=1e-16,
+                                   residual=self.residual)
+                return [features] + outs if self.layer_pooling == "all" else outs[-1]
         features_list = [features]                                            # :155-161
         previous = features
         for layer in range(self.n_layers_features_extractor):
