@@ -63,14 +63,21 @@ def model_config(args):
                 max_n_nodes=n_j * n_m, layers=args.layers, hidden=args.hidden, heads=args.heads)
 
 
+PPO_KW = dict(clip_coef=0.2, norm_adv=True, critic_loss="l2", ent_coef=0.05, vf_coef=0.5)   # alg/ppo.py:85-102
+
+
 def synth_targets(batch, n_nodes, seed):
+    """Rollout-buffer side of one minibatch (alg/ppo.py:556-564): masks, actions, advantages, returns, old
+    log-probabilities and old values."""
     g = torch.Generator().manual_seed(seed)
     masks = torch.rand(batch, n_nodes, generator=g) < 0.3
     masks[:, 0] = True
     action = torch.multinomial(masks.float(), 1, generator=g).squeeze(1)
     adv = torch.randn(batch, generator=g)
     ret = torch.randn(batch, generator=g)
-    return masks, action, adv, ret
+    old_lp = -torch.rand(batch, generator=g) * 2.0 - 4.0
+    old_v = torch.randn(batch, generator=g)
+    return masks, action, adv, ret, old_lp, old_v
 
 
 # ------------------------------------------------------------------------- reference / CPU arm
@@ -87,12 +94,14 @@ def cpu_step_fn(cfg, n_graphs, progress, seed0=0):
     from wheatley_b200_workload import jssp_batch
     agent = build_oracle(cfg)
     b = jssp_batch(cfg["n_j"], cfg["n_m"], n_graphs, seed0, progress)
-    masks, action, adv, ret = synth_targets(n_graphs, cfg["max_n_nodes"], 1)
+    from oracle import ppo_oracle
+    masks, action, adv, ret, old_lp, old_v = synth_targets(n_graphs, cfg["max_n_nodes"], 1)
     args_ = (b["src"], b["dst"], b["etype"], b["feat"], n_graphs, cfg["max_n_nodes"], b["n_task_nodes"])
 
     def step():
         agent.zero_grad(set_to_none=True)
-        loss = agent.loss(args_, action, masks, adv, ret)
+        logprob, entropy, value = agent.evaluate(args_, action, masks)
+        loss, _ = ppo_oracle.ppo_loss(logprob, entropy, value, old_lp, adv, ret, **PPO_KW)
         loss.backward()
         return loss.item()
     return step, b["n_edges"]
@@ -220,7 +229,7 @@ def run_b200(args):
     from wheatley_b200 import _lib
     from wheatley_b200.agent import JsspAgent
     from wheatley_b200.gnn_dgl import JsspBatch
-    from wheatley_b200.ppo import FlatAdam, FlatGradAllReduce, ppo_like_loss
+    from wheatley_b200.ppo import FlatAdam, FlatGradAllReduce, ppo_loss
     from wheatley_b200.workload import jssp_batch
 
     torch.backends.cuda.matmul.allow_tf32 = True       # the reference's matmul precision (psp/train_psp.py:47)
@@ -237,9 +246,9 @@ def run_b200(args):
     opt = FlatAdam(agent.parameters(), lr=2e-4, bucket=bucket)
 
     hb = jssp_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress)
-    masks, action, adv, ret = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
+    masks, action, adv, ret, old_lp, old_v = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
     host = dict(src=hb["src"], dst=hb["dst"], etype=hb["etype"], feat=hb["feat"], masks=masks,
-                action=action, adv=adv, ret=ret)
+                action=action, adv=adv, ret=ret, old_lp=old_lp, old_v=old_v)
     host = {k: v.contiguous().pin_memory() for k, v in host.items()}
     # the e2e / rollout legs start from the padded gym observation (what the reference's batching receives,
     # jssp/models/agent_observation.py:127-131): the batched graph is built on the device (wheatley_b200.batch)
@@ -247,7 +256,7 @@ def run_b200(args):
     from wheatley_b200.batch import jssp_batch_from_observation
     obs = {k: v.contiguous().pin_memory() for k, v in
            jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress).items()}
-    extras = {k: host[k] for k in ("masks", "action", "adv", "ret")}
+    extras = {k: host[k] for k in ("masks", "action", "adv", "ret", "old_lp", "old_v")}
     builder_kw = dict(conflicts="clique", graph_pooling="learn")
     h2d_bytes = (sum(v.numel() * v.element_size() for v in obs.values())
                  + sum(v.numel() * v.element_size() for v in extras.values()) + 4 * (B + 1) * 8)
@@ -264,7 +273,8 @@ def run_b200(args):
     def train_step(jb, d):
         bucket.zero()
         _, logprob, entropy, value, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
-        loss = ppo_like_loss(logprob, entropy, value, d["adv"], d["ret"])
+        # the clipped-PPO minibatch loss of alg/ppo.py:582-705 (one launch; statistics stay on the device)
+        loss, _stats = ppo_loss(logprob, entropy, value, d["old_lp"], d["adv"], d["ret"], d["old_v"], **PPO_KW)
         loss.backward()
         bucket.reduce()
         opt.step()
@@ -376,12 +386,21 @@ def run_b200(args):
     pf = BatchPrefetcher(dev)
     pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)
 
+    from wheatley_b200.prefetch import HostReadback
+    rb = HostReadback(depth=2)
+    e2e_losses = []
+
     def e2e_step():
         d, _ = pf.get()
         pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)     # next step's inputs
-        return train_step(d["batch"], d).item()
+        rb.push(train_step(d["batch"], d))                 # device->host read of THIS step's loss, asynchronous
+        if len(rb) > 1:
+            e2e_losses.append(float(rb.pop()))             # ... consumed one step later (HostReadback)
     ms_e2e_mean, _, _ = timed(e2e_step, max(3, args.steps), 5)
     e2e_spread = dict(timed.last_spread)
+    while len(rb):
+        e2e_losses.append(float(rb.pop()))
+    assert len(e2e_losses) == max(3, args.steps) + 5 and all(x == x for x in e2e_losses)    # every step's loss read
     pf.get()                                               # drain the last (unused) prefetch
     torch.cuda.synchronize()
     # every step is bracketed by its own event pair; the median is reported because single steps of this
@@ -390,7 +409,8 @@ def run_b200(args):
     t_med = torch.tensor([e2e_spread["median"]], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_med, op=dist.ReduceOp.MAX)
-    ms_e2e = float(t_med)
+    ms_e2e_median = float(t_med)
+    ms_e2e = ms_e2e_mean                                   # headline = MEAN over the timed steps (max over ranks)
 
     # ---- PPO env-steps/sec (BASELINE.json metric, second half): the learner side of one PPO iteration
     # (alg/ppo.py:196-206 rollout inference, :547-727 update) on this workload, per rank:
@@ -484,18 +504,22 @@ def run_b200(args):
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
                            l2="flushed between timed steps (256 MiB write)",
                            parallelism=f"dp{world}", gemm=dense_backend,
-                           step="plan reuse + fwd + masked head + loss + bwd + grad allreduce + Adam",
+                           step="plan reuse + trunk fwd + masked head + clipped-PPO loss (alg/ppo.py:582-705) + bwd + grad allreduce "
+                                "+ Adam",
                            launch=graph_note),
             "e2e": {"value": edges_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "ms_per_step_mean": ms_e2e_mean, "ms_per_step_spread": e2e_spread,
-                    "statistic": "median of the per-step CUDA-event times (rank 0 spread shown; max over ranks)",
+                    "ms_per_step_median": ms_e2e_median, "ms_per_step_spread": e2e_spread,
+                    "statistic": "mean of the per-step CUDA-event times over the timed steps (max over ranks; rank 0 "
+                                 "spread shown)",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "input": "padded gym observation (features, precedence edge_index, n_nodes, n_edges) + masks / "
                              "actions / advantages / returns in pinned host memory; the batched graph (clique "
                              "conflict edges, pool wiring) is built on the device by b200gat_jssp_batch_build",
                     "pipeline": "wheatley_b200.prefetch.BatchPrefetcher: step i+1's host->device copy, batch and "
-                                "plan build are queued on a side stream while step i trains; every timed step "
-                                "copies its inputs from pinned host memory and reads its loss back",
+                                "plan build are queued ahead of step i's kernels; every timed step copies its inputs "
+                                "from pinned host memory and reads its loss back (wheatley_b200.prefetch.HostReadback: "
+                                "asynchronous copy into pinned memory, consumed one step later, so the launch thread "
+                                "never waits on the GPU; ms_per_step_no_prefetch is the serial loop with loss.item())",
                     "ms_per_step_no_prefetch": ms_e2e_serial},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,

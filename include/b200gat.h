@@ -509,11 +509,16 @@ typedef struct b200gat_readout {
   int64_t n_task_rows;                       /* host copy of row_start[B]                                     */
   int32_t pooling;                           /* B200GAT_READOUT_*                                             */
   int64_t pool_row0;                         /* ROWS: pool node of graph b is row pool_row0 + b               */
+  int64_t out_ld;                            /* row stride of node_features / graph_embedding (F <= out_ld <  */
+                                             /* F + 128; the pad columns are written as zeros); 0 = F.  The   */
+                                             /* heads' first GEMM needs 16-byte aligned rows: F = 478 -> 480  */
 } b200gat_readout;
 int b200gat_readout_fwd(const b200gat_readout* r, float* node_features, float* graph_embedding, int32_t* argmax,
                         void* stream);
-int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node_features, const float* g_graph_embedding,
-                        const int32_t* argmax, float* const* g_src, int64_t n_rows_total, void* stream);
+/* ld_g_nf / ld_g_ge: row strides of the incoming gradients (0 = F) */
+int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node_features, int64_t ld_g_nf,
+                        const float* g_graph_embedding, int64_t ld_g_ge, const int32_t* argmax, float* const* g_src,
+                        int64_t n_rows_total, void* stream);
 
 /* ------------------------------------------------------------------ PPO update tail
  * b200gat_gae replaces the Python loop over the rollout steps of alg/ppo.py:276-299:

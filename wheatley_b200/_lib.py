@@ -138,7 +138,7 @@ class Readout(C.Structure):
     """``b200gat_readout`` (include/b200gat.h)."""
     _fields_ = [("n_src", C.c_int32), ("src", C.c_void_p * 16), ("width", C.c_int32 * 16), ("ld", C.c_int64 * 16),
                 ("n_graphs", C.c_int32), ("max_n_nodes", C.c_int32), ("row_start", C.c_void_p),
-                ("n_task_rows", C.c_int64), ("pooling", C.c_int32), ("pool_row0", C.c_int64)]
+                ("n_task_rows", C.c_int64), ("pooling", C.c_int32), ("pool_row0", C.c_int64), ("out_ld", C.c_int64)]
 
 
 TRUNK_MAX_LAYERS = 16
@@ -263,7 +263,7 @@ def _load():
     lib.b200gat_trunk_bwd.argtypes = [tp, tg, vp]
     rp = C.POINTER(Readout)
     lib.b200gat_readout_fwd.argtypes = [rp, vp, vp, vp, vp]
-    lib.b200gat_readout_bwd.argtypes = [rp, vp, vp, vp, C.POINTER(C.c_void_p), i64, vp]
+    lib.b200gat_readout_bwd.argtypes = [rp, vp, i64, vp, i64, vp, C.POINTER(C.c_void_p), i64, vp]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("b200gat_last_error", "b200gat_plan_scratch_elems", "b200gat_launch_count",

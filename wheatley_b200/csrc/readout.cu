@@ -24,7 +24,7 @@ struct ReadoutSrc {
 };
 
 __global__ void __launch_bounds__(128) k_readout_rows(ReadoutSrc S, const int32_t* __restrict__ row_start, int B,
-                                                      int max_n, int64_t pool_row0, float* __restrict__ nf,
+                                                      int max_n, int64_t pool_row0, int ld, float* __restrict__ nf,
                                                       float* __restrict__ ge) {
   const int F = S.off[S.n];
   int64_t row;          // source row, -1 = padding
@@ -33,16 +33,17 @@ __global__ void __launch_bounds__(128) k_readout_rows(ReadoutSrc S, const int32_
     const int b = blockIdx.x / max_n, r = blockIdx.x - b * max_n;
     const int s0 = row_start[b], n_b = row_start[b + 1] - s0;
     row = r < n_b ? (int64_t)s0 + r : -1;
-    out = nf + (int64_t)blockIdx.x * F;
+    out = nf + (int64_t)blockIdx.x * ld;
   } else {              // learned pooling: the pool node's row is the graph embedding
     const int b = blockIdx.x - B * max_n;
     row = pool_row0 + b;
-    out = ge + (int64_t)b * F;
+    out = ge + (int64_t)b * ld;
   }
   if (row < 0) {
-    for (int c = threadIdx.x; c < F; c += 128) out[c] = 0.f;
+    for (int c = threadIdx.x; c < ld; c += 128) out[c] = 0.f;
     return;
   }
+  if (threadIdx.x < ld - F) out[F + threadIdx.x] = 0.f;      // pad columns (ld - F < 4)
 #pragma unroll 1
   for (int i = 0; i < S.n; ++i) {
     const float* __restrict__ src = S.p[i] + row * S.ld[i];
@@ -55,19 +56,19 @@ __global__ void __launch_bounds__(128) k_readout_rows(ReadoutSrc S, const int32_
 template <int RY>
 __global__ void __launch_bounds__(32 * RY) k_readout_pool(const float* __restrict__ nf,
                                                           const int32_t* __restrict__ row_start, int max_n, int F,
-                                                          int mode, float* __restrict__ ge,
+                                                          int ld, int mode, float* __restrict__ ge,
                                                           int32_t* __restrict__ argmax) {
   __shared__ float sv[RY][33];
   __shared__ int si[RY][33];
   const int b = blockIdx.y, c = blockIdx.x * 32 + threadIdx.x, ty = threadIdx.y;
   const int n_b = row_start[b + 1] - row_start[b];
-  const float* base = nf + (int64_t)b * max_n * F;
+  const float* base = nf + (int64_t)b * max_n * ld;
   float best = -INFINITY, sum = 0.f;
   int bi = 0x7fffffff;
   if (c < F) {
 #pragma unroll 4
     for (int r = ty; r < n_b; r += RY) {
-      const float v = base[(int64_t)r * F + c];
+      const float v = base[(int64_t)r * ld + c];
       sum += v;
       if (v > best || (bi == 0x7fffffff)) { best = v; bi = r; }      // strict >: first index inside a lane
     }
@@ -82,19 +83,21 @@ __global__ void __launch_bounds__(32 * RY) k_readout_pool(const float* __restric
         const int i = si[k][threadIdx.x];
         if (i != 0x7fffffff && (bi == 0x7fffffff || v > best || (v == best && i < bi))) { best = v; bi = i; }
       }
-      ge[(int64_t)b * F + c] = best;
+      ge[(int64_t)b * ld + c] = best;
       argmax[(int64_t)b * F + c] = bi == 0x7fffffff ? -1 : bi;
     } else {
       // rows are summed lane-major then across lanes in lane order: fixed order, bit-reproducible
       for (int k = 1; k < RY; ++k) sum += sv[k][threadIdx.x];
-      ge[(int64_t)b * F + c] = n_b > 0 ? sum / (float)n_b : 0.f;
+      ge[(int64_t)b * ld + c] = n_b > 0 ? sum / (float)n_b : 0.f;
     }
   }
+  if (ty == 0 && c >= F && c < ld) ge[(int64_t)b * ld + c] = 0.f;       // pad columns
 }
 
 __global__ void __launch_bounds__(128) k_readout_bwd(ReadoutSrc S, const int32_t* __restrict__ row_start, int B,
                                                      int max_n, int64_t n_task_rows, int64_t pool_row0, int mode,
-                                                     const float* __restrict__ g_nf, const float* __restrict__ g_ge,
+                                                     const float* __restrict__ g_nf, int64_t ld_nf,
+                                                     const float* __restrict__ g_ge, int64_t ld_ge,
                                                      const int32_t* __restrict__ argmax) {
   const int F = S.off[S.n];
   const int64_t row = blockIdx.x;
@@ -116,14 +119,14 @@ __global__ void __launch_bounds__(128) k_readout_bwd(ReadoutSrc S, const int32_t
     __syncthreads();
     const int b = s_b;
     local = (int)(row - row_start[b]);
-    if (g_nf) gn = g_nf + ((int64_t)b * max_n + local) * F;
-    if (g_ge && mode == B200GAT_READOUT_MAX) { gg = g_ge + (int64_t)b * F; am = argmax + (int64_t)b * F; }
+    if (g_nf) gn = g_nf + ((int64_t)b * max_n + local) * ld_nf;
+    if (g_ge && mode == B200GAT_READOUT_MAX) { gg = g_ge + (int64_t)b * ld_ge; am = argmax + (int64_t)b * F; }
     if (g_ge && mode == B200GAT_READOUT_AVG) {
-      gg = g_ge + (int64_t)b * F;
+      gg = g_ge + (int64_t)b * ld_ge;
       scale = 1.f / (float)(row_start[b + 1] - row_start[b]);
     }
   } else if (mode == B200GAT_READOUT_ROWS && g_ge && row >= pool_row0 && row < pool_row0 + B) {
-    gg = g_ge + (row - pool_row0) * F;
+    gg = g_ge + (row - pool_row0) * ld_ge;
   }
 #pragma unroll 1
   for (int i = 0; i < S.n; ++i) {
@@ -173,28 +176,30 @@ extern "C" int b200gat_readout_fwd(const b200gat_readout* r, float* node_feature
   B200_CHECK_ARG(r->pooling != B200GAT_READOUT_MAX || argmax, "max pooling needs argmax");
   cudaStream_t st = (cudaStream_t)stream;
   const int F = S.off[S.n];
+  const int ld = r->out_ld ? (int)r->out_ld : F;
+  B200_CHECK_ARG(ld >= F && ld - F < 128, "out_ld must be F .. F + 127");
   const int64_t rows = (int64_t)r->n_graphs * r->max_n_nodes + (r->pooling == B200GAT_READOUT_ROWS ? r->n_graphs : 0);
   B200_CHECK_ARG(rows < (1ll << 31), "too many rows");
-  k_readout_rows<<<(unsigned)rows, 128, 0, st>>>(S, r->row_start, r->n_graphs, r->max_n_nodes, r->pool_row0,
+  k_readout_rows<<<(unsigned)rows, 128, 0, st>>>(S, r->row_start, r->n_graphs, r->max_n_nodes, r->pool_row0, ld,
                                                  node_features, graph_embedding);
   B200_CHECK_LAUNCH("k_readout_rows");
   if (r->pooling == B200GAT_READOUT_MAX || r->pooling == B200GAT_READOUT_AVG) {
     B200_CHECK_ARG(r->n_graphs <= 65535, "n_graphs <= 65535 for max / avg pooling");
-    dim3 grid((unsigned)ceil_div(F, 32), (unsigned)r->n_graphs);
+    dim3 grid((unsigned)ceil_div(ld, 32), (unsigned)r->n_graphs);
     if (r->max_n_nodes >= 256)
-      k_readout_pool<16><<<grid, dim3(32, 16), 0, st>>>(node_features, r->row_start, r->max_n_nodes, F, r->pooling,
-                                                        graph_embedding, argmax);
+      k_readout_pool<16><<<grid, dim3(32, 16), 0, st>>>(node_features, r->row_start, r->max_n_nodes, F, ld,
+                                                        r->pooling, graph_embedding, argmax);
     else
-      k_readout_pool<4><<<grid, dim3(32, 4), 0, st>>>(node_features, r->row_start, r->max_n_nodes, F, r->pooling,
+      k_readout_pool<4><<<grid, dim3(32, 4), 0, st>>>(node_features, r->row_start, r->max_n_nodes, F, ld, r->pooling,
                                                        graph_embedding, argmax);
     B200_CHECK_LAUNCH("k_readout_pool");
   }
   return B200GAT_OK;
 }
 
-extern "C" int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node_features,
-                                   const float* g_graph_embedding, const int32_t* argmax, float* const* g_src,
-                                   int64_t n_rows_total, void* stream) {
+extern "C" int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node_features, int64_t ld_g_nf,
+                                   const float* g_graph_embedding, int64_t ld_g_ge, const int32_t* argmax,
+                                   float* const* g_src, int64_t n_rows_total, void* stream) {
   ReadoutSrc S;
   B200_CHECK_ARG(g_src, "null g_src");
   int rc = fill_src(S, r, g_src);
@@ -203,9 +208,13 @@ extern "C" int b200gat_readout_bwd(const b200gat_readout* r, const float* g_node
   B200_CHECK_ARG(r->pooling != B200GAT_READOUT_MAX || !g_graph_embedding || argmax, "max pooling needs argmax");
   B200_CHECK_ARG(r->pooling != B200GAT_READOUT_ROWS || r->pool_row0 + r->n_graphs <= n_rows_total, "pool rows");
   if (n_rows_total == 0) return B200GAT_OK;
+  const int F = S.off[S.n];
+  if (!ld_g_nf) ld_g_nf = F;
+  if (!ld_g_ge) ld_g_ge = F;
+  B200_CHECK_ARG(ld_g_nf >= F && ld_g_ge >= F, "gradient row strides must be >= F");
   k_readout_bwd<<<(unsigned)n_rows_total, 128, 0, (cudaStream_t)stream>>>(
       S, r->row_start, r->n_graphs, r->max_n_nodes, r->n_task_rows, r->pool_row0, r->pooling, g_node_features,
-      g_graph_embedding, argmax);
+      ld_g_nf, g_graph_embedding, ld_g_ge, argmax);
   B200_CHECK_LAUNCH("k_readout_bwd");
   return B200GAT_OK;
 }

@@ -138,8 +138,8 @@ static int bwd_shape(const b200gat_trunk* t, TrunkShape* sh) {
     mlp_desc(&m, t, l, nullptr);
     b200gat_mlp_grads gr;
     memset(&gr, 0, sizeof(gr));
-    static float dummy[4];
-    for (int i = 0; i < L.n_mlp; ++i) gr.dW[i] = dummy;            // sizing only
+    alignas(16) static float dummy[4];
+    for (int i = 0; i < L.n_mlp; ++i) { gr.dW[i] = dummy; gr.db[i] = dummy; }   // sizing only (plan_gemm checks alignment)
     gr.gy = dummy;
     int64_t e = b200gat_mlp_bwd_workspace_elems(&m, &gr);
     gemm_ws = e > gemm_ws ? e : gemm_ws;
@@ -167,9 +167,9 @@ extern "C" int b200gat_trunk_supported(const b200gat_trunk* t) {
   TrunkShape sh;
   if (check_trunk(t, &sh, false) != B200GAT_OK) return 0;
   // the GEMM shapes themselves (the MLP ones are checked by b200gat_mlp_fwd's own requirements: widths % 4)
-  static float dummy[4];
+  alignas(16) static float dummy[4];
   b200gat_trunk probe = *t;
-  probe.wcat = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(dummy) + 15) & ~(uintptr_t)15);
+  probe.wcat = dummy;
   for (int l = 0; l < t->n_layers; ++l) {
     b200gat_gemm g;
     probe.layer[l].P = probe.wcat;

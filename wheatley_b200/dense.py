@@ -185,10 +185,31 @@ def _mlp_desc(x, Ws, bs, residual, zs, hs, y):
     return m
 
 
+def _pad4(n):
+    return (n + 3) // 4 * 4
+
+
+def _padded_rows_view(x):
+    """``x [M, K]`` with ``K % 4 != 0`` whose rows already sit ``roundup4(K)`` floats apart in storage that holds the
+    pad columns too (the trunk readout allocates its output that way, finite pad values): the ``[M, roundup4(K)]``
+    matrix over the same storage - no copy - else None."""
+    M, K = x.shape
+    Kp = _pad4(K)
+    if (x.stride(1) == 1 and x.stride(0) == Kp and x.data_ptr() % 16 == 0
+            and (x.storage_offset() + (M - 1) * Kp + Kp) * 4 <= x.untyped_storage().nbytes()):
+        return x.as_strided((M, Kp), (Kp, 1))
+    return None
+
+
 class _GeluMLPFused(torch.autograd.Function):
     """The whole ``Linear -> GELU -> ... -> Linear (+ residual)`` stack with ONE binding call per pass
     (``b200gat_mlp_fwd`` / ``b200gat_mlp_bwd``, which issue the tcgen05 GEMMs of ``_GeluMLP`` from C): the eager
-    PPO step is host-bound and an MLP's forward + backward cost ~400 us of host time call by call."""
+    PPO step is host-bound and an MLP's forward + backward cost ~400 us of host time call by call.
+
+    Widths that are not multiples of 4 floats (TMA rows must be 16-byte aligned: the 30-wide JSSP node features,
+    the 478-wide head input, the width-1 head outputs) are zero-padded HERE, outside autograd (the padding used to
+    be ``F.pad`` calls tracked by autograd: 20 launches + 10 backward nodes per step); the gradients are sliced back
+    as views."""
 
     @staticmethod
     def forward(ctx, x, residual, *params):
@@ -196,7 +217,23 @@ class _GeluMLPFused(torch.autograd.Function):
         Ws = [w.contiguous() for w in params[0::2]]
         bs = list(params[1::2])
         need = any(ctx.needs_input_grad)
-        M, dev = x.shape[0], x.device
+        M, K, dev = x.shape[0], x.shape[1], x.device
+        n_out = Ws[-1].shape[0]
+        pad_in, pad_out = (-K) % 4, (-n_out) % 4
+        if pad_in:
+            xv = _padded_rows_view(x)
+            x = xv if xv is not None else torch.nn.functional.pad(x, (0, pad_in))
+            Ws[0] = torch.nn.functional.pad(Ws[0], (0, pad_in))
+        elif not x.is_contiguous():
+            x = x.contiguous()
+        if pad_out:
+            Ws[-1] = torch.nn.functional.pad(Ws[-1], (0, 0, 0, pad_out))
+            if bs[-1] is not None:
+                bs[-1] = torch.nn.functional.pad(bs[-1], (0, pad_out))
+            if residual is not None:
+                residual = torch.nn.functional.pad(residual, (0, pad_out))
+        if residual is not None:
+            residual = residual.contiguous()
         f32 = dict(dtype=torch.float32, device=dev)
         hs = [torch.empty((M, Ws[i].shape[0]), **f32) for i in range(n - 1)]
         zs = [torch.empty((M, Ws[i].shape[0]), **f32) for i in range(n - 1)] if need else None
@@ -206,9 +243,10 @@ class _GeluMLPFused(torch.autograd.Function):
             _lib.check(_lib.lib.b200gat_mlp_fwd(m, _lib.stream_ptr()), "b200gat_mlp_fwd")
         ctx.n, ctx.has_res = n, residual is not None
         ctx.has_bias = [b is not None for b in bs]
+        ctx.K, ctx.n_out = K, n_out
         if need:
             ctx.save_for_backward(x, *Ws, *zs, *hs)
-        return y
+        return y[:, :n_out] if pad_out else y
 
     @staticmethod
     def backward(ctx, gy):
@@ -217,6 +255,11 @@ class _GeluMLPFused(torch.autograd.Function):
         x, Ws = saved[0], list(saved[1: 1 + n])
         rest = saved[1 + n:]
         zs, hs = list(rest[: n - 1]), list(rest[n - 1:])
+        K, n_out = ctx.K, ctx.n_out
+        pad_out = Ws[-1].shape[0] - n_out
+        gy_in = gy
+        if pad_out:
+            gy = torch.nn.functional.pad(gy, (0, pad_out))
         gy = gy.contiguous()
         M, dev = x.shape[0], x.device
         f32 = dict(dtype=torch.float32, device=dev)
@@ -242,20 +285,32 @@ class _GeluMLPFused(torch.autograd.Function):
         g.workspace, g.workspace_elems = ws.data_ptr(), ws_elems
         with _lib.device_guard(dev):
             _lib.check(_lib.lib.b200gat_mlp_bwd(m, g, _lib.stream_ptr()), "b200gat_mlp_bwd")
+        # slice the padding off again (views)
+        if dx is not None and dx.shape[1] != K:
+            dx = dx[:, :K]
+        if dWs[0] is not None and dWs[0].shape[1] != K:
+            dWs[0] = dWs[0][:, :K]
+        if pad_out:
+            if dWs[-1] is not None:
+                dWs[-1] = dWs[-1][:n_out]
+            if dbs[-1] is not None:
+                dbs[-1] = dbs[-1][:n_out]
         grads = []
         for i in range(n):
             grads += [dWs[i] if need[2 + 2 * i] else None, dbs[i] if need[3 + 2 * i] else None]
-        return (dx, gy if ctx.has_res and need[1] else None, *grads)
+        return (dx, gy_in if ctx.has_res and need[1] else None, *grads)
 
 
 def gelu_mlp(x, layers, residual=None):
-    """``layers``: the ``nn.Linear`` modules of a GELU MLP.  Widths that are not multiples of 4 floats are
-    zero-padded around the fused call (TMA rows must be 16-byte aligned): the 30-wide JSSP node features with
-    the first weight's columns, the width-1 head outputs with the last weight's rows; the padding changes
-    nothing and autograd slices the gradients back."""
+    """``layers``: the ``nn.Linear`` modules of a GELU MLP.  One fused call per pass when every hidden width is a
+    multiple of 4 floats (input / output widths are padded inside the call); GEMM by GEMM otherwise."""
     params = []
     for lin in layers:
         params += [lin.weight, lin.bias]
+    hidden_ok = all(p.shape[0] % 4 == 0 for p in params[0:-2:2])
+    if (hidden_ok and len(layers) <= _lib.MLP_MAX_LAYERS
+            and os.environ.get("WHEATLEY_B200_MLP_CALLS", "fused") == "fused"):
+        return _GeluMLPFused.apply(x, residual, *params)
     pad_in = (-x.shape[1]) % 4
     if pad_in:
         x = torch.nn.functional.pad(x, (0, pad_in))
@@ -268,10 +323,7 @@ def gelu_mlp(x, layers, residual=None):
             params[-1] = torch.nn.functional.pad(params[-1], (0, pad_out))
         if residual is not None:
             residual = torch.nn.functional.pad(residual, (0, pad_out))
-    hidden_ok = all(p.shape[0] % 4 == 0 for p in params[0:-2:2])
-    fn = _GeluMLPFused if (hidden_ok and len(layers) <= _lib.MLP_MAX_LAYERS
-                           and os.environ.get("WHEATLEY_B200_MLP_CALLS", "fused") == "fused") else _GeluMLP
-    y = fn.apply(x.contiguous(), None if residual is None else residual.contiguous(), *params)
+    y = _GeluMLP.apply(x.contiguous(), None if residual is None else residual.contiguous(), *params)
     return y[:, :n_out] if pad_out else y
 
 

@@ -20,7 +20,7 @@ from .edge_feats import TypedEdgeFeats, edge_tables
 from .eegatconv import DGLError, EGATConv
 from ._lib import B200GatError
 from .mlp import MLP
-from .readout import readout
+from .readout import readout, row_starts
 from .trunk import LayerSpec, fused_trunk, trunk_applicable
 
 
@@ -169,8 +169,11 @@ class GnnDGL(nn.Module):
             raise Exception(f"Graph pooling {self.graph_pooling} not recognized.")
         if b.num_task_nodes != b.batch_size * b.n_nodes:
             raise B200GatError("GnnDGL needs equal-sized graphs (the reference reshapes to [B, n_nodes, F], :405)")
+        if getattr(b, "row_start", None) is None:        # once per batch, shared by every epoch over it
+            b.row_start = row_starts([b.n_nodes] * b.batch_size, b.feat.device)
         node_features, graph_embedding = readout(self.layer_embeddings(b), [b.n_nodes] * b.batch_size,
-                                                 self.max_n_nodes, self.graph_pooling, pool_row0=b.num_task_nodes)
+                                                 self.max_n_nodes, self.graph_pooling, pool_row0=b.num_task_nodes,
+                                                 row_start=b.row_start)
         return node_features, graph_embedding.reshape(b.batch_size, 1, -1)
 
     def forward(self, b: JsspBatch):

@@ -99,3 +99,38 @@ class BatchPrefetcher:
             if isinstance(t, torch.Tensor) and t.is_cuda:
                 t.record_stream(main)
         return d, plan
+
+
+class HostReadback:
+    """Device -> host reads of per-step scalars (loss, the PPO statistics) WITHOUT stalling the launch thread: every
+    ``push`` queues an asynchronous copy into pinned memory behind the step's kernels and records an event; ``pop``
+    waits for the OLDEST outstanding event only.  A loop that pushes step i and pops step i-1 reads every step's
+    value, one step late, while the host is already launching the next step.  (``loss.item()`` makes the host wait
+    for the whole step, so the next step's launches start on an idle GPU: at 8 x Taillard 100x20 that serialisation
+    cost 1.5 ms of a 6.9 ms step.  The reference reads eight scalars per minibatch with ``.item()``,
+    alg/ppo.py:588-595,707-710, for logging and the per-epoch KL early stop, neither of which needs the value before
+    the next minibatch is launched.)"""
+
+    def __init__(self, depth=2, numel=1):
+        self.bufs = [torch.empty(numel, dtype=torch.float32, pin_memory=True) for _ in range(depth + 1)]
+        self.events = [torch.cuda.Event() for _ in range(depth + 1)]
+        self.head = self.tail = 0          # monotonically increasing push / pop counters
+
+    def __len__(self):
+        return self.head - self.tail
+
+    def push(self, t: torch.Tensor):
+        if len(self) >= len(self.bufs):
+            raise _lib.B200GatError("HostReadback is full: pop() before pushing more")
+        k = self.head % len(self.bufs)
+        self.bufs[k][: t.numel()].copy_(t.detach().reshape(-1), non_blocking=True)
+        self.events[k].record()
+        self.head += 1
+
+    def pop(self):
+        if not len(self):
+            raise _lib.B200GatError("HostReadback.pop() without a pending read")
+        k = self.tail % len(self.bufs)
+        self.events[k].synchronize()
+        self.tail += 1
+        return self.bufs[k].clone()

@@ -18,9 +18,14 @@ def row_starts(counts, device):
     """``[B+1]`` int32 device tensor: exclusive prefix of the per-graph task-node counts (host knowledge: the
     observation carries ``n_nodes``), one small copy per batch."""
     counts = np.asarray(counts, dtype=np.int64)
-    rs = np.zeros(len(counts) + 1, dtype=np.int32)
-    np.cumsum(counts, out=rs[1:])
-    return torch.from_numpy(rs).to(device, non_blocking=True)
+    if counts.size and (counts == counts[0]).all():          # equal-sized graphs: generated on the device
+        n, B = int(counts[0]), len(counts)
+        if n == 0:
+            return torch.zeros(B + 1, dtype=torch.int32, device=device)
+        return torch.arange(0, (B + 1) * n, n, dtype=torch.int32, device=device)
+    rs = torch.zeros(len(counts) + 1, dtype=torch.int32, pin_memory=True)      # pinned: legal under graph capture
+    np.cumsum(counts, out=rs.numpy()[1:])
+    return rs.to(device, non_blocking=True)
 
 
 class _Readout(torch.autograd.Function):
@@ -45,8 +50,12 @@ class _Readout(torch.autograd.Function):
             r.src[i], r.width[i], r.ld[i] = s.data_ptr(), widths[i], s.stride(0)
         r.n_graphs, r.max_n_nodes, r.row_start = B, max_n_nodes, row_start.data_ptr()
         r.n_task_rows, r.pooling, r.pool_row0 = n_task_rows, mode, pool_row0
-        nf = torch.empty((B, max_n_nodes, F), dtype=torch.float32, device=dev)
-        ge = torch.empty((B, F), dtype=torch.float32, device=dev) if mode != _lib.READOUT_NONE else None
+        # rows 16-byte aligned (zero pad columns; the returned tensors are the [..., :F] views): the heads' first
+        # GEMM reads them in place instead of through a padded 30 MB copy
+        Fp = (F + 3) // 4 * 4
+        r.out_ld = Fp
+        nf = torch.empty((B, max_n_nodes, Fp), dtype=torch.float32, device=dev)
+        ge = torch.empty((B, Fp), dtype=torch.float32, device=dev) if mode != _lib.READOUT_NONE else None
         am = torch.empty((B, F), dtype=torch.int32, device=dev) if mode == _lib.READOUT_MAX else None
         with _lib.device_guard(dev):
             _lib.check(_lib.lib.b200gat_readout_fwd(C.byref(r), _lib.ptr(nf), _lib.ptr(ge), _lib.ptr(am),
@@ -57,7 +66,9 @@ class _Readout(torch.autograd.Function):
         if ge is None:
             ge = nf.new_zeros((B, 0))
             ctx.mark_non_differentiable(ge)
-        return nf, ge
+        elif Fp != F:
+            ge = ge[:, :F]
+        return (nf[:, :, :F] if Fp != F else nf), ge
 
     @staticmethod
     def backward(ctx, g_nf, g_ge):
@@ -67,8 +78,18 @@ class _Readout(torch.autograd.Function):
         if g_nf is None and g_ge is None:
             return (None,) * (6 + len(widths))
         dev = row_start.device
-        g_nf = None if g_nf is None else g_nf.contiguous()
-        g_ge = None if g_ge is None else g_ge.contiguous()
+        F = sum(widths)
+        ld_nf = ld_ge = F
+        if g_nf is not None:      # a gradient that arrives with padded rows (the head's dx) is read in place
+            if g_nf.stride(2) == 1 and g_nf.stride(0) == max_n_nodes * g_nf.stride(1) and g_nf.stride(1) >= F:
+                ld_nf = g_nf.stride(1)
+            else:
+                g_nf = g_nf.contiguous()
+        if g_ge is not None:
+            if g_ge.stride(1) == 1 and g_ge.stride(0) >= F:
+                ld_ge = g_ge.stride(0)
+            else:
+                g_ge = g_ge.contiguous()
         grads = [torch.empty((n_rows, w), dtype=torch.float32, device=dev) if nd else None
                  for w, nd in zip(widths, need)]
         r = _lib.Readout()
@@ -79,8 +100,9 @@ class _Readout(torch.autograd.Function):
         r.n_task_rows, r.pooling, r.pool_row0 = n_task_rows, mode, pool_row0
         gp = (C.c_void_p * _lib.READOUT_MAX_SRC)(*[_lib.ptr(g) for g in grads])
         with _lib.device_guard(dev):
-            _lib.check(_lib.lib.b200gat_readout_bwd(C.byref(r), _lib.ptr(g_nf), _lib.ptr(g_ge), _lib.ptr(am), gp,
-                                                    n_rows, _lib.stream_ptr()), "b200gat_readout_bwd")
+            _lib.check(_lib.lib.b200gat_readout_bwd(C.byref(r), _lib.ptr(g_nf), ld_nf, _lib.ptr(g_ge), ld_ge,
+                                                    _lib.ptr(am), gp, n_rows, _lib.stream_ptr()),
+                       "b200gat_readout_bwd")
         return (None,) * 6 + tuple(grads)
 
 
