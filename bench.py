@@ -272,9 +272,10 @@ def run_b200(args):
 
     def train_step(jb, d):
         bucket.zero()
-        _, logprob, entropy, value, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
-        # the clipped-PPO minibatch loss of alg/ppo.py:582-705 (one launch; statistics stay on the device)
-        loss, _stats = ppo_loss(logprob, entropy, value, d["old_lp"], d["adv"], d["ret"], d["old_v"], **PPO_KW)
+        # alg/ppo.py:575-711 as one call: get_action_and_value + the clipped-PPO minibatch loss (statistics stay on
+        # the device); loss.backward() is the whole backward pass
+        loss, _stats = agent.ppo_minibatch(jb, d["action"], d["masks"], d["old_lp"], d["adv"], d["ret"], d["old_v"],
+                                           **PPO_KW)
         loss.backward()
         bucket.reduce()
         opt.step()

@@ -618,6 +618,7 @@ typedef struct b200gat_trunk_layer_grads {
 } b200gat_trunk_layer_grads;
 typedef struct b200gat_trunk_grads {
   float* g_x0;               /* [N, in_dim] or NULL                                                               */
+  const float* g_x0_in;      /* [N, in_dim] gradient reaching x0 from outside the trunk (added into g_x0) or NULL */
   float* workspace;          /* b200gat_trunk_bwd_workspace_elems floats, 16-byte aligned                         */
   int64_t workspace_elems;
   b200gat_trunk_layer_grads layer[B200GAT_TRUNK_MAX_LAYERS];
@@ -627,6 +628,64 @@ int64_t b200gat_trunk_wcat_elems(const b200gat_trunk* t);
 int64_t b200gat_trunk_bwd_workspace_elems(const b200gat_trunk* t);
 int b200gat_trunk_fwd(const b200gat_trunk* t, void* stream);
 int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_grads* g, void* stream);
+
+/* ------------------------------------------------------------------ whole PPO-minibatch evaluation (one call per pass)
+ * Everything alg/ppo.py:575-711 runs on the device for one minibatch - agent.get_action_and_value
+ * (generic/agent.py:190-231: trunk, value_net, action_net, masked categorical) and the clipped-PPO loss (:582-705) -
+ * from ONE host call forward and ONE backward:
+ *   pad jobs (16-byte aligned copies of ragged inputs / weights) -> [embedder MLP] -> b200gat_trunk_fwd ->
+ *   b200gat_readout_fwd -> action_net / value_net MLPs -> masked head -> b200gat_ppo_loss
+ * and the matching chain backward.  The host mirror's step was host-bound (5.6 ms of launch-side time per step
+ * through ~10 autograd nodes against 4.5 ms of device work); issued from C the same launches cost ~1 ms. */
+#define B200GAT_AGENT_MAX_PAD 8
+#define B200GAT_SRC_EXTERNAL 0 /* readout source the trunk did not produce (raw features) */
+#define B200GAT_SRC_X0 1       /* the trunk's input (embedder output)                      */
+#define B200GAT_SRC_LAYER0 2   /* + l: output of trunk layer l                             */
+typedef struct b200gat_pad_job {
+  const float* src;          /* [rows, cols], row stride ld_src                                                  */
+  float* dst;                /* [rows, ld_dst]: the copy, columns cols .. ld_dst-1 zero                          */
+  int64_t ld_src, ld_dst;
+  int32_t rows, cols;
+  int32_t rows_dst;          /* >= rows: rows .. rows_dst-1 of dst are zero too (0 = rows)                        */
+  int32_t reserved;
+} b200gat_pad_job;
+typedef struct b200gat_agent_step {
+  int32_t n_pad;
+  b200gat_pad_job pad[B200GAT_AGENT_MAX_PAD];
+  int32_t has_embedder;      /* 1: trunk.x0 = embedder(x) (jssp/models/gnn_dgl.py:355); 0: the caller built x0   */
+  b200gat_mlp embedder;      /* y must be trunk.x0                                                                */
+  b200gat_trunk trunk;
+  b200gat_readout readout;   /* out_ld must be a multiple of 4 (it is the action_net's input width)              */
+  int32_t src_kind[B200GAT_READOUT_MAX_SRC]; /* B200GAT_SRC_* of every readout source                            */
+  float* node_features;      /* [B, max_n_nodes, out_ld]                                                          */
+  float* graph_embedding;    /* [B, out_ld]                                                                       */
+  int32_t* argmax;           /* [B, F] (max pooling) or NULL                                                      */
+  b200gat_mlp action_net;    /* x = node_features, M = B * max_n_nodes; output width padded to 4, column 0 used  */
+  b200gat_mlp value_net;     /* x = graph_embedding, M = B                                                        */
+  const uint8_t* mask;       /* [B, >= max_n_nodes] or NULL                                                       */
+  int64_t ld_mask;
+  const int64_t* action;     /* [B]                                                                               */
+  float fill;                /* -1e20 (generic/agent.py:206)                                                      */
+  float* logits;             /* [B, max_n_nodes]                                                                  */
+  float* logp;               /* [B, max_n_nodes]                                                                  */
+  float* head;               /* [3, B]: logprob | entropy | value                                                 */
+  b200gat_ppo_loss_args loss;/* logprob / entropy / value are set by the call (rows of `head`)                    */
+  float* loss_out;           /* [9]: loss | the 8 statistics of b200gat_ppo_loss                                  */
+  float* g_head;             /* [3, B]: d loss / d (logprob, entropy, value)                                      */
+} b200gat_agent_step;
+typedef struct b200gat_agent_step_grads {
+  const float* g_loss;       /* device [1]: upstream gradient of the loss, or NULL (= 1)                          */
+  b200gat_mlp_grads embedder, action_net, value_net; /* dW / db (and embedder.dx) from the caller; the rest is   */
+                                                     /* carved out of `workspace` by the call                    */
+  b200gat_trunk_grads trunk; /* the layers' parameter gradients from the caller; g_y / g_x0 / workspace: the call */
+  float* g_src_ext[B200GAT_READOUT_MAX_SRC]; /* gradient of each EXTERNAL readout source [rows, width], or NULL  */
+  float* g_x0;               /* [N, in_dim] total gradient of trunk.x0 (has_embedder == 0), or NULL               */
+  float* workspace;
+  int64_t workspace_elems;
+} b200gat_agent_step_grads;
+int64_t b200gat_agent_bwd_workspace_elems(const b200gat_agent_step* a);
+int b200gat_agent_fwd(const b200gat_agent_step* a, void* stream);
+int b200gat_agent_bwd(const b200gat_agent_step* a, const b200gat_agent_step_grads* g, void* stream);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,7 @@ SYMBOLS = (
     "b200gat_gae", "b200gat_ppo_adv_moments", "b200gat_ppo_loss",
     "b200gat_trunk_supported", "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems",
     "b200gat_trunk_fwd", "b200gat_trunk_bwd",
+    "b200gat_agent_bwd_workspace_elems", "b200gat_agent_fwd", "b200gat_agent_bwd",
 )
 MLP_MAX_LAYERS = 8
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
@@ -169,8 +170,8 @@ class TrunkLayerGrads(C.Structure):
 
 class TrunkGrads(C.Structure):
     """``b200gat_trunk_grads`` (include/b200gat.h)."""
-    _fields_ = [("g_x0", C.c_void_p), ("workspace", C.c_void_p), ("workspace_elems", C.c_int64),
-                ("layer", TrunkLayerGrads * TRUNK_MAX_LAYERS)]
+    _fields_ = [("g_x0", C.c_void_p), ("g_x0_in", C.c_void_p), ("workspace", C.c_void_p),
+                ("workspace_elems", C.c_int64), ("layer", TrunkLayerGrads * TRUNK_MAX_LAYERS)]
 
 
 CRITIC = {"l2": 0, "l1": 1, "sl1": 2}
@@ -182,6 +183,33 @@ class PpoLossArgs(C.Structure):
                 ("entropy", C.c_void_p), ("value", C.c_void_p), ("returns", C.c_void_p), ("old_values", C.c_void_p),
                 ("clip_coef", C.c_float), ("norm_adv", C.c_int32), ("clip_vloss", C.c_int32),
                 ("critic_loss", C.c_int32), ("ent_coef", C.c_float), ("vf_coef", C.c_float), ("moments", C.c_void_p)]
+
+
+AGENT_MAX_PAD = 8
+SRC_EXTERNAL, SRC_X0, SRC_LAYER0 = 0, 1, 2
+
+
+class PadJob(C.Structure):
+    """``b200gat_pad_job`` (include/b200gat.h)."""
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("ld_src", C.c_int64), ("ld_dst", C.c_int64),
+                ("rows", C.c_int32), ("cols", C.c_int32), ("rows_dst", C.c_int32), ("reserved", C.c_int32)]
+
+
+class AgentStep(C.Structure):
+    """``b200gat_agent_step`` (include/b200gat.h)."""
+    _fields_ = [("n_pad", C.c_int32), ("pad", PadJob * AGENT_MAX_PAD), ("has_embedder", C.c_int32),
+                ("embedder", Mlp), ("trunk", Trunk), ("readout", Readout), ("src_kind", C.c_int32 * 16),
+                ("node_features", C.c_void_p), ("graph_embedding", C.c_void_p), ("argmax", C.c_void_p),
+                ("action_net", Mlp), ("value_net", Mlp), ("mask", C.c_void_p), ("ld_mask", C.c_int64),
+                ("action", C.c_void_p), ("fill", C.c_float), ("logits", C.c_void_p), ("logp", C.c_void_p),
+                ("head", C.c_void_p), ("loss", PpoLossArgs), ("loss_out", C.c_void_p), ("g_head", C.c_void_p)]
+
+
+class AgentStepGrads(C.Structure):
+    """``b200gat_agent_step_grads`` (include/b200gat.h)."""
+    _fields_ = [("g_loss", C.c_void_p), ("embedder", MlpGrads), ("action_net", MlpGrads), ("value_net", MlpGrads),
+                ("trunk", TrunkGrads), ("g_src_ext", C.c_void_p * 16), ("g_x0", C.c_void_p),
+                ("workspace", C.c_void_p), ("workspace_elems", C.c_int64)]
 
 
 class B200GatError(RuntimeError):
@@ -261,6 +289,11 @@ def _load():
     lib.b200gat_trunk_bwd_workspace_elems.restype = i64
     lib.b200gat_trunk_fwd.argtypes = [tp, vp]
     lib.b200gat_trunk_bwd.argtypes = [tp, tg, vp]
+    sp, sg = C.POINTER(AgentStep), C.POINTER(AgentStepGrads)
+    lib.b200gat_agent_bwd_workspace_elems.argtypes = [sp]
+    lib.b200gat_agent_bwd_workspace_elems.restype = i64
+    lib.b200gat_agent_fwd.argtypes = [sp, vp]
+    lib.b200gat_agent_bwd.argtypes = [sp, sg, vp]
     rp = C.POINTER(Readout)
     lib.b200gat_readout_fwd.argtypes = [rp, vp, vp, vp, vp]
     lib.b200gat_readout_bwd.argtypes = [rp, vp, i64, vp, i64, vp, C.POINTER(C.c_void_p), i64, vp]
@@ -271,7 +304,8 @@ def _load():
                         "b200gat_clique_scratch_elems", "b200gat_timing_clear_graph",
                         "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
                         "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges", "b200gat_psp_slot_words",
-                        "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems"):
+                        "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems",
+                        "b200gat_agent_bwd_workspace_elems"):
             fn.restype = C.c_int
     return lib
 

@@ -299,7 +299,7 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     float* out = l > 0 ? ws + sh.o_G[(l - 1) & 1] : gr->g_x0;
     if (!out) break;
     const float* r1 = t->residual ? Gy : nullptr;
-    const float* r2 = l > 0 ? gr->layer[l - 1].g_y : nullptr;
+    const float* r2 = l > 0 ? gr->layer[l - 1].g_y : gr->g_x0_in;
     const float* R = r1 ? r1 : r2;
     if (r1 && r2) {
       B200_CHECK_ARG(aligned16t(r1) && aligned16t(r2), "gradients must be 16-byte aligned");

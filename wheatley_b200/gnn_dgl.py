@@ -106,8 +106,8 @@ class GnnDGL(nn.Module):
         """Concatenation of all layers' node embeddings ``[N_total, F]`` (gnn_dgl.py:339-401)."""
         return torch.cat(self.layer_embeddings(b), dim=1)                       # :401
 
-    def layer_embeddings(self, b: JsspBatch):
-        """The list the reference concatenates at :401: input features, embedder output, every layer's output."""
+    def input_features(self, b: JsspBatch):
+        """Raw node features with the pool-node / machine-node rows overwritten by their embeddings (:341-351)."""
         features = b.feat
         if self.graph_pooling == "learn" and b.poolnodes is not None:           # :341-344
             features = features.clone()
@@ -116,14 +116,24 @@ class GnnDGL(nn.Module):
             ids = (torch.arange(self.max_n_machines, device=features.device) + 1).repeat(b.batch_size)
             features = features.clone()
             features[b.machinenodes] = self.node_embedder(ids)
-        features_list = [features]
-        features = self.embedder(features)                                      # :355
-        features_list.append(features)
-        efeats = TypedEdgeFeats(b.etype, self.edge_embedder[0].weight)          # :364
-        # all layers' projected edge-type tables with one GEMM (each layer would do its own 6-row one)
+        return features
+
+    def edge_features(self, b: JsspBatch):
+        """``edge_embedder[0](g.edata["type"])`` (:364) kept factored, with every layer's projected edge-type table
+        from one GEMM (each layer would do its own 6-row one)."""
+        efeats = TypedEdgeFeats(b.etype, self.edge_embedder[0].weight)
         efeats.tables = edge_tables(self.edge_embedder[0].weight,
                                     [fe.fc_fij.weight for fe in self.features_extractors],
                                     [fe.bias for fe in self.features_extractors])
+        return efeats
+
+    def layer_embeddings(self, b: JsspBatch):
+        """The list the reference concatenates at :401: input features, embedder output, every layer's output."""
+        features = self.input_features(b)
+        features_list = [features]
+        features = self.embedder(features)                                      # :355
+        features_list.append(features)
+        efeats = self.edge_features(b)
         specs = self._trunk_specs(efeats)
         if specs is not None and trunk_applicable(features, specs, self.features_extractors[0]._num_heads, self.hidden_dim):
             # all L layers behind one autograd node / one C-ABI call per pass (wheatley_b200.trunk)

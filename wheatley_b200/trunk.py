@@ -67,67 +67,135 @@ def _fill_layer(L, cfg, tensors, etype_sorted, attr_sorted, edge_mode):
     return pw, pb, attn, out_bias, table, affine, mw, mb
 
 
+def setup_trunk(t, view, cfg, etype_sorted, attr_sorted, x0, flat, need):
+    """Fill the ``b200gat_trunk`` struct ``t`` (a ``_lib.Trunk``, possibly embedded in a larger struct) and allocate
+    what the forward writes.  Returns ``(flat_c, keep, y)``: the contiguous parameter tensors, every tensor whose
+    storage ``t`` points into (keep them alive as long as ``t`` is used) and the ``[L, N, in_dim]`` layer outputs."""
+    nl, n_proj, n_mlp, H, D = cfg["n_layers"], cfg["n_proj"], cfg["n_mlp"], cfg["heads"], cfg["dim"]
+    per = 2 * n_proj + 4 + 2 * n_mlp
+    assert len(flat) == nl * per
+    dev = x0.device
+    flat_c = [_c(None if f is None else (f.reshape(-1) if i % per == 2 * n_proj else f)) for i, f in enumerate(flat)]
+    N, E, HD, in_dim = x0.shape[0], int(view.c.n_edges), H * D, x0.shape[1]
+    t.n_layers, t.in_dim, t.residual, t.n_nodes = nl, in_dim, int(cfg["residual"]), N
+    t.graph = C.pointer(view.c)
+    t.x0 = x0.data_ptr()
+    for l in range(nl):
+        filled = _fill_layer(t.layer[l], cfg, flat_c[l * per:(l + 1) * per], etype_sorted, attr_sorted,
+                             cfg["edge_mode"])
+        if filled[4] is not None:            # IndexError like nn.Embedding instead of an out-of-bounds gather
+            check_edge_types(etype_sorted, filled[4].shape[0])
+    if not _lib.lib.b200gat_trunk_supported(C.byref(t)):
+        raise _lib.B200GatError("trunk configuration not covered by b200gat_trunk_fwd (use the layer modules)")
+    f32 = dict(dtype=torch.float32, device=dev)
+    wcat = torch.empty(int(_lib.lib.b200gat_trunk_wcat_elems(C.byref(t))), **f32)
+    t.wcat = wcat.data_ptr()
+    dense = bool(_lib.lib.b200gat_conv_uses_cliques(t.graph, C.byref(t.layer[0].attn), C.byref(t.layer[0].ef)))
+    s_el = H * getattr(view, "s_elems", 0) if dense else 0
+    # saved activations: one allocation per kind for all layers (every layer's slice is read by the backward);
+    # without autograd every layer re-uses the first slice
+    nk = nl if need else 1
+    hid = [t.layer[0].dims[i + 1] for i in range(n_mlp - 1)]
+    P = torch.empty((nk, n_proj, N, HD), **f32)
+    conv_out = torch.empty((nk, N, HD), **f32)
+    s = torch.empty((nk, max(E, 1), H), **f32)
+    ml = torch.empty((nk, 2, N, H), **f32)
+    agg = torch.empty((nk, N, HD), **f32) if (need or dense) else None
+    s_dense = torch.empty((nk, max(s_el, 4)), **f32) if dense else None
+    hs = [torch.empty((nk, N, w), **f32) for w in hid]
+    zs = [torch.empty((nk, N, w), **f32) for w in hid] if need else []
+    y = torch.empty((nl, N, in_dim), **f32)
+    ptr = lambda a, k: a.data_ptr() + k * a.stride(0) * 4                          # noqa: E731
+    for l in range(nl):
+        L, k = t.layer[l], (l if need else 0)
+        L.P, L.conv_out, L.s_save = ptr(P, k), ptr(conv_out, k), ptr(s, k)
+        L.m_save = ptr(ml, k)
+        L.l_save = L.m_save + ml.stride(1) * 4
+        L.agg_save = None if agg is None else ptr(agg, k)
+        L.s_dense = None if s_dense is None else ptr(s_dense, k)
+        for i in range(n_mlp - 1):
+            L.h[i] = ptr(hs[i], k)
+            L.z[i] = ptr(zs[i], k) if zs else None
+        L.y = ptr(y, l)
+    keep = [x0, *flat_c, wcat, P, conv_out, s, ml, agg, s_dense, *hs, *zs, y, etype_sorted, attr_sorted]
+    return flat_c, keep, y
+
+
+def setup_trunk_grads(g, cfg, flat_c, shapes, dev):
+    """Fill the per-layer parameter-gradient pointers of ``g`` (a ``_lib.TrunkGrads``) and return the gradient
+    tensors in the order of the flat parameter list.  A handful of allocations for all layers: the concatenated
+    projection gradients, one zero-filled buffer for the atomically accumulated ones, one stacked tensor per MLP
+    weight / bias position."""
+    nl, n_proj, n_mlp, H, D = cfg["n_layers"], cfg["n_proj"], cfg["n_mlp"], cfg["heads"], cfg["dim"]
+    per = 2 * n_proj + 4 + 2 * n_mlp
+    HD = H * D
+    in_dim = flat_c[0].shape[1]
+    f32 = dict(dtype=torch.float32, device=dev)
+    sizes = []
+    for l in range(nl):
+        attn, _ob, table, affine = flat_c[l * per + 2 * n_proj: l * per + 2 * n_proj + 4]
+        sizes += [(attn.numel() + 3) // 4 * 4, 0 if table is None else (table.numel() + 3) // 4 * 4,
+                  0 if affine is None else (affine.numel() + 3) // 4 * 4]
+    zbuf = torch.zeros(sum(sizes), **f32)
+    dWp = torch.empty((nl, n_proj * HD, in_dim), **f32)
+    has_pb = flat_c[n_proj] is not None
+    dbp = torch.empty((nl, n_proj * HD), **f32) if has_pb else None
+    has_ob = flat_c[2 * n_proj + 1] is not None
+    g_ob = torch.empty((nl, HD), **f32) if has_ob else None
+    mw = [flat_c[2 * n_proj + 4 + i] for i in range(n_mlp)]
+    dWs = [torch.empty((nl,) + tuple(w.shape), **f32) for w in mw]                 # layers share their MLP shapes
+    dbs = [torch.empty((nl, w.shape[0]), **f32) if flat_c[2 * n_proj + 4 + n_mlp + i] is not None else None
+           for i, w in enumerate(mw)]
+    grads = [None] * (nl * per)
+    off = 0
+    zp = zbuf.data_ptr()
+    for l in range(nl):
+        G = g.layer[l]
+        base = l * per
+        attn, _ob, table, affine = flat_c[base + 2 * n_proj: base + 2 * n_proj + 4]
+        G.dWp = dWp.data_ptr() + l * dWp.stride(0) * 4
+        G.dbp = None if dbp is None else dbp.data_ptr() + l * dbp.stride(0) * 4
+        dWp_l = dWp[l]
+        for p in range(n_proj):
+            grads[base + p] = dWp_l[p * HD:(p + 1) * HD]
+            if has_pb:
+                grads[base + n_proj + p] = dbp[l, p * HD:(p + 1) * HD]
+        G.g_attn = zp + 4 * off
+        grads[base + 2 * n_proj] = zbuf[off: off + attn.numel()].view(shapes[base + 2 * n_proj])
+        off += sizes[3 * l]
+        if has_ob:
+            G.g_out_bias = g_ob.data_ptr() + l * HD * 4
+            grads[base + 2 * n_proj + 1] = g_ob[l]
+        if table is not None:
+            G.g_table = zp + 4 * off
+            grads[base + 2 * n_proj + 2] = zbuf[off: off + table.numel()].view(table.shape)
+        off += sizes[3 * l + 1]
+        if affine is not None:
+            G.g_affine = zp + 4 * off
+            grads[base + 2 * n_proj + 3] = zbuf[off: off + affine.numel()].view(affine.shape)
+        off += sizes[3 * l + 2]
+        for i in range(n_mlp):
+            G.dW[i] = dWs[i].data_ptr() + l * dWs[i].stride(0) * 4
+            grads[base + 2 * n_proj + 4 + i] = dWs[i][l]
+            if dbs[i] is not None:
+                G.db[i] = dbs[i].data_ptr() + l * dbs[i].stride(0) * 4
+                grads[base + 2 * n_proj + 4 + n_mlp + i] = dbs[i][l]
+    return grads
+
+
 class _TrunkFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, view, cfg, etype_sorted, attr_sorted, x0, *flat):
-        nl, n_proj, n_mlp, H, D = cfg["n_layers"], cfg["n_proj"], cfg["n_mlp"], cfg["heads"], cfg["dim"]
-        per = 2 * n_proj + 4 + 2 * n_mlp
-        assert len(flat) == nl * per
-        dev = x0.device
         x0 = _c(x0)
-        flat_c = [_c(None if t is None else (t.reshape(-1) if i % per == 2 * n_proj else t))
-                  for i, t in enumerate(flat)]
-        N, E, HD, in_dim = x0.shape[0], int(view.c.n_edges), H * D, x0.shape[1]
-        edge_mode = cfg["edge_mode"]
         need = any(ctx.needs_input_grad)
         t = _lib.Trunk()
-        t.n_layers, t.in_dim, t.residual, t.n_nodes = nl, in_dim, int(cfg["residual"]), N
-        t.graph = C.pointer(view.c)
-        t.x0 = x0.data_ptr()
-        layers = []
-        for l in range(nl):
-            layers.append(_fill_layer(t.layer[l], cfg, flat_c[l * per:(l + 1) * per], etype_sorted, attr_sorted,
-                                      edge_mode))
-            if layers[-1][4] is not None:       # IndexError like nn.Embedding instead of an out-of-bounds gather
-                check_edge_types(etype_sorted, layers[-1][4].shape[0])
-        if not _lib.lib.b200gat_trunk_supported(C.byref(t)):
-            raise _lib.B200GatError("trunk configuration not covered by b200gat_trunk_fwd (use the layer modules)")
-        f32 = dict(dtype=torch.float32, device=dev)
-        wcat = torch.empty(int(_lib.lib.b200gat_trunk_wcat_elems(C.byref(t))), **f32)
-        t.wcat = wcat.data_ptr()
-        dense = bool(_lib.lib.b200gat_conv_uses_cliques(t.graph, C.byref(t.layer[0].attn), C.byref(t.layer[0].ef)))
-        s_el = H * getattr(view, "s_elems", 0) if dense else 0
-        # saved activations: one allocation per kind for all layers (every layer's slice is read by the backward);
-        # without autograd every layer re-uses the first slice
-        nk = nl if need else 1
-        hid = [t.layer[0].dims[i + 1] for i in range(n_mlp - 1)]
-        P = torch.empty((nk, n_proj, N, HD), **f32)
-        conv_out = torch.empty((nk, N, HD), **f32)
-        s = torch.empty((nk, max(E, 1), H), **f32)
-        ml = torch.empty((nk, 2, N, H), **f32)
-        agg = torch.empty((nk, N, HD), **f32) if (need or dense) else None
-        s_dense = torch.empty((nk, max(s_el, 4)), **f32) if dense else None
-        hs = [torch.empty((nk, N, w), **f32) for w in hid]
-        zs = [torch.empty((nk, N, w), **f32) for w in hid] if need else None
-        y = torch.empty((nl, N, in_dim), **f32)
-        for l in range(nl):
-            L, k = t.layer[l], (l if need else 0)
-            L.P, L.conv_out, L.s_save = P[k].data_ptr(), conv_out[k].data_ptr(), s[k].data_ptr()
-            L.m_save, L.l_save = ml[k, 0].data_ptr(), ml[k, 1].data_ptr()
-            L.agg_save = None if agg is None else agg[k].data_ptr()
-            L.s_dense = None if s_dense is None else s_dense[k].data_ptr()
-            for i in range(n_mlp - 1):
-                L.h[i] = hs[i][k].data_ptr()
-                L.z[i] = None if zs is None else zs[i][k].data_ptr()
-            L.y = y[l].data_ptr()
-        with _lib.device_guard(dev):
+        flat_c, keep, y = setup_trunk(t, view, cfg, etype_sorted, attr_sorted, x0, flat, need)
+        with _lib.device_guard(x0.device):
             _lib.check(_lib.lib.b200gat_trunk_fwd(C.byref(t), _lib.stream_ptr()), "b200gat_trunk_fwd")
         if need:
             ctx.t, ctx.view, ctx.cfg = t, view, cfg
-            # raw pointers in ctx.t stay valid while these are alive
             ctx.n_flat = len(flat_c)
-            ctx.save_for_backward(x0, *flat_c, wcat, P, conv_out, s, ml, agg, s_dense, *hs, *zs, y, etype_sorted,
-                                  attr_sorted)
+            ctx.save_for_backward(*keep)          # raw pointers in ctx.t stay valid while these are alive
             ctx.shapes = [None if f is None else f.shape for f in flat]
             ctx.set_materialize_grads(False)
         return tuple(y.unbind(0))
@@ -135,71 +203,20 @@ class _TrunkFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, *g_ys):
         t, cfg = ctx.t, ctx.cfg
-        nl, n_proj, n_mlp, H, D = cfg["n_layers"], cfg["n_proj"], cfg["n_mlp"], cfg["heads"], cfg["dim"]
-        per = 2 * n_proj + 4 + 2 * n_mlp
+        nl = cfg["n_layers"]
         saved = ctx.saved_tensors
         x0, flat_c = saved[0], list(saved[1: 1 + ctx.n_flat])
         if all(g is None for g in g_ys):
-            return (None,) * (5 + nl * per)
+            return (None,) * (5 + len(flat_c))
         dev = x0.device
         f32 = dict(dtype=torch.float32, device=dev)
-        N, in_dim, HD = x0.shape[0], x0.shape[1], H * D
         g = _lib.TrunkGrads()
         g_ys = [None if gy is None else _c(gy) for gy in g_ys]
         if g_ys[-1] is None:
-            g_ys[-1] = torch.zeros((N, in_dim), **f32)
-        # small accumulated gradients (attn, table, affine of every layer): one zero-filled buffer
-        sizes = []
+            g_ys[-1] = torch.zeros(tuple(x0.shape), **f32)
+        grads = setup_trunk_grads(g, cfg, flat_c, ctx.shapes, dev)
         for l in range(nl):
-            attn, _ob, table, affine = flat_c[l * per + 2 * n_proj: l * per + 2 * n_proj + 4]
-            sizes += [(attn.numel() + 3) // 4 * 4, 0 if table is None else (table.numel() + 3) // 4 * 4,
-                      0 if affine is None else (affine.numel() + 3) // 4 * 4]
-        zbuf = torch.zeros(sum(sizes), **f32)
-        dWp = torch.empty((nl, n_proj * HD, in_dim), **f32)
-        has_pb = flat_c[n_proj] is not None
-        dbp = torch.empty((nl, n_proj * HD), **f32) if has_pb else None
-        has_ob = flat_c[2 * n_proj + 1] is not None
-        g_ob = torch.empty((nl, HD), **f32) if has_ob else None
-        grads = [None] * (nl * per)
-        off = 0
-        keep_alive = []
-        for l in range(nl):
-            G = g.layer[l]
-            base = l * per
-            attn, _ob, table, affine = flat_c[base + 2 * n_proj: base + 2 * n_proj + 4]
-            G.g_y = _lib.ptr(g_ys[l])
-            G.dWp = dWp[l].data_ptr()
-            G.dbp = None if dbp is None else dbp[l].data_ptr()
-            for p in range(n_proj):
-                grads[base + p] = dWp[l, p * HD:(p + 1) * HD]
-                if has_pb:
-                    grads[base + n_proj + p] = dbp[l, p * HD:(p + 1) * HD]
-            ga = zbuf[off: off + attn.numel()]
-            off += sizes[3 * l]
-            G.g_attn = ga.data_ptr()
-            grads[base + 2 * n_proj] = ga.view(ctx.shapes[base + 2 * n_proj])
-            if has_ob:
-                G.g_out_bias = g_ob[l].data_ptr()
-                grads[base + 2 * n_proj + 1] = g_ob[l]
-            if table is not None:
-                gt = zbuf[off: off + table.numel()].view(table.shape)
-                G.g_table = gt.data_ptr()
-                grads[base + 2 * n_proj + 2] = gt
-            off += sizes[3 * l + 1]
-            if affine is not None:
-                gf = zbuf[off: off + affine.numel()].view(affine.shape)
-                G.g_affine = gf.data_ptr()
-                grads[base + 2 * n_proj + 3] = gf
-            off += sizes[3 * l + 2]
-            for i in range(n_mlp):
-                W = flat_c[base + 2 * n_proj + 4 + i]
-                dW = torch.empty_like(W)
-                G.dW[i] = dW.data_ptr()
-                grads[base + 2 * n_proj + 4 + i] = dW
-                if flat_c[base + 2 * n_proj + 4 + n_mlp + i] is not None:
-                    db = torch.empty(W.shape[0], **f32)
-                    G.db[i] = db.data_ptr()
-                    grads[base + 2 * n_proj + 4 + n_mlp + i] = db
+            g.layer[l].g_y = _lib.ptr(g_ys[l])
         g_x0 = torch.empty_like(x0) if ctx.needs_input_grad[4] else None
         g.g_x0 = _lib.ptr(g_x0)
         ws_elems = int(_lib.lib.b200gat_trunk_bwd_workspace_elems(C.byref(t)))
@@ -212,16 +229,20 @@ class _TrunkFn(torch.autograd.Function):
         return (None, None, None, None, g_x0, *grads)
 
 
+def trunk_cfg(specs, heads, dim, slope, eps, residual):
+    s0 = specs[0]
+    mode = _lib.EDGE_NONE if s0.table is None else (_lib.EDGE_TABLE if s0.affine is None else _lib.EDGE_AFFINE)
+    return dict(n_layers=len(specs), n_proj=len(s0.proj_w), n_mlp=len(s0.mlp_w), heads=int(heads), dim=int(dim),
+                slope=float(slope), eps=float(eps), residual=bool(residual), edge_mode=mode)
+
+
 def fused_trunk(view, etype_sorted, attr_sorted, x0, specs, *, heads, dim, slope, eps, residual):
     """Outputs of the L layers, ``[N, in_dim]`` each.  ``view``: the plan / clique view the layers' edge mode
     selects (``EdgeFeatures.graph_view``); ``etype_sorted`` / ``attr_sorted``: per-edge type ids / attributes in the
     plan's destination-sorted order (shared by all layers)."""
     if not x0.is_cuda:
         raise _lib.B200GatError("wheatley_b200 kernels need CUDA tensors (no CPU fallback)")
-    s0 = specs[0]
-    mode = _lib.EDGE_NONE if s0.table is None else (_lib.EDGE_TABLE if s0.affine is None else _lib.EDGE_AFFINE)
-    cfg = dict(n_layers=len(specs), n_proj=len(s0.proj_w), n_mlp=len(s0.mlp_w), heads=int(heads), dim=int(dim),
-               slope=float(slope), eps=float(eps), residual=bool(residual), edge_mode=mode)
+    cfg = trunk_cfg(specs, heads, dim, slope, eps, residual)
     flat = []
     for sp in specs:
         flat += sp.flat()
