@@ -18,14 +18,35 @@ constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;  // 2048
 constexpr int kWarpSortMax = 256;
 
+// Warp-aggregated atomics: consecutive edges of a batched schedule graph share an endpoint (the conflict-clique
+// edges of one task are stored together), so a warp's 32 atomics on one counter become one.
+__device__ __forceinline__ void agg_inc(int32_t* base, int key, bool on) {
+  const unsigned act = __ballot_sync(0xffffffffu, on);
+  if (!on) return;
+  const unsigned peers = __match_any_sync(act, key);
+  if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(base + key, __popc(peers));
+}
+// slot = (old value of base[key]) + rank among the warp's lanes with the same key
+__device__ __forceinline__ int agg_slot(int32_t* base, int key, bool on) {
+  const unsigned act = __ballot_sync(0xffffffffu, on);
+  if (!on) return 0;
+  const unsigned peers = __match_any_sync(act, key);
+  const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+  int old = 0;
+  if (lane == leader) old = atomicAdd(base + key, __popc(peers));
+  old = __shfl_sync(peers, old, leader);
+  return old + __popc(peers & ((1u << lane) - 1u));
+}
+
 __global__ void k_count(const int64_t* __restrict__ src, const int64_t* __restrict__ dst, int64_t E,
                         int32_t N, int32_t* __restrict__ in_ptr, int32_t* __restrict__ out_ptr,
                         int32_t* __restrict__ stats, int vec) {
   // two edges per thread: one 16-byte load per endpoint array when both are 16-byte aligned
   int64_t i = (int64_t)(blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
   int bad = 0;
-  if (i + 1 < E) {
-    longlong2 s, d;
+  longlong2 s = make_longlong2(-1, -1), d = make_longlong2(-1, -1);
+  const bool has0 = i < E, has1 = i + 1 < E;
+  if (has1) {
     if (vec) {
       s = *reinterpret_cast<const longlong2*>(src + i);
       d = *reinterpret_cast<const longlong2*>(dst + i);
@@ -33,15 +54,16 @@ __global__ void k_count(const int64_t* __restrict__ src, const int64_t* __restri
       s = make_longlong2(src[i], src[i + 1]);
       d = make_longlong2(dst[i], dst[i + 1]);
     }
-    if (s.x < 0 || s.x >= N || d.x < 0 || d.x >= N) bad++;
-    else { atomicAdd(&in_ptr[d.x + 1], 1); atomicAdd(&out_ptr[s.x + 1], 1); }
-    if (s.y < 0 || s.y >= N || d.y < 0 || d.y >= N) bad++;
-    else { atomicAdd(&in_ptr[d.y + 1], 1); atomicAdd(&out_ptr[s.y + 1], 1); }
-  } else if (i < E) {
-    int64_t s = src[i], d = dst[i];
-    if (s < 0 || s >= N || d < 0 || d >= N) bad++;
-    else { atomicAdd(&in_ptr[d + 1], 1); atomicAdd(&out_ptr[s + 1], 1); }
+  } else if (has0) {
+    s.x = src[i]; d.x = dst[i];
   }
+  const bool ok0 = has0 && s.x >= 0 && s.x < N && d.x >= 0 && d.x < N;
+  const bool ok1 = has1 && s.y >= 0 && s.y < N && d.y >= 0 && d.y < N;
+  bad = (has0 && !ok0) + (has1 && !ok1);
+  agg_inc(in_ptr + 1, (int)d.x, ok0);
+  agg_inc(out_ptr + 1, (int)s.x, ok0);
+  agg_inc(in_ptr + 1, (int)d.y, ok1);
+  agg_inc(out_ptr + 1, (int)s.y, ok1);
   if (bad) atomicAdd(&stats[2], bad);
 }
 
@@ -120,11 +142,14 @@ __global__ void k_fill(const int64_t* __restrict__ src, const int64_t* __restric
                        int32_t* __restrict__ fill_out, int32_t* __restrict__ tmp_in,
                        int32_t* __restrict__ tmp_out) {
   int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (e >= E) return;
-  int64_t s = src[e], d = dst[e];
-  if (s < 0 || s >= N || d < 0 || d >= N) return;
-  tmp_in[in_ptr[d] + atomicAdd(&fill_in[d], 1)] = (int32_t)e;
-  tmp_out[out_ptr[s] + atomicAdd(&fill_out[s], 1)] = (int32_t)e;
+  int64_t s = -1, d = -1;
+  if (e < E) { s = src[e]; d = dst[e]; }
+  const bool ok = e < E && s >= 0 && s < N && d >= 0 && d < N;
+  const int si = agg_slot(fill_in, (int)d, ok);
+  const int so = agg_slot(fill_out, (int)s, ok);
+  if (!ok) return;
+  tmp_in[in_ptr[d] + si] = (int32_t)e;
+  tmp_out[out_ptr[s] + so] = (int32_t)e;
 }
 
 // ---- stable order inside segments: rank by counting -------------------------------------
@@ -275,9 +300,11 @@ __global__ void k_gather_i32_range(const int32_t* __restrict__ table, const int3
     lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
     hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
   }
+  // 1.6 M edges = 50 k warps hammering two addresses cost 79 us; the range converges after the first few warps, so
+  // look (a plain, possibly stale read: the atomic re-checks) before touching it
   if ((threadIdx.x & 31) == 0 && lo <= hi) {
-    atomicMin(range, lo);
-    atomicMax(range + 1, hi);
+    if (lo < *reinterpret_cast<volatile int32_t*>(range)) atomicMin(range, lo);
+    if (hi > *reinterpret_cast<volatile int32_t*>(range + 1)) atomicMax(range + 1, hi);
   }
 }
 __global__ void k_init_range(int32_t* range) {
