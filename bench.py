@@ -31,7 +31,13 @@ WORKLOADS = {  # name: (n_jobs, n_machines, default graphs per GPU)
     "taillard15x15": (15, 15, 128),
     "taillard30x20": (30, 20, 64),
     "jssp10x10": (10, 10, 128),
+    # PSP / PyG flavour = the reference's LIVE trainer (psp.train_psp): GATv2 layers, PspEdgeEmbedder
+    # edge features, resource-node conflicts, learned pool node
+    "psp272": (4, 4, 1536),                # 272.sh:1: --batch_size 1536 --hidden_dim 32 --n_layers 4 --conflicts node
+    "psp_taillard100x20": (100, 20, 8),
 }
+PSP_DEFAULTS = {"psp272": dict(hidden=32, layers=4, conflicts="node"),
+                "psp_taillard100x20": dict(hidden=64, layers=6, conflicts="node")}
 METRIC = "gnn_fwd_bwd_graph_edges_per_sec"
 UNIT = "edges/s"
 
@@ -44,8 +50,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="taillard100x20", choices=sorted(WORKLOADS))
     ap.add_argument("--graphs-per-gpu", type=int, default=0)
-    ap.add_argument("--layers", type=int, default=6)
-    ap.add_argument("--hidden", type=int, default=64)
+    ap.add_argument("--layers", type=int, default=0, help="0 = the workload's default (6; 4 for psp272)")
+    ap.add_argument("--hidden", type=int, default=0, help="0 = the workload's default (64; 32 for psp272)")
+    ap.add_argument("--conflicts", default=None, help="PSP workloads: node (default) | clique")
     ap.add_argument("--heads", type=int, default=4)
     ap.add_argument("--progress", type=float, default=0.0, help="episode progress of the graph snapshot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -59,8 +66,12 @@ def parse():
 
 def model_config(args):
     n_j, n_m, b = WORKLOADS[args.workload]
-    return dict(n_j=n_j, n_m=n_m, graphs=args.graphs_per_gpu or b, input_dim=6 + n_m + 4,
-                max_n_nodes=n_j * n_m, layers=args.layers, hidden=args.hidden, heads=args.heads)
+    psp = args.workload.startswith("psp")
+    dflt = PSP_DEFAULTS.get(args.workload, dict(hidden=64, layers=6, conflicts="clique"))
+    return dict(n_j=n_j, n_m=n_m, graphs=args.graphs_per_gpu or b, input_dim=16 if psp else 6 + n_m + 4,
+                max_n_nodes=n_j * n_m + (2 if psp else 0), layers=args.layers or dflt["layers"],
+                hidden=args.hidden or dflt["hidden"], heads=args.heads, psp=psp,
+                conflicts=(args.conflicts or dflt["conflicts"]) if psp else "clique")
 
 
 PPO_KW = dict(clip_coef=0.2, norm_adv=True, critic_loss="l2", ent_coef=0.05, vf_coef=0.5)   # alg/ppo.py:85-102
@@ -89,8 +100,42 @@ def build_oracle(cfg, seed=0):
     return trunk_oracle.OracleAgent(gnn, cfg["input_dim"] + cfg["hidden"] * (cfg["layers"] + 1))
 
 
+def cpu_step_fn_psp(cfg, n_graphs, progress, seed0=0):
+    """PSP flavour on the host cores: the numpy batch oracle's graph (built once, outside the timed step, like the
+    GPU arm's resident leg) through the oracle GnnMP trunk, heads and the PPO loss, fwd + bwd."""
+    import numpy as np
+    from oracle import head_oracle, ppo_oracle, psp_batch_oracle as pbo, trunk_oracle
+    from wheatley_b200_workload import psp_taillard_graph
+    graphs = [psp_taillard_graph(cfg["n_j"], cfg["n_m"], seed0 + b, progress=progress) for b in range(n_graphs)]
+    b = pbo.psp_batch(graphs, cfg["conflicts"], "learn", True)
+    torch.manual_seed(0)
+    gnn = trunk_oracle.OracleGnnMP(16, "learn", cfg["max_n_nodes"], 3, cfg["layers"], cfg["hidden"], "gelu",
+                                   cfg["heads"], conflicts=cfg["conflicts"])
+    F = 16 + cfg["hidden"] * (cfg["layers"] + 1)
+    vn, an = trunk_oracle.OracleMLP(3, F, 64, 1, False, "gelu"), trunk_oracle.OracleMLP(3, F, 64, 1, False, "gelu")
+    params = list(gnn.parameters()) + list(vn.parameters()) + list(an.parameters())
+    masks, action, adv, ret, old_lp, old_v = synth_targets(n_graphs, cfg["max_n_nodes"], 1)
+    T = lambda a: torch.from_numpy(np.asarray(a))                                          # noqa: E731
+    rn = b["resource_nodes"]
+    args_ = (T(b["edge_index"]), T(b["type"]), T(b["att_rc"]).float(), T(b["att_rp"]).float(), T(b["feat"]).float(),
+             n_graphs, b["num_nodes"], b["n_nodes"].tolist() if n_graphs > 1 else int(b["n_nodes"][0]),
+             b["poolnodes"].tolist(), None if rn is None else rn.tolist(), T(b["res_cal_id"]).float())
+
+    def step():
+        for p in params:
+            p.grad = None
+        nf, ge = gnn(*args_)
+        _, logprob, entropy, _ = head_oracle.action_and_logprob(an(nf).squeeze(-1), action, masks)
+        loss, _ = ppo_oracle.ppo_loss(logprob, entropy, vn(ge), old_lp, adv, ret, **PPO_KW)
+        loss.backward()
+        return loss.item()
+    return step, int(b["edge_index"].shape[1])
+
+
 def cpu_step_fn(cfg, n_graphs, progress, seed0=0):
     """The oracle's fwd+bwd over ``n_graphs`` graphs of the workload on the host cores."""
+    if cfg["psp"]:
+        return cpu_step_fn_psp(cfg, n_graphs, progress, seed0)
     from wheatley_b200_workload import jssp_batch
     agent = build_oracle(cfg)
     b = jssp_batch(cfg["n_j"], cfg["n_m"], n_graphs, seed0, progress)
@@ -110,7 +155,7 @@ def cpu_step_fn(cfg, n_graphs, progress, seed0=0):
 def time_cpu(cfg, args, steps, warmup, budget_s=None):
     """Bounded CPU sample: graphs per step chosen so a step is ~1-3 s of host work."""
     torch.set_num_threads(os.cpu_count() or 1)
-    n_graphs = 1 if cfg["n_j"] * cfg["n_m"] >= 1000 else min(cfg["graphs"], 16)
+    n_graphs = 1 if cfg["n_j"] * cfg["n_m"] >= 1000 else min(cfg["graphs"], 256 if cfg["psp"] else 16)
     step, edges = cpu_step_fn(cfg, n_graphs, args.progress)
     for _ in range(warmup):
         step()
@@ -145,8 +190,12 @@ def run_reference(args):
 
 
 def workload_config(args, cfg, graphs, note=None):
-    c = {"workload": f"{args.workload} DGL-flavour clique conflicts + learned pool node, progress {args.progress}",
-         "graphs_per_gpu": graphs, "nodes_per_graph": cfg["max_n_nodes"] + 1, "layers": cfg["layers"],
+    what = (f"PSP / PyG flavour (GATv2 layers, PspEdgeEmbedder), conflicts={cfg['conflicts']} + learned pool node"
+            if cfg["psp"] else "DGL-flavour clique conflicts + learned pool node")
+    c = {"workload": f"{args.workload} {what}, progress {args.progress}",
+         "graphs_per_gpu": graphs, "nodes_per_graph": cfg["max_n_nodes"] + 1 + (cfg["n_m"] if cfg["psp"] and
+                                                                               cfg["conflicts"] == "node" else 0),
+         "layers": cfg["layers"],
          "hidden": cfg["hidden"], "heads": cfg["heads"], "mlp_layers": 3, "activation": "gelu"}
     if note:
         c["note"] = note
@@ -239,36 +288,69 @@ def run_b200(args):
     cfg = model_config(args)
     B = cfg["graphs"]
     torch.manual_seed(0)                               # identical replicas on every rank
-    agent = JsspAgent(cfg["input_dim"], cfg["max_n_nodes"], cfg["n_m"], cfg["hidden"], cfg["layers"],
-                      cfg["heads"]).to(dev)
+    psp = cfg["psp"]
+    if psp:
+        from wheatley_b200.agent import PspAgent
+        agent = PspAgent(cfg["max_n_nodes"], cfg["n_m"], hidden_dim=cfg["hidden"], n_layers=cfg["layers"],
+                         n_heads=cfg["heads"], conflicts=cfg["conflicts"]).to(dev)
+    else:
+        agent = JsspAgent(cfg["input_dim"], cfg["max_n_nodes"], cfg["n_m"], cfg["hidden"], cfg["layers"],
+                          cfg["heads"]).to(dev)
     bucket = FlatGradAllReduce(list(agent.parameters()))
     # Adam of alg/ppo.py on ONE flat parameter / the all-reduced flat gradient (ppo.FlatAdam)
     opt = FlatAdam(agent.parameters(), lr=2e-4, bucket=bucket)
 
-    hb = jssp_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress)
     masks, action, adv, ret, old_lp, old_v = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
-    host = dict(src=hb["src"], dst=hb["dst"], etype=hb["etype"], feat=hb["feat"], masks=masks,
-                action=action, adv=adv, ret=ret, old_lp=old_lp, old_v=old_v)
-    host = {k: v.contiguous().pin_memory() for k, v in host.items()}
-    # the e2e / rollout legs start from the padded gym observation (what the reference's batching receives,
-    # jssp/models/agent_observation.py:127-131): the batched graph is built on the device (wheatley_b200.batch)
-    from wheatley_b200.workload import jssp_observation_batch
-    from wheatley_b200.batch import jssp_batch_from_observation
-    obs = {k: v.contiguous().pin_memory() for k, v in
-           jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress).items()}
-    extras = {k: host[k] for k in ("masks", "action", "adv", "ret", "old_lp", "old_v")}
-    builder_kw = dict(conflicts="clique", graph_pooling="learn")
-    h2d_bytes = (sum(v.numel() * v.element_size() for v in obs.values())
-                 + sum(v.numel() * v.element_size() for v in extras.values()) + 4 * (B + 1) * 8)
-    N, E, NT = hb["n_nodes"], hb["n_edges"], hb["n_task_nodes"]
+    extras = dict(masks=masks, action=action, adv=adv, ret=ret, old_lp=old_lp, old_v=old_v)
+    extras = {k: v.contiguous().pin_memory() for k, v in extras.items()}
+    from wheatley_b200.prefetch import BatchPrefetcher
+    if psp:
+        # the e2e / rollout legs start from the wire-format observation slots the env workers write
+        # (wheatley_b200.wire); the batched graph is built on the device (wheatley_b200.psp_batch)
+        from wheatley_b200.wire import PspArena
+        from wheatley_b200.workload import psp_taillard_graph
+        arena = PspArena.from_graphs([psp_taillard_graph(cfg["n_j"], cfg["n_m"], rank * B + b, progress=args.progress)
+                                      for b in range(B)])
+        h2d_bytes = (arena.tensor[:B].numel() * arena.tensor.element_size() + 5 * (B + 1) * 8
+                     + sum(v.numel() * v.element_size() for v in extras.values()))
+        input_note = ("arena of wire-format observation slots (wheatley_b200.wire: features, resources, precedence / "
+                      "resource-priority edges per graph) + masks / actions / advantages / returns / old log-probs / "
+                      "old values in pinned host memory; self loops, reverse edges, resource / pool nodes and their "
+                      "wiring are built on the device by b200gat_psp_batch_build")
+
+        def build_batch():
+            return agent.preprocess(arena)
+
+        def submit(pf):
+            pf.submit_psp(agent, arena, extras)
+        probe = build_batch()
+        N, E, NT = int(probe[0].ndata("feat").shape[0]), int(probe[0].edge_index.shape[1]), int(probe[2])
+        del probe
+    else:
+        # the e2e / rollout legs start from the padded gym observation (what the reference's batching receives,
+        # jssp/models/agent_observation.py:127-131): the batched graph is built on the device (wheatley_b200.batch)
+        from wheatley_b200.workload import jssp_observation_batch
+        from wheatley_b200.batch import jssp_batch_from_observation
+        obs = {k: v.contiguous().pin_memory() for k, v in
+               jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress).items()}
+        builder_kw = dict(conflicts="clique", graph_pooling="learn")
+        h2d_bytes = (sum(v.numel() * v.element_size() for v in obs.values())
+                     + sum(v.numel() * v.element_size() for v in extras.values()) + 4 * (B + 1) * 8)
+        input_note = ("padded gym observation (features, precedence edge_index, n_nodes, n_edges) + masks / actions / "
+                      "advantages / returns / old log-probs / old values in pinned host memory; the batched graph "
+                      "(clique conflict edges, pool wiring) is built on the device by b200gat_jssp_batch_build")
+
+        def build_batch():
+            return jssp_batch_from_observation(obs, dev, cfg["max_n_nodes"], **builder_kw)[0]
+
+        def submit(pf):
+            pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)
+        probe = build_batch()
+        N, E, NT = int(probe.plan.n_nodes), int(probe.plan.n_edges), int(probe.num_task_nodes)
+        del probe
 
     def to_dev():
-        return {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-
-    def make_batch(d):
-        plan = wb.GraphPlan(d["src"], d["dst"], N)
-        pool = torch.arange(NT, NT + B, device=dev)
-        return JsspBatch(plan, d["etype"], d["feat"], B, cfg["max_n_nodes"], NT, poolnodes=pool)
+        return {k: v.to(dev, non_blocking=True) for k, v in extras.items()}
 
     def train_step(jb, d):
         bucket.zero()
@@ -295,13 +377,16 @@ def run_b200(args):
             _lib.timing_enable(True)                       # per-kernel events over the timed steps only
         l0 = _lib.launch_count()
         total = 0.0
-        evs = []
+        evs, host_ms = [], []
+        allocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
         for _ in range(steps):
             flush.zero_()                                  # L2 flush, outside the event pair
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            th = time.perf_counter()
             e0.record()
             fn()
             e1.record()
+            host_ms.append((time.perf_counter() - th) * 1e3)
             evs.append((e0, e1))
             if graphed:                                    # read the graph's per-kernel event pairs of this replay
                 torch.cuda.synchronize()
@@ -310,8 +395,14 @@ def run_b200(args):
         if world > 1:
             dist.barrier()
         clocks = smp.stop() if smp else None
-        per_step = sorted(a.elapsed_time(b) for a, b in evs)
-        timed.last_spread = {"min": per_step[0], "median": per_step[len(per_step) // 2], "max": per_step[-1]}
+        raw = [a.elapsed_time(b) for a, b in evs]
+        per_step = sorted(raw)
+        imax = raw.index(per_step[-1])
+        timed.last_spread = {"min": per_step[0], "median": per_step[len(per_step) // 2], "max": per_step[-1],
+                             "max_at_step": imax, "host_ms_of_that_step": host_ms[imax],
+                             "host_ms_median": sorted(host_ms)[len(host_ms) // 2],
+                             "cudaMalloc_calls_in_timed_region":
+                                 torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - allocs0}
         total = sum(per_step)
         launches = _lib.launch_count() - l0
         t = torch.tensor([total], device=dev, dtype=torch.float64)
@@ -321,7 +412,7 @@ def run_b200(args):
 
     # ---- value: inputs resident in HBM, plan prebuilt (topology is layer- and epoch-invariant)
     d_res = to_dev()
-    jb_res = make_batch(d_res)
+    jb_res = build_batch()
     torch.cuda.synchronize()
     step_fn, graph, graph_note = (lambda: train_step(jb_res, d_res)), None, "eager launches"
     tgraph, captured = None, 0
@@ -370,12 +461,15 @@ def run_b200(args):
     import gc
     gc.collect()
     gc.freeze()
+    # ... and hand the caching allocator one large free block to carve the eager legs' tensors from: its pools keep
+    # growing for the first dozens of steps (a cudaMalloc costs 0.2 ms - tens of ms of host time inside a step)
+    reserve = torch.empty(6 << 30, dtype=torch.uint8, device=dev)
+    del reserve
 
     # ---- e2e: host buffers in, loss out, through the public module API, every step
     def e2e_step_serial():
         d = {k: v.to(dev, non_blocking=True) for k, v in extras.items()}
-        jb, _ = jssp_batch_from_observation(obs, dev, cfg["max_n_nodes"], **builder_kw)
-        return train_step(jb, d).item()                    # .item(): device->host read of the loss
+        return train_step(build_batch(), d).item()         # .item(): device->host read of the loss
     E2E_WARMUP = max(args.warmup, 20)     # the caching allocator still grows (cudaMalloc: 5-200 ms) for ~15 steps
     timed(e2e_step_serial, max(3, args.steps), E2E_WARMUP)
     ms_e2e_serial = timed.last_spread["median"]
@@ -384,9 +478,8 @@ def run_b200(args):
     # pinned host memory and reads ITS loss back, but the copy + plan build of step i+1 are queued on a side
     # stream while step i trains (the copy engine and the plan kernels run under the step's kernels, and the
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
-    from wheatley_b200.prefetch import BatchPrefetcher
     pf = BatchPrefetcher(dev)
-    pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)
+    submit(pf)
 
     from wheatley_b200.prefetch import HostReadback
     rb = HostReadback(depth=2)
@@ -394,7 +487,7 @@ def run_b200(args):
 
     def e2e_step():
         d, _ = pf.get()
-        pf.submit_observation(obs, cfg["max_n_nodes"], extras, **builder_kw)     # next step's inputs
+        submit(pf)                                         # next step's inputs
         rb.push(train_step(d["batch"], d))                 # device->host read of THIS step's loss, asynchronous
         if len(rb) > 1:
             e2e_losses.append(float(rb.pop()))             # ... consumed one step later (HostReadback)
@@ -423,7 +516,7 @@ def run_b200(args):
     # (jssp/env, psp/env) are out of scope and not in the figure.
     def rollout_step():
         masks_d = extras["masks"].to(dev, non_blocking=True)
-        jb, _ = jssp_batch_from_observation(obs, dev, cfg["max_n_nodes"], **builder_kw)
+        jb = build_batch()
         with torch.no_grad():
             action, _, _, _, _ = agent.get_action_and_value(jb, None, masks_d)
         return action.cpu()
@@ -467,10 +560,13 @@ def run_b200(args):
     bwd_ms = (tm["conv_bwd_dst"][0] + tm["conv_bwd_src"][0] + tm.get("clq_bwd_mma", (0.0, 0))[0]
               + tm.get("clq_bwd_elem", (0.0, 0))[0])
     per = {}
+    # P projected node tensors (3 EGAT, 2 GATv2), T bytes of edge features per edge (type id; + 5 fp32
+    # attributes for the PSP edge embedder)
+    PT = dict(P=2, T=24) if psp else dict(P=3, T=4)
     if fwd_n:
-        per["conv_fwd"] = (fwd_ms / fwd_n, algorithmic_bytes("conv_fwd", N, E, HD, H))
+        per["conv_fwd"] = (fwd_ms / fwd_n, algorithmic_bytes("conv_fwd", N, E, HD, H, **PT))
     if bd_n:
-        per["conv_bwd"] = (bwd_ms / bd_n, algorithmic_bytes("conv_bwd", N, E, HD, H))
+        per["conv_bwd"] = (bwd_ms / bd_n, algorithmic_bytes("conv_bwd", N, E, HD, H, **PT))
     dom = max(per, key=lambda k: per[k][0] * (fwd_n if k == "conv_fwd" else bd_n)) if per else None
     ms_share = ms_instr if graph is not None else ms_dev
     share_note = (f"per-kernel CUDA events inside an instrumented replay of the same graph ({ms_share:.3f} ms/step; "
@@ -514,9 +610,7 @@ def run_b200(args):
                     "statistic": "mean of the per-step CUDA-event times over the timed steps (max over ranks; rank 0 "
                                  "spread shown)",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
-                    "input": "padded gym observation (features, precedence edge_index, n_nodes, n_edges) + masks / "
-                             "actions / advantages / returns in pinned host memory; the batched graph (clique "
-                             "conflict edges, pool wiring) is built on the device by b200gat_jssp_batch_build",
+                    "input": input_note,
                     "pipeline": "wheatley_b200.prefetch.BatchPrefetcher: step i+1's host->device copy, batch and "
                                 "plan build are queued ahead of step i's kernels; every timed step copies its inputs "
                                 "from pinned host memory and reads its loss back (wheatley_b200.prefetch.HostReadback: "

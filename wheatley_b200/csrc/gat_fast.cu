@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
     const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
     const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
     float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
-    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem) {
+    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem) {
   constexpr int HD = 32 * VPL;
   constexpr int U = 2;                      // edges in flight (register budget: 128/thread)
   extern __shared__ float sh[];
@@ -378,7 +378,12 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
   // tab_in_smem: 0 = atomics on the global table, 1 = one shared table per CTA (shared fp32 atomics, which are
   // CAS loops on sm_100), 2 = one private table per warp (plain read-modify-write: lane l owns its VPL columns)
-  const int n_sh = HD + (tab_in_smem == 2 ? kWarps * A.T * HD : tab_in_smem == 1 ? A.T * HD : 0);
+  const int n_tab = tab_in_smem == 2 ? kWarps * A.T * HD : tab_in_smem == 1 ? A.T * HD : 0;
+  // aff_in_smem: one private [K][HD] block per warp for the gradient of the affine map (lane l owns its VPL columns:
+  // plain read-modify-write).  Global atomics here were 2.0 of 2.4 ms per layer on the PSP node-conflict graphs:
+  // every resource-conflict edge carries two non-zero attributes, i.e. 2 * HD atomics on the same 2 * HD addresses.
+  float* sh_aff = sh + HD + n_tab;
+  const int n_sh = HD + n_tab + (aff_in_smem ? kWarps * A.K * HD : 0);
   for (int i = threadIdx.x; i < n_sh; i += kFastThreads) sh[i] = 0.f;
   __syncthreads();
 
@@ -492,8 +497,17 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
               for (int kk = 0; kk < A.K; ++kk) {
                 const float av = __ldg(A.attr + pos * A.K + kk);
                 if (av != 0.f) {
+                  if (aff_in_smem) {
+                    float* dst = sh_aff + ((wi * A.K + kk) * HD + c0);
+                    float old[VPL];
+                    ldrow_s<VPL>(old, dst);
 #pragma unroll
-                  for (int i = 0; i < VPL; ++i) atomicAdd(g_affine + (int64_t)kk * HD + c0 + i, gz[i] * av);
+                    for (int i = 0; i < VPL; ++i) old[i] = fmaf(gz[i], av, old[i]);
+                    strow<VPL>(dst, old);
+                  } else {
+#pragma unroll
+                    for (int i = 0; i < VPL; ++i) atomicAdd(g_affine + (int64_t)kk * HD + c0 + i, gz[i] * av);
+                  }
                 }
               }
             }
@@ -536,6 +550,14 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
   } else if (tab_in_smem) {
     for (int i = threadIdx.x; i < A.T * HD; i += kFastThreads)
       if (sh_tab[i] != 0.f) atomicAdd(g_table + i, sh_tab[i]);
+  }
+  if (aff_in_smem) {
+    for (int i = threadIdx.x; i < A.K * HD; i += kFastThreads) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w2 = 0; w2 < kWarps; ++w2) sum += sh_aff[w2 * A.K * HD + i];
+      if (sum != 0.f) atomicAdd(g_affine + i, sum);
+    }
   }
 }
 
@@ -786,8 +808,11 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   const int64_t tab_bytes = (int64_t)A.T * HD * 4;
   const int tab_in_smem = A.emode == B200GAT_EDGE_NONE ? 0 : kWarps * tab_bytes <= 64 * 1024 ? 2
                           : tab_bytes <= 40 * 1024 ? 1 : 0;
+  const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
+  const int aff_in_smem = affine && (int64_t)kWarps * A.K * HD * 4 <= 64 * 1024 ? 1 : 0;
   const size_t smem = sizeof(float) * (HD + (tab_in_smem == 2 ? (size_t)kWarps * A.T * HD
-                                             : tab_in_smem == 1 ? (size_t)A.T * HD : 0));
+                                             : tab_in_smem == 1 ? (size_t)A.T * HD : 0) +
+                                       (aff_in_smem ? (size_t)kWarps * A.K * HD : 0));
   float* alpha = gs + (n_pos > 0 ? n_pos : (int64_t)A.E) * A.H;   // edge positions may be those of the full graph
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
@@ -801,7 +826,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
     FAST_DISPATCH(vpl, lph, alias,
                   (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
                       A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
-                      gs, alpha, tab_in_smem)));
+                      gs, alpha, tab_in_smem, aff_in_smem)));
     if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
       const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
       if (vpl == 2) k_hub_merge_bwd<2><<<mb, kFastThreads, 0, st>>>(A, gPj);

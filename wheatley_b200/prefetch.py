@@ -82,6 +82,20 @@ class BatchPrefetcher:
             return d, jb.plan, done
         self._enqueue(job)
 
+    def submit_psp(self, agent, arena, extras: dict = None, n_graphs=None, **preprocess_kw):
+        """Queue an arena of PSP wire-format observation slots (``wheatley_b200.wire``): copies, the device batch
+        builder (``agent.preprocess`` = psp/models/agent.py:298-406 on the device), the plan.  ``get()`` returns the
+        extras with the 9-tuple of ``preprocess`` under key ``"batch"``."""
+        def job():
+            with self._stream():
+                d = {k: v.to(self.device, non_blocking=True) for k, v in (extras or {}).items()}
+                obs = agent.preprocess(arena, n_graphs, defer=True, **preprocess_kw)
+                d["batch"] = obs
+                done = torch.cuda.Event()
+                done.record()
+            return d, obs[0].plan, done
+        self._enqueue(job)
+
     def get(self):
         """``(device_tensors, plan)`` of the oldest submitted batch, usable on the current stream."""
         if not self._pending:
