@@ -50,6 +50,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="taillard100x20", choices=sorted(WORKLOADS))
     ap.add_argument("--graphs-per-gpu", type=int, default=0)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --graphs-per-gpu graphs on every rank; strong: --graphs graphs in total, split over "
+                         "the ranks in contiguous shards balanced by edge count (ppo.shard_by_edges)")
+    ap.add_argument("--graphs", type=int, default=0, help="strong scaling: graphs of the global minibatch")
     ap.add_argument("--layers", type=int, default=0, help="0 = the workload's default (6; 4 for psp272)")
     ap.add_argument("--hidden", type=int, default=0, help="0 = the workload's default (64; 32 for psp272)")
     ap.add_argument("--conflicts", default=None, help="PSP workloads: node (default) | clique")
@@ -287,6 +291,24 @@ def run_b200(args):
                      if _dense.tf32_path_enabled() else "cublas TF32")
     cfg = model_config(args)
     B = cfg["graphs"]
+    seed_base = rank * B                               # weak scaling: every rank its own B graphs
+    if args.scaling == "strong":
+        # one global minibatch of G graphs (BASELINE config 5: "minibatches sharded across 8 B200"); ranks take
+        # contiguous shards of whole graphs balanced by edge count; the loss is evaluated as this rank's share of
+        # the GLOBAL mean (ppo_minibatch(sharded=True): advantage moments all-reduced), the gradients are SUMMED
+        from wheatley_b200.ppo import shard_by_edges
+        from wheatley_b200.workload import jssp_observation as _one_obs
+        G = args.graphs or cfg["graphs"] * 1
+        if cfg["psp"]:
+            per_graph = [1] * G
+        else:
+            per_graph = [int(_one_obs(cfg["n_j"], cfg["n_m"], g_, None, args.progress)["n_edges"]) for g_ in range(G)]
+        lo, hi = shard_by_edges(per_graph, world)[rank]
+        B, seed_base = hi - lo, lo
+        if B <= 0:
+            raise SystemExit(f"rank {rank}: empty shard ({G} graphs over {world} ranks)")
+        cfg["graphs"] = B
+    sharded = args.scaling == "strong" and world > 1
     torch.manual_seed(0)                               # identical replicas on every rank
     psp = cfg["psp"]
     if psp:
@@ -300,7 +322,7 @@ def run_b200(args):
     # Adam of alg/ppo.py on ONE flat parameter / the all-reduced flat gradient (ppo.FlatAdam)
     opt = FlatAdam(agent.parameters(), lr=2e-4, bucket=bucket)
 
-    masks, action, adv, ret, old_lp, old_v = synth_targets(B, cfg["max_n_nodes"], 1 + rank)
+    masks, action, adv, ret, old_lp, old_v = synth_targets(B, cfg["max_n_nodes"], 1 + seed_base)
     extras = dict(masks=masks, action=action, adv=adv, ret=ret, old_lp=old_lp, old_v=old_v)
     extras = {k: v.contiguous().pin_memory() for k, v in extras.items()}
     from wheatley_b200.prefetch import BatchPrefetcher
@@ -309,7 +331,7 @@ def run_b200(args):
         # (wheatley_b200.wire); the batched graph is built on the device (wheatley_b200.psp_batch)
         from wheatley_b200.wire import PspArena
         from wheatley_b200.workload import psp_taillard_graph
-        arena = PspArena.from_graphs([psp_taillard_graph(cfg["n_j"], cfg["n_m"], rank * B + b, progress=args.progress)
+        arena = PspArena.from_graphs([psp_taillard_graph(cfg["n_j"], cfg["n_m"], seed_base + b, progress=args.progress)
                                       for b in range(B)])
         h2d_bytes = (arena.tensor[:B].numel() * arena.tensor.element_size() + 5 * (B + 1) * 8
                      + sum(v.numel() * v.element_size() for v in extras.values()))
@@ -332,7 +354,7 @@ def run_b200(args):
         from wheatley_b200.workload import jssp_observation_batch
         from wheatley_b200.batch import jssp_batch_from_observation
         obs = {k: v.contiguous().pin_memory() for k, v in
-               jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=rank * B, progress=args.progress).items()}
+               jssp_observation_batch(cfg["n_j"], cfg["n_m"], B, seed0=seed_base, progress=args.progress).items()}
         builder_kw = dict(conflicts="clique", graph_pooling="learn")
         h2d_bytes = (sum(v.numel() * v.element_size() for v in obs.values())
                      + sum(v.numel() * v.element_size() for v in extras.values()) + 4 * (B + 1) * 8)
@@ -357,9 +379,9 @@ def run_b200(args):
         # alg/ppo.py:575-711 as one call: get_action_and_value + the clipped-PPO minibatch loss (statistics stay on
         # the device); loss.backward() is the whole backward pass
         loss, _stats = agent.ppo_minibatch(jb, d["action"], d["masks"], d["old_lp"], d["adv"], d["ret"], d["old_v"],
-                                           **PPO_KW)
+                                           sharded=sharded, **PPO_KW)
         loss.backward()
-        bucket.reduce()
+        bucket.reduce(average=not sharded)     # sharded: the loss is already this rank's share of the global mean
         opt.step()
         return loss
 
@@ -596,7 +618,7 @@ def run_b200(args):
                     "share_basis": share_note}
     line = {"metric": METRIC, "value": edges_total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None,
+            "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32 (conv kernels fp32; dense projections TF32 like the reference)",
             "data": "synthetic",
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,

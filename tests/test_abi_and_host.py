@@ -443,3 +443,91 @@ def test_gnn_mp_state_dict_names_match_reference_golden(built, golden_dir):
         for k, v in sd.items():
             assert tuple(v.shape) == g[f"{tag}.p.{k}"].shape, k
         assert gnn.features_dim == g[f"{tag}.node_features"].shape[2]
+
+
+_GLOO_UNEQUAL = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, %r)
+rank, world = int(sys.argv[1]), int(sys.argv[2])
+os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=sys.argv[3], RANK=str(rank), WORLD_SIZE=str(world))
+dist.init_process_group("gloo", rank=rank, world_size=world)
+import wheatley_b200
+from wheatley_b200.ppo import FlatGradAllReduce, adv_moments, shard_by_edges
+torch.manual_seed(0)
+model = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+ref = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+ref.load_state_dict(model.state_dict())
+x = torch.randn(11, 6)
+(ref(x).sum(1).mean()).backward()                      # the single-process global-batch mean
+lo, hi = shard_by_edges([5, 1, 1, 1, 1, 1, 1, 1, 1, 1, 50], world)[rank]      # UNEQUAL shards: 10 | 1 samples
+assert (lo, hi) == ((0, 10), (10, 11))[rank]
+bucket = FlatGradAllReduce(model.parameters())
+# (a) every rank evaluates the mean over ITS shard; the ranks' gradients are weighted by their sample counts
+bucket.zero()
+model(x[lo:hi]).sum(1).mean().backward()
+bucket.reduce(n_local=hi - lo)
+for p, q in zip(model.parameters(), ref.parameters()):
+    assert torch.allclose(p.grad, q.grad, atol=1e-6), ("weighted", (p.grad - q.grad).abs().max())
+# (b) every rank evaluates its SHARE of the global mean (what ppo_loss(sharded=True) returns): plain SUM
+bucket.zero()
+(model(x[lo:hi]).sum(1).sum() / 11).backward()
+bucket.reduce(average=False)
+for p, q in zip(model.parameters(), ref.parameters()):
+    assert torch.allclose(p.grad, q.grad, atol=1e-6), ("sum", (p.grad - q.grad).abs().max())
+# (c) the advantage statistics of the global minibatch from one all-reduce of three doubles (alg/ppo.py:602-605)
+adv = torch.randn(11, generator=torch.Generator().manual_seed(3)) * 2 + 1
+m = adv_moments(adv[lo:hi])
+dist.all_reduce(m)
+n, s1, s2 = m.tolist()
+mean, std = s1 / n, ((s2 - s1 * s1 / n) / (n - 1)) ** 0.5
+assert n == 11 and abs(mean - float(adv.mean())) < 1e-6 and abs(std - float(adv.std())) < 1e-6
+dist.destroy_process_group()
+print("ok", rank)
+'''
+
+
+def test_unequal_shards_world_size_2_gloo(built, tmp_path):
+    """ADVICE r1: ``reduce()`` divided by ``world`` whatever the shard sizes.  Unequal shards (``shard_by_edges``)
+    must still give the gradient of the global-batch mean: weighted by the ranks' sample counts, or a plain SUM of
+    losses that are already shares of the global mean; and the per-minibatch advantage normalisation uses the
+    GLOBAL mean / std (SURVEY 8e)."""
+    script = tmp_path / "gloo_unequal.py"
+    script.write_text(_GLOO_UNEQUAL % ROOT)
+    port = str(31500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), "2", port], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+
+
+def test_flat_adam_reference_state_round_trip(built):
+    """ADVICE r1: the reference resumes with ``optimizer.load_state_dict`` (alg/ppo.py:447-461).  FlatAdam exports /
+    imports its moments in ``torch.optim.Adam``'s per-parameter layout."""
+    import wheatley_b200
+    from wheatley_b200.ppo import FlatAdam
+    torch.manual_seed(0)
+    a = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+    b = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+    b.load_state_dict(a.state_dict())
+    oa, ob = FlatAdam(a.parameters(), lr=3e-3), torch.optim.Adam(b.parameters(), lr=3e-3)
+    x = torch.randn(7, 6)
+    for _ in range(3):
+        oa.zero_grad(); ob.zero_grad()
+        a(x).square().mean().backward(); b(x).square().mean().backward()
+        oa.step(); ob.step()
+    sd = oa.reference_state_dict()
+    ref = ob.state_dict()
+    for i in ref["state"]:
+        assert torch.allclose(sd["state"][i]["exp_avg"], ref["state"][i]["exp_avg"], atol=1e-7)
+        assert torch.allclose(sd["state"][i]["exp_avg_sq"], ref["state"][i]["exp_avg_sq"], atol=1e-9)
+    # a fresh FlatAdam resumed from the reference optimizer's own state continues identically
+    c = wheatley_b200.MLP(3, 6, 8, 2, False, "gelu")
+    c.load_state_dict(b.state_dict())
+    oc = FlatAdam(c.parameters(), lr=3e-3)
+    oc.load_reference_state_dict(ref)
+    oc.zero_grad(); ob.zero_grad()
+    c(x).square().mean().backward(); b(x).square().mean().backward()
+    oc.step(); ob.step()
+    for p, q in zip(c.parameters(), b.parameters()):
+        assert torch.allclose(p, q, atol=1e-6)
