@@ -371,3 +371,13 @@ def device_guard(device):
     if idx is None or idx == torch._C._cuda_getDevice():
         return _NO_GUARD
     return torch.cuda.device(idx)
+
+
+def eager_only(fn):
+    """The fused ops call the C-ABI through ctypes with raw device pointers: nothing a tracing compiler can look
+    into.  The reference wraps its trunks in ``torch.compile(dynamic=True)`` (psp/models/gnn_mp.py:139-300); marked
+    ``torch.compiler.disable`` these functions run eagerly inside such a wrapper (a clean graph break around one
+    call) instead of failing in the tracer."""
+    import torch
+    dis = getattr(getattr(torch, "compiler", None), "disable", None)
+    return dis(fn) if dis is not None else fn

@@ -21,6 +21,7 @@ import ctypes as C
 import torch
 
 from . import _lib
+from ._lib import eager_only
 from .readout import POOLING
 from .trunk import _c, setup_trunk, setup_trunk_grads
 
@@ -275,6 +276,7 @@ class _AgentStepFn(torch.autograd.Function):
         return (None, g_ext, g_xin, None, None, None, None, None, None, *grads)
 
 
+@eager_only
 def agent_step(spec, ext, xin, action, mask_u8, old_logprob, advantages, returns, old_values, flat):
     """``(loss, stats [8], aux [3, B] = logprob | entropy | value)``; ``stats`` in the order of ``STATS``."""
     return _AgentStepFn.apply(spec, ext, xin, action, mask_u8, old_logprob, advantages, returns, old_values, *flat)

@@ -14,6 +14,7 @@ import os
 import torch
 
 from . import _lib
+from ._lib import eager_only
 
 
 def gemm_backend() -> str:
@@ -56,6 +57,7 @@ def _fwd_supported(x, W):
             and W.shape[0] % 4 == 0)
 
 
+@eager_only
 def linear_fwd(x, W, b=None, gelu=False, residual=None, want_z=True):
     """``z = x W^T + b`` ; returns ``(z or None, out)`` with ``out = gelu(z)`` when ``gelu`` else
     ``z (+ residual)``.  x [M, K] contiguous, W [N, K]."""
@@ -79,6 +81,7 @@ def linear_fwd(x, W, b=None, gelu=False, residual=None, want_z=True):
     return None, (z if residual is None else z + residual)
 
 
+@eager_only
 def linear_dx(dy, W, z_prev=None):
     """``dx = dy W`` (``* gelu'(z_prev)`` when given).  dy [M, N], W [N, K] -> [M, K]."""
     M, N = dy.shape
@@ -96,6 +99,7 @@ def linear_dx(dy, W, z_prev=None):
     return dx
 
 
+@eager_only
 def linear_dw(dy, x, want_bias=False):
     """``dW = dy^T x``: dy [M, N], x [M, K] -> [N, K] (reduction over the M rows, split-K); with
     ``want_bias`` also ``db = dy.sum(0)`` (row sums of the A operand, from the same launch).
@@ -111,6 +115,7 @@ def linear_dw(dy, x, want_bias=False):
     return dy.t() @ x, (colsum(dy) if want_bias else None)
 
 
+@eager_only
 def colsum(x):
     """Bias gradient ``x.sum(0)`` of a contiguous [M, N] tensor, deterministic."""
     M, N = x.shape
@@ -301,6 +306,7 @@ class _GeluMLPFused(torch.autograd.Function):
         return (dx, gy_in if ctx.has_res and need[1] else None, *grads)
 
 
+@eager_only
 def gelu_mlp(x, layers, residual=None):
     """``layers``: the ``nn.Linear`` modules of a GELU MLP.  One fused call per pass when every hidden width is a
     multiple of 4 floats (input / output widths are padded inside the call); GEMM by GEMM otherwise."""
@@ -373,6 +379,7 @@ class _Proj3(torch.autograd.Function):
         return dx, dw[:HD], dw[HD: 2 * HD], dw[2 * HD:]
 
 
+@eager_only
 def project3(x, w_i, w_j, w_v):
     """``(x w_i^T, x w_j^T, x w_v^T)``; one tcgen05 launch when covered, three library GEMMs otherwise."""
     HD, K = w_i.shape
@@ -383,6 +390,7 @@ def project3(x, w_i, w_j, w_v):
     return lin(x, w_i), lin(x, w_j), lin(x, w_v)
 
 
+@eager_only
 def dense_linear(x, weight, bias=None):
     """Single ``Linear`` (``lin_l`` / ``lin_r`` of the PyG-flavour layers, psp/graph/graph_conv.py:33-40):
     the one-layer case of the fused path (forward, dx and dW + bias row sums on ``b200gat_gemm_tf32``) when

@@ -3,6 +3,7 @@ called from).  No PyTorch fallback exists: CPU tensors raise."""
 import torch
 
 from . import _lib
+from ._lib import eager_only
 from .plan import GraphPlan, check_edge_types
 
 
@@ -33,6 +34,7 @@ class EdgeFeatures:
         return cls(_lib.EDGE_NONE)
 
 
+@eager_only
 def project_edge_feats(plan: GraphPlan, efeats, weight, pre_bias=None) -> EdgeFeatures:
     """Edge term of the logit, ``Pe = efeats @ weight.T (+ pre_bias)``, in the cheapest exact form:
     typed/affine factors are projected as a T-row table (+ a K-row affine map) and gathered
@@ -167,6 +169,7 @@ class _FusedGATConv(torch.autograd.Function):
                 g_attn_bias, g_bias, g_table, g_dense, None, g_affine, None)
 
 
+@eager_only
 def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_ADDITIVE, slope=0.2,
                    eps=0.0, attn_bias=None, out_bias=None, edge_feats: EdgeFeatures = None):
     """Returns ``(out [N, H*D], (s, m, l))``; ``V=None`` means V aliases Pi."""
@@ -182,6 +185,7 @@ def fused_gat_conv(plan, Pi, Pj, V, attn, *, heads, dim, flavour=_lib.FLAVOUR_AD
     return out, (s, m, l, s_dense if s_dense.numel() else None, view)
 
 
+@eager_only
 def attention_weights(plan: GraphPlan, saved, heads: int, eps: float) -> torch.Tensor:
     """alpha [E, H] in the original edge order from the logits saved by the forward."""
     s, m, l, s_dense, view = saved
@@ -193,6 +197,7 @@ def attention_weights(plan: GraphPlan, saved, heads: int, eps: float) -> torch.T
     return alpha
 
 
+@eager_only
 def edge_output(plan: GraphPlan, Pi, Pj, edge_feats: EdgeFeatures, *, heads, dim, slope, attn):
     """f_out [E, H, D] = leaky_relu(Pi[src]+Pj[dst]+Pe) (no autograd: materialised on request)."""
     Pi, Pj = _f32c(Pi.detach()), _f32c(Pj.detach())
@@ -299,11 +304,13 @@ def _mask_u8(action_masks, n, device):
     return mk.view(torch.uint8)
 
 
+@eager_only
 def masked_log_softmax(logits, action_masks=None, fill=-1e20):
     """(logp [B,n], entropy [B], argmax [B]) of the masked categorical."""
     return _MaskedHead.apply(logits, _mask_u8(action_masks, logits.shape[1], logits.device), float(fill))
 
 
+@eager_only
 def masked_logprob_entropy(logits, action, action_masks=None, fill=-1e20):
     return _MaskedHeadEval.apply(logits, _mask_u8(action_masks, logits.shape[1], logits.device), action,
                                  float(fill))

@@ -11,6 +11,7 @@ import os
 import torch
 
 from . import _lib
+from ._lib import eager_only
 
 
 def _orders_and_hubs(in_ptr, in_src, out_ptr, out_dst, N, dev):
@@ -347,6 +348,7 @@ def check_edge_types(etype_sorted: torch.Tensor, n_types: int):
         raise IndexError(f"edge type out of range: types span [{lo}, {hi}], the edge-type table has {n_types} rows")
 
 
+@eager_only
 def plan_for_edge_index(edge_index: torch.Tensor, n_nodes: int, holder=None) -> GraphPlan:
     """Plan cache: the plan is stored on ``holder`` (the graph object the reference passes
     around, or the edge_index tensor itself) and reused while it is the SAME tensor object, unchanged."""

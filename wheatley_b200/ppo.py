@@ -11,6 +11,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
+from ._lib import eager_only
 
 
 def ppo_like_loss(logprob, entropy, value, advantages, returns, ent_coef=0.05, vf_coef=2.0):
@@ -23,6 +24,7 @@ def ppo_like_loss(logprob, entropy, value, advantages, returns, ent_coef=0.05, v
     return pg - ent_coef * entropy.mean() + vf_coef * v
 
 
+@eager_only
 def gae(rewards, values, dones, next_value, next_done, gamma, gae_lambda, sigma=1.0):
     """``(advantages, returns)`` of alg/ppo.py:276-299 on the device (``b200gat_gae``): ``rewards`` / ``values``
     ``[T, E, R]``, ``dones [T, E]``, ``next_value [E, R]``, ``next_done [E]``; bit-exact against the reference's fp32
@@ -89,6 +91,7 @@ class _PpoLoss(torch.autograd.Function):
                 (g[2] * g_loss).view(s_val) if need[2] else None, None, None, None, None, None, None)
 
 
+@eager_only
 def ppo_loss(logprob, entropy, value, old_logprob, advantages, returns, old_values=None, *, clip_coef=0.2,
              norm_adv=True, clip_vloss=False, critic_loss="l2", ent_coef=0.0, vf_coef=0.5, update=1,
              unmasked_probs=None, group=None, sharded=False):
@@ -121,6 +124,7 @@ def ppo_loss(logprob, entropy, value, old_logprob, advantages, returns, old_valu
     return loss, stats
 
 
+@eager_only
 def adv_moments(advantages):
     """``double[3] {count, sum, sum of squares}`` of this rank's advantages (``b200gat_ppo_adv_moments``)."""
     a = advantages.detach().to(torch.float32).reshape(-1).contiguous()

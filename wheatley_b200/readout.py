@@ -9,6 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from ._lib import eager_only
 
 POOLING = {None: _lib.READOUT_NONE, "none": _lib.READOUT_NONE, "max": _lib.READOUT_MAX, "avg": _lib.READOUT_AVG,
            "learn": _lib.READOUT_ROWS, "learninv": _lib.READOUT_ROWS}
@@ -106,6 +107,7 @@ class _Readout(torch.autograd.Function):
         return (None,) * 6 + tuple(grads)
 
 
+@eager_only
 def readout(sources, counts, max_n_nodes, pooling, pool_row0=0, row_start=None):
     """``(node_features [B, max_n_nodes, F], graph_embedding [B, F] or None)`` from the per-layer node tensors
     ``sources`` (each ``[N_total, w_i]``; their concatenation along dim 1 is never materialised).

@@ -12,6 +12,7 @@ import os
 import torch
 
 from . import _lib
+from ._lib import eager_only
 from .dense import tf32_path_enabled
 from .plan import check_edge_types
 
@@ -236,6 +237,7 @@ def trunk_cfg(specs, heads, dim, slope, eps, residual):
                 slope=float(slope), eps=float(eps), residual=bool(residual), edge_mode=mode)
 
 
+@eager_only
 def fused_trunk(view, etype_sorted, attr_sorted, x0, specs, *, heads, dim, slope, eps, residual):
     """Outputs of the L layers, ``[N, in_dim]`` each.  ``view``: the plan / clique view the layers' edge mode
     selects (``EdgeFeatures.graph_view``); ``etype_sorted`` / ``attr_sorted``: per-edge type ids / attributes in the
