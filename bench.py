@@ -529,24 +529,68 @@ def run_b200(args):
     ms_e2e_median = float(t_med)
     ms_e2e = ms_e2e_mean                                   # headline = MEAN over the timed steps (max over ranks)
 
-    # ---- PPO env-steps/sec (BASELINE.json metric, second half): the learner side of one PPO iteration
-    # (alg/ppo.py:196-206 rollout inference, :547-727 update) on this workload, per rank:
-    #   rollout step  = host observation of `num_envs` graphs -> device, plan, trunk + head forward under
-    #                   no_grad, sampled action read back to the host (the env needs it, alg/ppo.py:206)
-    #   update        = n_epochs passes over the rollout in minibatches of `batch` graphs = the e2e step above
-    # env-steps/s = num_envs / (t_rollout + n_epochs * (num_envs / batch) * t_update); the CPU simulators
-    # (jssp/env, psp/env) are out of scope and not in the figure.
+    # ---- PPO env-steps/sec (BASELINE.json metric, second half): a TIMED PPO iteration of alg/ppo.py on this workload,
+    # per rank, with an in-process dummy environment (the CPU simulators jssp/env, psp/env are out of scope, SURVEY
+    # 8f N2: the dummy env returns the same observation arrays and a seeded reward every step):
+    #   rollout  (alg/ppo.py:157-206): T steps x num_envs graphs: host observation -> device batch build -> trunk +
+    #            heads under no_grad -> sampled action read back to the host (env.step needs it) -> reward / done in
+    #   GAE      (:276-299) on the device (b200gat_gae)
+    #   update   (:539-728): n_epochs passes over the T minibatches (one rollout step's graphs each, shuffled): batch
+    #            build, agent.ppo_minibatch, backward, gradient all-reduce, Adam; the statistics of an epoch are read
+    #            back ONCE for the KL early stop (:741-749), all-reduced so that every rank stops together
+    from wheatley_b200.ppo import gae as device_gae
+    T_roll, n_epochs = 8, 3
+    rng_env = torch.Generator().manual_seed(7 + rank)
+
     def rollout_step():
         masks_d = extras["masks"].to(dev, non_blocking=True)
         jb = build_batch()
         with torch.no_grad():
-            action, _, _, _, _ = agent.get_action_and_value(jb, None, masks_d)
-        return action.cpu()
-    timed(rollout_step, max(3, args.steps), 5)
+            action, logprob, _, value, _ = agent.get_action_and_value(jb, None, masks_d)
+        return action.cpu(), logprob, value.reshape(-1)
+
+    def ppo_iteration():
+        lps, vals, acts, rews = [], [], [], []
+        for _t in range(T_roll):
+            a_host, lp, v = rollout_step()                               # device->host sync, like alg/ppo.py:206
+            rews.append(torch.rand(B, generator=rng_env).pin_memory().to(dev, non_blocking=True))   # env.step
+            lps.append(lp); vals.append(v); acts.append(a_host.pin_memory().to(dev, non_blocking=True))
+        rewards = torch.stack(rews).unsqueeze(-1)
+        values = torch.stack(vals).unsqueeze(-1)
+        dones = torch.zeros((T_roll, B), device=dev)
+        _, _, next_v = rollout_step()
+        adv, ret = device_gae(rewards, values, dones, next_v.unsqueeze(-1), torch.ones(B, device=dev), 1.0, 1.0)
+        masks_d = extras["masks"].to(dev, non_blocking=True)
+        stop = False
+        for _ep in range(n_epochs):
+            kl = torch.zeros(1, device=dev)
+            for mb in torch.randperm(T_roll, generator=rng_env).tolist():
+                bucket.zero()
+                loss, stats = agent.ppo_minibatch(build_batch(), acts[mb], masks_d, lps[mb], adv[mb, :, 0],
+                                                  ret[mb, :, 0], values[mb, :, 0], sharded=sharded, **PPO_KW)
+                loss.backward()
+                bucket.reduce(average=not sharded)
+                opt.step()
+                kl += stats[3]
+            if world > 1:
+                dist.all_reduce(kl)
+            stop = float(kl) / (T_roll * world) > 1e9                    # one read-back per epoch (target_kl check)
+            if stop:
+                break
+        return T_roll * B
+
+    ppo_iteration()                                                      # warm-up
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_ppo = time.perf_counter()
+    n_it = 2
+    env_steps = sum(ppo_iteration() for _ in range(n_it))
+    torch.cuda.synchronize()
+    t_ppo = time.perf_counter() - t_ppo
+    timed(lambda: rollout_step()[0], max(3, args.steps), 5)
     ms_roll = timed.last_spread["median"]
-    n_epochs = 10                                           # args.py:113-117 default
-    ppo_rate = B / ((ms_roll + n_epochs * ms_e2e) * 1e-3)
-    ppo_all = torch.tensor([ppo_rate], device=dev, dtype=torch.float64)
+    ppo_all = torch.tensor([env_steps / t_ppo], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ppo_all)
 
@@ -641,10 +685,12 @@ def run_b200(args):
                     "ms_per_step_no_prefetch": ms_e2e_serial, "warmup_steps": E2E_WARMUP},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,
-                    "minibatch_graphs": B, "n_epochs": n_epochs, "rollout_ms_per_step": ms_roll,
-                    "update_ms_per_minibatch": ms_e2e,
-                    "definition": "num_envs / (t_rollout + n_epochs * t_update), learner side only: host "
-                                  "observation in, sampled action out per rollout step; env simulators excluded",
+                    "minibatch_graphs": B, "n_epochs": n_epochs, "rollout_steps": T_roll,
+                    "rollout_ms_per_step": ms_roll, "iteration_ms": t_ppo / n_it * 1e3,
+                    "definition": "TIMED loop, wall clock: (rollout of rollout_steps x num_envs env steps with the "
+                                  "sampled action read back every step, GAE on the device, n_epochs x rollout_steps "
+                                  "minibatch updates with one statistics read-back per epoch) / elapsed; dummy "
+                                  "in-process environment, CPU simulators excluded; all ranks summed",
                     "rollout_graph_edges_per_sec": edges_per_rank_note(E, ms_roll, world)}}
     if world == 1 and not args.no_cpu_baseline:
         cb, _, _ = time_cpu(cfg, args, 1000, 1, budget_s=args.cpu_seconds)
