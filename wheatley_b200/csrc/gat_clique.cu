@@ -20,6 +20,7 @@
 //   final   : normalise, write out / agg_save / m_save / l_save; raw logits go to s_dense[h][v][u]
 #include <atomic>
 #include <math.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "gat_kernels.cuh"
 
@@ -717,6 +718,307 @@ __global__ void __launch_bounds__(256, 2) k_clq_bwd_elem(CliqueArgs A, const flo
   }
 }
 
+// ------------------------------------------------------------------------------------------ backward, fused
+// Parts 1 and 2 in ONE kernel for blocks of more than 64 members (one item per CTA): d loss / d logit never leaves
+// the CTA (part 1 writes the [v][u] tile part 2 reads straight into shared memory: no 26 MB gs_dense round trip per
+// layer, no gsum_u / gsum_v arrays, one staging of the block instead of two) and, with two CTAs per SM running out
+// of phase, the latency-bound tensor-core phase of one overlaps the issue-bound element-wise phase of the other.
+// Shared memory: [V | G | m | linv | dot | gsv] (phase 1; -Pj' overlays V in phase 2) | gs tile | gsum_v | gsum_u | ids.
+__host__ __device__ inline int clique_bwdf_floats(int ru, int rv, int gu) {
+  const int sg = 4 * gu > kD ? 4 * gu : kD;
+  return 2 * rv * kSB + 4 * rv + ru * sg + 3 * ru;
+}
+
+template <int VB>
+__device__ __forceinline__ void bwdf_chunk(const CliqueArgs& A, const BwdSmem& S, float (&acc)[8][4], float& gsu0,
+                                           float& gsu1, int n, int u0, int u1, int vbase, int g, int t,
+                                           const float* __restrict__ sd, float* __restrict__ sGs, int SG, int npad) {
+  float c[VB][4], sv[VB][4];
+#pragma unroll
+  for (int j = 0; j < VB; ++j) {          // saved logits first: their latency hides behind mma #1
+    c[j][0] = c[j][1] = c[j][2] = c[j][3] = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int u = (q & 2) ? u1 : u0, v = vbase + 8 * j + 2 * t + (q & 1);
+      sv[j][q] = (u < n && v < n) ? __ldg(sd + v * npad + u) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    uint32_t ah[4], al[4];
+    split_tf32(S.v[u0 * kSB + k * 8 + t], ah[0], al[0]);
+    split_tf32(S.v[u1 * kSB + k * 8 + t], ah[1], al[1]);
+    split_tf32(S.v[u0 * kSB + k * 8 + t + 4], ah[2], al[2]);
+    split_tf32(S.v[u1 * kSB + k * 8 + t + 4], ah[3], al[3]);
+    uint32_t bh0[VB], bl0[VB], bh1[VB], bl1[VB];
+#pragma unroll
+    for (int j = 0; j < VB; ++j) {
+      const float* gp = S.g + (vbase + 8 * j + g) * kSB + k * 8 + t;
+      split_tf32(gp[0], bh0[j], bl0[j]);
+      split_tf32(gp[4], bh1[j], bl1[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], al[0], al[1], al[2], al[3], bh0[j], bh1[j]);
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bl0[j], bl1[j]);
+#pragma unroll
+    for (int j = 0; j < VB; ++j) mma_tf32(c[j], ah[0], ah[1], ah[2], ah[3], bh0[j], bh1[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < VB; ++j) {
+    const int va = vbase + 8 * j + 2 * t, vb = va + 1;
+    const float ma = S.m[va], mb = S.m[vb], ia = S.linv[va], ib = S.linv[vb], da = S.dot[va], db = S.dot[vb];
+    float al4[4], gs4[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int u = (q & 2) ? u1 : u0, v = (q & 1) ? vb : va;
+      const bool ok = u < n && v < n && u != v;
+      float a = 0.f, gsv = 0.f;
+      if (ok) {
+        a = __expf(sv[j][q] - ((q & 1) ? mb : ma)) * ((q & 1) ? ib : ia);
+        gsv = a * (c[j][q] - ((q & 1) ? db : da));
+      }
+      if (u < n && v < n) sGs[v * SG + u] = gsv;
+      al4[q] = a; gs4[q] = gsv;
+    }
+    gsu0 += gs4[0] + gs4[1];
+    gsu1 += gs4[2] + gs4[3];
+    float ca = gs4[0] + gs4[2], cb = gs4[1] + gs4[3];
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+      ca += __shfl_xor_sync(0xffffffffu, ca, o);
+      cb += __shfl_xor_sync(0xffffffffu, cb, o);
+    }
+    if (g == 0) {
+      atomicAdd(S.gsv + va, ca);
+      atomicAdd(S.gsv + vb, cb);
+    }
+    uint32_t ah[4], al[4];
+    split_tf32(al4[0], ah[0], al[0]);
+    split_tf32(al4[2], ah[1], al[1]);
+    split_tf32(al4[1], ah[2], al[2]);
+    split_tf32(al4[3], ah[3], al[3]);
+    const float* ga = S.g + va * kSB + g;
+#pragma unroll
+    for (int nq = 0; nq < 8; nq += 4) {
+      uint32_t bh0[4], bl0[4], bh1[4], bl1[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        split_tf32(ga[(nq + i) * 8], bh0[i], bl0[i]);
+        split_tf32(ga[kSB + (nq + i) * 8], bh1[i], bl1[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], al[0], al[1], al[2], al[3], bh0[i], bh1[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], ah[0], ah[1], ah[2], ah[3], bl0[i], bl1[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) mma_tf32(acc[nq + i], ah[0], ah[1], ah[2], ah[3], bh0[i], bh1[i]);
+    }
+  }
+}
+
+template <int GU>
+__global__ void __launch_bounds__(256, 2) k_clq_bwd_fused(CliqueArgs A, const float* __restrict__ Pi,
+                                                           const float* __restrict__ Pj, const float* __restrict__ V,
+                                                           const float* __restrict__ G, const float* __restrict__ agg,
+                                                           const float* __restrict__ s_dense,
+                                                           const float* __restrict__ m_save,
+                                                           const float* __restrict__ l_save, float* __restrict__ gPi,
+                                                           float* __restrict__ gPj, float* __restrict__ gV,
+                                                           float* __restrict__ g_attn, float* __restrict__ g_table) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int SG = 4 * GU;
+  constexpr int SGW = SG > kD ? SG : kD;
+  const int item = blockIdx.x;
+  const int b = item / A.H, h = item - b * A.H;
+  const int n = A.blk_ptr[b + 1] - A.blk_ptr[b];
+  const int32_t* __restrict__ nodes = A.blk_nodes + A.blk_ptr[b];
+  const int type = A.blk_type[b];
+  const int hoff = h * kD, npad = (n + 3) & ~3;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const BwdSmem S = bwd_views(smem, A.rv);
+  float* sGs = smem + 2 * A.rv * kSB + 4 * A.rv;   // [ru][SGW] gs[v][u], zero beyond the block
+  float* sGv = sGs + A.ru * SGW;                  // [ru] slope * gsum_v
+  float* sGu = sGv + A.ru;                        // [ru] slope * gsum_u
+  int* sNode = reinterpret_cast<int*>(sGu + A.ru);
+  const float* sd = s_dense + (int64_t)A.blk_soff[b] * A.H + (int64_t)h * n * npad;
+
+  // ---------------------------------------------------------------- phase 1: stage V, G, softmax state
+  for (int idx = tid; idx < A.rv * 16; idx += 256) {
+    const int row = idx >> 4, c4 = (idx & 15) * 4;
+    float4 vv = make_float4(0.f, 0.f, 0.f, 0.f), gg = vv, ag = vv;
+    float mm = 0.f, ll = 0.f;
+    if (row < n) {
+      const int64_t node = nodes[row];
+      vv = __ldg(reinterpret_cast<const float4*>(V + node * A.HD + hoff + c4));
+      gg = __ldg(reinterpret_cast<const float4*>(G + node * A.HD + hoff + c4));
+      ag = __ldg(reinterpret_cast<const float4*>(agg + node * A.HD + hoff + c4));
+      if ((idx & 15) == 0) {
+        mm = m_save[node * A.H + h];
+        ll = 1.f / (l_save[node * A.H + h] + A.eps);
+      }
+    }
+    *reinterpret_cast<float4*>(S.v + row * kSB + c4) = vv;
+    *reinterpret_cast<float4*>(S.g + row * kSB + c4) = gg;
+    float d = gg.x * ag.x + gg.y * ag.y + gg.z * ag.z + gg.w * ag.w;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+    if ((idx & 15) == 0) {
+      S.dot[row] = d;
+      S.m[row] = mm;
+      S.linv[row] = ll;
+      S.gsv[row] = 0.f;
+    }
+  }
+  for (int idx = tid; idx < A.ru * SGW / 4; idx += 256)
+    reinterpret_cast<float4*>(sGs)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int row = tid; row < A.ru; row += 256) {
+    sNode[row] = row < n ? nodes[row] : 0;
+    sGu[row] = 0.f;
+  }
+  __syncthreads();
+  if (warp * 16 < n) {
+    const int g = lane >> 2, t = lane & 3;
+    const int u0 = warp * 16 + g, u1 = u0 + 8;
+    float acc[8][4];
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) { acc[nb][0] = acc[nb][1] = acc[nb][2] = acc[nb][3] = 0.f; }
+    float gsu0 = 0.f, gsu1 = 0.f;
+    const int nvb = (n + 7) >> 3;
+    int vb = 0;
+    for (; vb + 4 <= nvb; vb += 4) bwdf_chunk<4>(A, S, acc, gsu0, gsu1, n, u0, u1, vb * 8, g, t, sd, sGs, SGW, npad);
+    switch (nvb - vb) {
+      case 3: bwdf_chunk<3>(A, S, acc, gsu0, gsu1, n, u0, u1, vb * 8, g, t, sd, sGs, SGW, npad); break;
+      case 2: bwdf_chunk<2>(A, S, acc, gsu0, gsu1, n, u0, u1, vb * 8, g, t, sd, sGs, SGW, npad); break;
+      case 1: bwdf_chunk<1>(A, S, acc, gsu0, gsu1, n, u0, u1, vb * 8, g, t, sd, sGs, SGW, npad); break;
+      default: break;
+    }
+    gsu0 += __shfl_xor_sync(0xffffffffu, gsu0, 1);
+    gsu0 += __shfl_xor_sync(0xffffffffu, gsu0, 2);
+    gsu1 += __shfl_xor_sync(0xffffffffu, gsu1, 1);
+    gsu1 += __shfl_xor_sync(0xffffffffu, gsu1, 2);
+    const bool ok0 = u0 < n, ok1 = u1 < n;
+    if (t == 0) {
+      if (ok0) sGu[u0] = A.slope * gsu0;
+      if (ok1) sGu[u1] = A.slope * gsu1;
+    }
+    const int64_t n0 = ok0 ? sNode[u0] : 0, n1 = ok1 ? sNode[u1] : 0;
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      const int col = hoff + nb * 8 + 2 * t;
+      if (ok0) {
+        float2* p = reinterpret_cast<float2*>(gV + n0 * A.HD + col);
+        float2 o = *p;
+        *p = make_float2(o.x + acc[nb][0], o.y + acc[nb][1]);
+      }
+      if (ok1) {
+        float2* p = reinterpret_cast<float2*>(gV + n1 * A.HD + col);
+        float2 o = *p;
+        *p = make_float2(o.x + acc[nb][2], o.y + acc[nb][3]);
+      }
+    }
+  }
+  __syncthreads();
+  // ---------------------------------------------------------------- phase 2 (the body of k_clq_bwd_elem)
+  float* sNPj = smem;                              // [n][64] -(Pj + table), over the dead V tile
+  for (int row = tid; row < n; row += 256) sGv[row] = A.slope * S.gsv[row];
+  __syncthreads();                                 // S.gsv lives inside the region sNPj is about to overwrite
+#pragma unroll 4
+  for (int idx = tid; idx < n * 16; idx += 256) {
+    const int row = idx >> 4, c4 = (idx & 15) * 4;
+    const int64_t node = sNode[row];
+    float4 pj = __ldg(reinterpret_cast<const float4*>(Pj + node * A.HD + hoff + c4));
+    if (A.table) {
+      const float4 tb = __ldg(reinterpret_cast<const float4*>(A.table + (int64_t)type * A.HD + hoff + c4));
+      pj.x += tb.x; pj.y += tb.y; pj.z += tb.z; pj.w += tb.w;
+    }
+    *reinterpret_cast<float4*>(sNPj + row * kD + c4) = make_float4(-pj.x, -pj.y, -pj.z, -pj.w);
+  }
+  const int dl = lane >> 2, ug = lane & 3;
+  const int d = warp * 8 + dl, col = hoff + d;
+  const int u0 = ug * GU;
+  const float c1 = 1.f - A.slope;
+  const float at = __ldg(A.attn + col);
+  float pi[GU], qu[GU];
+#pragma unroll
+  for (int j = 0; j < GU; ++j) {
+    qu[j] = 0.f;
+    pi[j] = (u0 + j < n) ? __ldg(Pi + (int64_t)sNode[u0 + j] * A.HD + col) : 0.f;
+  }
+  __syncthreads();
+
+  float gat = 0.f, tab = 0.f;
+  float qv_pend = 0.f, q_pend = 0.f;
+  auto finish = [&](int v, float qv, float q) {
+    if (ug == 0) {
+      const float gq = fmaf(c1, qv, sGv[v]);
+      gat = fmaf(-q, gq, gat);
+      const float t = at * gq;
+      tab += t;
+      sNPj[v * kD + d] = t;
+    }
+  };
+  for (int v = 0; v < n; ++v) {
+    const float q = sNPj[v * kD + d];
+    float4 g4[GU / 4];
+#pragma unroll
+    for (int k = 0; k < GU / 4; ++k) g4[k] = *reinterpret_cast<const float4*>(sGs + v * SGW + u0 + 4 * k);
+    float qa[4] = {0.f, 0.f, 0.f, 0.f};
+    const float r1 = __shfl_xor_sync(0xffffffffu, qv_pend, 1);
+#pragma unroll
+    for (int j = 0; j < GU / 2; ++j) {
+      const float4 g = g4[j >> 2];
+      const float gsv = (j & 3) == 0 ? g.x : (j & 3) == 1 ? g.y : (j & 3) == 2 ? g.z : g.w;
+      if (pi[j] > q) { qu[j] += gsv; qa[j & 3] += gsv; }
+    }
+    const float qv1 = qv_pend + r1;
+    const float r2 = __shfl_xor_sync(0xffffffffu, qv1, 2);
+#pragma unroll
+    for (int j = GU / 2; j < GU; ++j) {
+      const float4 g = g4[j >> 2];
+      const float gsv = (j & 3) == 0 ? g.x : (j & 3) == 1 ? g.y : (j & 3) == 2 ? g.z : g.w;
+      if (pi[j] > q) { qu[j] += gsv; qa[j & 3] += gsv; }
+    }
+    if (v > 0) finish(v - 1, qv1 + r2, q_pend);
+    qv_pend = (qa[0] + qa[1]) + (qa[2] + qa[3]);
+    q_pend = q;
+  }
+  {
+    float qv = qv_pend + __shfl_xor_sync(0xffffffffu, qv_pend, 1);
+    qv += __shfl_xor_sync(0xffffffffu, qv, 2);
+    if (n > 0) finish(n - 1, qv, q_pend);
+  }
+  __syncthreads();                 // every warp is done with the gs tile: reuse it for the d Pi rows [u][64]
+#pragma unroll
+  for (int j = 0; j < GU; ++j) {
+    if (u0 + j < n) {
+      const float g0 = fmaf(c1, qu[j], sGu[u0 + j]);
+      gat = fmaf(pi[j], g0, gat);
+      sGs[(u0 + j) * kD + d] = at * g0;
+    }
+  }
+  gat += __shfl_xor_sync(0xffffffffu, gat, 1);
+  gat += __shfl_xor_sync(0xffffffffu, gat, 2);
+  if (ug == 0) {
+    atomicAdd(g_attn + col, gat);
+    if (g_table) atomicAdd(g_table + (int64_t)type * A.HD + col, tab);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < n * 16; idx += 256) {     // coalesced read-modify-write of the node rows
+    const int row = idx >> 4, c4 = (idx & 15) * 4;
+    const int64_t node = sNode[row];
+    float4* pj = reinterpret_cast<float4*>(gPj + node * A.HD + hoff + c4);
+    float4* pi4 = reinterpret_cast<float4*>(gPi + node * A.HD + hoff + c4);
+    const float4 aj = *reinterpret_cast<const float4*>(sNPj + row * kD + c4);
+    const float4 ai = *reinterpret_cast<const float4*>(sGs + row * kD + c4);
+    float4 oj = *pj, oi = *pi4;
+    oj.x += aj.x; oj.y += aj.y; oj.z += aj.z; oj.w += aj.w;
+    *pj = oj;
+    oi.x += ai.x; oi.y += ai.y; oi.z += ai.z; oi.w += ai.w;
+    *pi4 = oi;
+  }
+}
+
 // ------------------------------------------------------------------------------------------ host side
 static bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -804,6 +1106,29 @@ int clique_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
                      aligned16p(gPi) && aligned16p(gPj) && aligned16p(gV) && aligned16p(scratch),
                  "clique kernels need 16-byte aligned tensors");
   if (A.table) B200_CHECK_ARG(g_table, "null g_table");
+  {
+    // blocks of more than 64 members: parts 1 and 2 fused (gs stays in shared memory)
+    const int gu = (((g->cliques->max_block + 3) / 4) + 3) & ~3;
+    const size_t smem_f = (size_t)clique_bwdf_floats(A.ru, A.rv, gu) * sizeof(float);
+    static const bool no_fused = getenv("B200GAT_NO_FUSED_CLQ_BWD") != nullptr;
+    if (A.ipc == 1 && A.tiles <= 8 && smem_f <= 227 * 1024 && !no_fused) {
+      ScopedTimer tm(B200GAT_TIMING_CLQ_BWD_ELEM, st);
+      float* gt = A.table ? g_table : nullptr;
+#define CLQ_BWDF(GU_)                                                                                          \
+  case GU_:                                                                                                    \
+    if ((rc = set_smem<k_clq_bwd_fused<GU_>>(smem_f, "k_clq_bwd_fused"))) return rc;                           \
+    k_clq_bwd_fused<GU_><<<A.n_items, 256, smem_f, st>>>(A, Pi, Pj, V, g_out, agg_save, s_dense, m_save,        \
+                                                         l_save, gPi, gPj, gV, g_attn, gt);                    \
+    break;
+      switch (gu) {
+        CLQ_BWDF(20) CLQ_BWDF(24) CLQ_BWDF(28) CLQ_BWDF(32)
+        default: set_error("k_clq_bwd_fused: block size %d not covered", g->cliques->max_block); return B200GAT_ERR_UNSUPPORTED;
+      }
+#undef CLQ_BWDF
+      B200_CHECK_LAUNCH("k_clq_bwd_fused");
+      return B200GAT_OK;
+    }
+  }
   float* gs_dense = scratch;
   float* gsum_u = gs_dense + (((int64_t)g->cliques->s_elems * A.H + 3) & ~3ll);
   float* gsum_v = gsum_u + (int64_t)g->n_nodes * A.H;
