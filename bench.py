@@ -500,7 +500,7 @@ def run_b200(args):
     # pinned host memory and reads ITS loss back, but the copy + plan build of step i+1 are queued on a side
     # stream while step i trains (the copy engine and the plan kernels run under the step's kernels, and the
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
-    pf = BatchPrefetcher(dev)
+    pf = BatchPrefetcher(dev, side_stream=os.environ.get("BENCH_PREFETCH_SIDE_STREAM", "0") == "1")
     submit(pf)
 
     from wheatley_b200.prefetch import HostReadback

@@ -37,8 +37,7 @@ def main():
         jb, _ = jssp_batch_from_observation(obs, dev, n_j * n_m, conflicts="clique", graph_pooling="learn")
         t.append(time.perf_counter())
         bucket.zero()
-        _, lp, ent, val, _ = agent.get_action_and_value(jb, d["action"], d["masks"])
-        loss, _ = ppo_loss(lp, ent, val, d["old_lp"], d["adv"], d["ret"], d["old_v"], **kw)
+        loss, _ = agent.ppo_minibatch(jb, d["action"], d["masks"], d["old_lp"], d["adv"], d["ret"], d["old_v"], **kw)
         t.append(time.perf_counter())
         loss.backward()
         t.append(time.perf_counter())
@@ -70,7 +69,7 @@ def main():
             for _ in range(3):
                 step()
             torch.cuda.synchronize()
-        print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=45, max_name_column_width=60))
+        print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=70, max_name_column_width=70))
         return
     pr = cProfile.Profile()
     pr.enable()
