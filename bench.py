@@ -477,6 +477,17 @@ def run_b200(args):
     tm = _lib.timing_read()
     _lib.timing_enable(False)
 
+    # ---- the same step with fp32-exact matmuls (the JSSP entry point of the reference never sets
+    # torch.set_float32_matmul_precision("high"), only psp/train_psp.py:47 does): dense projections on the library's
+    # fp32 GEMM, layer-by-layer host mirror, eager launches.  Reported beside `value`, which runs the TF32 dense path.
+    ms_fp32 = None
+    if os.environ.get("BENCH_SKIP_FP32_DENSE", "0") != "1":
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            ms_fp32, _, _ = timed(lambda: train_step(jb_res, d_res), max(3, args.steps // 2), 3)
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = True
+
     # The eager legs below are host-bound (~350 launches per step): a full cyclic-GC pass over the ~10^6 long-lived
     # objects of torch + this process costs 10-40 ms and showed up as 2-4 outlier steps in 20.  Freeze what exists
     # (standard practice for latency-sensitive loops); objects created from here on are still collected.
@@ -639,15 +650,21 @@ def run_b200(args):
                   "the event nodes serialise launches, `value` is timed on the plain graph)"
                   if graph is not None else "per-kernel CUDA events in the timed eager steps")
     roofline = None
-    # DRAM traffic of the kernel class per launch, from the committed ncu --set full capture of this workload
+    # DRAM traffic of the kernel class per launch, from the committed ncu --set full capture of this workload -
+    # accepted only when it was made with the attention kernels this run uses (SHA-1 of their sources)
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r1m_traffic.json")) as f:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from make_traffic import kernel_source_sha
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             tr = json.load(f)
-        if (tr["workload"], tr["graphs_per_gpu"], tr["hidden"], tr["heads"]) == (args.workload, B, cfg["hidden"],
-                                                                              cfg["heads"]) and dom in tr:
+        same = (tr["workload"], tr["graphs_per_gpu"], tr["hidden"], tr["heads"]) == (args.workload, B, cfg["hidden"],
+                                                                                 cfg["heads"])
+        if same and dom in tr and tr.get("kernel_source_sha") == kernel_source_sha():
             traffic, traffic_src = tr[dom], tr["source"]
-    except (OSError, KeyError, ValueError):
+        elif same:
+            traffic_src = "stale: profiles/r2_traffic.json was captured with other kernel sources"
+    except (OSError, KeyError, ValueError, ImportError):
         pass
     if dom:
         ms, byt = per[dom]
@@ -663,7 +680,14 @@ def run_b200(args):
     line = {"metric": METRIC, "value": edges_total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None,
-            "dtype": "f32 (conv kernels fp32; dense projections TF32 like the reference)",
+            "dtype": "f32 (attention kernels fp32; dense projections TF32 = the matmul precision of the reference's "
+                     "live PSP trainer, psp/train_psp.py:47; its JSSP entry point runs fp32 matmuls: see "
+                     "fp32_dense for that configuration)",
+            "fp32_dense": None if ms_fp32 is None else {
+                "ms_per_step": ms_fp32, "value": edges_total / (ms_fp32 * 1e-3), "unit": UNIT,
+                "note": "same step, torch.backends.cuda.matmul.allow_tf32 = False: dense projections on the library "
+                        "fp32 GEMM through the layer-by-layer host mirror (eager launches); the configuration the "
+                        "1e-4 parity tests run"},
             "data": "synthetic",
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
                            l2="flushed between timed steps (256 MiB write)",
