@@ -477,9 +477,10 @@ def run_b200(args):
     tm = _lib.timing_read()
     _lib.timing_enable(False)
 
-    # ---- the same step with fp32-exact matmuls (the JSSP entry point of the reference never sets
-    # torch.set_float32_matmul_precision("high"), only psp/train_psp.py:47 does): dense projections on the library's
-    # fp32 GEMM, layer-by-layer host mirror, eager launches.  Reported beside `value`, which runs the TF32 dense path.
+    # ---- the same step with fp32-accurate matmuls (the JSSP entry point of the reference never sets
+    # torch.set_float32_matmul_precision("high"), only psp/train_psp.py:47 does): allow_tf32 = False switches
+    # b200gat_gemm_tf32 to 3xTF32 split arithmetic (three tcgen05.mma per k step, fp32 matmul accuracy: the
+    # configuration the 1e-4 parity tests run).  Same fused step, eager launches.  Reported beside `value`.
     ms_fp32 = None
     if os.environ.get("BENCH_SKIP_FP32_DENSE", "0") != "1":
         torch.backends.cuda.matmul.allow_tf32 = False
@@ -685,9 +686,9 @@ def run_b200(args):
                      "fp32_dense for that configuration)",
             "fp32_dense": None if ms_fp32 is None else {
                 "ms_per_step": ms_fp32, "value": edges_total / (ms_fp32 * 1e-3), "unit": UNIT,
-                "note": "same step, torch.backends.cuda.matmul.allow_tf32 = False: dense projections on the library "
-                        "fp32 GEMM through the layer-by-layer host mirror (eager launches); the configuration the "
-                        "1e-4 parity tests run"},
+                "note": "same step, torch.backends.cuda.matmul.allow_tf32 = False: the tcgen05 GEMM runs 3xTF32 split "
+                        "arithmetic (B200GAT_GEMM_FP32X3, fp32 matmul accuracy; eager launches): the configuration "
+                        "the 1e-4 parity tests run"},
             "data": "synthetic",
             "config": dict(workload_config(args, cfg, B), edges_per_gpu=E, nodes_per_gpu=N,
                            l2="flushed between timed steps (256 MiB write)",

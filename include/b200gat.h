@@ -440,6 +440,16 @@ typedef struct b200gat_gemm {
   float* a_rowsum;          /* optional [M], a_major 1 only: sum_k A(m, k) - the bias gradient when A = dy  */
                             /* (dW GEMM); exact fp32 sums of the staged tiles by the idle epilogue warps */
 } b200gat_gemm;
+/* Arithmetic of b200gat_gemm_tf32 and of everything built on it (MLP / trunk / agent calls), process-wide like
+ * torch.backends.cuda.matmul.allow_tf32, which the host mirror copies into it before every call:
+ *   B200GAT_GEMM_TF32   operands truncated to TF32 by the tensor core (allow_tf32 = True; psp/train_psp.py:47)
+ *   B200GAT_GEMM_FP32X3 3xTF32 split arithmetic: a_hi*b_hi + a_hi*b_lo + a_lo*b_hi with lo = x - trunc(x), three
+ *                       tcgen05.mma per k step, ~2^-20 relative per product = fp32 matmul accuracy (allow_tf32 =
+ *                       False: the reference's JSSP entry point, and the 1e-4 parity tests)                        */
+#define B200GAT_GEMM_TF32 0
+#define B200GAT_GEMM_FP32X3 1
+void b200gat_gemm_precision(int mode);
+int b200gat_gemm_precision_get(void);
 int b200gat_gemm_supported(const b200gat_gemm* g);
 int64_t b200gat_gemm_workspace_elems(const b200gat_gemm* g);
 int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream);

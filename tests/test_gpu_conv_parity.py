@@ -65,6 +65,27 @@ def perturb(mod, gen):
             p.add_(0.1 * torch.randn(p.shape, generator=gen, dtype=p.dtype))
 
 
+def grid(t, q):
+    """Round to multiples of 1/q in [-2, 2].  With node / edge features on a 1/8 grid and the weights that feed the
+    pre-activation on a 1/32 grid, every pre-activation z = Pi[u] + Pj[v] + Pe (+ b) is computed EXACTLY in fp32 by
+    any correct implementation (all partial sums fit 24 bits), so kernel and fp64 oracle take the same side of the
+    leaky_relu kink on every element.  With unrestricted random inputs about one pre-activation in 1e6 lands within
+    fp32 rounding of 0 and takes the other slope depending on how the projections were rounded (library fp32 GEMM,
+    3xTF32 tcgen05 GEMM and the oracle differ at the 1e-7 level), which moves single gradient entries by up to 1e-3
+    of the maximum - a property of evaluating the layer in fp32, not of a kernel (same device as
+    tests/test_gpu_clique.py)."""
+    return torch.round(t.clamp(-2, 2) * q) / q
+
+
+def grid_params(mod, names):
+    with torch.no_grad():
+        for k, p in mod.named_parameters():
+            if k in names:
+                p.copy_(grid(p, 32))
+
+
+GRAD_X_REL = REL
+
 CASES = [  # N, E, Fin, D, H
     (17, 60, 6, 5, 3),
     (300, 4000, 64, 64, 4),
@@ -84,13 +105,14 @@ def test_egat_matches_oracle(wb, N, E, Fin, D, H, efmode):
     Et = src.shape[0]
     ref = gat_oracle.OracleEGATConv(Fin, Fin, D, D, H).double()
     perturb(ref, gen)
+    grid_params(ref, ("fc_ni.weight", "fc_nj.weight", "fc_fij.weight", "bias"))
     layer = wb.EGATConv(Fin, Fin, D, D, H).cuda()
     load_state(layer, ref)
-    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64)
+    x = grid(torch.randn(N, Fin, generator=gen, dtype=torch.float64), 8)
     T = 7
     etype = torch.from_numpy(rng.integers(0, T, Et)).long()
-    table = torch.randn(T, Fin, generator=gen, dtype=torch.float64)
-    ef_dense = table[etype] if efmode == "typed" else torch.randn(Et, Fin, generator=gen, dtype=torch.float64)
+    table = grid(torch.randn(T, Fin, generator=gen, dtype=torch.float64), 8)
+    ef_dense = table[etype] if efmode == "typed" else grid(torch.randn(Et, Fin, generator=gen, dtype=torch.float64), 8)
     R = torch.randn(N, H, D, generator=gen, dtype=torch.float64)
 
     xr = x.clone().requires_grad_(True)
@@ -107,7 +129,7 @@ def test_egat_matches_oracle(wb, N, E, Fin, D, H, efmode):
     assert_close(h, h_ref, "h_out")
     assert_close(a, a_ref, "attention")
     assert_close(f.materialize(), f_ref, "f_out")
-    assert_close(xg.grad, xr.grad, "grad x")
+    assert_close(xg.grad, xr.grad, "grad x", rel=GRAD_X_REL)
     assert_close(efg.grad, efr.grad, "grad efeats")
     for (k, p), (_, pr) in zip(layer.named_parameters(), ref.named_parameters()):
         assert_close(p.grad, pr.grad, "grad " + k)
@@ -168,20 +190,21 @@ def test_gatv2_matches_oracle(wb, N, E, Fin, D, H, efmode):
     Et = src.shape[0]
     ref = gat_oracle.OracleGATv2Conv(Fin, D, H, edge_dim=Fin).double()
     perturb(ref, gen)
+    grid_params(ref, ("lin_l.weight", "lin_l.bias", "lin_r.weight", "lin_r.bias", "lin_edge.weight"))
     layer = wb.GATv2Conv(Fin, D, H, add_self_loops=False, edge_dim=Fin).cuda()
     load_state(layer, ref)
-    x = torch.randn(N, Fin, generator=gen, dtype=torch.float64)
+    x = grid(torch.randn(N, Fin, generator=gen, dtype=torch.float64), 8)
     R = torch.randn(N, H * D, generator=gen, dtype=torch.float64)
     Tn, K = 16, 5
     etype = torch.from_numpy(rng.integers(0, Tn, Et)).long()
-    table = torch.randn(Tn, Fin, generator=gen, dtype=torch.float64)
-    attrs = torch.randn(Et, K, generator=gen, dtype=torch.float64)
+    table = grid(torch.randn(Tn, Fin, generator=gen, dtype=torch.float64), 8)
+    attrs = grid(torch.randn(Et, K, generator=gen, dtype=torch.float64), 8)
     attrs[torch.rand(Et, generator=gen) < 0.5] = 0.0
-    aw = torch.randn(Fin, K, generator=gen, dtype=torch.float64)
+    aw = grid(torch.randn(Fin, K, generator=gen, dtype=torch.float64), 8)
     leaves_ref = [t.clone().requires_grad_(True) for t in (table, aw)]
     leaves_gpu = [t.float().cuda().requires_grad_(True) for t in (table, aw)]
     if efmode == "dense":
-        ea_ref = torch.randn(Et, Fin, generator=gen, dtype=torch.float64).requires_grad_(True)
+        ea_ref = grid(torch.randn(Et, Fin, generator=gen, dtype=torch.float64), 8).requires_grad_(True)
         ea_gpu = ea_ref.detach().float().cuda().requires_grad_(True)
         leaves_ref, leaves_gpu = [ea_ref], [ea_gpu]
     elif efmode == "affine":
@@ -204,7 +227,7 @@ def test_gatv2_matches_oracle(wb, N, E, Fin, D, H, efmode):
     (out * R.float().cuda()).sum().backward()
     assert_close(out, out_ref, "out")
     assert_close(alpha, alpha_ref, "alpha")
-    assert_close(xg.grad, xr.grad, "grad x")
+    assert_close(xg.grad, xr.grad, "grad x", rel=GRAD_X_REL)
     for i, (a, b) in enumerate(zip(leaves_gpu, leaves_ref)):
         assert_close(a.grad, b.grad, f"grad edge leaf {i}")
     for (k, p), (_, pr) in zip(layer.named_parameters(), ref.named_parameters()):
@@ -300,7 +323,7 @@ def test_gatv3_matches_oracle(wb, N, E, Fin, D, H):
     out = layer(xg, ei.cuda())
     (out * R.float().cuda()).sum().backward()
     assert_close(out, ref(x, ei), "out")
-    assert_close(xg.grad, xr.grad, "grad x")
+    assert_close(xg.grad, xr.grad, "grad x", rel=GRAD_X_REL)
     for (k, p), (_, pr) in zip(layer.named_parameters(), ref.named_parameters()):
         if k == "lin_edge.weight":
             continue

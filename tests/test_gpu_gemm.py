@@ -249,3 +249,33 @@ def test_graphconv_pyg_flavour_with_tf32_projections(wb, tf32):
     for k, p_ in layer.conv.named_parameters():
         q = dict(ref.named_parameters())[k]
         assert rel(p_.grad, q.grad) < 5e-2, k
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 64), (16008, 256, 256), (16008, 64, 768), (333, 464, 64), (4100, 36, 192)])
+def test_fp32x3_mode_has_fp32_matmul_accuracy(wb, M, K, N):
+    """``allow_tf32 = False``: b200gat_gemm_tf32 runs 3xTF32 split arithmetic (B200GAT_GEMM_FP32X3, three
+    tcgen05.mma per k step on hi / lo operand tiles).  Forward (K-major operands), dx (MN-major B) and dW (both
+    MN-major, split-K, bias row sums) against fp64: <= 1e-5 of the largest entry (measured 3.5e-6; an fp32 matmul
+    gives 1-2e-6, the TF32 path 1-3e-3)."""
+    from wheatley_b200 import _lib, dense
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        g = torch.Generator().manual_seed(M + K + N)
+        x = torch.randn(M, K, generator=g).cuda()
+        W = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
+        b = torch.randn(N, generator=g).cuda()
+        dy = torch.randn(M, N, generator=g).cuda()
+        l0 = launches()
+        _, y = dense.linear_fwd(x, W, b)
+        assert launches() > l0 and _lib.lib.b200gat_gemm_precision_get() == _lib.GEMM_FP32X3
+        assert rel(y, x.double() @ W.double().t() + b.double()) < 1e-5
+        z, h = dense.linear_fwd(x, W, b, gelu=True)
+        assert rel(h, torch.nn.functional.gelu(x.double() @ W.double().t() + b.double())) < 1e-5
+        dx = dense.linear_dx(dy, W)
+        assert rel(dx, dy.double() @ W.double()) < 1e-5
+        dW, db = dense.linear_dw(dy, x, want_bias=True)
+        assert rel(dW, dy.double().t() @ x.double()) < 1e-5
+        assert rel(db, dy.double().sum(0)) < 1e-5
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev

@@ -25,6 +25,7 @@ SYMBOLS = (
     "b200gat_clique_scratch_elems", "b200gat_clique_build", "b200gat_conv_uses_cliques",
     "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
     "b200gat_gemm_supported", "b200gat_gemm_workspace_elems", "b200gat_gemm_tf32",
+    "b200gat_gemm_precision", "b200gat_gemm_precision_get",
     "b200gat_colsum_scratch_elems", "b200gat_colsum",
     "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
     "b200gat_jssp_batch_edges", "b200gat_jssp_batch_build",
@@ -261,6 +262,9 @@ def _load():
     lib.b200gat_gemm_workspace_elems.argtypes = [mp]
     lib.b200gat_gemm_workspace_elems.restype = i64
     lib.b200gat_gemm_tf32.argtypes = [mp, vp]
+    lib.b200gat_gemm_precision.argtypes = [C.c_int]
+    lib.b200gat_gemm_precision.restype = None
+    lib.b200gat_gemm_precision_get.argtypes = []
     lib.b200gat_colsum_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_colsum_scratch_elems.restype = i64
     lib.b200gat_colsum.argtypes = [vp, i64, i64, i64, vp, vp, vp]
@@ -305,7 +309,7 @@ def _load():
                         "b200gat_gemm_workspace_elems", "b200gat_colsum_scratch_elems",
                         "b200gat_mlp_bwd_workspace_elems", "b200gat_jssp_batch_edges", "b200gat_psp_slot_words",
                         "b200gat_trunk_wcat_elems", "b200gat_trunk_bwd_workspace_elems",
-                        "b200gat_agent_bwd_workspace_elems"):
+                        "b200gat_agent_bwd_workspace_elems", "b200gat_gemm_precision"):
             fn.restype = C.c_int
     return lib
 
@@ -345,10 +349,28 @@ def ptr(t):
     return None if t is None else t.data_ptr()
 
 
+GEMM_TF32, GEMM_FP32X3 = 0, 1
+_gemm_mode = [GEMM_TF32]
+
+
+def sync_gemm_precision():
+    """Copy ``torch.backends.cuda.matmul.allow_tf32`` into the library's process-wide GEMM arithmetic switch:
+    TF32 operands when matmuls may use TF32 (the reference's live trainer, psp/train_psp.py:47), 3xTF32 split
+    arithmetic (fp32 matmul accuracy, three tcgen05.mma per k step) when they may not."""
+    import torch
+    mode = GEMM_TF32 if torch.backends.cuda.matmul.allow_tf32 else GEMM_FP32X3
+    if mode != _gemm_mode[0]:
+        lib.b200gat_gemm_precision(mode)
+        _gemm_mode[0] = mode
+
+
 def stream_ptr():
     """Raw ``cudaStream_t`` of torch's current stream on the current device (the cheap accessor:
-    ``torch.cuda.current_stream()`` builds a Python object, ~10 us per call on the eager path)."""
+    ``torch.cuda.current_stream()`` builds a Python object, ~10 us per call on the eager path).  Every C-ABI call
+    fetches its stream here right before the call, so this is also where the GEMM arithmetic switch is kept in
+    step with torch's matmul-precision flag."""
     import torch
+    sync_gemm_precision()
     return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
 
 

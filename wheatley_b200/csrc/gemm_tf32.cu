@@ -15,10 +15,13 @@
 #include <cuda.h>
 #include <math.h>
 #include <stdlib.h>
+#include <atomic>
 #include "common.cuh"
 
 namespace b200gat {
 namespace {
+
+std::atomic<int> g_gemm_x3{0};   // b200gat_gemm_precision(): 0 = TF32 operands, 1 = 3xTF32 split (fp32-level accuracy)
 
 constexpr int BM = 128;      // rows of the output tile = TMEM lanes
 constexpr int BK = 32;       // fp32 per stage row = 128 bytes = one swizzle span
@@ -144,16 +147,24 @@ __device__ __forceinline__ float dgelu_f(float z) {
 }
 
 // ------------------------------------------------------------------------------------------- the kernel
-template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __grid_constant__ CUtensorMap tmA,
+// X3 = 3xTF32 split arithmetic (fp32-level accuracy, for torch.backends.cuda.matmul.allow_tf32 == False): the tensor
+// core reads only the upper 19 bits of an fp32 operand, so hi = x as it lies in shared memory and lo = x - trunc(x)
+// (exact in fp32); a_hi*b_hi + a_hi*b_lo + a_lo*b_hi reproduces the fp32 product to ~2^-20 relative.  The lo tiles
+// are written by the (otherwise idle) epilogue warps into a second copy of the stage - same swizzled layout, the
+// split is element-wise - and the MMA warp issues three tcgen05.mma per k step.  Two stages instead of three.
+template <int BN, bool A_MN, bool B_MN, bool X3>
+__global__ void __launch_bounds__(320, ((BN == 256 || X3) ? 1 : 2)) k_gemm_tf32(const __grid_constant__ CUtensorMap tmA,
                                                    const __grid_constant__ CUtensorMap tmB, GemmArgs p) {
   constexpr int B_STAGE_BYTES = BN * BK * 4;
-  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr int TILE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;          // what the TMA fills per stage
+  constexpr int STAGE_BYTES = X3 ? 2 * TILE_BYTES : TILE_BYTES;      // X3: A | B | A_lo | B_lo
+  constexpr int NST = X3 ? 2 : STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle-128B tiles need 1024-byte alignment
-  __shared__ __align__(8) uint64_t bars[2 * STAGES + 1];
+  __shared__ __align__(8) uint64_t bars[3 * STAGES + 1];
   __shared__ uint32_t tmem_base_s;
   const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[STAGES]), accum_bar = smem_u32(&bars[2 * STAGES]);
+  const uint32_t lo0 = smem_u32(&bars[2 * STAGES + 1]);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mt = blockIdx.x, nt = blockIdx.y;
   const int kb0 = blockIdx.z * p.kb_per_split;
@@ -165,9 +176,10 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
   // the MMA commit plus these 128 readers.
   const bool rowsum = A_MN && p.a_rowsum != nullptr && nt == 0;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < NST; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, rowsum ? 129 : 1);
+      mbar_init(lo0 + 8 * s, 256);
     }
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -187,12 +199,12 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
   if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
     for (int i = 0; i < nkb; ++i) {
-      const int s = i % STAGES;
-      const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
+      const int s = i % NST;
+      const uint32_t ph = (uint32_t)(i / NST) & 1u;
       if (lane == 0) {
         mbar_wait(empty0 + 8 * s, ph ^ 1u);
         const uint32_t fb = full0 + 8 * s;
-        mbar_expect_tx(fb, STAGE_BYTES);
+        mbar_expect_tx(fb, TILE_BYTES);
         const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
         const int kb = kb0 + i;
         if (!A_MN) {
@@ -218,10 +230,10 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
     for (int i = 0; i < nkb; ++i) {
-      const int s = i % STAGES;
-      const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
+      const int s = i % NST;
+      const uint32_t ph = (uint32_t)(i / NST) & 1u;
       if (lane == 0) {
-        mbar_wait(full0 + 8 * s, ph);
+        mbar_wait((X3 ? lo0 : full0) + 8 * s, ph);       // X3: the lo tiles are written (implies the stage is full)
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
 #pragma unroll
@@ -230,7 +242,18 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
                                    : smem_desc(sa + k * 32, 16, 1024, 2);
           const uint64_t bd = B_MN ? smem_desc(sb + k * p.mn_kadv, p.mn_lbo, p.mn_sbo, p.mn_layout)
                                    : smem_desc(sb + k * 32, 16, 1024, 2);
-          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          if constexpr (X3) {
+            const uint32_t la = sa + TILE_BYTES, lb = sb + TILE_BYTES;
+            const uint64_t adl = A_MN ? smem_desc(la + k * p.mn_kadv, p.mn_lbo, p.mn_sbo, p.mn_layout)
+                                      : smem_desc(la + k * 32, 16, 1024, 2);
+            const uint64_t bdl = B_MN ? smem_desc(lb + k * p.mn_kadv, p.mn_lbo, p.mn_sbo, p.mn_layout)
+                                      : smem_desc(lb + k * 32, 16, 1024, 2);
+            umma_tf32(tmem_base, adl, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);     // small terms first
+            umma_tf32(tmem_base, ad, bdl, idesc, 1u);
+            umma_tf32(tmem_base, ad, bd, idesc, 1u);
+          } else {
+            umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
         }
         umma_commit(empty0 + 8 * s);                 // frees the stage when these MMAs have read it
         if (i == nkb - 1) umma_commit(accum_bar);    // accumulator complete
@@ -253,22 +276,46 @@ __global__ void __launch_bounds__(320, (BN == 256 ? 1 : 2)) k_gemm_tf32(const __
                        : nullptr;
     const bool dgelu = p.epi == B200GAT_EPI_DGELU, gelu = p.epi == B200GAT_EPI_GELU;
     bool waited = false;
-    if (rowsum && warp < 4) {
+    const bool do_rowsum = rowsum && warp < 4;
+    if (X3 || do_rowsum) {
       // MN-major A stage: 4 boxes of 32 mn columns x 32 k rows (128 B per row, 32-byte chunks xor-ed with row & 3)
       const int t = threadIdx.x, c = t & 31;
-      const uint8_t* a_tile = smem_raw + (base - smem_u32(smem_raw)) + (t >> 5) * 4096 + (c & 7) * 4;
+      uint8_t* ring = smem_raw + (base - smem_u32(smem_raw));
+      const uint8_t* a_tile = ring + (t >> 5) * 4096 + (c & 7) * 4;
       float sum = 0.f;
       for (int i = 0; i < nkb; ++i) {
-        const int s2 = i % STAGES;
-        mbar_wait(full0 + 8 * s2, (uint32_t)(i / STAGES) & 1u);
-        const uint8_t* st_base = a_tile + s2 * STAGE_BYTES;
+        const int s2 = i % NST;
+        mbar_wait(full0 + 8 * s2, (uint32_t)(i / NST) & 1u);
+        if constexpr (X3) {
+          // lo = x - trunc_tf32(x) for every element of the A and B tiles of this stage (element-wise: the lo tiles
+          // inherit the swizzled layout), then make the generic-proxy writes visible to the tensor core's reads
+          const float4* src = reinterpret_cast<const float4*>(ring + s2 * STAGE_BYTES);
+          float4* dst = reinterpret_cast<float4*>(ring + s2 * STAGE_BYTES + TILE_BYTES);
+#pragma unroll 4
+          for (int idx = t; idx < TILE_BYTES / 16; idx += 256) {
+            const float4 x = src[idx];
+            float4 l;
+            l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+            l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+            l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+            l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+            dst[idx] = l;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(lo0 + 8 * s2) : "memory");
+        }
+        if (do_rowsum) {
+          const uint8_t* st_base = a_tile + s2 * STAGE_BYTES;
 #pragma unroll 8
-        for (int row = 0; row < BK; ++row)
-          sum += *reinterpret_cast<const float*>(st_base + row * 128 + (((c >> 3) ^ (row & 3)) << 5));
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s2) : "memory");
+          for (int row = 0; row < BK; ++row)
+            sum += *reinterpret_cast<const float*>(st_base + row * 128 + (((c >> 3) ^ (row & 3)) << 5));
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s2) : "memory");
+        }
       }
-      const int row = mt * BM + t;
-      if (row < p.M) p.a_rowsum[(long long)blockIdx.z * p.rowsum_split_stride + row] = sum;
+      if (do_rowsum) {
+        const int row = mt * BM + t;
+        if (row < p.M) p.a_rowsum[(long long)blockIdx.z * p.rowsum_split_stride + row] = sum;
+      }
     }
 #pragma unroll 1
     for (int c = hf * (BN / 2); c < (hf + 1) * (BN / 2); c += 32) {
@@ -530,19 +577,19 @@ int plan_gemm(const b200gat_gemm* g, Shape* s, bool report) {
 #undef GEMM_REQ
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool X3>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, dim3 grid, cudaStream_t st) {
-  constexpr size_t smem = (size_t)STAGES * (A_STAGE_BYTES + BN * BK * 4) + 1024 + 2048;   // + alignment + ones tile
+  constexpr size_t smem = (X3 ? (size_t)2 * 2 : (size_t)STAGES) * (A_STAGE_BYTES + BN * BK * 4) + 1024 + 2048;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(k_gemm_tf32<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+    if (cudaFuncSetAttribute(k_gemm_tf32<BN, A_MN, B_MN, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
         cudaSuccess) {
       set_error("k_gemm_tf32: cudaFuncSetAttribute(%zu) failed", smem);
       return B200GAT_ERR_CUDA;
     }
     attr_set = true;
   }
-  k_gemm_tf32<BN, A_MN, B_MN><<<grid, 320, smem, st>>>(ta, tb, a);
+  k_gemm_tf32<BN, A_MN, B_MN, X3><<<grid, 320, smem, st>>>(ta, tb, a);
   B200_CHECK_LAUNCH("k_gemm_tf32");
   return B200GAT_OK;
 }
@@ -551,6 +598,11 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, dim3
 }  // namespace b200gat
 
 using namespace b200gat;
+
+extern "C" void b200gat_gemm_precision(int mode) { g_gemm_x3.store(mode == B200GAT_GEMM_FP32X3 ? 1 : 0); }
+extern "C" int b200gat_gemm_precision_get(void) {
+  return g_gemm_x3.load() ? B200GAT_GEMM_FP32X3 : B200GAT_GEMM_TF32;
+}
 
 extern "C" int b200gat_gemm_supported(const b200gat_gemm* g) {
   if (!g) return 0;
@@ -610,13 +662,15 @@ extern "C" int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream) {
   }
   dim3 grid((unsigned)s.m_tiles, (unsigned)s.n_tiles, (unsigned)s.splits);
   ScopedTimer tm(a_mn ? B200GAT_TIMING_GEMM_DW : (b_mn ? B200GAT_TIMING_GEMM_DX : B200GAT_TIMING_GEMM), st);
-#define GEMM_LAUNCH(BN_)                                                           \
-  (a_mn ? (b_mn ? launch<BN_, true, true>(ta, tb, a, grid, st)                     \
-                : launch<BN_, true, false>(ta, tb, a, grid, st))                   \
-        : (b_mn ? launch<BN_, false, true>(ta, tb, a, grid, st)                    \
-                : launch<BN_, false, false>(ta, tb, a, grid, st)))
+#define GEMM_LAUNCH2(BN_, X3_)                                                     \
+  (a_mn ? (b_mn ? launch<BN_, true, true, X3_>(ta, tb, a, grid, st)                \
+                : launch<BN_, true, false, X3_>(ta, tb, a, grid, st))              \
+        : (b_mn ? launch<BN_, false, true, X3_>(ta, tb, a, grid, st)               \
+                : launch<BN_, false, false, X3_>(ta, tb, a, grid, st)))
+#define GEMM_LAUNCH(BN_) (g_gemm_x3.load(std::memory_order_relaxed) ? GEMM_LAUNCH2(BN_, true) : GEMM_LAUNCH2(BN_, false))
   rc = s.bn == 256 ? GEMM_LAUNCH(256) : (s.bn == 128 ? GEMM_LAUNCH(128) : GEMM_LAUNCH(64));
 #undef GEMM_LAUNCH
+#undef GEMM_LAUNCH2
   if (rc) return rc;
   if (s.splits > 1) {
     const long long n4 = g->M * g->N / 4, r4 = g->a_rowsum ? g->M / 4 : 0;

@@ -210,20 +210,25 @@ __global__ void k_sort_large(const int32_t* __restrict__ ptr, const int32_t* __r
 }
 
 // ---- finish -----------------------------------------------------------------------------
-__global__ void k_finish_in(const int64_t* __restrict__ src, int64_t E,
+// Edges with an endpoint outside [0, N) are counted (stats[2]) and left out of both CSRs: only the first
+// in_ptr[N] (= out_ptr[N]) positions of the sorted arrays are defined; the rest is never written and must not be
+// dereferenced (an uninitialised edge id there was an out-of-bounds read whenever the scratch held stale data).
+__global__ void k_finish_in(const int64_t* __restrict__ src, int64_t E, const int32_t* __restrict__ in_ptr, int32_t N,
                             const int32_t* __restrict__ in_eid, int32_t* __restrict__ in_src,
                             int32_t* __restrict__ inv) {
   int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (p >= E) return;
+  if (p >= in_ptr[N]) { in_src[p] = 0; return; }
   int e = in_eid[p];
   in_src[p] = (int32_t)src[e];
   inv[e] = (int32_t)p;
 }
-__global__ void k_finish_out(const int64_t* __restrict__ dst, int64_t E,
+__global__ void k_finish_out(const int64_t* __restrict__ dst, int64_t E, const int32_t* __restrict__ out_ptr, int32_t N,
                              const int32_t* __restrict__ out_eid, const int32_t* __restrict__ inv,
                              int32_t* __restrict__ out_dst, int32_t* __restrict__ out_pos) {
   int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (q >= E) return;
+  if (q >= out_ptr[N]) { out_dst[q] = 0; out_pos[q] = 0; return; }
   int e = out_eid[q];
   out_dst[q] = (int32_t)dst[e];
   out_pos[q] = inv[e];
@@ -402,8 +407,8 @@ extern "C" int b200gat_plan_build(const int64_t* edge_src, const int64_t* edge_d
     k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(in_ptr, tmp_in, in_eid, large_in, counters + 0);
     k_sort_large<<<2 * kNumSMs, 256, 0, st>>>(out_ptr, tmp_out, out_eid, large_out, counters + 1);
     B200_CHECK_LAUNCHES("k_sort", 4);
-    k_finish_in<<<eb, 256, 0, st>>>(edge_src, E, in_eid, in_src, inv);
-    k_finish_out<<<eb, 256, 0, st>>>(edge_dst, E, out_eid, inv, out_dst, out_pos);
+    k_finish_in<<<eb, 256, 0, st>>>(edge_src, E, in_ptr, (int32_t)N, in_eid, in_src, inv);
+    k_finish_out<<<eb, 256, 0, st>>>(edge_dst, E, out_ptr, (int32_t)N, out_eid, inv, out_dst, out_pos);
     B200_CHECK_LAUNCHES("k_finish", 2);
   }
   if (N > 0) {

@@ -22,7 +22,10 @@ def gemm_backend() -> str:
 
 
 def tf32_path_enabled() -> bool:
-    return gemm_backend() != "cublas" and torch.backends.cuda.matmul.allow_tf32
+    """The hand-written tcgen05 GEMM is used unless ``WHEATLEY_B200_GEMM=cublas``: with TF32 operands when
+    ``torch.backends.cuda.matmul.allow_tf32`` is set, with 3xTF32 split arithmetic (fp32 matmul accuracy) when it is
+    not (``_lib.sync_gemm_precision``)."""
+    return gemm_backend() != "cublas"
 
 
 def _ok(t):
