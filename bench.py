@@ -513,24 +513,27 @@ def run_b200(args):
     # stream while step i trains (the copy engine and the plan kernels run under the step's kernels, and the
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
     pf = BatchPrefetcher(dev, side_stream=os.environ.get("BENCH_PREFETCH_SIDE_STREAM", "0") == "1")
-    submit(pf)
+    DEPTH = 2                      # batches / loss reads in flight: the launch thread may run two steps ahead of the
+    for _ in range(DEPTH):         # GPU, so a short stall of the (shared) host does not idle the device
+        submit(pf)
 
     from wheatley_b200.prefetch import HostReadback
-    rb = HostReadback(depth=2)
+    rb = HostReadback(depth=DEPTH + 1)
     e2e_losses = []
 
     def e2e_step():
         d, _ = pf.get()
         submit(pf)                                         # next step's inputs
         rb.push(train_step(d["batch"], d))                 # device->host read of THIS step's loss, asynchronous
-        if len(rb) > 1:
-            e2e_losses.append(float(rb.pop()))             # ... consumed one step later (HostReadback)
+        if len(rb) > DEPTH:
+            e2e_losses.append(float(rb.pop()))             # ... consumed DEPTH steps later (HostReadback)
     ms_e2e_mean, _, _ = timed(e2e_step, max(3, args.steps), E2E_WARMUP)
     e2e_spread = dict(timed.last_spread)
     while len(rb):
         e2e_losses.append(float(rb.pop()))
     assert len(e2e_losses) == max(3, args.steps) + E2E_WARMUP and all(x == x for x in e2e_losses)   # every loss read
-    pf.get()                                               # drain the last (unused) prefetch
+    for _ in range(DEPTH):
+        pf.get()                                           # drain the unused prefetches
     torch.cuda.synchronize()
     # every step is bracketed by its own event pair; the median is reported because single steps of this
     # host-bound loop occasionally stall for 20-200 ms on the shared box (seen with identical inputs and a frozen
