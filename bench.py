@@ -535,9 +535,8 @@ def run_b200(args):
     for _ in range(DEPTH):
         pf.get()                                           # drain the unused prefetches
     torch.cuda.synchronize()
-    # every step is bracketed by its own event pair; the median is reported because single steps of this
-    # host-bound loop occasionally stall for 20-200 ms on the shared box (seen with identical inputs and a frozen
-    # GC; mean, min and max are kept beside it).  Multi-rank: the slowest rank's median.
+    # every step is bracketed by its own event pair: the headline is the MEAN over the timed steps; the median
+    # (slowest rank's), min and max are reported beside it in ms_per_step_median / ms_per_step_spread
     t_med = torch.tensor([e2e_spread["median"]], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_med, op=dist.ReduceOp.MAX)

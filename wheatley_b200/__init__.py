@@ -31,10 +31,12 @@ from .graph_conv import GraphConv, GATv2Conv, GATv3Conv
 from .mlp import MLP
 from .gnn_mp import GnnFlat, GnnMP
 from . import agent_head
+from .gnn_dgl import GnnDGL
+from .agent import JsspAgent, PspAgent
 
 __all__ = [
     "B200GatError", "GraphPlan", "plan_for_edge_index", "TypedEdgeFeats", "AffineEdgeFeats",
     "EdgeFeatures", "fused_gat_conv", "attention_weights", "edge_output", "masked_log_softmax",
     "masked_logprob_entropy", "EGATConv", "EEGATConv", "DGLError", "GraphConv", "GATv2Conv",
-    "GATv3Conv", "MLP", "GnnMP", "GnnFlat", "agent_head",
+    "GATv3Conv", "MLP", "GnnMP", "GnnFlat", "GnnDGL", "JsspAgent", "PspAgent", "agent_head",
 ]
