@@ -457,6 +457,17 @@ int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream);
 int64_t b200gat_colsum_scratch_elems(int64_t M, int64_t N);
 int b200gat_colsum(const float* X, int64_t M, int64_t N, int64_t ld, float* out, float* scratch,
                    void* stream);
+/* b200gat_colsum without a scratch argument and without any allocation, for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * The slab partials live in a file-scope device array of
+ * 2 * 148 * B200GAT_COLSUM_NOALLOC_MAX_N floats (1.16 MiB) that every GPU loading the library holds until exit.
+ * N > B200GAT_COLSUM_NOALLOC_MAX_N -> B200GAT_ERR_UNSUPPORTED (b200gat_last_error says so); any M.  Same summation
+ * order as b200gat_colsum, so the results are bitwise equal.  Every call shares the array (it keeps the last call's
+ * partials; nothing needs to start at zero): calls that overlap on the GPU - two streams, two host threads - race.
+ * Calls no cudaMalloc / cudaFree / allocating library routine; the array's device address is looked up once per
+ * device (cudaGetSymbolAddress) with that device current.                                                        */
+#define B200GAT_COLSUM_NOALLOC_MAX_N 1024
+int b200gat_colsum_noalloc(const float* X, int64_t M, int64_t N, int64_t ld, float* out, void* stream);
 
 /* ------------------------------------------------------------------ fused GELU MLP (one call per pass)
  * generic/mlp.py:70-77 with activation GELU and no LayerNorm (the default configuration, args.py:335-348):

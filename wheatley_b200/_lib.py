@@ -26,7 +26,7 @@ SYMBOLS = (
     "b200gat_timing_collect_graph", "b200gat_timing_clear_graph",
     "b200gat_gemm_supported", "b200gat_gemm_workspace_elems", "b200gat_gemm_tf32",
     "b200gat_gemm_precision", "b200gat_gemm_precision_get",
-    "b200gat_colsum_scratch_elems", "b200gat_colsum",
+    "b200gat_colsum_scratch_elems", "b200gat_colsum", "b200gat_colsum_noalloc",
     "b200gat_mlp_fwd", "b200gat_mlp_bwd_workspace_elems", "b200gat_mlp_bwd",
     "b200gat_jssp_batch_edges", "b200gat_jssp_batch_build",
     "b200gat_psp_slot_words", "b200gat_psp_batch_sizes", "b200gat_psp_batch_build",
@@ -268,6 +268,7 @@ def _load():
     lib.b200gat_colsum_scratch_elems.argtypes = [i64, i64]
     lib.b200gat_colsum_scratch_elems.restype = i64
     lib.b200gat_colsum.argtypes = [vp, i64, i64, i64, vp, vp, vp]
+    lib.b200gat_colsum_noalloc.argtypes = [vp, i64, i64, i64, vp, vp]
     lp, lg = C.POINTER(Mlp), C.POINTER(MlpGrads)
     lib.b200gat_mlp_fwd.argtypes = [lp, vp]
     lib.b200gat_mlp_bwd_workspace_elems.argtypes = [lp, lg]

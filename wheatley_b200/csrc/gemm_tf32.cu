@@ -706,3 +706,61 @@ extern "C" int b200gat_colsum(const float* X, int64_t M, int64_t N, int64_t ld, 
   B200_CHECK_LAUNCHES("k_colsum", 2);
   return B200GAT_OK;
 }
+
+// ------------------------------------------------------------------------------------------- no-allocation variant
+// b200gat_colsum for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the slab partials live in a file-scope device array instead of a caller-provided scratch buffer.
+// 2 * 148 slabs x B200GAT_COLSUM_NOALLOC_MAX_N columns x 4 B = 1.16 MiB, held by every GPU that loads the library
+// until the process exits.  Every call shares the array: calls that overlap on the GPU (two streams, two threads)
+// race on it.  Nothing has to start at zero: k_colsum_partial writes every partial k_colsum_finish reads.
+static __device__ __align__(256) float g_colsum_static[2 * kNumSMs * B200GAT_COLSUM_NOALLOC_MAX_N];
+
+// Device address of the array on the CURRENT device, resolved once per device (in host code the symbol's name is a
+// host-side stand-in, not a device pointer).
+static int colsum_static_ptr(float** ptr) {
+  constexpr int kMaxDev = 64;
+  static std::atomic<float*> cache[kMaxDev];
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    set_error("b200gat_colsum_noalloc: no current CUDA device (or device ordinal >= %d)", kMaxDev);
+    return B200GAT_ERR_CUDA;
+  }
+  float* p = cache[dev].load(std::memory_order_acquire);
+  if (!p) {
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static);
+    if (e != cudaSuccess || !p) {
+      set_error("b200gat_colsum_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return B200GAT_ERR_CUDA;
+    }
+    cache[dev].store(p, std::memory_order_release);
+  }
+  *ptr = p;
+  return B200GAT_OK;
+}
+
+extern "C" int b200gat_colsum_noalloc(const float* X, int64_t M, int64_t N, int64_t ld, float* out, void* stream) {
+  B200_CHECK_ARG(N > 0 && out, "null output / empty width");
+  if (N > B200GAT_COLSUM_NOALLOC_MAX_N) {
+    set_error("b200gat_colsum_noalloc: N = %lld exceeds the static scratch (B200GAT_COLSUM_NOALLOC_MAX_N = %d "
+              "columns); use b200gat_colsum with a caller-provided scratch buffer",
+              (long long)N, B200GAT_COLSUM_NOALLOC_MAX_N);
+    return B200GAT_ERR_UNSUPPORTED;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (M <= 0) {
+    if (cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), st) != cudaSuccess) return B200GAT_ERR_CUDA;
+    return B200GAT_OK;
+  }
+  B200_CHECK_ARG(X && ld >= N, "null input / leading dimension smaller than the width");
+  float* scratch = nullptr;
+  int rc = colsum_static_ptr(&scratch);
+  if (rc) return rc;
+  // same slab decomposition as b200gat_colsum: identical summation order, identical result
+  const int64_t slabs_max = M < 2 * kNumSMs ? M : 2 * kNumSMs;
+  const int rows = (int)ceil_div(M, slabs_max);
+  const int slabs = (int)ceil_div(M, rows);
+  k_colsum_partial<<<slabs, 256, 0, st>>>(X, M, (int)N, ld, rows, scratch);
+  k_colsum_finish<<<(unsigned)ceil_div(N, 8), 256, 0, st>>>(scratch, slabs, (int)N, out);
+  B200_CHECK_LAUNCHES("k_colsum(noalloc)", 2);
+  return B200GAT_OK;
+}
