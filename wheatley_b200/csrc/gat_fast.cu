@@ -165,10 +165,12 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, floa
   const int v = A.hub_dst[w];
   const float* rec0 = A.hub_scratch + (int64_t)w * P * (HD + kHubRec);
   float M = -INFINITY;
+#pragma unroll 8
   for (int p = 0; p < P; ++p) M = fmaxf(M, rec0[(int64_t)p * (HD + kHubRec) + HD + lane]);
   float acc[VPL], l = 0.f;
 #pragma unroll
   for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+#pragma unroll 4                         // four slices' loads in flight: one warp per hub, pure latency
   for (int p = 0; p < P; ++p) {
     const float* rec = rec0 + (int64_t)p * (HD + kHubRec);
     const float mp = rec[HD + lane];
@@ -396,6 +398,7 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, floa
   float acc[VPL];
 #pragma unroll
   for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+#pragma unroll 4
   for (int p = 0; p < P; ++p) {
     float pa[VPL];
     ldrow<VPL>(pa, A.hub_scratch + ((int64_t)w * P + p) * (HD + kHubRec) + c0);
@@ -573,13 +576,21 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   if (A.N == 0) return B200GAT_OK;
   A.node_blk = node_blk;
   A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
-  const unsigned blocks = node_ctas(A.N) + A.hub_blocks;
   const bool alias = (V == Pi);
   ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
-  FAST_DISPATCH(vpl, lph, alias,
-                (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
-                                                                              l_save, agg_save)));
-  B200_CHECK_LAUNCH("k_fwd_fast");
+  // low-degree graphs: the windowed kernel takes the nodes, the kernel below only runs its hub CTAs
+  const bool win = win_enabled(A);
+  if (win) {
+    rc = win_fwd(A, vpl, lph, alias, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, st);
+    if (rc) return rc;
+  }
+  const unsigned blocks = (win ? 0 : node_ctas(A.N)) + A.hub_blocks;
+  if (blocks) {
+    FAST_DISPATCH(vpl, lph, alias,
+                  (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
+                                                                                l_save, agg_save)));
+    B200_CHECK_LAUNCH("k_fwd_fast");
+  }
   if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
     const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
     switch (vpl) {
@@ -612,6 +623,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   const int HD = 32 * vpl;
   const unsigned nblocks = node_ctas(A.N);
   const bool alias = (V == Pi);
+  const bool win = win_enabled(A);
   B200_CHECK_ARG(alias == (gV == gPi), "gV must alias gPi exactly when V aliases Pi");
   const int64_t tab_bytes = (int64_t)A.T * HD * 4;
   const int tab_in_smem = A.emode == B200GAT_EDGE_NONE ? 0 : kWarps * tab_bytes <= 64 * 1024 ? 2
@@ -625,16 +637,24 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_DST, st);
     A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
-    const unsigned blocks = nblocks + A.hub_blocks;
+    if (win) {
+      rc = win_bwd_dst(A, vpl, lph, alias, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table,
+                       g_affine, gs, alpha, st);
+      if (rc) return rc;
+    }
+    const unsigned blocks = (win ? 0 : nblocks) + A.hub_blocks;
     if (smem > 48 * 1024) {
       FAST_DISPATCH(vpl, lph, alias,
                     (cudaFuncSetAttribute(k_bwd_dst_fast<VPL, LPH, ALIAS>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
     }
-    FAST_DISPATCH(vpl, lph, alias,
-                  (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
-                      A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
-                      gs, alpha, tab_in_smem, aff_in_smem)));
+    if (blocks) {
+      FAST_DISPATCH(vpl, lph, alias,
+                    (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
+                        A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
+                        gs, alpha, tab_in_smem, aff_in_smem)));
+      note_launch(1);
+    }
     if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
       const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
       if (vpl == 2) k_hub_merge_bwd<2><<<mb, kFastThreads, 0, st>>>(A, gPj);
@@ -646,12 +666,19 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   {
     ScopedTimer tm(B200GAT_TIMING_CONV_BWD_SRC, st);
     A.hub_blocks = (A.hub_src && A.n_hub_src && A.hub_degree > 0) ? kHubBlocks : 0;
-    const unsigned blocks = nblocks + A.hub_blocks;
-    FAST_DISPATCH(vpl, lph, alias,
-                  (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
-                                                                                   gPi, gV)));
+    if (win) {
+      rc = win_bwd_src(A, vpl, lph, alias, Pi, Pj, g_out, gs, alpha, gPi, gV, st);
+      if (rc) return rc;
+    }
+    const unsigned blocks = (win ? 0 : nblocks) + A.hub_blocks;
+    if (blocks) {
+      FAST_DISPATCH(vpl, lph, alias,
+                    (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
+                                                                                     gPi, gV)));
+      note_launch(1);
+    }
   }
-  B200_CHECK_LAUNCHES("k_bwd_fast", 2);
+  B200_CHECK_LAUNCHES("k_bwd_fast", 0);
   return B200GAT_OK;
 }
 
