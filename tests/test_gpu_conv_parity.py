@@ -53,6 +53,23 @@ def random_graph(rng, n, e, self_loops=True, hub=None):
     return torch.from_numpy(src[perm]).long(), torch.from_numpy(dst[perm]).long()
 
 
+def banded_graph(rng, n, self_loops=True):
+    """The structure the windowed kernels (csrc/gat_win.cu) are selected for (E <= 8 N): job chains of 10 nodes with
+    forward and reversed precedence edges, self loops, and a pool node (the last one: a hub when n > 257) wired to
+    and from every other node."""
+    i = np.arange(n - 2)
+    i = i[(i + 1) % 10 != 0]
+    pool = n - 1
+    others = np.arange(n - 1)
+    src = np.concatenate([i, i + 1, others, np.full(n - 1, pool)])
+    dst = np.concatenate([i + 1, i, np.full(n - 1, pool), others])
+    if self_loops:
+        src = np.concatenate([src, np.arange(n)])
+        dst = np.concatenate([dst, np.arange(n)])
+    perm = rng.permutation(src.shape[0])
+    return torch.from_numpy(src[perm]).long(), torch.from_numpy(dst[perm]).long()
+
+
 def load_state(dst_mod, src_mod):
     with torch.no_grad():
         sd = {k: v.detach().float() for k, v in src_mod.state_dict().items()}
@@ -95,13 +112,32 @@ CASES = [  # N, E, Fin, D, H
 ]
 
 
+BANDED_CASES = [  # N, Fin, D, H: H*D = 256 / 128 / 64; 403 and 150 are not multiples of the 16-node window
+    (403, 16, 64, 4),
+    (403, 16, 32, 4),
+    (150, 8, 16, 4),
+    (1040, 8, 64, 4),
+]
+
+
 @pytest.mark.parametrize("N,E,Fin,D,H", CASES)
 @pytest.mark.parametrize("efmode", ["dense", "typed"])
 def test_egat_matches_oracle(wb, N, E, Fin, D, H, efmode):
+    _egat_vs_oracle(wb, N, E, Fin, D, H, efmode, "random")
+
+
+@pytest.mark.parametrize("N,Fin,D,H", BANDED_CASES)
+def test_egat_banded_graph_matches_oracle(wb, N, Fin, D, H):
+    """Low-degree banded graph with a hub: the windowed kernels (k_fwd_win / k_bwd_dst_win / k_bwd_src_win) + the hub
+    CTAs of the warp-per-node kernels."""
+    _egat_vs_oracle(wb, N, 0, Fin, D, H, "typed", "banded")
+
+
+def _egat_vs_oracle(wb, N, E, Fin, D, H, efmode, graph):
     from oracle import gat_oracle
     rng = np.random.default_rng(N * 7 + E)
     gen = torch.Generator().manual_seed(N + E)
-    src, dst = random_graph(rng, N, E, hub=3)
+    src, dst = random_graph(rng, N, E, hub=3) if graph == "random" else banded_graph(rng, N)
     Et = src.shape[0]
     ref = gat_oracle.OracleEGATConv(Fin, Fin, D, D, H).double()
     perturb(ref, gen)
@@ -182,10 +218,24 @@ def test_egat_zero_in_degree_raises(wb):
 @pytest.mark.parametrize("N,E,Fin,D,H", CASES)
 @pytest.mark.parametrize("efmode", ["dense", "affine", "typed", "none"])
 def test_gatv2_matches_oracle(wb, N, E, Fin, D, H, efmode):
+    _gatv2_vs_oracle(wb, N, E, Fin, D, H, efmode, "random")
+
+
+@pytest.mark.parametrize("N,Fin,D,H", BANDED_CASES)
+@pytest.mark.parametrize("efmode", ["affine", "none"])
+def test_gatv2_banded_graph_matches_oracle(wb, N, Fin, D, H, efmode):
+    """V aliasing Pi and the affine edge term on the windowed kernels."""
+    _gatv2_vs_oracle(wb, N, 0, Fin, D, H, efmode, "banded")
+
+
+def _gatv2_vs_oracle(wb, N, E, Fin, D, H, efmode, graph):
     from oracle import gat_oracle
     rng = np.random.default_rng(N * 3 + E)
     gen = torch.Generator().manual_seed(N * 5 + E)
-    src, dst = random_graph(rng, N, E, self_loops=False, hub=1)    # isolated destinations allowed
+    if graph == "random":
+        src, dst = random_graph(rng, N, E, self_loops=False, hub=1)    # isolated destinations allowed
+    else:
+        src, dst = banded_graph(rng, N, self_loops=False)
     ei = torch.stack([src, dst])
     Et = src.shape[0]
     ref = gat_oracle.OracleGATv2Conv(Fin, D, H, edge_dim=Fin).double()

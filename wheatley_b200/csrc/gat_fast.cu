@@ -66,12 +66,14 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
         for (int j0 = 0; j0 < n; j0 += kUnroll) {
           float pi[kUnroll][VPL], vv[ALIAS ? 1 : kUnroll][VPL];
           int tt[kUnroll], pp[kUnroll];
+          float aa[kUnroll];
 #pragma unroll
           for (int k = 0; k < kUnroll; ++k) {
             const int idx = min(j0 + k, n - 1);
             const int u = __shfl_sync(0xffffffffu, my_u, idx);
             tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
             pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
+            aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
             ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
             if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
           }
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
             float z[VPL];
 #pragma unroll
             for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-            if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+            if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
             float part = 0.f;
 #pragma unroll
             for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
@@ -276,12 +278,14 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
         for (int j0 = 0; j0 < n; j0 += U) {
           float pi[U][VPL], vv[ALIAS ? 1 : U][VPL], sv[U];
           int tt[U], pp[U];
+          float aa[U];
 #pragma unroll
           for (int k = 0; k < U; ++k) {
             const int idx = min(j0 + k, n - 1);
             const int u = __shfl_sync(0xffffffffu, my_u, idx);
             tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
             pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
+            aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
             ldrow<VPL>(pi[k], Pi + (int64_t)u * HD + c0);
             if constexpr (!ALIAS) ldrow<VPL>(vv[k], V + (int64_t)u * HD + c0);
             sv[k] = __ldg(s_save + (int64_t)pp[k] * A.H + h);
@@ -309,7 +313,7 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
             float z[VPL];
 #pragma unroll
             for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-            if (affine && valid) affine_add<VPL>(A, pos, c0, z);
+            if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
             float gz[VPL];
 #pragma unroll
             for (int i = 0; i < VPL; ++i) {
@@ -321,7 +325,7 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
             }
             if (affine && valid) {
               for (int kk = 0; kk < A.K; ++kk) {
-                const float av = __ldg(A.attr + pos * A.K + kk);
+                const float av = __shfl_sync(0xffffffffu, aa[k], kk);
                 if (av != 0.f) {
                   if (aff_in_smem) {
                     float* dst = sh_aff + ((wi * A.K + kk) * HD + c0);
@@ -449,11 +453,13 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fas
         for (int j0 = 0; j0 < n; j0 += kUnroll) {
           float pj[kUnroll][VPL], gg[kUnroll][VPL], gsv[kUnroll], al[kUnroll];
           int tt[kUnroll], pp[kUnroll];
+          float aa[kUnroll];
 #pragma unroll
           for (int k = 0; k < kUnroll; ++k) {
             const int idx = min(j0 + k, n - 1);
             const int v = __shfl_sync(0xffffffffu, my_v, idx);
             pp[k] = __shfl_sync(0xffffffffu, my_pos, idx);
+            aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
             tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
             ldrow<VPL>(pj[k], Pj + (int64_t)v * HD + c0);
             ldrow<VPL>(gg[k], G + (int64_t)v * HD + c0);
@@ -471,7 +477,7 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fas
             float z[VPL];
 #pragma unroll
             for (int i = 0; i < VPL; ++i) z[i] = pj[k][i] + pt[i];
-            if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+            if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
 #pragma unroll
             for (int i = 0; i < VPL; ++i) {
               gpi[i] = fmaf(gsv[k], z[i] > 0.f ? at[i] : ats[i], gpi[i]);

@@ -87,12 +87,18 @@ __device__ __forceinline__ void type_row(const FastArgs& A, int t, int c0, const
 #pragma unroll
   for (int i = 0; i < VPL; ++i) qt[i] = base[i] + pe[i];
 }
-// Affine part of the edge term: z += sum_k attr[pos,k] * affine[k]   (warp-uniform branches)
+// Affine part of the edge term: z += sum_k attr[pos,k] * affine[k].  The K <= 8 attributes of an edge are fetched by
+// the first K lanes in ONE load, issued together with the edge's row gathers (affine_fetch), and broadcast by shuffles
+// here; the rows of the affine map stay in L1.  (A first version read attr[pos,k] inside this loop: K dependent
+// global round trips per edge, which made the PSP workloads latency-bound.)
+__device__ __forceinline__ float affine_fetch(const FastArgs& A, int64_t pos, int lane) {
+  return lane < A.K ? __ldg(A.attr + pos * A.K + lane) : 0.f;
+}
 template <int VPL>
-__device__ __forceinline__ void affine_add(const FastArgs& A, int64_t pos, int c0, float (&z)[VPL]) {
+__device__ __forceinline__ void affine_add(const FastArgs& A, float my_attr, int c0, float (&z)[VPL]) {
   for (int k = 0; k < A.K; ++k) {
-    const float av = __ldg(A.attr + pos * A.K + k);
-    if (av != 0.f) {
+    const float av = __shfl_sync(0xffffffffu, my_attr, k);
+    if (av != 0.f) {                                   // warp-uniform
       float w[VPL];
       ldrow<VPL>(w, A.affine + (int64_t)k * (32 * VPL) + c0);
 #pragma unroll

@@ -171,12 +171,14 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
           for (int j0 = 0; j0 < n; j0 += U) {
             float pi[U][VPL], vv[ALIAS ? 1 : U][VPL];
             int tt[U], pp[U];
+            float aa[U];
 #pragma unroll
             for (int k = 0; k < U; ++k) {
               const int idx = min(j0 + k, n - 1);
               const int u = __shfl_sync(0xffffffffu, my_u, idx);
               tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
               pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
+              aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
               const int ul = u - w0;
               if ((unsigned)ul < (unsigned)nw) {
                 ldrow_s<VPL>(pi[k], w_pi + ul * HD + c0);
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
               float z[VPL];
 #pragma unroll
               for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-              if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+              if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
               float part = 0.f;
 #pragma unroll
               for (int i = 0; i < VPL; ++i) part = fmaf(at[i], leaky(z[i], A.slope), part);
@@ -329,12 +331,14 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
           for (int j0 = 0; j0 < n; j0 += U) {
             float pi[U][VPL], vv[ALIAS ? 1 : U][VPL], sv[U];
             int tt[U], pp[U];
+            float aa[U];
 #pragma unroll
             for (int k = 0; k < U; ++k) {
               const int idx = min(j0 + k, n - 1);
               const int u = __shfl_sync(0xffffffffu, my_u, idx);
               tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
               pp[k] = __shfl_sync(0xffffffffu, my_p, idx);
+              aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
               const int ul = u - w0;
               if ((unsigned)ul < (unsigned)nw) {
                 ldrow_s<VPL>(pi[k], w_pi + ul * HD + c0);
@@ -368,7 +372,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
               float z[VPL];
 #pragma unroll
               for (int i = 0; i < VPL; ++i) z[i] = pi[k][i] + qt[i];
-              if (affine && valid) affine_add<VPL>(A, pos, c0, z);
+              if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
               float gz[VPL];
 #pragma unroll
               for (int i = 0; i < VPL; ++i) {
@@ -380,7 +384,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
               }
               if (affine && valid) {
                 for (int kk = 0; kk < A.K; ++kk) {
-                  const float av = __ldg(A.attr + pos * A.K + kk);
+                  const float av = __shfl_sync(0xffffffffu, aa[k], kk);
                   if (av != 0.f) {
                     if (aff_in_smem) {
                       float* dst = sh_aff + ((wi * A.K + kk) * HD + c0);
@@ -498,11 +502,13 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
           for (int j0 = 0; j0 < n; j0 += U) {
             float pj[U][VPL], gg[U][VPL], gsv[U], al[U];
             int tt[U], pp[U];
+            float aa[U];
 #pragma unroll
             for (int k = 0; k < U; ++k) {
               const int idx = min(j0 + k, n - 1);
               const int v = __shfl_sync(0xffffffffu, my_v, idx);
               pp[k] = __shfl_sync(0xffffffffu, my_pos, idx);
+              aa[k] = affine ? affine_fetch(A, pp[k], lane) : 0.f;
               tt[k] = __shfl_sync(0xffffffffu, my_t, idx);
               const int vl = v - w0;
               if ((unsigned)vl < (unsigned)nw) {
@@ -526,7 +532,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
               float z[VPL];
 #pragma unroll
               for (int i = 0; i < VPL; ++i) z[i] = pj[k][i] + pt[i];
-              if (affine && valid) affine_add<VPL>(A, pp[k], c0, z);
+              if (affine && valid) affine_add<VPL>(A, aa[k], c0, z);
 #pragma unroll
               for (int i = 0; i < VPL; ++i) {
                 gpi[i] = fmaf(gsv[k], z[i] > 0.f ? at[i] : ats[i], gpi[i]);
@@ -556,7 +562,7 @@ unsigned win_ctas(int64_t N, int per_sm) {
 
 template <auto Kernel>
 int win_set_smem(size_t bytes) {
-  if (bytes <= 48 * 1024) return B200GAT_OK;
+  if (bytes + sizeof(WinIdx) + 64 <= 48 * 1024) return B200GAT_OK;      // static + dynamic within the default limit
   cudaError_t e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e != cudaSuccess) {
     set_error("gat_win: cudaFuncSetAttribute(%zu bytes): %s", bytes, cudaGetErrorString(e));
