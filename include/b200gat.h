@@ -115,7 +115,13 @@ typedef struct b200gat_graph_s {
   /* Dense clique blocks of this graph and the CSR of the edges outside them, or NULL/NULL.      */
   const struct b200gat_cliques_s* cliques;
   const struct b200gat_graph_s* residual;
+  /* B200GAT_GRAPH_LOW_DEGREE: every node that is not a hub has at most ~32 in- and out-edges (host knowledge: the  */
+  /* plan's degree statistics, or the residual of a clique view).  The attention kernels then take runs of 16        */
+  /* consecutive nodes per CTA with the runs' rows and adjacency staged in shared memory (csrc/gat_win.cu) instead   */
+  /* of one warp per node in the locality order.  A scheduling hint: it never changes a result beyond rounding.      */
+  int32_t flags;
 } b200gat_graph;
+#define B200GAT_GRAPH_LOW_DEGREE 1
 
 /* ------------------------------------------------------------------ clique blocks
  * Machine-conflict cliques (jssp/utils/utils.py:460-478; psp/utils/utils.py:62-92) are complete

@@ -70,6 +70,18 @@ def banded_graph(rng, n, self_loops=True):
     return torch.from_numpy(src[perm]).long(), torch.from_numpy(dst[perm]).long()
 
 
+def _graph_arg(wb, src, dst, N, graph, edge_index=None):
+    """What the layer is called with: the COO as the reference passes it, or - banded graphs - a prebuilt plan
+    flagged B200GAT_GRAPH_LOW_DEGREE, which selects the windowed kernels (the plan sets the flag itself only when no
+    adjacency list is longer than 32; here the pool node's is, on purpose: hub CTAs, multi-chunk segments)."""
+    if graph != "banded":
+        return edge_index.cuda() if edge_index is not None else (src.cuda(), dst.cuda(), N)
+    from wheatley_b200 import _lib
+    plan = wb.GraphPlan(src.cuda(), dst.cuda(), N)
+    plan.c.flags |= _lib.GRAPH_LOW_DEGREE
+    return plan
+
+
 def load_state(dst_mod, src_mod):
     with torch.no_grad():
         sd = {k: v.detach().float() for k, v in src_mod.state_dict().items()}
@@ -159,7 +171,7 @@ def _egat_vs_oracle(wb, N, E, Fin, D, H, efmode, graph):
     xg = x.float().cuda().requires_grad_(True)
     efg = (table if efmode == "typed" else ef_dense).float().cuda().requires_grad_(True)
     efeats = wb.TypedEdgeFeats(etype.cuda(), efg) if efmode == "typed" else efg
-    h, f, a = layer((src.cuda(), dst.cuda(), N), xg, efeats, get_attention=True)
+    h, f, a = layer(_graph_arg(wb, src, dst, N, graph), xg, efeats, get_attention=True)
     (h * R.float().cuda()).sum().backward()
 
     assert_close(h, h_ref, "h_out")
@@ -273,7 +285,7 @@ def _gatv2_vs_oracle(wb, N, E, Fin, D, H, efmode, graph):
         ref.lin_edge.weight, ref.att, ref.bias)
     (out_ref * R).sum().backward()
     xg = x.float().cuda().requires_grad_(True)
-    out, (_, alpha) = layer(xg, ei.cuda(), ea_gpu, return_attention_weights=True)
+    out, (_, alpha) = layer(xg, _graph_arg(wb, src, dst, N, graph, ei), ea_gpu, return_attention_weights=True)
     (out * R.float().cuda()).sum().backward()
     assert_close(out, out_ref, "out")
     assert_close(alpha, alpha_ref, "alpha")

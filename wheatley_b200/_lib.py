@@ -12,6 +12,8 @@ EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
 MAX_ATTR = 8
 HUB_DEGREE = 256
 HUB_PARTS = 16        # CTAs a hub destination's in-edges are split over
+GRAPH_LOW_DEGREE = 1  # b200gat_graph.flags
+LOW_DEGREE_MAX = 32   # longest non-hub adjacency list of a graph flagged GRAPH_LOW_DEGREE
 HUB_REC = 256 + 64    # floats per partial record (include/b200gat.h)
 FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1
 
@@ -61,7 +63,8 @@ Graph._fields_ = [("n_nodes", C.c_int32), ("n_edges", C.c_int32),
                 ("hub_degree", C.c_int32), ("hub_dst", C.c_void_p), ("n_hub_dst", C.c_void_p),
                 ("hub_src", C.c_void_p), ("n_hub_src", C.c_void_p),
                 ("hub_scratch", C.c_void_p), ("hub_parts", C.c_int32), ("hub_cap", C.c_int32),
-                ("in_pos", C.c_void_p), ("cliques", C.POINTER(Cliques)), ("residual", C.POINTER(Graph))]
+                ("in_pos", C.c_void_p), ("cliques", C.POINTER(Cliques)), ("residual", C.POINTER(Graph)),
+                ("flags", C.c_int32)]
 
 
 class Attn(C.Structure):

@@ -23,24 +23,26 @@
 namespace b200gat {
 
 // ------------------------------------------------------------------------------ forward
+// The work of CTA `block` of a grid of `nblocks` (the kernel below; the windowed kernels of gat_win.cuh run the hub
+// CTAs of this function at the front of their own grids: block < hub_blocks == nblocks).
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
-    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+__device__ __forceinline__ void fwd_fast_cta(
+    const FastArgs& A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
-    float* __restrict__ l_save, float* __restrict__ agg_save) {
+    float* __restrict__ l_save, float* __restrict__ agg_save, int block, int nblocks) {
   constexpr int HD = 32 * VPL;
   __shared__ float sm_acc[kWarps][HD];
   __shared__ float sm_m[kWarps][32], sm_l[kWarps][32];
   const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
   const bool head_lead = (lane % LPH) == 0;
-  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
+  const bool hub_block = block < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
   const int n_hub = hub_block ? *A.n_hub_dst : 0;
   const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
   const int n_items = hub_block ? n_hub * P : (A.N + kWarps - 1) / kWarps;      // node CTAs: groups of kWarps nodes
-  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
-  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
+  const int item0 = hub_block ? block : block - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : nblocks - A.hub_blocks;
   float at[VPL];
   ldrow<VPL>(at, A.attn + c0);
 
@@ -153,6 +155,14 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
   }
 }
 
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+    float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
+    float* __restrict__ l_save, float* __restrict__ agg_save) {
+  fwd_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, (int)blockIdx.x, (int)gridDim.x);
+}
+
 // Merge the partial softmax states of the slices of each split hub (in slice order) and finalise.
 template <int VPL, int LPH>
 __global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, float* __restrict__ out,
@@ -190,15 +200,15 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, floa
 // Dynamic shared memory: sh_gat[HD] (d attn of the CTA) + sh_tab[T][HD] (d edge table of the CTA,
 // when it fits).  Static: per-warp partial d Pj rows for the hub merge.
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fast(
-    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+__device__ __forceinline__ void bwd_dst_fast_cta(
+    const FastArgs& A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
     const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
     float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
-    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem) {
+    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem, float* sh,
+    int block, int nblocks) {
   constexpr int HD = 32 * VPL;
   constexpr int U = 2;                      // edges in flight (register budget: 128/thread)
-  extern __shared__ float sh[];
   __shared__ float sm_part[kWarps][HD];
   float* sh_gat = sh;
   float* sh_tab = sh + HD;
@@ -217,12 +227,12 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
 
   const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
   const bool head_lead = (lane % LPH) == 0;
-  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
+  const bool hub_block = block < A.hub_blocks;
   const int n_hub = hub_block ? *A.n_hub_dst : 0;
   const int P = hub_block ? hub_parts_of(A, n_hub) : 1;
   const int n_items = hub_block ? n_hub * P : (A.N + kWarps - 1) / kWarps;
-  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
-  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
+  const int item0 = hub_block ? block : block - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : nblocks - A.hub_blocks;
   float at[VPL], gat[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
@@ -391,6 +401,18 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
   }
 }
 
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
+    const float* __restrict__ s_save, const float* __restrict__ m_save, const float* __restrict__ l_save,
+    const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
+    float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
+    float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem) {
+  extern __shared__ float sh[];
+  bwd_dst_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, s_save, m_save, l_save, agg_save, G, gPj, g_attn, g_table, g_affine,
+                                    gs_out, alpha_out, tab_in_smem, aff_in_smem, sh, (int)blockIdx.x, (int)gridDim.x);
+}
+
 // Sum the partial d Pj rows of the slices of each split hub (in slice order).
 template <int VPL>
 __global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, float* __restrict__ gPj) {
@@ -414,19 +436,19 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, floa
 
 // ------------------------------------------------------------------------------ backward, by source
 template <int VPL, int LPH, bool ALIAS>
-__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fast(
-    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
+__device__ __forceinline__ void bwd_src_fast_cta(
+    const FastArgs& A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
     const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
-    float* __restrict__ gV) {
+    float* __restrict__ gV, int block, int nblocks) {
   constexpr int HD = 32 * VPL;
   __shared__ float sm_part[kWarps][2 * HD];
   const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31, c0 = lane * VPL, h = lane / LPH;
-  const bool hub_block = (int)blockIdx.x < A.hub_blocks;
+  const bool hub_block = block < A.hub_blocks;
   const bool typed = A.emode != B200GAT_EDGE_NONE;
   const bool affine = A.emode == B200GAT_EDGE_AFFINE && A.K > 0;
   const int n_items = hub_block ? *A.n_hub_src : (A.N + kWarps - 1) / kWarps;
-  const int item0 = hub_block ? blockIdx.x : blockIdx.x - A.hub_blocks;
-  const int istep = hub_block ? A.hub_blocks : gridDim.x - A.hub_blocks;
+  const int item0 = hub_block ? block : block - A.hub_blocks;
+  const int istep = hub_block ? A.hub_blocks : nblocks - A.hub_blocks;
   float at[VPL], ats[VPL];
   ldrow<VPL>(at, A.attn + c0);
 #pragma unroll
@@ -516,6 +538,14 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fas
   }
 }
 
+template <int VPL, int LPH, bool ALIAS>
+__global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fast(
+    FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
+    const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
+    float* __restrict__ gV) {
+  bwd_src_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, G, gs_in, alpha_in, gPi, gV, (int)blockIdx.x, (int)gridDim.x);
+}
+
 // ------------------------------------------------------------------------------ dispatch
 static bool shape_of(const b200gat_attn* a, int& vpl, int& lph) {
   const int HD = a->heads * a->dim;
@@ -549,7 +579,7 @@ static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a,
   B200_CHECK_ARG(g->n_nodes == 0 || (g->in_ptr && g->out_ptr), "null CSR pointers");
   B200_CHECK_ARG(g->n_edges == 0 || (g->in_src && g->out_dst && g->out_pos), "null CSR edge arrays");
   B200_CHECK_ARG(a->attn, "null attn");
-  A.N = g->n_nodes; A.E = g->n_edges;
+  A.N = g->n_nodes; A.E = g->n_edges; A.flags = g->flags;
   A.in_ptr = g->in_ptr; A.in_src = g->in_src; A.out_ptr = g->out_ptr; A.out_dst = g->out_dst;
   A.out_pos = g->out_pos; A.dst_order = g->dst_order; A.src_order = g->src_order;
   A.in_pos = g->in_pos; A.node_blk = nullptr;
@@ -584,13 +614,13 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   A.hub_blocks = (A.hub_dst && A.n_hub_dst && A.hub_degree > 0) ? kHubBlocks : 0;
   const bool alias = (V == Pi);
   ScopedTimer tm(B200GAT_TIMING_CONV_FWD, st);
-  // low-degree graphs: the windowed kernel takes the nodes, the kernel below only runs its hub CTAs
+  // graphs flagged low-degree: the windowed kernel (its first CTAs are this kernel's hub CTAs)
   const bool win = win_enabled(A);
   if (win) {
     rc = win_fwd(A, vpl, lph, alias, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, st);
     if (rc) return rc;
   }
-  const unsigned blocks = (win ? 0 : node_ctas(A.N)) + A.hub_blocks;
+  const unsigned blocks = win ? 0 : node_ctas(A.N) + A.hub_blocks;
   if (blocks) {
     FAST_DISPATCH(vpl, lph, alias,
                   (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
@@ -648,7 +678,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
                        g_affine, gs, alpha, st);
       if (rc) return rc;
     }
-    const unsigned blocks = (win ? 0 : nblocks) + A.hub_blocks;
+    const unsigned blocks = win ? 0 : nblocks + A.hub_blocks;
     if (smem > 48 * 1024) {
       FAST_DISPATCH(vpl, lph, alias,
                     (cudaFuncSetAttribute(k_bwd_dst_fast<VPL, LPH, ALIAS>,
@@ -676,7 +706,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
       rc = win_bwd_src(A, vpl, lph, alias, Pi, Pj, g_out, gs, alpha, gPi, gV, st);
       if (rc) return rc;
     }
-    const unsigned blocks = (win ? 0 : nblocks) + A.hub_blocks;
+    const unsigned blocks = win ? 0 : nblocks + A.hub_blocks;
     if (blocks) {
       FAST_DISPATCH(vpl, lph, alias,
                     (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
@@ -689,3 +719,6 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
 }
 
 }  // namespace b200gat
+
+// The windowed kernels call the *_fast_cta functions above for their hub CTAs: same translation unit.
+#include "gat_win.cuh"

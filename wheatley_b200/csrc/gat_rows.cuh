@@ -9,7 +9,7 @@
 namespace b200gat {
 
 struct FastArgs {
-  int N, E;
+  int N, E, flags;
   const int32_t *in_ptr, *in_src, *out_ptr, *out_dst, *out_pos, *dst_order, *src_order;
   const int32_t *in_pos;      // residual graphs: position of each in-edge in the full dst-sorted order
   const int32_t *node_blk;    // clique members (>= 0): the forward leaves their softmax state un-normalised

@@ -15,8 +15,10 @@
 //             every 4: same result up to rounding); a source row comes from the window when w0 <= u < w0 + W
 //             (self loops and job neighbours) and from global memory otherwise (pool node, run boundaries)
 //
-// Hub nodes (degree > hub_degree) are skipped: the hub CTAs of gat_fast.cu take them (fast_fwd / fast_bwd launch those
-// kernels with the hub blocks only).
+// Hub nodes (degree > hub_degree) are skipped by the runs: the first hub_blocks CTAs of each grid are the hub CTAs of
+// gat_fast.cu (fwd_fast_cta / bwd_dst_fast_cta / bwd_src_fast_cta), so the hubs overlap with the runs instead of
+// costing a launch of their own (measured as separate launches: +19 us per kernel at 8 x Taillard 100x20).
+// Included at the end of gat_fast.cu (one translation unit: the hub CTAs are the *_fast_cta functions defined there).
 #include <stdlib.h>
 #include "gat_rows.cuh"
 
@@ -120,6 +122,10 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
   __shared__ __align__(8) unsigned long long s_bar;
   float* w_pi = w_rows;
   float* w_v = ALIAS ? w_rows : w_rows + kWinW * HD;
+  if ((int)blockIdx.x < A.hub_blocks) {      // hub CTAs (whole CTA: uniform branch)
+    fwd_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, (int)blockIdx.x, A.hub_blocks);
+    return;
+  }
   const uint32_t bar = w_smem_u32(&s_bar);
   if (threadIdx.x == 0) w_mbar_init(bar, 1);
   __syncthreads();
@@ -132,7 +138,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
   uint32_t phase = 0;
   const int n_runs = (A.N + kWinW - 1) / kWinW;
 
-  for (int run = blockIdx.x; run < n_runs; run += gridDim.x) {
+  for (int run = blockIdx.x - A.hub_blocks; run < n_runs; run += gridDim.x - A.hub_blocks) {
     const int w0 = run * kWinW, nw = min(kWinW, A.N - w0);
     win_begin(bar, w0, nw, HD, w_pi, Pi, ALIAS ? nullptr : w_v, V, ix, A.in_ptr);
     float q[kWinNPW][VPL];                                       // own rows: in flight under the index round trips
@@ -256,6 +262,12 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
   const int n_tab = tab_in_smem == 2 ? kWarps * A.T * HD : tab_in_smem == 1 ? A.T * HD : 0;
   float* sh_aff = sh + HD + n_tab;
   const int n_sh = HD + n_tab + (aff_in_smem ? kWarps * A.K * HD : 0);
+  if ((int)blockIdx.x < A.hub_blocks) {      // hub CTAs: same accumulators, at the same place of the dynamic array
+    bwd_dst_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, s_save, m_save, l_save, agg_save, G, gPj, g_attn, g_table,
+                                      g_affine, gs_out, alpha_out, tab_in_smem, aff_in_smem, sh, (int)blockIdx.x,
+                                      A.hub_blocks);
+    return;
+  }
   for (int i = threadIdx.x; i < n_sh; i += kFastThreads) sh[i] = 0.f;
   const uint32_t bar = w_smem_u32(&s_bar);
   if (threadIdx.x == 0) w_mbar_init(bar, 1);
@@ -270,7 +282,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
   uint32_t phase = 0;
   const int n_runs = (A.N + kWinW - 1) / kWinW;
 
-  for (int run = blockIdx.x; run < n_runs; run += gridDim.x) {
+  for (int run = blockIdx.x - A.hub_blocks; run < n_runs; run += gridDim.x - A.hub_blocks) {
     const int w0 = run * kWinW, nw = min(kWinW, A.N - w0);
     win_begin(bar, w0, nw, HD, w_pi, Pi, ALIAS ? nullptr : w_v, V, ix, A.in_ptr);
     __syncthreads();
@@ -451,6 +463,10 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
   __shared__ __align__(8) unsigned long long s_bar;
   float* w_pj = w_rows;
   float* w_g = w_rows + kWinW * HD;
+  if ((int)blockIdx.x < A.hub_blocks) {      // hub CTAs
+    bwd_src_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, G, gs_in, alpha_in, gPi, gV, (int)blockIdx.x, A.hub_blocks);
+    return;
+  }
   const uint32_t bar = w_smem_u32(&s_bar);
   if (threadIdx.x == 0) w_mbar_init(bar, 1);
   __syncthreads();
@@ -464,7 +480,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
   uint32_t phase = 0;
   const int n_runs = (A.N + kWinW - 1) / kWinW;
 
-  for (int run = blockIdx.x; run < n_runs; run += gridDim.x) {
+  for (int run = blockIdx.x - A.hub_blocks; run < n_runs; run += gridDim.x - A.hub_blocks) {
     const int w0 = run * kWinW, nw = min(kWinW, A.N - w0);
     win_begin(bar, w0, nw, HD, w_pj, Pj, w_g, G, ix, A.out_ptr);
     float pr[kWinNPW][VPL];
@@ -562,7 +578,7 @@ unsigned win_ctas(int64_t N, int per_sm) {
 
 template <auto Kernel>
 int win_set_smem(size_t bytes) {
-  if (bytes + sizeof(WinIdx) + 64 <= 48 * 1024) return B200GAT_OK;      // static + dynamic within the default limit
+  if (bytes <= 16 * 1024) return B200GAT_OK;      // static (indices, hub merge buffers) + dynamic within 48 KB
   cudaError_t e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e != cudaSuccess) {
     set_error("gat_win: cudaFuncSetAttribute(%zu bytes): %s", bytes, cudaGetErrorString(e));
@@ -583,8 +599,11 @@ int win_occ() {
 
 }  // namespace
 
-// Low average degree: the per-node latency chain, not the row traffic, bounds the warp-per-node kernels.
-// B200GAT_WIN=0 keeps them; B200GAT_WIN=1 forces the windowed kernels on every graph.
+// Graphs flagged B200GAT_GRAPH_LOW_DEGREE by the plan (short adjacency lists everywhere except the hubs): the per-node
+// latency chain, not the row traffic, bounds the warp-per-node kernels there.  A long non-hub list would be walked by
+// one warp two edges at a time (measured on the PSP node-conflict graphs, ~100 in-edges per resource node: 1.4x
+// slower than the warp-per-node kernels), hence a flag from the host and not a mean-degree test here.
+// B200GAT_WIN=0 keeps the warp-per-node kernels; B200GAT_WIN=1 forces the windowed ones on every graph.
 bool win_enabled(const FastArgs& A) {
   static const int mode = [] {
     const char* e = getenv("B200GAT_WIN");
@@ -592,14 +611,14 @@ bool win_enabled(const FastArgs& A) {
   }();
   if (mode == 0) return false;
   if (mode == 1) return true;
-  return A.N >= 4 * kWinW && (int64_t)A.E <= 8ll * A.N;
+  return (A.flags & B200GAT_GRAPH_LOW_DEGREE) != 0;
 }
 
 int win_fwd(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, const float* Pj, const float* V,
             float* out, float* s_save, float* m_save, float* l_save, float* agg_save, cudaStream_t st) {
   const size_t smem = sizeof(float) * (size_t)(alias ? 1 : 2) * kWinW * 32 * vpl;
   const int occ = win_occ();
-  const unsigned blocks = win_ctas(A.N, occ);
+  const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_fwd_win<VPL, LPH, ALIAS, 3>>(smem)));
@@ -632,7 +651,7 @@ int win_bwd_dst(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
                                        (tab_in_smem == 2 ? (size_t)kWarps * A.T * HD
                                         : tab_in_smem == 1 ? (size_t)A.T * HD : 0) +
                                        (aff_in_smem ? (size_t)kWarps * A.K * HD : 0));
-  const unsigned blocks = win_ctas(A.N, 2);
+  const unsigned blocks = win_ctas(A.N, 2) + A.hub_blocks;
   int rc = B200GAT_OK;
   FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_dst_win<VPL, LPH, ALIAS>>(smem)));
   if (rc) return rc;
@@ -648,7 +667,7 @@ int win_bwd_src(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
                 const float* gs_in, const float* alpha_in, float* gPi, float* gV, cudaStream_t st) {
   const size_t smem = sizeof(float) * (size_t)2 * kWinW * 32 * vpl;
   const int occ = win_occ();
-  const unsigned blocks = win_ctas(A.N, occ);
+  const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_src_win<VPL, LPH, ALIAS, 3>>(smem)));

@@ -130,6 +130,9 @@ class CliqueView:
                                     src_order, hub_dst, hub_src, n_hub, in_pos=r_in_pos)
         with _lib.device_guard(dev):
             self._hub_scratch = _attach_hub_scratch(self._res_c, n_hub_dst, dev)
+        # what is left outside the blocks of a schedule graph: self loops, job chains and the pool star (a hub)
+        if Er <= 8 * N and N >= 64:
+            self._res_c.flags |= _lib.GRAPH_LOW_DEGREE
         self._cl = _lib.Cliques(self.n_blocks, self.max_block, self.n_members, self.s_elems,
                                 _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes), _lib.ptr(self.blk_type),
                                 _lib.ptr(self.blk_soff), _lib.ptr(self.node_blk), _lib.ptr(self.node_run),
@@ -221,6 +224,9 @@ class GraphPlan:
     def _set_stats_host(self, host):
         self._stats_host = tuple(int(x) for x in host[:4])
         self._hub_scratch = _attach_hub_scratch(self._c, int(host[4]), self.device)
+        # short adjacency lists everywhere (small PSP graphs): the windowed kernels (csrc/gat_win.cu)
+        if max(self._stats_host[1], self._stats_host[3]) <= _lib.LOW_DEGREE_MAX and self.n_nodes >= 64:
+            self._c.flags |= _lib.GRAPH_LOW_DEGREE
 
     def prepare(self, etype=None, defer=False):
         """Build everything the layers will ask for (host counts, the clique view of this edge typing) now, with
