@@ -21,6 +21,13 @@ struct ScopedTimer {
   bool on_, capturing_;
 };
 
+bool timing_enabled();     // b200gat_timing_enable(1) is in effect
+
+// The weight / bias gradients of b200gat_mlp_bwd alone (mlp_tf32.cu), for a caller that has already run the input
+// -gradient chain with gr->dW[] = NULL (so gr->dz[] hold every hidden layer's d loss / d z): used by trunk.cu to
+// issue them on a side stream.
+int mlp_bwd_dw(const b200gat_mlp* m, const b200gat_mlp_grads* gr, void* stream);
+
 #define B200_CHECK_ARG(cond, msg)                       \
   do {                                                  \
     if (!(cond)) {                                      \

@@ -27,6 +27,8 @@ static std::vector<EvPair> g_graph_pairs[B200GAT_TIMING_CLASSES];
 static double g_ms[B200GAT_TIMING_CLASSES];
 static int64_t g_cnt[B200GAT_TIMING_CLASSES];
 
+bool timing_enabled() { return g_timing.load(std::memory_order_relaxed); }
+
 ScopedTimer::ScopedTimer(int cls, cudaStream_t st) : cls_(cls), st_(st), on_(false) {
   if (!g_timing.load(std::memory_order_relaxed) || cls < 0 || cls >= B200GAT_TIMING_CLASSES) return;
   if (cudaEventCreate(&e0_) != cudaSuccess || cudaEventCreate(&e1_) != cudaSuccess) return;

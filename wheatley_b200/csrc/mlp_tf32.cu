@@ -84,6 +84,27 @@ extern "C" int64_t b200gat_mlp_bwd_workspace_elems(const b200gat_mlp* m, const b
   return need;
 }
 
+int b200gat::mlp_bwd_dw(const b200gat_mlp* m, const b200gat_mlp_grads* gr, void* stream) {
+  if (!check_mlp(m, "mlp_bwd_dw")) return B200GAT_ERR_INVALID;
+  B200_CHECK_ARG(gr && gr->gy, "null gradient descriptor / gy");
+  const int n = m->n_layers;
+  for (int i = n - 1; i >= 0; --i) {
+    if (!gr->dW[i]) {
+      B200_CHECK_ARG(!gr->db[i], "a bias gradient needs its weight gradient (row sums ride on that GEMM)");
+      continue;
+    }
+    const float* dz = i == n - 1 ? gr->gy : gr->dz[i];
+    B200_CHECK_ARG(dz, "weight gradients need dz of every hidden layer");
+    b200gat_gemm g;
+    dw_desc(&g, m, gr, i, dz);
+    g.workspace = gr->workspace; g.workspace_elems = gr->workspace_elems;
+    if (b200gat_gemm_workspace_elems(&g) > gr->workspace_elems) g.workspace = nullptr;   // runs unsplit
+    const int rc = b200gat_gemm_tf32(&g, stream);
+    if (rc) return rc;
+  }
+  return B200GAT_OK;
+}
+
 extern "C" int b200gat_mlp_bwd(const b200gat_mlp* m, const b200gat_mlp_grads* gr, void* stream) {
   if (!check_mlp(m, "b200gat_mlp_bwd")) return B200GAT_ERR_INVALID;
   B200_CHECK_ARG(gr && gr->gy, "null gradient descriptor / gy");

@@ -2,7 +2,9 @@
 // jssp/models/gnn_dgl.py:366-399 / psp/models/gnn_flat.py:170-253 issued from ONE C-ABI call per pass.
 // Host code plus two small glue kernels; every heavy launch is one of the library's own entry points
 // (b200gat_gemm_tf32, b200gat_conv_fwd/bwd, b200gat_mlp_fwd/bwd, b200gat_colsum).
+#include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include "common.cuh"
 
 namespace b200gat {
@@ -32,6 +34,49 @@ __global__ void __launch_bounds__(256) k_add2(const float4* __restrict__ a, cons
 }
 
 static inline int64_t up4(int64_t x) { return (x + 3) & ~3ll; }
+
+// Side stream of the backward pass.  The weight-gradient GEMMs (split-K over the node dimension + their reduce, 13 % of
+// the step's kernel time) feed nothing but the optimizer, so they are issued on a second stream, forked from and
+// joined back into the caller's stream with events: they run under the attention backward of the same layer, whose
+// clique kernels leave a third of the SMs idle in their last wave.  Works the same under CUDA graph capture (the
+// side stream joins the capture through the event).  One stream + four events per device, created on the first call
+// that is not being captured (creating them is not a capturable operation); B200GAT_DW_OVERLAP=0 disables it.
+struct Aux {
+  cudaStream_t s = nullptr;
+  cudaEvent_t m1 = nullptr, m2 = nullptr, a1 = nullptr, a2 = nullptr;
+  bool ok = false;
+};
+static Aux* aux_for(cudaStream_t main) {
+  static const bool enabled = [] {
+    const char* e = getenv("B200GAT_DW_OVERLAP");
+    return !(e && e[0] == '0');
+  }();
+  if (!enabled || timing_enabled()) return nullptr;      // per-class timing wants the serial order
+  constexpr int kMaxDev = 64;
+  static Aux aux[kMaxDev];
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return nullptr;
+  std::lock_guard<std::mutex> lk(mu);
+  Aux& a = aux[dev];
+  if (!a.ok) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(main, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
+    if (cudaStreamCreateWithFlags(&a.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    cudaEvent_t* ev[4] = {&a.m1, &a.m2, &a.a1, &a.a2};
+    for (auto e : ev)
+      if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    a.ok = true;
+  }
+  return &a;
+}
+// aux waits for everything queued on main so far / main waits for everything queued on aux so far
+static bool fork_to(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
+  return cudaEventRecord(ev, main) == cudaSuccess && cudaStreamWaitEvent(aux, ev, 0) == cudaSuccess;
+}
+static bool join_from(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
+  return cudaEventRecord(ev, aux) == cudaSuccess && cudaStreamWaitEvent(main, ev, 0) == cudaSuccess;
+}
 
 struct TrunkShape {
   int HD;
@@ -255,6 +300,15 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
   float* ws = gr->workspace;
   const int64_t N = t->n_nodes, HD = sh.HD, part = N * HD, n_in = N * t->in_dim;
   const float* Gy = gr->layer[t->n_layers - 1].g_y;          // total gradient of the current layer's output
+  Aux* aux = aux_for(st);
+  bool mlp_dw_pending = false, proj_dw_pending = false;      // side-stream work main has not waited for yet
+#define AUX_REQ(call)                                                        \
+  do {                                                                       \
+    if (!(call)) {                                                           \
+      set_error("b200gat_trunk_bwd: event fork / join failed: %s", cudaGetErrorString(cudaGetLastError()));  \
+      return B200GAT_ERR_CUDA;                                               \
+    }                                                                        \
+  } while (0)
   for (int l = t->n_layers - 1; l >= 0; --l) {
     const b200gat_trunk_layer& L = t->layer[l];
     const b200gat_trunk_layer_grads& G = gr->layer[l];
@@ -268,10 +322,22 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     memset(&mg, 0, sizeof(mg));
     mg.gy = Gy;
     mg.dx = ws + sh.o_gconv;
-    for (int i = 0; i < L.n_mlp; ++i) { mg.dW[i] = G.dW[i]; mg.db[i] = G.db[i]; }
     for (int i = 0; i < L.n_mlp - 1; ++i) mg.dz[i] = ws + sh.o_dz[i];
     mg.workspace = ws + sh.o_gemm; mg.workspace_elems = sh.gemm_elems;
-    if ((rc = b200gat_mlp_bwd(&m, &mg, stream))) return rc;
+    if (aux) {
+      // the chain below overwrites dz[] (read by the previous layer's MLP weight gradients on the side stream)
+      if (mlp_dw_pending) AUX_REQ(cudaStreamWaitEvent(st, aux->a1, 0) == cudaSuccess);
+      mlp_dw_pending = false;
+      if ((rc = b200gat_mlp_bwd(&m, &mg, stream))) return rc;             // input-gradient chain only
+      for (int i = 0; i < L.n_mlp; ++i) { mg.dW[i] = G.dW[i]; mg.db[i] = G.db[i]; }
+      AUX_REQ(fork_to(st, aux->s, aux->m1));
+      if ((rc = mlp_bwd_dw(&m, &mg, aux->s))) return rc;
+      AUX_REQ(cudaEventRecord(aux->a1, aux->s) == cudaSuccess);
+      mlp_dw_pending = true;
+    } else {
+      for (int i = 0; i < L.n_mlp; ++i) { mg.dW[i] = G.dW[i]; mg.db[i] = G.db[i]; }
+      if ((rc = b200gat_mlp_bwd(&m, &mg, stream))) return rc;
+    }
     const float* g_conv = ws + sh.o_gconv;
     if (G.g_out_bias && (rc = b200gat_colsum(g_conv, N, HD, HD, G.g_out_bias, ws + sh.o_colsum, stream))) return rc;
     // ---- fused attention backward: gPi | gPj | gV side by side
@@ -281,6 +347,9 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     const float* V = L.n_proj == 3 ? L.P + 2 * part : Pi;
     b200gat_attn a = L.attn;
     a.out_bias = nullptr;
+    // the attention backward overwrites gP (read by the previous layer's projection weight gradient)
+    if (proj_dw_pending) AUX_REQ(cudaStreamWaitEvent(st, aux->a2, 0) == cudaSuccess);
+    proj_dw_pending = false;
     if ((rc = b200gat_conv_bwd(t->graph, &a, &L.ef, Pi, Pj, V, L.s_save, L.m_save, L.l_save, L.agg_save, L.s_dense,
                                g_conv, gP, gP + part, L.n_proj == 3 ? gP + 2 * part : gP, G.g_attn, nullptr,
                                G.g_table, nullptr, G.g_affine, ws + sh.o_gs, stream)))
@@ -294,7 +363,14 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     proj_dw_desc(&g, t, sh, l, x, gP, G.dWp);
     g.workspace = ws + sh.o_gemm; g.workspace_elems = sh.gemm_elems;
     if (b200gat_gemm_workspace_elems(&g) > sh.gemm_elems) g.workspace = nullptr;
-    if ((rc = b200gat_gemm_tf32(&g, stream))) return rc;
+    if (aux) {
+      AUX_REQ(fork_to(st, aux->s, aux->m2));
+      if ((rc = b200gat_gemm_tf32(&g, aux->s))) return rc;
+      AUX_REQ(cudaEventRecord(aux->a2, aux->s) == cudaSuccess);
+      proj_dw_pending = true;
+    } else if ((rc = b200gat_gemm_tf32(&g, stream))) {
+      return rc;
+    }
     // ---- gradient of the layer's input = gP Wcat (+ residual path) (+ what reaches that tensor from outside)
     float* out = l > 0 ? ws + sh.o_G[(l - 1) & 1] : gr->g_x0;
     if (!out) break;
@@ -319,5 +395,9 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     if ((rc = b200gat_gemm_tf32(&g, stream))) return rc;
     Gy = out;
   }
+  // join: everything queued on the side stream precedes whatever the caller queues next
+  if (mlp_dw_pending) AUX_REQ(cudaStreamWaitEvent(st, aux->a1, 0) == cudaSuccess);
+  if (proj_dw_pending) AUX_REQ(cudaStreamWaitEvent(st, aux->a2, 0) == cudaSuccess);
+#undef AUX_REQ
   return B200GAT_OK;
 }
