@@ -217,12 +217,27 @@ extern "C" int b200gat_agent_bwd(const b200gat_agent_step* a, const b200gat_agen
   ga.gy = gya; ga.dx = ws + sh.o_dxa;
   for (int i = 0; i < a->action_net.n_layers - 1; ++i) ga.dz[i] = ws + sh.o_dz_a[i];
   ga.workspace = ws + sh.o_gemm; ga.workspace_elems = sh.gemm_elems;
-  if ((rc = b200gat_mlp_bwd(&a->action_net, &ga, stream))) return rc;
+  // weight gradients on the side stream (trunk.cu "Side stream of the backward pass"): input-gradient chain here,
+  // then the dW GEMMs over there, in the order of the calls (they share the split-K workspace)
+  AuxStream* aux = aux_stream_for(st);
+  auto mlp_bwd = [&](const b200gat_mlp* m, b200gat_mlp_grads* gr) -> int {
+    if (!aux) return b200gat_mlp_bwd(m, gr, stream);
+    b200gat_mlp_grads chain = *gr;
+    for (int i = 0; i < m->n_layers; ++i) { chain.dW[i] = nullptr; chain.db[i] = nullptr; }
+    int r = b200gat_mlp_bwd(m, &chain, stream);
+    if (r) return r;
+    if (!aux_fork(st, aux->s, aux->m1)) {
+      set_error("b200gat_agent_bwd: event fork failed: %s", cudaGetErrorString(cudaGetLastError()));
+      return B200GAT_ERR_CUDA;
+    }
+    return mlp_bwd_dw(m, gr, aux->s);
+  };
+  if ((rc = mlp_bwd(&a->action_net, &ga))) return rc;
   b200gat_mlp_grads gv = g->value_net;
   gv.gy = gyv; gv.dx = ws + sh.o_dxv;
   for (int i = 0; i < a->value_net.n_layers - 1; ++i) gv.dz[i] = ws + sh.o_dz_v[i];
   gv.workspace = ws + sh.o_gemm; gv.workspace_elems = sh.gemm_elems;
-  if ((rc = b200gat_mlp_bwd(&a->value_net, &gv, stream))) return rc;
+  if ((rc = mlp_bwd(&a->value_net, &gv))) return rc;
   // ---- readout backward: every source's gradient
   float* g_src[B200GAT_READOUT_MAX_SRC];
   for (int i = 0; i < B200GAT_READOUT_MAX_SRC; ++i) g_src[i] = nullptr;
@@ -256,7 +271,12 @@ extern "C" int b200gat_agent_bwd(const b200gat_agent_step* a, const b200gat_agen
     ge.gy = ws + sh.o_gx0;
     for (int i = 0; i < a->embedder.n_layers - 1; ++i) ge.dz[i] = ws + sh.o_dz_e[i];
     ge.workspace = ws + sh.o_gemm; ge.workspace_elems = sh.gemm_elems;
-    if ((rc = b200gat_mlp_bwd(&a->embedder, &ge, stream))) return rc;
+    if ((rc = mlp_bwd(&a->embedder, &ge))) return rc;
+  }
+  // everything queued on the side stream precedes whatever the caller queues next
+  if (aux && !aux_join(st, aux->s, aux->a1)) {
+    set_error("b200gat_agent_bwd: event join failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return B200GAT_ERR_CUDA;
   }
   return B200GAT_OK;
 }

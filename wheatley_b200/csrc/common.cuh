@@ -28,6 +28,16 @@ bool timing_enabled();     // b200gat_timing_enable(1) is in effect
 // issue them on a side stream.
 int mlp_bwd_dw(const b200gat_mlp* m, const b200gat_mlp_grads* gr, void* stream);
 
+// Side stream for work that only produces parameter gradients (trunk.cu has the definition and the rationale).
+struct AuxStream {
+  cudaStream_t s = nullptr;
+  cudaEvent_t m1 = nullptr, m2 = nullptr, a1 = nullptr, a2 = nullptr;   // recorded on main (m*) / on the side stream (a*)
+  bool ok = false;
+};
+AuxStream* aux_stream_for(cudaStream_t main);                           // NULL: run everything on `main`
+bool aux_fork(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev);     // aux waits for what main has queued so far
+bool aux_join(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev);     // main waits for what aux has queued so far
+
 #define B200_CHECK_ARG(cond, msg)                       \
   do {                                                  \
     if (!(cond)) {                                      \

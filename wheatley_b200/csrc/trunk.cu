@@ -35,30 +35,26 @@ __global__ void __launch_bounds__(256) k_add2(const float4* __restrict__ a, cons
 
 static inline int64_t up4(int64_t x) { return (x + 3) & ~3ll; }
 
-// Side stream of the backward pass.  The weight-gradient GEMMs (split-K over the node dimension + their reduce, 13 % of
-// the step's kernel time) feed nothing but the optimizer, so they are issued on a second stream, forked from and
-// joined back into the caller's stream with events: they run under the attention backward of the same layer, whose
-// clique kernels leave a third of the SMs idle in their last wave.  Works the same under CUDA graph capture (the
-// side stream joins the capture through the event).  One stream + four events per device, created on the first call
-// that is not being captured (creating them is not a capturable operation); B200GAT_DW_OVERLAP=0 disables it.
-struct Aux {
-  cudaStream_t s = nullptr;
-  cudaEvent_t m1 = nullptr, m2 = nullptr, a1 = nullptr, a2 = nullptr;
-  bool ok = false;
-};
-static Aux* aux_for(cudaStream_t main) {
+// Side stream of the backward pass (declared in common.cuh, shared with agent.cu).  The weight-gradient GEMMs (split-K
+// over the node dimension + their reduce, 13 % of the step's kernel time) feed nothing but the optimizer, so they are
+// issued on a second stream, forked from and joined back into the caller's stream with events: they run under the
+// attention backward of the same layer, whose clique kernels leave a third of the SMs idle in their last wave.  Works
+// the same under CUDA graph capture (the side stream joins the capture through the event).  One stream + four events
+// per device, created on the first call that is not being captured (creating them is not a capturable operation);
+// B200GAT_DW_OVERLAP=0 disables it.
+AuxStream* aux_stream_for(cudaStream_t main) {
   static const bool enabled = [] {
     const char* e = getenv("B200GAT_DW_OVERLAP");
     return !(e && e[0] == '0');
   }();
   if (!enabled || timing_enabled()) return nullptr;      // per-class timing wants the serial order
   constexpr int kMaxDev = 64;
-  static Aux aux[kMaxDev];
+  static AuxStream aux[kMaxDev];
   static std::mutex mu;
   int dev = -1;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return nullptr;
   std::lock_guard<std::mutex> lk(mu);
-  Aux& a = aux[dev];
+  AuxStream& a = aux[dev];
   if (!a.ok) {
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(main, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
@@ -70,11 +66,10 @@ static Aux* aux_for(cudaStream_t main) {
   }
   return &a;
 }
-// aux waits for everything queued on main so far / main waits for everything queued on aux so far
-static bool fork_to(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
+bool aux_fork(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
   return cudaEventRecord(ev, main) == cudaSuccess && cudaStreamWaitEvent(aux, ev, 0) == cudaSuccess;
 }
-static bool join_from(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
+bool aux_join(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev) {
   return cudaEventRecord(ev, aux) == cudaSuccess && cudaStreamWaitEvent(main, ev, 0) == cudaSuccess;
 }
 
@@ -300,7 +295,7 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
   float* ws = gr->workspace;
   const int64_t N = t->n_nodes, HD = sh.HD, part = N * HD, n_in = N * t->in_dim;
   const float* Gy = gr->layer[t->n_layers - 1].g_y;          // total gradient of the current layer's output
-  Aux* aux = aux_for(st);
+  AuxStream* aux = aux_stream_for(st);
   bool mlp_dw_pending = false, proj_dw_pending = false;      // side-stream work main has not waited for yet
 #define AUX_REQ(call)                                                        \
   do {                                                                       \
@@ -330,7 +325,7 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
       mlp_dw_pending = false;
       if ((rc = b200gat_mlp_bwd(&m, &mg, stream))) return rc;             // input-gradient chain only
       for (int i = 0; i < L.n_mlp; ++i) { mg.dW[i] = G.dW[i]; mg.db[i] = G.db[i]; }
-      AUX_REQ(fork_to(st, aux->s, aux->m1));
+      AUX_REQ(aux_fork(st, aux->s, aux->m1));
       if ((rc = mlp_bwd_dw(&m, &mg, aux->s))) return rc;
       AUX_REQ(cudaEventRecord(aux->a1, aux->s) == cudaSuccess);
       mlp_dw_pending = true;
@@ -364,7 +359,7 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     g.workspace = ws + sh.o_gemm; g.workspace_elems = sh.gemm_elems;
     if (b200gat_gemm_workspace_elems(&g) > sh.gemm_elems) g.workspace = nullptr;
     if (aux) {
-      AUX_REQ(fork_to(st, aux->s, aux->m2));
+      AUX_REQ(aux_fork(st, aux->s, aux->m2));
       if ((rc = b200gat_gemm_tf32(&g, aux->s))) return rc;
       AUX_REQ(cudaEventRecord(aux->a2, aux->s) == cudaSuccess);
       proj_dw_pending = true;
