@@ -400,7 +400,9 @@ def run_b200(args):
         l0 = _lib.launch_count()
         total = 0.0
         evs, host_ms = [], []
-        allocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+        ms0 = torch.cuda.memory_stats(dev)
+        allocs0, frees0 = ms0.get("num_device_alloc", 0), ms0.get("num_device_free", 0)
+        reserved0 = torch.cuda.memory_reserved(dev)
         for _ in range(steps):
             flush.zero_()                                  # L2 flush, outside the event pair
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -424,7 +426,10 @@ def run_b200(args):
                              "max_at_step": imax, "host_ms_of_that_step": host_ms[imax],
                              "host_ms_median": sorted(host_ms)[len(host_ms) // 2],
                              "cudaMalloc_calls_in_timed_region":
-                                 torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - allocs0}
+                                 torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - allocs0,
+                             "cudaFree_calls_in_timed_region":
+                                 torch.cuda.memory_stats(dev).get("num_device_free", 0) - frees0,
+                             "reserved_mib_start_end": [reserved0 >> 20, torch.cuda.memory_reserved(dev) >> 20]}
         total = sum(per_step)
         launches = _lib.launch_count() - l0
         t = torch.tensor([total], device=dev, dtype=torch.float64)

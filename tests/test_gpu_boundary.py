@@ -74,3 +74,42 @@ def test_inplace_residual_add_on_the_layer_output(wb):
     out += R                                             # in place, like the reference
     out.square().sum().backward()
     assert torch.allclose(xa.grad, xb.grad, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("flavour", ["jssp", "psp"])
+def test_batches_are_freed_by_reference_counting(flavour):
+    """No reference cycle through a batch, its plan and the plan's clique view: dropping the last reference frees the
+    device tensors at once.  (A plan <-> view cycle and ``PspGraphData._graph = self`` used to leave every minibatch
+    to the cyclic garbage collector: the caching allocator grew by ~3 MiB per step and stalled for 10-200 ms whenever a
+    late collection returned the lot.)"""
+    import gc
+    import weakref
+    if flavour == "jssp":
+        from wheatley_b200.batch import jssp_batch_from_observation
+        from wheatley_b200.workload import jssp_observation_batch
+        obs = jssp_observation_batch(10, 4, 3, seed0=0, progress=0.3)
+
+        def build():
+            jb, _ = jssp_batch_from_observation(obs, "cuda", 40, conflicts="clique", graph_pooling="learn")
+            return jb, jb.plan
+    else:
+        from wheatley_b200.psp_batch import preprocess
+        from wheatley_b200.wire import PspArena
+        from wheatley_b200.workload import psp_taillard_graph
+        arena = PspArena.from_graphs([psp_taillard_graph(4, 4, b, progress=0.0) for b in range(8)])
+
+        def build():
+            tup = preprocess(arena, "cuda", conflicts="clique", graph_pooling="learn")
+            return tup, tup[0].plan
+    build()                                   # warm caches (library handles, allocator)
+    gc.collect()
+    gc.disable()
+    try:
+        holder, plan = build()
+        view = plan.clique_view(plan.sort_edge_ints(torch.zeros(plan.n_edges, dtype=torch.int64, device="cuda")))
+        refs = [weakref.ref(plan), weakref.ref(view), weakref.ref(plan.in_ptr)]
+        assert view.plan is plan
+        del holder, plan, view
+        assert all(r() is None for r in refs), [type(r()).__name__ for r in refs if r() is not None]
+    finally:
+        gc.enable()
