@@ -588,13 +588,14 @@ int win_set_smem(size_t bytes) {
 }
 
 // Resident CTAs per SM the forward / by-source kernels are built for: 2 (128 registers, two edges in flight) or
-// 3 (80 registers, one edge in flight).  B200GAT_WIN_OCC overrides.
-int win_occ() {
-  static const int occ = [] {
+// 3 (80 registers, one edge in flight).  B200GAT_WIN_OCC=2|3 overrides.
+int win_occ(int vpl) {
+  static const int forced = [] {
     const char* e = getenv("B200GAT_WIN_OCC");
-    return e && atoi(e) == 3 ? 3 : 2;
+    return e ? atoi(e) : 0;
   }();
-  return occ;
+  if (forced == 2 || forced == 3) return forced;
+  return vpl <= 4 ? 3 : 2;      // H*D <= 128: 80 registers hold a row pair without spills (psp272: 2.92 vs 3.00 ms)
 }
 
 }  // namespace
@@ -617,7 +618,7 @@ bool win_enabled(const FastArgs& A) {
 int win_fwd(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, const float* Pj, const float* V,
             float* out, float* s_save, float* m_save, float* l_save, float* agg_save, cudaStream_t st) {
   const size_t smem = sizeof(float) * (size_t)(alias ? 1 : 2) * kWinW * 32 * vpl;
-  const int occ = win_occ();
+  const int occ = win_occ(vpl);
   const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
@@ -666,7 +667,7 @@ int win_bwd_dst(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
 int win_bwd_src(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, const float* Pj, const float* G,
                 const float* gs_in, const float* alpha_in, float* gPi, float* gV, cudaStream_t st) {
   const size_t smem = sizeof(float) * (size_t)2 * kWinW * 32 * vpl;
-  const int occ = win_occ();
+  const int occ = win_occ(vpl);
   const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
