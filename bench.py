@@ -517,7 +517,8 @@ def run_b200(args):
     # pinned host memory and reads ITS loss back, but the copy + plan build of step i+1 are queued on a side
     # stream while step i trains (the copy engine and the plan kernels run under the step's kernels, and the
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
-    pf = BatchPrefetcher(dev, side_stream=os.environ.get("BENCH_PREFETCH_SIDE_STREAM", "0") == "1")
+    SIDE = os.environ.get("BENCH_PREFETCH_SIDE_STREAM", "1") == "1"     # measured: 4.75 (side stream) vs 5.23 ms
+    pf = BatchPrefetcher(dev, side_stream=SIDE)
     DEPTH = 2                      # batches / loss reads in flight: the launch thread may run two steps ahead of the
     for _ in range(DEPTH):         # GPU, so a short stall of the (shared) host does not idle the device
         submit(pf)
@@ -709,8 +710,10 @@ def run_b200(args):
                                  "spread shown)",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "input": input_note,
-                    "pipeline": "wheatley_b200.prefetch.BatchPrefetcher: step i+1's host->device copy, batch and "
-                                "plan build are queued ahead of step i's kernels; every timed step copies its inputs "
+                    "pipeline": "wheatley_b200.prefetch.BatchPrefetcher(side_stream=%s): step i+1's host->device "
+                                "copy, batch and plan build are queued %s; every timed step copies its inputs "
+                                % (SIDE, "on a side stream and run under step i's kernels" if SIDE
+                                   else "ahead of step i's kernels on the same stream") +
                                 "from pinned host memory and reads its loss back (wheatley_b200.prefetch.HostReadback: "
                                 "asynchronous copy into pinned memory, consumed one step later, so the launch thread "
                                 "never waits on the GPU; ms_per_step_no_prefetch is the serial loop with loss.item())",

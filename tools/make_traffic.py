@@ -6,7 +6,8 @@ made with other kernels (a committed constant goes stale silently).
 import hashlib, json, os, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-KERNEL_SOURCES = ("gat_fast.cu", "gat_clique.cu", "gat_generic.cu", "gat_api.cu", "gat_kernels.cuh", "common.cuh")
+KERNEL_SOURCES = ("gat_fast.cu", "gat_win.cuh", "gat_rows.cuh", "gat_clique.cu", "gat_generic.cu", "gat_api.cu",
+                  "gat_kernels.cuh", "common.cuh")
 
 
 def kernel_source_sha():

@@ -45,7 +45,10 @@ def launches(path):
         u = row["Metric Unit"]
         v = v / 1e3 if u == "ns" else v * 1e3 if u == "ms" else v
         name = re.sub(r"^void ", "", row["Kernel Name"])
-        name = re.sub(r"[<(].*", "", name)[:72]
+        name = name.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
+        m = re.match(r"(b200gat::k_\w+)(<[^>]*>)?", name)        # template arguments kept for our kernels (tile shapes)
+        name = (m.group(1) + (m.group(2) or "")) if m else re.sub(r"[<(].*", "", name)
+        name = name[:72]
         tot[name] += v
         cnt[name] += 1
     T = sum(tot.values())
