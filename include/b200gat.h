@@ -106,6 +106,9 @@ typedef struct b200gat_graph_s {
   /* Optional scratch for splitting hub destinations over several CTAs: hub_cap * hub_parts records   */
   /* of (256 + 64) floats; used when the device-side hub count fits hub_cap, ignored (NULL/0) else.   */
   /* One conv call at a time may use a graph's scratch (single-stream use, like the reference).       */
+  /* With flag B200GAT_GRAPH_HUB_COUNTERS the records are followed by hub_cap int32 arrival counters, ZERO when a conv */
+  /* call starts (the kernels leave them at zero): the slice that arrives last merges its hub inside the kernel       */
+  /* instead of a merge launch of its own.                                                                             */
   float* hub_scratch;
   int32_t hub_parts;
   int32_t hub_cap;
@@ -122,6 +125,8 @@ typedef struct b200gat_graph_s {
   int32_t flags;
 } b200gat_graph;
 #define B200GAT_GRAPH_LOW_DEGREE 1
+#define B200GAT_GRAPH_HUB_COUNTERS 2
+#define B200GAT_HUB_RECORD (256 + 64)   /* floats per hub_scratch record */
 
 /* ------------------------------------------------------------------ clique blocks
  * Machine-conflict cliques (jssp/utils/utils.py:460-478; psp/utils/utils.py:62-92) are complete

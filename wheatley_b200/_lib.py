@@ -12,7 +12,7 @@ EDGE_NONE, EDGE_TABLE, EDGE_DENSE, EDGE_AFFINE = 0, 1, 2, 3
 MAX_ATTR = 8
 HUB_DEGREE = 256
 HUB_PARTS = 16        # CTAs a hub destination's in-edges are split over
-GRAPH_LOW_DEGREE = 1  # b200gat_graph.flags
+GRAPH_LOW_DEGREE, GRAPH_HUB_COUNTERS = 1, 2  # b200gat_graph.flags
 LOW_DEGREE_MAX = 32   # longest non-hub adjacency list of a graph flagged GRAPH_LOW_DEGREE
 HUB_REC = 256 + 64    # floats per partial record (include/b200gat.h)
 FLAVOUR_ADDITIVE, FLAVOUR_DOT = 0, 1

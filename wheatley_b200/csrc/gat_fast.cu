@@ -148,6 +148,8 @@ __device__ __forceinline__ void fwd_fast_cta(
         rec[HD + lane] = m;
         rec[HD + 32 + lane] = l;
         finalize = false;
+        if (A.hub_cnt && hub_arrive(A, item / P, P, lane))
+          hub_merge_fwd_one<VPL, LPH>(A, item / P, P, lane, out, m_save, l_save, agg_save);
       }
     }
     if (finalize)
@@ -169,31 +171,10 @@ __global__ void __launch_bounds__(kFastThreads) k_hub_merge_fwd(FastArgs A, floa
                                                                 float* __restrict__ m_save,
                                                                 float* __restrict__ l_save,
                                                                 float* __restrict__ agg_save) {
-  constexpr int HD = 32 * VPL;
   const int n_hub = *A.n_hub_dst, P = hub_parts_of(A, n_hub);
   const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (P == 1 || w >= n_hub) return;
-  const int c0 = lane * VPL, h = lane / LPH;
-  const int v = A.hub_dst[w];
-  const float* rec0 = A.hub_scratch + (int64_t)w * P * (HD + kHubRec);
-  float M = -INFINITY;
-#pragma unroll 8
-  for (int p = 0; p < P; ++p) M = fmaxf(M, rec0[(int64_t)p * (HD + kHubRec) + HD + lane]);
-  float acc[VPL], l = 0.f;
-#pragma unroll
-  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
-#pragma unroll 4                         // four slices' loads in flight: one warp per hub, pure latency
-  for (int p = 0; p < P; ++p) {
-    const float* rec = rec0 + (int64_t)p * (HD + kHubRec);
-    const float mp = rec[HD + lane];
-    const float f = mp == -INFINITY ? 0.f : __expf(mp - M);  // empty slice
-    l = fmaf(rec[HD + 32 + lane], f, l);
-    float pa[VPL];
-    ldrow<VPL>(pa, rec + c0);
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) acc[i] = fmaf(pa[i], f, acc[i]);
-  }
-  fwd_finalize<VPL>(A, v, true, acc, M, l, c0, h, (lane % LPH) == 0, out, m_save, l_save, agg_save);
+  hub_merge_fwd_one<VPL, LPH>(A, w, P, lane, out, m_save, l_save, agg_save);
 }
 
 // ------------------------------------------------------------------------------ backward, by destination
@@ -366,8 +347,12 @@ __device__ __forceinline__ void bwd_dst_fast_cta(
 #pragma unroll
           for (int i = 0; i < VPL; ++i) gpj[i] += sm_part[w2][c0 + i];
         }
-        if (P > 1) strow<VPL>(A.hub_scratch + (int64_t)item * (HD + kHubRec) + c0, gpj);   // slice partial
-        else strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
+        if (P > 1) {
+          strow<VPL>(A.hub_scratch + (int64_t)item * (HD + kHubRec) + c0, gpj);               // slice partial
+          if (A.hub_cnt && hub_arrive(A, item / P, P, lane)) hub_merge_bwd_one<VPL>(A, item / P, P, lane, gPj);
+        } else {
+          strow<VPL>(gPj + (int64_t)v * HD + c0, gpj);
+        }
       }
       __syncthreads();
     } else if (it.active) {
@@ -416,22 +401,10 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
 // Sum the partial d Pj rows of the slices of each split hub (in slice order).
 template <int VPL>
 __global__ void __launch_bounds__(kFastThreads) k_hub_merge_bwd(FastArgs A, float* __restrict__ gPj) {
-  constexpr int HD = 32 * VPL;
   const int n_hub = *A.n_hub_dst, P = hub_parts_of(A, n_hub);
   const int w = (blockIdx.x * kFastThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (P == 1 || w >= n_hub) return;
-  const int c0 = lane * VPL;
-  float acc[VPL];
-#pragma unroll
-  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
-#pragma unroll 4
-  for (int p = 0; p < P; ++p) {
-    float pa[VPL];
-    ldrow<VPL>(pa, A.hub_scratch + ((int64_t)w * P + p) * (HD + kHubRec) + c0);
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) acc[i] += pa[i];
-  }
-  strow<VPL>(gPj + (int64_t)A.hub_dst[w] * HD + c0, acc);
+  hub_merge_bwd_one<VPL>(A, w, P, lane, gPj);
 }
 
 // ------------------------------------------------------------------------------ backward, by source
@@ -586,6 +559,9 @@ static int fill_fast(FastArgs& A, const b200gat_graph* g, const b200gat_attn* a,
   A.hub_dst = g->hub_dst; A.n_hub_dst = g->n_hub_dst; A.hub_src = g->hub_src; A.n_hub_src = g->n_hub_src;
   A.hub_degree = g->hub_degree; A.hub_blocks = 0;
   A.hub_scratch = g->hub_scratch; A.hub_parts = g->hub_parts; A.hub_cap = g->hub_cap;
+  A.hub_cnt = (g->hub_scratch && (g->flags & B200GAT_GRAPH_HUB_COUNTERS) && g->hub_parts > 1 && g->hub_cap > 0)
+                  ? reinterpret_cast<int*>(g->hub_scratch + (int64_t)g->hub_cap * g->hub_parts * B200GAT_HUB_RECORD)
+                  : nullptr;
   A.H = a->heads; A.slope = a->slope; A.eps = a->softmax_eps; A.attn = a->attn; A.out_bias = a->out_bias;
   A.emode = ef ? ef->mode : B200GAT_EDGE_NONE;
   A.T = ef ? ef->n_types : 0; A.K = ef ? ef->n_attr : 0;
@@ -627,7 +603,7 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
                                                                                 l_save, agg_save)));
     B200_CHECK_LAUNCH("k_fwd_fast");
   }
-  if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
+  if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0 && !A.hub_cnt) {
     const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
     switch (vpl) {
       case 2: FAST_DISPATCH_LPH(2, lph, false, (k_hub_merge_fwd<VPL, LPH><<<mb, kFastThreads, 0, st>>>(A, out, m_save, l_save, agg_save))) break;
@@ -691,7 +667,7 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
                         gs, alpha, tab_in_smem, aff_in_smem)));
       note_launch(1);
     }
-    if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0) {
+    if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0 && !A.hub_cnt) {
       const unsigned mb = (unsigned)ceil_div((int64_t)A.hub_cap * 32, kFastThreads);
       if (vpl == 2) k_hub_merge_bwd<2><<<mb, kFastThreads, 0, st>>>(A, gPj);
       else if (vpl == 4) k_hub_merge_bwd<4><<<mb, kFastThreads, 0, st>>>(A, gPj);

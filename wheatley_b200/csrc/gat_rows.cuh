@@ -17,6 +17,7 @@ struct FastArgs {
   int hub_degree, hub_blocks;   // hub_blocks = 0 disables segment splitting
   float* hub_scratch;           // [hub_cap][hub_parts][HD + 64] partial states of split hub segments, or NULL
   int hub_parts, hub_cap;
+  int* hub_cnt;                 // [hub_cap] arrival counters of the slices (zero between launches), or NULL
   int H;
   float slope, eps;
   const float *attn, *out_bias;
@@ -56,6 +57,21 @@ __device__ __forceinline__ void ldrow_s(float (&r)[VPL], const float* p) {     /
     r[0] = a.x; r[1] = a.y;
   } else {
     r[0] = p[0];
+  }
+}
+template <int VPL>
+__device__ __forceinline__ void ldrow_cg(float (&r)[VPL], const float* p) {    // L2-coherent (written by other CTAs)
+  if constexpr (VPL == 8) {
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(p)), b = __ldcg(reinterpret_cast<const float4*>(p) + 1);
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+  } else if constexpr (VPL == 4) {
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(p));
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+  } else if constexpr (VPL == 2) {
+    const float2 a = __ldcg(reinterpret_cast<const float2*>(p));
+    r[0] = a.x; r[1] = a.y;
+  } else {
+    r[0] = __ldcg(p);
   }
 }
 template <int VPL>
@@ -189,6 +205,67 @@ __device__ __forceinline__ void fwd_finalize(const FastArgs& A, int v, bool any,
     m_save[(int64_t)v * A.H + h] = any ? m : 0.f;
     l_save[(int64_t)v * A.H + h] = l;
   }
+}
+
+// Merge of the slices of split hub `w` (its index in the hub list), by ONE warp, in slice order (so the result does
+// not depend on which CTA runs it): the last slice to arrive (hub_arrive) does it inside the hub CTA; without arrival
+// counters the k_hub_merge_* kernels do it in a launch of their own.
+template <int VPL, int LPH>
+__device__ __forceinline__ void hub_merge_fwd_one(const FastArgs& A, int w, int P, int lane, float* __restrict__ out,
+                                                  float* __restrict__ m_save, float* __restrict__ l_save,
+                                                  float* __restrict__ agg_save) {
+  constexpr int HD = 32 * VPL;
+  const int c0 = lane * VPL, h = lane / LPH;
+  const int v = A.hub_dst[w];
+  const float* rec0 = A.hub_scratch + (int64_t)w * P * (HD + kHubRec);
+  float M = -INFINITY;
+#pragma unroll 8
+  for (int p = 0; p < P; ++p) M = fmaxf(M, __ldcg(rec0 + (int64_t)p * (HD + kHubRec) + HD + lane));
+  float acc[VPL], l = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+#pragma unroll 4                         // four slices' loads in flight: one warp per hub, pure latency
+  for (int p = 0; p < P; ++p) {
+    const float* rec = rec0 + (int64_t)p * (HD + kHubRec);
+    const float mp = __ldcg(rec + HD + lane);
+    const float f = mp == -INFINITY ? 0.f : __expf(mp - M);  // empty slice
+    l = fmaf(__ldcg(rec + HD + 32 + lane), f, l);
+    float pa[VPL];
+    ldrow_cg<VPL>(pa, rec + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] = fmaf(pa[i], f, acc[i]);
+  }
+  fwd_finalize<VPL>(A, v, true, acc, M, l, c0, h, (lane % LPH) == 0, out, m_save, l_save, agg_save);
+}
+template <int VPL>
+__device__ __forceinline__ void hub_merge_bwd_one(const FastArgs& A, int w, int P, int lane, float* __restrict__ gPj) {
+  constexpr int HD = 32 * VPL;
+  const int c0 = lane * VPL;
+  float acc[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+#pragma unroll 4
+  for (int p = 0; p < P; ++p) {
+    float pa[VPL];
+    ldrow_cg<VPL>(pa, A.hub_scratch + ((int64_t)w * P + p) * (HD + kHubRec) + c0);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] += pa[i];
+  }
+  strow<VPL>(gPj + (int64_t)A.hub_dst[w] * HD + c0, acc);
+}
+// Called by warp 0 of a hub CTA after it has parked the partial of one slice of hub `w`: true (for the whole warp) in
+// the warp whose slice arrived last.  The counter is back at zero when the kernel ends.
+__device__ __forceinline__ bool hub_arrive(const FastArgs& A, int w, int P, int lane) {
+  __threadfence();                       // the partial is visible device-wide before the arrival is
+  __syncwarp();
+  int last = 0;
+  if (lane == 0) {
+    last = atomicAdd(A.hub_cnt + w, 1) == P - 1;
+    if (last) A.hub_cnt[w] = 0;
+  }
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (last) __threadfence();             // the other slices' partials are read after their arrivals were seen
+  return last != 0;
 }
 
 // Template dispatch on (VPL, LPH, ALIAS).

@@ -51,8 +51,11 @@ def _attach_hub_scratch(g, n_hub_dst, dev):
     """Scratch for splitting each hub destination over HUB_PARTS CTAs (include/b200gat.h)."""
     if n_hub_dst <= 0:
         return None
-    scratch = torch.empty(n_hub_dst * _lib.HUB_PARTS * _lib.HUB_REC, dtype=torch.float32, device=dev)
+    n_rec = n_hub_dst * _lib.HUB_PARTS * _lib.HUB_REC
+    scratch = torch.empty(n_rec + n_hub_dst, dtype=torch.float32, device=dev)
+    scratch[n_rec:].zero_()                 # the slices' arrival counters (int32 zeros; the kernels leave them at zero)
     g.hub_scratch, g.hub_parts, g.hub_cap = scratch.data_ptr(), _lib.HUB_PARTS, n_hub_dst
+    g.flags |= _lib.GRAPH_HUB_COUNTERS
     return scratch
 
 
