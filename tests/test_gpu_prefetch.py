@@ -133,3 +133,52 @@ def test_flat_adam_on_the_agent_matches_torch_adam(wb):
                 assert float((p - q).abs().max()) <= 1e-6 * max(float(q.abs().max()), 1e-3), (it, k)
     finally:
         torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def test_psp_batches_prefetched_on_the_side_stream_train_identically(wb):
+    """PSP arenas through ``submit_psp`` on the side stream, two batches in flight, graphs whose pool node is a hub
+    (> 256 in-edges: the split-hub path with its zero-filled arrival counters, which ``plan.finish()`` queues on the
+    side stream after the event recorded at submit time): the losses equal those of batches built directly on the
+    main stream, bit for bit (the forward is deterministic), step after step."""
+    from wheatley_b200.agent import PspAgent
+    from wheatley_b200.prefetch import BatchPrefetcher
+    from wheatley_b200.wire import PspArena
+    from wheatley_b200.workload import psp_taillard_graph
+    n_j, n_m, B, steps = 20, 15, 2, 6
+    arenas = [PspArena.from_graphs([psp_taillard_graph(n_j, n_m, 10 * s + b, progress=0.0) for b in range(B)])
+              for s in range(steps)]
+    max_n = n_j * n_m + 2
+    torch.manual_seed(0)
+    agent = PspAgent(max_n, n_m, hidden_dim=64, n_layers=2, conflicts="node").cuda()
+    g = torch.Generator().manual_seed(3)
+    masks = torch.rand(B, max_n, generator=g) < 0.3
+    masks[:, 0] = True
+    extras = dict(masks=masks, action=torch.multinomial(masks.float(), 1, generator=g).squeeze(1),
+                  adv=torch.randn(B, generator=g), ret=torch.randn(B, generator=g),
+                  old_lp=-torch.rand(B, generator=g) - 4.0, old_v=torch.randn(B, generator=g))
+    extras = {k: v.contiguous().pin_memory() for k, v in extras.items()}
+    kw = dict(clip_coef=0.2, norm_adv=True, critic_loss="l2", ent_coef=0.05, vf_coef=0.5)
+
+    def step(obs, d):
+        for p in agent.parameters():
+            p.grad = None
+        loss, _ = agent.ppo_minibatch(obs, d["action"], d["masks"], d["old_lp"], d["adv"], d["ret"], d["old_v"], **kw)
+        loss.backward()
+        return loss.detach().clone()
+
+    dd = {k: v.cuda() for k, v in extras.items()}
+    direct = [step(agent.preprocess(a), dd) for a in arenas]
+    torch.cuda.synchronize()
+    assert direct[0].isfinite() and agent.preprocess(arenas[0])[0].plan.stats_host()[1] > 256       # a hub
+    pf = BatchPrefetcher("cuda:0", side_stream=True)
+    pf.submit_psp(agent, arenas[0], extras)
+    pf.submit_psp(agent, arenas[1], extras)
+    piped = []
+    for i in range(steps):
+        d, _ = pf.get()
+        if i + 2 < steps:
+            pf.submit_psp(agent, arenas[i + 2], extras)
+        piped.append(step(d["batch"], d))                   # no sync between the steps
+    torch.cuda.synchronize()
+    for a, b in zip(direct, piped):
+        assert torch.equal(a, b), (float(a), float(b))

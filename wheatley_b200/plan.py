@@ -145,7 +145,10 @@ class CliqueView:
         with _lib.device_guard(dev):
             self._hub_scratch = _attach_hub_scratch(self._res_c, n_hub_dst, dev)
         # what is left outside the blocks of a schedule graph: self loops, job chains and the pool star (a hub)
-        if Er <= 8 * N and N >= 64:
+        # - provided the pool node IS a hub: with 100-225 in-edges (10x10, 15x15 graphs) it is neither short nor split,
+        # and one warp walking it two edges at a time is the kernel's tail (measured: 10x10 x 128 4.2 vs 3.6 ms)
+        full_max = max(plan._stats_host[1], plan._stats_host[3]) if plan._stats_host else 0
+        if Er <= 8 * N and N >= 64 and (full_max > _lib.HUB_DEGREE or full_max <= _lib.LOW_DEGREE_MAX):
             self._res_c.flags |= _lib.GRAPH_LOW_DEGREE
         self._cl = _lib.Cliques(self.n_blocks, self.max_block, self.n_members, self.s_elems,
                                 _lib.ptr(self.blk_ptr), _lib.ptr(self.blk_nodes), _lib.ptr(self.blk_type),

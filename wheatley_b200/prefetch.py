@@ -34,6 +34,29 @@ from . import _lib
 from .plan import GraphPlan
 
 
+def _cuda_tensors(obj):
+    """Every CUDA tensor reachable from ``obj`` through lists, tuples, dicts and plain objects (``JsspBatch``,
+    ``PspGraphData``, ``GraphPlan``, ``CliqueView`` ...): what must be handed to ``Tensor.record_stream`` when a
+    batch built on the side stream is used on another one."""
+    seen, out, stack = set(), [], [obj]
+    while stack:
+        o = stack.pop()
+        if id(o) in seen or o is None or isinstance(o, (int, float, str, bytes, bool, torch.nn.Module)):
+            continue
+        seen.add(id(o))
+        if isinstance(o, torch.Tensor):
+            if o.is_cuda:
+                out.append(o)
+                stack.extend(v for v in getattr(o, "__dict__", {}).values() if isinstance(v, torch.Tensor))
+        elif isinstance(o, (list, tuple, set)):
+            stack.extend(o)
+        elif isinstance(o, dict):
+            stack.extend(o.values())
+        elif hasattr(o, "__dict__") and type(o).__module__.startswith("wheatley_b200"):
+            stack.extend(vars(o).values())
+    return out
+
+
 class BatchPrefetcher:
     def __init__(self, device, src_key="src", dst_key="dst", etype_key="etype", side_stream=False):
         # (a worker thread for the submissions was tried: the step's own launches and the worker's contend for
@@ -106,12 +129,13 @@ class BatchPrefetcher:
             return d, plan
         main = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self.side):
-            plan.finish()               # allocations stay on the side pool
+            plan.finish()               # allocations stay on the side pool; zero-fills the hub arrival counters
+            done = torch.cuda.Event()   # (a kernel queued AFTER the event of submit time)
+            done.record()
         main.wait_event(done)
         # the tensors were allocated on the side stream's pool and are used (and eventually freed) on `main`
-        for t in list(d.values()) + plan.tensors():
-            if isinstance(t, torch.Tensor) and t.is_cuda:
-                t.record_stream(main)
+        for t in _cuda_tensors([d, plan]):
+            t.record_stream(main)
         return d, plan
 
 
