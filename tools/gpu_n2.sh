@@ -10,7 +10,5 @@ try:
 except Exception as ex: print('no json', ex)
 PY
 }
-run r2p_weak_n$N
-run r2p_strong30x20_n$N --scaling strong --workload taillard30x20 --graphs 128
-timeout 600 python bench.py --no-cpu-baseline --workload taillard30x20 --graphs-per-gpu 128 > gpurun_out/r2p_strong30x20_n1.json 2> gpurun_out/r2p_strong30x20_n1.err; python -c "
-import json; d=json.load(open('gpurun_out/r2p_strong30x20_n1.json')); print('n1 30x20x128 ms/step', round(d['ms_per_step'],3), 'value %.3e'%d['value'], 'e2e', round(d['e2e']['ms_per_step'],3))"
+run r2z_weak_n$N
+run r2z_strong30x20_n$N --scaling strong --workload taillard30x20 --graphs 128
