@@ -517,30 +517,47 @@ def run_b200(args):
     # pinned host memory and reads ITS loss back, but the copy + plan build of step i+1 are queued on a side
     # stream while step i trains (the copy engine and the plan kernels run under the step's kernels, and the
     # plan's device->host read of its counts no longer waits on an idle GPU).  K timed steps = K copies.
-    SIDE = os.environ.get("BENCH_PREFETCH_SIDE_STREAM", "1") == "1"     # measured: 4.75 (side stream) vs 5.23 ms
-    pf = BatchPrefetcher(dev, side_stream=SIDE)
-    DEPTH = 2                      # batches / loss reads in flight: the launch thread may run two steps ahead of the
-    for _ in range(DEPTH):         # GPU, so a short stall of the (shared) host does not idle the device
-        submit(pf)
-
     from wheatley_b200.prefetch import HostReadback
-    rb = HostReadback(depth=DEPTH + 1)
-    e2e_losses = []
+    DEPTH = 2                      # batches / loss reads in flight: the launch thread may run two steps ahead of the
+                                   # GPU, so a short stall of the (shared) host does not idle the device
 
-    def e2e_step():
-        d, _ = pf.get()
-        submit(pf)                                         # next step's inputs
-        rb.push(train_step(d["batch"], d))                 # device->host read of THIS step's loss, asynchronous
-        if len(rb) > DEPTH:
-            e2e_losses.append(float(rb.pop()))             # ... consumed DEPTH steps later (HostReadback)
-    ms_e2e_mean, _, _ = timed(e2e_step, max(3, args.steps), E2E_WARMUP)
-    e2e_spread = dict(timed.last_spread)
-    while len(rb):
-        e2e_losses.append(float(rb.pop()))
-    assert len(e2e_losses) == max(3, args.steps) + E2E_WARMUP and all(x == x for x in e2e_losses)   # every loss read
-    for _ in range(DEPTH):
-        pf.get()                                           # drain the unused prefetches
-    torch.cuda.synchronize()
+    def run_e2e(side):
+        pf = BatchPrefetcher(dev, side_stream=side)
+        for _ in range(DEPTH):
+            submit(pf)
+        rb = HostReadback(depth=DEPTH + 1)
+        losses = []
+
+        def e2e_step():
+            d, _ = pf.get()
+            submit(pf)                                         # next step's inputs
+            rb.push(train_step(d["batch"], d))                 # device->host read of THIS step's loss, asynchronous
+            if len(rb) > DEPTH:
+                losses.append(float(rb.pop()))                 # ... consumed DEPTH steps later (HostReadback)
+        mean, _, _ = timed(e2e_step, max(3, args.steps), E2E_WARMUP)
+        spread = dict(timed.last_spread)
+        while len(rb):
+            losses.append(float(rb.pop()))
+        assert len(losses) == max(3, args.steps) + E2E_WARMUP and all(x == x for x in losses)   # every loss read
+        for _ in range(DEPTH):
+            pf.get()                                           # drain the unused prefetches
+        torch.cuda.synchronize()
+        return mean, spread
+
+    # Placement of the prefetched copies / builds is the user's choice (BatchPrefetcher(side_stream=...)): on a side
+    # stream they run under the previous step's kernels (wins when the step is GPU-bound: 4.6 vs 5.2 ms at 8 x Taillard
+    # 100x20), at the price of record_stream bookkeeping per tensor on the host (loses when the loop is host-bound:
+    # 6.8 vs 5.6 ms at psp272).  Both are measured; the better one is the headline, both are reported.
+    forced = os.environ.get("BENCH_PREFETCH_SIDE_STREAM")
+    e2e_runs = {}
+    for side in ([forced == "1"] if forced in ("0", "1") else [False, True]):
+        e2e_runs[side] = run_e2e(side)
+    choice = torch.tensor([min(e2e_runs, key=lambda k: e2e_runs[k][0])], device=dev, dtype=torch.int32)
+    if world > 1:
+        dist.broadcast(choice, 0)                              # every rank reports the placement rank 0 picked
+    SIDE = bool(int(choice))
+    ms_e2e_mean, e2e_spread = e2e_runs[SIDE]
+    e2e_by_placement = {("side_stream" if k else "same_stream"): v[0] for k, v in e2e_runs.items()}
     # every step is bracketed by its own event pair: the headline is the MEAN over the timed steps; the median
     # (slowest rank's), min and max are reported beside it in ms_per_step_median / ms_per_step_spread
     t_med = torch.tensor([e2e_spread["median"]], device=dev, dtype=torch.float64)
@@ -717,7 +734,8 @@ def run_b200(args):
                                 "from pinned host memory and reads its loss back (wheatley_b200.prefetch.HostReadback: "
                                 "asynchronous copy into pinned memory, consumed one step later, so the launch thread "
                                 "never waits on the GPU; ms_per_step_no_prefetch is the serial loop with loss.item())",
-                    "ms_per_step_no_prefetch": ms_e2e_serial, "warmup_steps": E2E_WARMUP},
+                    "ms_per_step_no_prefetch": ms_e2e_serial, "ms_per_step_by_prefetch_placement": e2e_by_placement,
+                    "warmup_steps": E2E_WARMUP},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "ppo": {"env_steps_per_sec": float(ppo_all), "unit": "env-steps/s", "num_envs_per_gpu": B,
                     "minibatch_graphs": B, "n_epochs": n_epochs, "rollout_steps": T_roll,
