@@ -586,6 +586,8 @@ def run_b200(args):
             action, logprob, _, value, _ = agent.get_action_and_value(jb, None, masks_d)
         return action.cpu(), logprob, value.reshape(-1)
 
+    pf_upd = BatchPrefetcher(dev, side_stream=SIDE)      # update phase: the placement the e2e leg found better
+
     def ppo_iteration():
         lps, vals, acts, rews = [], [], [], []
         for _t in range(T_roll):
@@ -601,9 +603,14 @@ def run_b200(args):
         stop = False
         for _ep in range(n_epochs):
             kl = torch.zeros(1, device=dev)
-            for mb in torch.randperm(T_roll, generator=rng_env).tolist():
+            order = torch.randperm(T_roll, generator=rng_env).tolist()
+            submit(pf_upd)                                               # the epoch's first minibatch
+            for i, mb in enumerate(order):
+                d_mb, _ = pf_upd.get()
+                if i + 1 < len(order):
+                    submit(pf_upd)                                       # next minibatch's copies / batch / plan build
                 bucket.zero()
-                loss, stats = agent.ppo_minibatch(build_batch(), acts[mb], masks_d, lps[mb], adv[mb, :, 0],
+                loss, stats = agent.ppo_minibatch(d_mb["batch"], acts[mb], masks_d, lps[mb], adv[mb, :, 0],
                                                   ret[mb, :, 0], values[mb, :, 0], sharded=sharded, **PPO_KW)
                 loss.backward()
                 bucket.reduce(average=not sharded)
@@ -742,7 +749,8 @@ def run_b200(args):
                     "rollout_ms_per_step": ms_roll, "iteration_ms": t_ppo / n_it * 1e3,
                     "definition": "TIMED loop, wall clock: (rollout of rollout_steps x num_envs env steps with the "
                                   "sampled action read back every step, GAE on the device, n_epochs x rollout_steps "
-                                  "minibatch updates with one statistics read-back per epoch) / elapsed; dummy "
+                                  "minibatch updates, the next minibatch's batch build prefetched, with one "
+                                  "statistics read-back per epoch) / elapsed; dummy "
                                   "in-process environment, CPU simulators excluded; all ranks summed",
                     "rollout_graph_edges_per_sec": edges_per_rank_note(E, ms_roll, world)}}
     if world == 1 and not args.no_cpu_baseline:
