@@ -558,6 +558,8 @@ def run_b200(args):
     SIDE = bool(int(choice))
     ms_e2e_mean, e2e_spread = e2e_runs[SIDE]
     e2e_by_placement = {("side_stream" if k else "same_stream"): v[0] for k, v in e2e_runs.items()}
+    e2e_spread["other_placement"] = {("side_stream" if k else "same_stream"): v[1]
+                                     for k, v in e2e_runs.items() if k != SIDE}
     # every step is bracketed by its own event pair: the headline is the MEAN over the timed steps; the median
     # (slowest rank's), min and max are reported beside it in ms_per_step_median / ms_per_step_spread
     t_med = torch.tensor([e2e_spread["median"]], device=dev, dtype=torch.float64)

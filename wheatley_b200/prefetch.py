@@ -10,9 +10,9 @@ Two placements:
 * ``side_stream=False`` (default): everything on the caller's stream, ahead of the step's kernels.  No
   cross-stream bookkeeping; right for raw observations (``submit_observation``: 2 MB of copies per minibatch).
 * ``side_stream=True``: copies and kernels on a side stream, so that a LARGE copy (the 41 MB int64 COO of an
-  already batched graph, ``submit``) runs on the copy engine under the step's kernels; tensors change streams
-  through ``record_stream``, which costs ~0.3 ms of host time per step in allocator events - worth it only for
-  copies of that size (measured: 8.5 -> 7.75 ms with the COO, slower than the default with observations).
+  already batched graph, ``submit``) runs on the copy engine and the batch / plan kernels run under the step's
+  kernels; the two streams are ordered by one event per submit / get (``_side_waits_for_main``).  Wins when the step
+  is GPU-bound (8 x Taillard 100x20: 4.6 vs 5.2 ms end to end).
 
 The reference builds each minibatch on the host inside the update loop (alg/ppo.py:547-727 ->
 jssp/models/agent_observation / gnn_dgl.py:272-286) with nothing overlapped; this is the B200-side counterpart
@@ -34,29 +34,6 @@ from . import _lib
 from .plan import GraphPlan
 
 
-def _cuda_tensors(obj):
-    """Every CUDA tensor reachable from ``obj`` through lists, tuples, dicts and plain objects (``JsspBatch``,
-    ``PspGraphData``, ``GraphPlan``, ``CliqueView`` ...): what must be handed to ``Tensor.record_stream`` when a
-    batch built on the side stream is used on another one."""
-    seen, out, stack = set(), [], [obj]
-    while stack:
-        o = stack.pop()
-        if id(o) in seen or o is None or isinstance(o, (int, float, str, bytes, bool, torch.nn.Module)):
-            continue
-        seen.add(id(o))
-        if isinstance(o, torch.Tensor):
-            if o.is_cuda:
-                out.append(o)
-                stack.extend(v for v in getattr(o, "__dict__", {}).values() if isinstance(v, torch.Tensor))
-        elif isinstance(o, (list, tuple, set)):
-            stack.extend(o)
-        elif isinstance(o, dict):
-            stack.extend(o.values())
-        elif hasattr(o, "__dict__") and type(o).__module__.startswith("wheatley_b200"):
-            stack.extend(vars(o).values())
-    return out
-
-
 class BatchPrefetcher:
     def __init__(self, device, src_key="src", dst_key="dst", etype_key="etype", side_stream=False):
         # (a worker thread for the submissions was tried: the step's own launches and the worker's contend for
@@ -72,7 +49,22 @@ class BatchPrefetcher:
         self._pending.append(job())
 
     def _stream(self):
-        return torch.cuda.stream(self.side) if self.side is not None else contextlib.nullcontext()
+        if self.side is None:
+            return contextlib.nullcontext()
+        self._side_waits_for_main()
+        return torch.cuda.stream(self.side)
+
+    def _side_waits_for_main(self):
+        """Memory discipline of the side-stream placement.  A batch is allocated from the side stream's pool, used by
+        the training step on the caller's stream and freed by reference counting once that step has been QUEUED, at
+        which point the allocator may hand its blocks to the side stream's next allocation.  Everything queued on the
+        side stream therefore first waits for what the caller's stream has been given so far: one event per submit /
+        get instead of ``Tensor.record_stream`` on each of a batch's ~70 tensors (0.3 ms of host time per step, which
+        made this placement lose whenever the loop was host-bound).  Contract: a prefetched batch is consumed on the
+        stream that is current when ``get()`` is called."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.side.wait_event(ev)
 
     def submit(self, host: dict, n_nodes: int):
         """Queue the copies of ``host`` (a dict of pinned CPU tensors) and the plan build on the side stream."""
@@ -128,14 +120,12 @@ class BatchPrefetcher:
             plan.finish()               # waits for the counts' event only (queued ahead of the previous step)
             return d, plan
         main = torch.cuda.current_stream(self.device)
+        self._side_waits_for_main()
         with torch.cuda.stream(self.side):
             plan.finish()               # allocations stay on the side pool; zero-fills the hub arrival counters
             done = torch.cuda.Event()   # (a kernel queued AFTER the event of submit time)
             done.record()
         main.wait_event(done)
-        # the tensors were allocated on the side stream's pool and are used (and eventually freed) on `main`
-        for t in _cuda_tensors([d, plan]):
-            t.record_stream(main)
         return d, plan
 
 
