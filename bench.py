@@ -712,6 +712,18 @@ def run_b200(args):
                                     "gbps": v[1] / (v[0] * 1e-3) / 1e9} for k, v in per.items()},
                     "share_of_step": {k: (t_ms / args.steps) / ms_share for k, (t_ms, _) in tm.items() if t_ms},
                     "share_basis": share_note}
+        # The second roofline DESIGN.md section 5 states beside the HBM one: the logit is non-linear inside the sum, so
+        # every feature-edge (E x H x D) costs >= 3 fp32 issue slots forward (add, max, fma; the aggregation is on the
+        # tensor cores) and >= 6 backward; 148 SMs x 4 schedulers x 32 lanes issue per clock.
+        clk = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+        fe = float(E) * cfg["heads"] * cfg["hidden"]
+        lanes = 148 * 4 * 32
+        floors = {"conv_fwd": 3 * fe / lanes / clk * 1e3, "conv_bwd": 6 * fe / lanes / clk * 1e3}
+        roofline["fp32_issue_bound"] = {
+            "model": "E*H*D feature-edges x (3 forward | 6 backward) fp32 issue slots / (148 SMs x 4 schedulers x 32 "
+                     "lanes x measured SM clock), per conv launch group (one layer, this rank's batch)",
+            "floor_ms": floors,
+            "frac": {k: floors[k] / per[k][0] for k in floors if k in per}}
     line = {"metric": METRIC, "value": edges_total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None,
