@@ -26,8 +26,11 @@ namespace b200gat {
 
 namespace {
 
-constexpr int kWinW = 16;                 // nodes per run
-constexpr int kWinNPW = kWinW / kWarps;   // nodes per warp
+#ifndef B200GAT_WIN_W
+#define B200GAT_WIN_W 16
+#endif
+constexpr int kWinW = 16;                 // nodes per run, backward by destination (its accumulators need the room)
+constexpr int kWinWide = B200GAT_WIN_W;   // nodes per run, forward and backward by source (32 was measured: 3-8 % slower)
 constexpr int kWinEdges = 768;            // staged adjacency entries per run (longer runs read them from global)
 
 __device__ __forceinline__ uint32_t w_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -62,14 +65,16 @@ __device__ __forceinline__ void w_bulk_g2s(uint32_t dst, const void* src, uint32
 __device__ __forceinline__ void w_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // The adjacency of one run, staged in shared memory.
-struct WinIdx {
-  int ptr[kWinW + 1];
-  int nbr[kWinEdges], pos[kWinEdges], typ[kWinEdges];
+template <int W>
+struct WinIdxT {
+  int ptr[W + 1];
+  int nbr[kWinEdges * (W / 16)], pos[kWinEdges * (W / 16)], typ[kWinEdges * (W / 16)];
 };
 
 // Start of a run: thread 0 queues the row copies, the first threads fetch the run's segment bounds.
+template <int W>
 __device__ __forceinline__ void win_begin(uint32_t bar, int w0, int nw, int HD, float* w_a, const float* ga,
-                                          float* w_b, const float* gb, WinIdx& ix,
+                                          float* w_b, const float* gb, WinIdxT<W>& ix,
                                           const int32_t* __restrict__ ptr) {
   if (threadIdx.x == 0) {
     const uint32_t bytes = (uint32_t)nw * HD * 4u;
@@ -81,10 +86,11 @@ __device__ __forceinline__ void win_begin(uint32_t bar, int w0, int nw, int HD, 
   if ((int)threadIdx.x <= nw) ix.ptr[threadIdx.x] = ptr[w0 + threadIdx.x];
 }
 // After a __syncthreads: every thread stages one adjacency entry per 256 (neighbour, edge position, edge type).
-__device__ __forceinline__ bool win_stage_idx(const FastArgs& A, WinIdx& ix, int nw, const int32_t* __restrict__ nbr,
+template <int W>
+__device__ __forceinline__ bool win_stage_idx(const FastArgs& A, WinIdxT<W>& ix, int nw, const int32_t* __restrict__ nbr,
                                               const int32_t* __restrict__ pos, bool typed) {
   const int eb = ix.ptr[0], ne = ix.ptr[nw] - eb;
-  if (ne > kWinEdges) return false;
+  if (ne > kWinEdges * (W / 16)) return false;
   for (int t = threadIdx.x; t < ne; t += kFastThreads) {
     const int p = pos ? pos[eb + t] : eb + t;
     ix.nbr[t] = nbr[eb + t];
@@ -94,7 +100,8 @@ __device__ __forceinline__ bool win_stage_idx(const FastArgs& A, WinIdx& ix, int
   return true;
 }
 // One lane's adjacency entry of the chunk [e0, e0 + n) of a segment.
-__device__ __forceinline__ void win_entry(const FastArgs& A, const WinIdx& ix, bool staged, int eb, int e0, int n,
+template <int W>
+__device__ __forceinline__ void win_entry(const FastArgs& A, const WinIdxT<W>& ix, bool staged, int eb, int e0, int n,
                                           int lane, const int32_t* __restrict__ nbr,
                                           const int32_t* __restrict__ pos, bool typed, int& my_u, int& my_p,
                                           int& my_t) {
@@ -118,10 +125,10 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
   constexpr int HD = 32 * VPL;
   constexpr int U = OCC >= 3 ? 1 : 2;     // edges in flight (register budget: 80 / thread at 3 CTAs per SM)
   extern __shared__ __align__(128) float w_rows[];
-  __shared__ WinIdx ix;
+  __shared__ WinIdxT<kWinWide> ix;
   __shared__ __align__(8) unsigned long long s_bar;
   float* w_pi = w_rows;
-  float* w_v = ALIAS ? w_rows : w_rows + kWinW * HD;
+  float* w_v = ALIAS ? w_rows : w_rows + kWinWide * HD;
   if ((int)blockIdx.x < A.hub_blocks) {      // hub CTAs (whole CTA: uniform branch)
     fwd_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, (int)blockIdx.x, A.hub_blocks);
     return;
@@ -136,16 +143,17 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
   float at[VPL];
   ldrow<VPL>(at, A.attn + c0);
   uint32_t phase = 0;
-  const int n_runs = (A.N + kWinW - 1) / kWinW;
+  const int n_runs = (A.N + kWinWide - 1) / kWinWide;
 
   for (int run = blockIdx.x - A.hub_blocks; run < n_runs; run += gridDim.x - A.hub_blocks) {
-    const int w0 = run * kWinW, nw = min(kWinW, A.N - w0);
+    const int w0 = run * kWinWide, nw = min(kWinWide, A.N - w0);
     win_begin(bar, w0, nw, HD, w_pi, Pi, ALIAS ? nullptr : w_v, V, ix, A.in_ptr);
-    float q[kWinNPW][VPL];                                       // own rows: in flight under the index round trips
+    constexpr int kPre = kWinWide / kWarps < 2 ? kWinWide / kWarps : 2;
+    float qpre[kPre][VPL];                                   // first own rows: in flight under the index round trips
 #pragma unroll
-    for (int j = 0; j < kWinNPW; ++j) {
+    for (int j = 0; j < kPre; ++j) {
       const int vl = wi + j * kWarps;
-      if (vl < nw) ldrow<VPL>(q[j], Pj + (int64_t)(w0 + vl) * HD + c0);
+      if (vl < nw) ldrow<VPL>(qpre[j], Pj + (int64_t)(w0 + vl) * HD + c0);
     }
     __syncthreads();
     const bool staged = win_stage_idx(A, ix, nw, A.in_src, A.in_pos, typed);
@@ -155,7 +163,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
     const int eb = ix.ptr[0];
 
 #pragma unroll
-    for (int j = 0; j < kWinNPW; ++j) {
+    for (int j = 0; j < (kWinWide / kWarps); ++j) {
       const int vl = wi + j * kWarps;
       if (vl >= nw) continue;
       const int v = w0 + vl;
@@ -166,9 +174,15 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
       for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
       float m = -INFINITY, l = 0.f;
       if (re > rb) {
-        float qt[VPL];
+        float q[VPL], qt[VPL];
+        if (j < kPre) {
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) qt[i] = q[j][i];
+          for (int i = 0; i < VPL; ++i) q[i] = qpre[j < kPre ? j : 0][i];
+        } else {
+          ldrow<VPL>(q, Pj + (int64_t)v * HD + c0);
+        }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) qt[i] = q[i];
         int t_cur = -1;
         for (int e0 = rb; e0 < re; e0 += 32) {
           const int n = min(32, re - e0);
@@ -200,7 +214,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
               const bool valid = j0 + k < n;
               if (typed && tt[k] != t_cur) {
                 t_cur = tt[k];
-                type_row<VPL>(A, t_cur, c0, q[j], qt);
+                type_row<VPL>(A, t_cur, c0, q, qt);
               }
               float z[VPL];
 #pragma unroll
@@ -250,7 +264,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
   constexpr int HD = 32 * VPL;
   constexpr int U = 2;
   extern __shared__ __align__(128) float w_rows[];
-  __shared__ WinIdx ix;
+  __shared__ WinIdxT<kWinW> ix;
   __shared__ __align__(8) unsigned long long s_bar;
   float* w_pi = w_rows;
   float* w_v = ALIAS ? w_rows : w_rows + kWinW * HD;
@@ -292,7 +306,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
     phase ^= 1u;
     const int eb = ix.ptr[0];
 
-    for (int j = 0; j < kWinNPW; ++j) {
+    for (int j = 0; j < (kWinW / kWarps); ++j) {
       const int vl = wi + j * kWarps;
       if (vl >= nw) continue;
       const int v = w0 + vl;
@@ -459,10 +473,10 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
   constexpr int HD = 32 * VPL;
   constexpr int U = OCC >= 3 ? 1 : 2;
   extern __shared__ __align__(128) float w_rows[];
-  __shared__ WinIdx ix;
+  __shared__ WinIdxT<kWinWide> ix;
   __shared__ __align__(8) unsigned long long s_bar;
   float* w_pj = w_rows;
-  float* w_g = w_rows + kWinW * HD;
+  float* w_g = w_rows + kWinWide * HD;
   if ((int)blockIdx.x < A.hub_blocks) {      // hub CTAs
     bwd_src_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, G, gs_in, alpha_in, gPi, gV, (int)blockIdx.x, A.hub_blocks);
     return;
@@ -478,16 +492,17 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
 #pragma unroll
   for (int i = 0; i < VPL; ++i) ats[i] = at[i] * A.slope;
   uint32_t phase = 0;
-  const int n_runs = (A.N + kWinW - 1) / kWinW;
+  const int n_runs = (A.N + kWinWide - 1) / kWinWide;
 
   for (int run = blockIdx.x - A.hub_blocks; run < n_runs; run += gridDim.x - A.hub_blocks) {
-    const int w0 = run * kWinW, nw = min(kWinW, A.N - w0);
+    const int w0 = run * kWinWide, nw = min(kWinWide, A.N - w0);
     win_begin(bar, w0, nw, HD, w_pj, Pj, w_g, G, ix, A.out_ptr);
-    float pr[kWinNPW][VPL];
+    constexpr int kPre = kWinWide / kWarps < 2 ? kWinWide / kWarps : 2;
+    float ppre[kPre][VPL];
 #pragma unroll
-    for (int j = 0; j < kWinNPW; ++j) {
+    for (int j = 0; j < kPre; ++j) {
       const int ul = wi + j * kWarps;
-      if (ul < nw) ldrow<VPL>(pr[j], Pi + (int64_t)(w0 + ul) * HD + c0);
+      if (ul < nw) ldrow<VPL>(ppre[j], Pi + (int64_t)(w0 + ul) * HD + c0);
     }
     __syncthreads();
     const bool staged = win_stage_idx(A, ix, nw, A.out_dst, A.out_pos, typed);
@@ -497,7 +512,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
     const int eb = ix.ptr[0];
 
 #pragma unroll
-    for (int j = 0; j < kWinNPW; ++j) {
+    for (int j = 0; j < (kWinWide / kWarps); ++j) {
       const int ul = wi + j * kWarps;
       if (ul >= nw) continue;
       const int u = w0 + ul;
@@ -507,9 +522,15 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
 #pragma unroll
       for (int i = 0; i < VPL; ++i) { gpi[i] = 0.f; gv[i] = 0.f; }
       if (re > rb) {
-        float pt[VPL];
+        float pr[VPL], pt[VPL];
+        if (j < kPre) {
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) pt[i] = pr[j][i];
+          for (int i = 0; i < VPL; ++i) pr[i] = ppre[j < kPre ? j : 0][i];
+        } else {
+          ldrow<VPL>(pr, Pi + (int64_t)u * HD + c0);
+        }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) pt[i] = pr[i];
         int t_cur = -1;
         for (int q0 = rb; q0 < re; q0 += 32) {
           const int n = min(32, re - q0);
@@ -543,7 +564,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
               const bool valid = j0 + k < n;
               if (typed && tt[k] != t_cur) {
                 t_cur = tt[k];
-                type_row<VPL>(A, t_cur, c0, pr[j], pt);
+                type_row<VPL>(A, t_cur, c0, pr, pt);
               }
               float z[VPL];
 #pragma unroll
@@ -571,8 +592,8 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
   }
 }
 
-unsigned win_ctas(int64_t N, int per_sm) {
-  const int64_t runs = ceil_div(N, kWinW), cap = (int64_t)per_sm * kNumSMs;
+unsigned win_ctas(int64_t N, int per_sm, int W) {
+  const int64_t runs = ceil_div(N, W), cap = (int64_t)per_sm * kNumSMs;
   return (unsigned)(runs < cap ? runs : cap);
 }
 
@@ -617,9 +638,9 @@ bool win_enabled(const FastArgs& A) {
 
 int win_fwd(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, const float* Pj, const float* V,
             float* out, float* s_save, float* m_save, float* l_save, float* agg_save, cudaStream_t st) {
-  const size_t smem = sizeof(float) * (size_t)(alias ? 1 : 2) * kWinW * 32 * vpl;
+  const size_t smem = sizeof(float) * (size_t)(alias ? 1 : 2) * kWinWide * 32 * vpl;
   const int occ = win_occ(vpl);
-  const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
+  const unsigned blocks = win_ctas(A.N, occ, kWinWide) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_fwd_win<VPL, LPH, ALIAS, 3>>(smem)));
@@ -652,7 +673,7 @@ int win_bwd_dst(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
                                        (tab_in_smem == 2 ? (size_t)kWarps * A.T * HD
                                         : tab_in_smem == 1 ? (size_t)A.T * HD : 0) +
                                        (aff_in_smem ? (size_t)kWarps * A.K * HD : 0));
-  const unsigned blocks = win_ctas(A.N, 2) + A.hub_blocks;
+  const unsigned blocks = win_ctas(A.N, 2, kWinW) + A.hub_blocks;
   int rc = B200GAT_OK;
   FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_dst_win<VPL, LPH, ALIAS>>(smem)));
   if (rc) return rc;
@@ -666,9 +687,9 @@ int win_bwd_dst(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
 
 int win_bwd_src(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, const float* Pj, const float* G,
                 const float* gs_in, const float* alpha_in, float* gPi, float* gV, cudaStream_t st) {
-  const size_t smem = sizeof(float) * (size_t)2 * kWinW * 32 * vpl;
+  const size_t smem = sizeof(float) * (size_t)2 * kWinWide * 32 * vpl;
   const int occ = win_occ(vpl);
-  const unsigned blocks = win_ctas(A.N, occ) + A.hub_blocks;
+  const unsigned blocks = win_ctas(A.N, occ, kWinWide) + A.hub_blocks;
   int rc = B200GAT_OK;
   if (occ == 3) {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_src_win<VPL, LPH, ALIAS, 3>>(smem)));
