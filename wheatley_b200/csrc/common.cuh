@@ -59,6 +59,30 @@ bool aux_join(cudaStream_t main, cudaStream_t aux, cudaEvent_t ev);     // main 
 
 constexpr int kNumSMs = 148;  // B200
 
+// Programmatic dependent launch.  A kernel launched through launch_k() may become resident while the kernel before it
+// on the stream is still running its LAST wave (every CTA of that kernel has executed pdl_sync()'s trigger or exited):
+// its CTAs are scheduled, run pdl_sync() and block there until the predecessor has completed and its writes are
+// visible.  The launch latency and the ramp-up of ~180 back-to-back dependent kernels per step come off the critical
+// path; nothing is read or written before the wait, so results cannot change.  Every kernel launched through
+// launch_k() MUST call pdl_sync() before its first global access.  B200GAT_PDL=0 launches them the ordinary way
+// (the two instructions are no-ops then).
+bool pdl_enabled();
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_trigger(); pdl_wait(); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 __device__ __forceinline__ float warp_sum(float v) {

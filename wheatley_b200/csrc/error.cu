@@ -1,4 +1,5 @@
 // Error string, launch counter and the optional per-kernel-class event timing.
+#include <stdlib.h>
 #include <stdarg.h>
 #include <atomic>
 #include <mutex>
@@ -26,6 +27,14 @@ static std::vector<EvPair> g_pending[B200GAT_TIMING_CLASSES];
 static std::vector<EvPair> g_graph_pairs[B200GAT_TIMING_CLASSES];
 static double g_ms[B200GAT_TIMING_CLASSES];
 static int64_t g_cnt[B200GAT_TIMING_CLASSES];
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200GAT_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
 
 bool timing_enabled() { return g_timing.load(std::memory_order_relaxed); }
 

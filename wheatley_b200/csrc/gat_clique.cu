@@ -255,6 +255,7 @@ __global__ void __launch_bounds__(256, 2) k_clq_fwd(CliqueArgs A, const float* _
                                                      float* __restrict__ out, float* __restrict__ s_dense,
                                                      float* __restrict__ m_save, float* __restrict__ l_save,
                                                      float* __restrict__ agg_save) {
+  pdl_sync();
   extern __shared__ __align__(16) float smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot = warp / A.tiles, vt = warp - slot * A.tiles;
@@ -826,6 +827,7 @@ __global__ void __launch_bounds__(256, 2) k_clq_bwd_fused(CliqueArgs A, const fl
                                                            const float* __restrict__ l_save, float* __restrict__ gPi,
                                                            float* __restrict__ gPj, float* __restrict__ gV,
                                                            float* __restrict__ g_attn, float* __restrict__ g_table) {
+  pdl_sync();
   extern __shared__ __align__(16) float smem[];
   constexpr int SG = 4 * GU;
   constexpr int SGW = SG > kD ? SG : kD;
@@ -1084,10 +1086,10 @@ int clique_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
   ScopedTimer tm(B200GAT_TIMING_CLQ_FWD, st);
   if (alias) {
     if ((rc = set_smem<k_clq_fwd<true>>(smem, "k_clq_fwd"))) return rc;
-    k_clq_fwd<true><<<grid, block, smem, st>>>(A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
+    launch_k(k_clq_fwd<true>, dim3(grid), dim3(block), smem, st, A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
   } else {
     if ((rc = set_smem<k_clq_fwd<false>>(smem, "k_clq_fwd"))) return rc;
-    k_clq_fwd<false><<<grid, block, smem, st>>>(A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
+    launch_k(k_clq_fwd<false>, dim3(grid), dim3(block), smem, st, A, Pi, Pj, V, out, s_dense, m_save, l_save, agg_save);
   }
   B200_CHECK_LAUNCH("k_clq_fwd");
   return B200GAT_OK;
@@ -1117,8 +1119,8 @@ int clique_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge
 #define CLQ_BWDF(GU_)                                                                                          \
   case GU_:                                                                                                    \
     if ((rc = set_smem<k_clq_bwd_fused<GU_>>(smem_f, "k_clq_bwd_fused"))) return rc;                           \
-    k_clq_bwd_fused<GU_><<<A.n_items, 256, smem_f, st>>>(A, Pi, Pj, V, g_out, agg_save, s_dense, m_save,        \
-                                                         l_save, gPi, gPj, gV, g_attn, gt);                    \
+    launch_k(k_clq_bwd_fused<GU_>, dim3(A.n_items), dim3(256), smem_f, st, A, Pi, Pj, V, g_out, agg_save, s_dense, \
+             m_save, l_save, gPi, gPj, gV, g_attn, gt);                                                        \
     break;
       switch (gu) {
         CLQ_BWDF(20) CLQ_BWDF(24) CLQ_BWDF(28) CLQ_BWDF(32)

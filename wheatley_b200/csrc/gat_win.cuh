@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_fwd_win(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
     float* __restrict__ l_save, float* __restrict__ agg_save) {
+  pdl_sync();
   constexpr int HD = 32 * VPL;
   constexpr int U = OCC >= 3 ? 1 : 2;     // edges in flight (register budget: 80 / thread at 3 CTAs per SM)
   extern __shared__ __align__(128) float w_rows[];
@@ -261,6 +262,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) k_bwd_dst_win(
     const float* __restrict__ agg_save, const float* __restrict__ G, float* __restrict__ gPj,
     float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
     float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem) {
+  pdl_sync();
   constexpr int HD = 32 * VPL;
   constexpr int U = 2;
   extern __shared__ __align__(128) float w_rows[];
@@ -470,6 +472,7 @@ __global__ void __launch_bounds__(kFastThreads, OCC) k_bwd_src_win(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
     const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
     float* __restrict__ gV) {
+  pdl_sync();
   constexpr int HD = 32 * VPL;
   constexpr int U = OCC >= 3 ? 1 : 2;
   extern __shared__ __align__(128) float w_rows[];
@@ -646,14 +649,14 @@ int win_fwd(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi, co
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_fwd_win<VPL, LPH, ALIAS, 3>>(smem)));
     if (rc) return rc;
     FAST_DISPATCH(vpl, lph, alias,
-                  (k_fwd_win<VPL, LPH, ALIAS, 3><<<blocks, kFastThreads, smem, st>>>(A, Pi, Pj, V, out, s_save,
-                                                                                     m_save, l_save, agg_save)));
+                  (launch_k(k_fwd_win<VPL, LPH, ALIAS, 3>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj, V, out,
+                            s_save, m_save, l_save, agg_save)));
   } else {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_fwd_win<VPL, LPH, ALIAS, 2>>(smem)));
     if (rc) return rc;
     FAST_DISPATCH(vpl, lph, alias,
-                  (k_fwd_win<VPL, LPH, ALIAS, 2><<<blocks, kFastThreads, smem, st>>>(A, Pi, Pj, V, out, s_save,
-                                                                                     m_save, l_save, agg_save)));
+                  (launch_k(k_fwd_win<VPL, LPH, ALIAS, 2>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj, V, out,
+                            s_save, m_save, l_save, agg_save)));
   }
   B200_CHECK_LAUNCH("k_fwd_win");
   return B200GAT_OK;
@@ -678,9 +681,9 @@ int win_bwd_dst(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
   FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_dst_win<VPL, LPH, ALIAS>>(smem)));
   if (rc) return rc;
   FAST_DISPATCH(vpl, lph, alias,
-                (k_bwd_dst_win<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
-                    A, Pi, Pj, V, s_save, m_save, l_save, agg_save, G, gPj, g_attn, g_table, g_affine, gs_out,
-                    alpha_out, tab_in_smem, aff_in_smem)));
+                (launch_k(k_bwd_dst_win<VPL, LPH, ALIAS>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj, V, s_save,
+                          m_save, l_save, agg_save, G, gPj, g_attn, g_table, g_affine, gs_out, alpha_out, tab_in_smem,
+                          aff_in_smem)));
   B200_CHECK_LAUNCH("k_bwd_dst_win");
   return B200GAT_OK;
 }
@@ -695,14 +698,14 @@ int win_bwd_src(const FastArgs& A, int vpl, int lph, bool alias, const float* Pi
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_src_win<VPL, LPH, ALIAS, 3>>(smem)));
     if (rc) return rc;
     FAST_DISPATCH(vpl, lph, alias,
-                  (k_bwd_src_win<VPL, LPH, ALIAS, 3><<<blocks, kFastThreads, smem, st>>>(A, Pi, Pj, G, gs_in,
-                                                                                         alpha_in, gPi, gV)));
+                  (launch_k(k_bwd_src_win<VPL, LPH, ALIAS, 3>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj, G,
+                            gs_in, alpha_in, gPi, gV)));
   } else {
     FAST_DISPATCH(vpl, lph, alias, (rc = win_set_smem<k_bwd_src_win<VPL, LPH, ALIAS, 2>>(smem)));
     if (rc) return rc;
     FAST_DISPATCH(vpl, lph, alias,
-                  (k_bwd_src_win<VPL, LPH, ALIAS, 2><<<blocks, kFastThreads, smem, st>>>(A, Pi, Pj, G, gs_in,
-                                                                                         alpha_in, gPi, gV)));
+                  (launch_k(k_bwd_src_win<VPL, LPH, ALIAS, 2>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj, G,
+                            gs_in, alpha_in, gPi, gV)));
   }
   B200_CHECK_LAUNCH("k_bwd_src_win");
   return B200GAT_OK;

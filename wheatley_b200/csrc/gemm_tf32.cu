@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(320, ((BN == 256 || X3) ? 1 : 2)) k_gemm_tf32(
   // mn columns, k ascending: deterministic) before the stage is released - the stage's "empty" barrier then counts
   // the MMA commit plus these 128 readers.
   const bool rowsum = A_MN && p.a_rowsum != nullptr && nt == 0;
+  pdl_trigger();                // the next kernel may be scheduled once every CTA of this one is running
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
       mbar_init(full0 + 8 * s, 1);
@@ -195,6 +196,7 @@ __global__ void __launch_bounds__(320, ((BN == 256 || X3) ? 1 : 2)) k_gemm_tf32(
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = tmem_base_s;
+  pdl_wait();                   // barriers and TMEM are set up; no global access before the predecessor has completed
 
   if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
@@ -382,6 +384,7 @@ __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__
                                                        long long n4, float* __restrict__ out,
                                                        const float* __restrict__ ws_rs, long long rs_stride,
                                                        long long r4, float* __restrict__ out_rs) {
+  pdl_sync();
   __shared__ float4 part[8][32];
   const int lane = threadIdx.x & 31, zl = threadIdx.x >> 5;
   const long long dblocks = (n4 + 31) / 32;
@@ -591,7 +594,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, dim3
     }
     attr_set = true;
   }
-  k_gemm_tf32<BN, A_MN, B_MN, X3><<<grid, 320, smem, st>>>(ta, tb, a);
+  launch_k(k_gemm_tf32<BN, A_MN, B_MN, X3>, grid, dim3(320), smem, st, ta, tb, a);
   B200_CHECK_LAUNCH("k_gemm_tf32");
   return B200GAT_OK;
 }
@@ -677,8 +680,8 @@ extern "C" int b200gat_gemm_tf32(const b200gat_gemm* g, void* stream) {
   if (s.splits > 1) {
     const long long n4 = g->M * g->N / 4, r4 = g->a_rowsum ? g->M / 4 : 0;
     const unsigned blocks = (unsigned)(ceil_div(n4, 32) + ceil_div(r4, 32));
-    k_splitk_reduce<<<blocks, 256, 0, st>>>(g->workspace, s.splits, g->M * g->N, n4, g->D, a.a_rowsum, g->M, r4,
-                                            g->a_rowsum);
+    launch_k(k_splitk_reduce, dim3(blocks), dim3(256), 0, st, g->workspace, s.splits, g->M * g->N, n4, g->D, a.a_rowsum,
+             g->M, r4, g->a_rowsum);
     B200_CHECK_LAUNCH("k_splitk_reduce");
   }
   return B200GAT_OK;

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) k_concat_segs(CopySegs S, float* __restri
 
 __global__ void __launch_bounds__(256) k_add2(const float4* __restrict__ a, const float4* __restrict__ b,
                                               float4* __restrict__ o, int64_t n4) {
+  pdl_sync();
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i < n4) {
     const float4 x = a[i], y = b[i];
@@ -374,9 +375,8 @@ extern "C" int b200gat_trunk_bwd(const b200gat_trunk* t, const b200gat_trunk_gra
     const float* R = r1 ? r1 : r2;
     if (r1 && r2) {
       B200_CHECK_ARG(aligned16t(r1) && aligned16t(r2), "gradients must be 16-byte aligned");
-      k_add2<<<(unsigned)ceil_div(n_in / 4, 256), 256, 0, st>>>(reinterpret_cast<const float4*>(r1),
-                                                               reinterpret_cast<const float4*>(r2),
-                                                               reinterpret_cast<float4*>(ws + sh.o_R), n_in / 4);
+      launch_k(k_add2, dim3((unsigned)ceil_div(n_in / 4, 256)), dim3(256), 0, st, reinterpret_cast<const float4*>(r1),
+               reinterpret_cast<const float4*>(r2), reinterpret_cast<float4*>(ws + sh.o_R), n_in / 4);
       B200_CHECK_LAUNCH("k_add2");
       R = ws + sh.o_R;
     }
