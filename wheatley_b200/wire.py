@@ -47,6 +47,8 @@ class PspObsLayout:
         self.off_rpr = o
         o += 4 * self.max_rp
         assert o <= self.slot_words
+        # [max_nodes * max_res, max_res] one-hot: column of each entry of the row-major ``resources`` block
+        self.res_select = np.tile(np.eye(self.max_res, dtype=np.float32), (self.max_nodes, 1))
 
     @classmethod
     def for_graphs(cls, graphs):
