@@ -74,7 +74,7 @@ static void drain() {
 using namespace b200gat;
 
 extern "C" const char* b200gat_last_error(void) { return g_err; }
-extern "C" int b200gat_version(void) { return 200; }
+extern "C" int b200gat_version(void) { return 210; }   // 2.1: graph flags, no-alloc colsum, side stream, dependent launches
 extern "C" int64_t b200gat_launch_count(void) { return g_launches.load(); }
 extern "C" void b200gat_timing_enable(int on) {
   std::lock_guard<std::mutex> lk(g_tmu);
