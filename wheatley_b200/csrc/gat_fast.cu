@@ -162,7 +162,6 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_fwd_fast(
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ V,
     float* __restrict__ out, float* __restrict__ s_save, float* __restrict__ m_save,
     float* __restrict__ l_save, float* __restrict__ agg_save) {
-  pdl_sync();
   fwd_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, out, s_save, m_save, l_save, agg_save, (int)blockIdx.x, (int)gridDim.x);
 }
 
@@ -395,7 +394,6 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_dst_fas
     float* __restrict__ g_attn, float* __restrict__ g_table, float* __restrict__ g_affine,
     float* __restrict__ gs_out, float* __restrict__ alpha_out, int tab_in_smem, int aff_in_smem) {
   extern __shared__ float sh[];
-  pdl_sync();
   bwd_dst_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, V, s_save, m_save, l_save, agg_save, G, gPj, g_attn, g_table, g_affine,
                                     gs_out, alpha_out, tab_in_smem, aff_in_smem, sh, (int)blockIdx.x, (int)gridDim.x);
 }
@@ -518,7 +516,6 @@ __global__ void __launch_bounds__(kFastThreads, B200GAT_FAST_MINB) k_bwd_src_fas
     FastArgs A, const float* __restrict__ Pi, const float* __restrict__ Pj, const float* __restrict__ G,
     const float* __restrict__ gs_in, const float* __restrict__ alpha_in, float* __restrict__ gPi,
     float* __restrict__ gV) {
-  pdl_sync();
   bwd_src_fast_cta<VPL, LPH, ALIAS>(A, Pi, Pj, G, gs_in, alpha_in, gPi, gV, (int)blockIdx.x, (int)gridDim.x);
 }
 
@@ -602,8 +599,8 @@ int fast_fwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
   const unsigned blocks = win ? 0 : node_ctas(A.N) + A.hub_blocks;
   if (blocks) {
     FAST_DISPATCH(vpl, lph, alias,
-                  (launch_k(k_fwd_fast<VPL, LPH, ALIAS>, dim3(blocks), dim3(kFastThreads), 0, st, A, Pi, Pj, V, out,
-                            s_save, m_save, l_save, agg_save)));
+                  (k_fwd_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, V, out, s_save, m_save,
+                                                                                l_save, agg_save)));
     B200_CHECK_LAUNCH("k_fwd_fast");
   }
   if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0 && !A.hub_cnt) {
@@ -665,9 +662,9 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
     }
     if (blocks) {
       FAST_DISPATCH(vpl, lph, alias,
-                    (launch_k(k_bwd_dst_fast<VPL, LPH, ALIAS>, dim3(blocks), dim3(kFastThreads), smem, st, A, Pi, Pj,
-                              V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine, gs, alpha,
-                              tab_in_smem, aff_in_smem)));
+                    (k_bwd_dst_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, smem, st>>>(
+                        A, Pi, Pj, V, s_save, m_save, l_save, agg_save, g_out, gPj, g_attn, g_table, g_affine,
+                        gs, alpha, tab_in_smem, aff_in_smem)));
       note_launch(1);
     }
     if (A.hub_blocks && A.hub_scratch && A.hub_parts > 1 && A.hub_cap > 0 && !A.hub_cnt) {
@@ -688,8 +685,8 @@ int fast_bwd(const b200gat_graph* g, const b200gat_attn* a, const b200gat_edge_f
     const unsigned blocks = win ? 0 : nblocks + A.hub_blocks;
     if (blocks) {
       FAST_DISPATCH(vpl, lph, alias,
-                    (launch_k(k_bwd_src_fast<VPL, LPH, ALIAS>, dim3(blocks), dim3(kFastThreads), 0, st, A, Pi, Pj,
-                              g_out, gs, alpha, gPi, gV)));
+                    (k_bwd_src_fast<VPL, LPH, ALIAS><<<blocks, kFastThreads, 0, st>>>(A, Pi, Pj, g_out, gs, alpha,
+                                                                                     gPi, gV)));
       note_launch(1);
     }
   }
