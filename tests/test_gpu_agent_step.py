@@ -132,50 +132,3 @@ def test_ppo_minibatch_without_tf32_takes_the_module_path(wb):
         assert torch.isfinite(loss) and stats.shape == (8,)
     finally:
         torch.backends.cuda.matmul.allow_tf32 = prev
-
-
-@pytest.mark.parametrize("flavour", ["jssp", "psp"])
-def test_rollout_inference_through_the_fused_forward_equals_module_path(wb, tf32, flavour):
-    """``get_action_and_value(obs, None, masks)`` under ``no_grad`` (the rollout of alg/ppo.py:157-206) runs as one
-    ``b200gat_agent_fwd`` call; with the same RNG state it returns the module path's sample, log-probability,
-    entropy, value and unmasked logits."""
-    from wheatley_b200 import _lib
-    if flavour == "jssp":
-        from wheatley_b200.agent import JsspAgent
-        from wheatley_b200.batch import jssp_batch_from_observation
-        from wheatley_b200.workload import jssp_observation_batch
-        n_j, n_m, B = 12, 5, 3
-        obs = jssp_observation_batch(n_j, n_m, B, seed0=4, progress=0.4)
-        torch.manual_seed(2)
-        agent = JsspAgent(obs["features"].shape[2], n_j * n_m, n_m, 64, 3, 4).cuda()
-        n = n_j * n_m
-        make_obs = lambda: jssp_batch_from_observation(obs, "cuda", n, conflicts="clique", graph_pooling="learn")[0]
-    else:
-        from wheatley_b200.agent import PspAgent
-        from wheatley_b200.wire import PspArena
-        from wheatley_b200.workload import psp_taillard_graph
-        B, n = 7, 18
-        torch.manual_seed(0)
-        agent = PspAgent(n, 4, hidden_dim=32, n_layers=4, n_heads=4, conflicts="node").cuda()
-        arena = PspArena.from_graphs([psp_taillard_graph(4, 4, 3 + b, n_rp=b % 3, progress=0.1 * b) for b in range(B)])
-        make_obs = lambda: agent.preprocess(arena)
-    masks = targets(B, n, 5)["masks"]
-    out = {}
-    for mode in ("layers", "fused"):
-        os.environ["WHEATLEY_B200_TRUNK"] = mode
-        torch.manual_seed(11)
-        x = make_obs()
-        n0 = _lib.launch_count()
-        with torch.no_grad():
-            a, lp, ent, v, dist = agent.get_action_and_value(x, None, masks)
-        out[mode] = (a, lp, ent, v, dist.logits, _lib.launch_count() - n0)
-    la, fu = out["layers"], out["fused"]
-    assert torch.equal(la[0], fu[0]) and bool(masks.gather(1, fu[0].unsqueeze(1)).all())
-    assert la[3].shape == fu[3].shape and la[4].shape == fu[4].shape
-    for i, what in ((1, "logprob"), (2, "entropy"), (3, "value"), (4, "logits")):
-        assert rel(fu[i], la[i]) < 1e-6, what
-    assert fu[5] <= la[5] + 4            # same kernels (+ the pad job and the unused loss of the fused call)
-    # with autograd on, or an action given, the module path is taken (the fused call has no graph to return)
-    os.environ["WHEATLEY_B200_TRUNK"] = "fused"
-    _, lp2, _, _, _ = agent.get_action_and_value(make_obs(), fu[0], masks)
-    assert lp2.requires_grad and rel(lp2, fu[1]) < 1e-6

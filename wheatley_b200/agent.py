@@ -6,7 +6,7 @@ import torch
 from torch import nn
 
 from . import _lib
-from .agent_head import AgentHeadMixin, LazyCategorical
+from .agent_head import AgentHeadMixin
 from .agent_step import STATS, StepSpec, agent_step
 from .functional import _mask_u8
 from .gnn_dgl import GnnDGL
@@ -58,31 +58,9 @@ class PpoMinibatchMixin:
             dist.all_reduce(cfg["moments"], op=dist.ReduceOp.SUM, group=group)
         spec = StepSpec(ppo=cfg, **spec_kw)
         mask = _mask_u8(action_masks, n_logits, xin.device)
-        loss, stats, _aux, _logits, _logp = agent_step(spec, ext, xin, actions, mask, old_logprobs, advantages, returns,
-                                                       old_values, flat)
+        loss, stats, _aux = agent_step(spec, ext, xin, actions, mask, old_logprobs, advantages, returns, old_values,
+                                       flat)
         return loss, stats
-
-    def get_action_and_value(self, x, action=None, action_masks=None, deterministic=False):
-        """generic/agent.py:190-231.  Rollout inference (no action given, sampling, autograd off) on a covered
-        configuration runs as ONE C-ABI call (``b200gat_agent_fwd``: embedder, trunk, readout, both heads, masked
-        log-softmax) instead of the module-by-module forward: the launch thread needed 1.4 ms to issue 1.5 ms of
-        device work for 8 x Taillard 100x20.  Same kernels, same values; the sample is drawn from the same
-        probabilities with the same ``torch.multinomial`` call as the module path."""
-        if action is None and not deterministic and not torch.is_grad_enabled() and trunk_enabled():
-            built = self._step_inputs(x)
-            if built is not None:
-                spec_kw, ext, xin, flat, n_logits = built
-                B, dev = len(spec_kw["counts"]), xin.device
-                zf = torch.zeros(B, dtype=torch.float32, device=dev)       # loss operands: evaluated, not used
-                spec = StepSpec(ppo=dict(clip_coef=0.2, norm_adv=False, clip_vloss=False, critic_loss="l2",
-                                         ent_coef=0.0, vf_coef=0.5), **spec_kw)
-                mask = _mask_u8(action_masks, n_logits, dev)
-                _, _, aux, logits, logp = agent_step(spec, ext, xin, torch.zeros(B, dtype=torch.int64, device=dev),
-                                                     mask, zf, zf, zf, zf, flat)
-                act = torch.multinomial(logp.exp(), 1, True).squeeze(-1)
-                logprob = logp.gather(-1, act.unsqueeze(-1)).squeeze(-1)
-                return act, logprob, aux[1], aux[2].unsqueeze(-1), LazyCategorical(logits)
-        return super().get_action_and_value(x, action, action_masks, deterministic)
 
 
 class JsspAgent(PpoMinibatchMixin, AgentHeadMixin, nn.Module):

@@ -207,12 +207,11 @@ class _AgentStepFn(torch.autograd.Function):
             ctx.trunk_flat = flat_c
         stats = loss_out[1:]
         aux = head.view(3, B)
-        logits2, logp2 = logits.view(B, max_n), logp.view(B, max_n)
-        ctx.mark_non_differentiable(stats, aux, logits2, logp2)
-        return loss_out[0], stats, aux, logits2, logp2
+        ctx.mark_non_differentiable(stats, aux)
+        return loss_out[0], stats, aux
 
     @staticmethod
-    def backward(ctx, g_loss, _g_stats, _g_aux, _g_logits, _g_logp):
+    def backward(ctx, g_loss, _g_stats, _g_aux):
         a, spec = ctx.a, ctx.spec
         ne, nt, na, nv, N, F, Fp = ctx.sizes
         tc = spec.trunk_cfg
@@ -279,7 +278,5 @@ class _AgentStepFn(torch.autograd.Function):
 
 @eager_only
 def agent_step(spec, ext, xin, action, mask_u8, old_logprob, advantages, returns, old_values, flat):
-    """``(loss, stats [8], aux [3, B] = logprob | entropy | value, logits [B, max_n], logp [B, max_n])``; ``stats`` in
-    the order of ``STATS``; ``logits`` / ``logp`` = the action head's raw and masked log-softmax outputs (what rollout
-    inference samples from, ``PpoMinibatchMixin.get_action_and_value``); only ``loss`` is differentiable."""
+    """``(loss, stats [8], aux [3, B] = logprob | entropy | value)``; ``stats`` in the order of ``STATS``."""
     return _AgentStepFn.apply(spec, ext, xin, action, mask_u8, old_logprob, advantages, returns, old_values, *flat)
