@@ -414,6 +414,38 @@ def test_wire_format_round_trip_and_gather(built):
     assert np.array_equal(np.frombuffer(shm, dtype=np.int32, count=layout.slot_words), shared.words[0])
 
 
+def test_psp_sizes_table_matches_a_direct_count(built):
+    """``psp_batch.psp_sizes`` (the host-side offset table the device builder is launched with: no device->host read)
+    against a direct per-graph count and the numpy oracle's edge totals, ragged graphs, both conflict modes."""
+    import numpy as np
+    from oracle import psp_batch_oracle as pbo
+    from wheatley_b200.psp_batch import psp_sizes
+    from wheatley_b200.wire import PspArena
+    from wheatley_b200.workload import psp_taillard_graph
+    graphs = [psp_taillard_graph(4, 4, 1, n_rp=3), psp_taillard_graph(3, 2, 2), psp_taillard_graph(5, 3, 3, n_rp=1),
+              psp_taillard_graph(6, 4, 4, progress=0.5)]
+    arena = PspArena.from_graphs(graphs, pin=False)
+    users = [(g["resources"] != 0).sum(0) for g in graphs]                         # per graph: users per resource
+    for conflicts in ("clique", "node", "att"):
+        meta, n_res, unused = psp_sizes(arena, len(graphs), conflicts)
+        m = meta.numpy()
+        assert m.shape == (5, len(graphs) + 1) and (m[:, 0] == 0).all()
+        assert np.array_equal(np.diff(m[0]), [g["feat"].shape[0] for g in graphs])
+        assert np.array_equal(np.diff(m[1]), [g["prec"].shape[1] for g in graphs])
+        assert np.array_equal(np.diff(m[2]), [g["rp"].shape[1] for g in graphs])
+        want_rc = [int((c * (c - 1)).sum()) if conflicts == "clique" else 0 for c in users]
+        want_us = [int(c.sum()) if conflicts == "node" else 0 for c in users]
+        assert np.array_equal(np.diff(m[3]), want_rc) and np.array_equal(np.diff(m[4]), want_us)
+        assert n_res == max(g["resources"].shape[1] for g in graphs)
+        total = np.zeros(n_res, dtype=np.int64)
+        for c in users:
+            total[: len(c)] += c
+        assert unused == sum(1 << r for r in range(n_res) if total[r] == 0)
+    ref = pbo.psp_batch(graphs, "clique", "learn", True)
+    rc = int((np.asarray(ref["type"]) == 3).sum())                                 # edge type 3 = resource conflict
+    assert rc == int(psp_sizes(arena, len(graphs), "clique")[0][3, -1])
+
+
 def test_psp_sizes_and_oracle_agree_on_survey_table(built):
     """PyG-flavour node / edge counts per graph at t = 0 from the numpy oracle on generated graphs."""
     from oracle import psp_batch_oracle as pbo
